@@ -1,0 +1,316 @@
+/*
+ * tdfo_b200.h — C ABI of the B200-native sparse-embedding hot path.
+ *
+ * This is the drop-in boundary for the one path massquantity/tdfo delegates to
+ * torchrec / fbgemm_gpu: KeyedJaggedTensor plumbing, the (sharded) embedding
+ * lookup, and the sort/unique backward with the optimizer fused in.  The
+ * reference has no C FFI of its own: it reaches this path through
+ * `torch.ops.fbgemm.*` and the torchrec Python modules.  Every entry point
+ * below names the reference call site (path relative to /root/reference) whose
+ * third-party implementation it replaces.
+ *
+ * Conventions
+ *  - Plain pointers and sizes only.  Unless a parameter is marked HOST, every
+ *    pointer is a device pointer on the current CUDA device.
+ *  - `stream` is a `cudaStream_t` passed as `void*` (NULL = legacy default
+ *    stream).  All work is enqueued on it; nothing synchronises the host.
+ *  - No entry point allocates or frees device memory.  Kernels that need
+ *    workspace take a caller-owned `scratch` pointer; the matching
+ *    `*_scratch_bytes` function (pure host arithmetic) says how large it must
+ *    be.  Scratch must be 256-byte aligned.
+ *  - Return value: TDFO_OK (0) or a negative TDFO_ERR_* code; the message is
+ *    available from tdfo_last_error() (thread-local).
+ *  - ids (`indices`) are int64, `lengths` are int32, `offsets` are int64 and
+ *    are *complete* cumulative sums (`offsets[0] == 0`, `n + 1` entries).
+ *  - Out-of-range ids never touch memory: the lookup is skipped (treated as a
+ *    zero row) and bit TDFO_FLAG_INDEX_OOB is OR-ed into `*err_flag` (a device
+ *    word the caller zeroes and reads back lazily).  `err_flag` may be NULL.
+ *  - Row size `D * sizeof(element)` must be a multiple of 16 bytes (128-bit
+ *    vector loads); tables must be 16-byte aligned.
+ */
+#ifndef TDFO_B200_H
+#define TDFO_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TDFO_ABI_VERSION 1
+
+/* return codes */
+#define TDFO_OK                 0
+#define TDFO_ERR_INVALID_ARG   (-1)
+#define TDFO_ERR_CUDA          (-2)
+#define TDFO_ERR_UNSUPPORTED   (-3)
+#define TDFO_ERR_SCRATCH       (-4)
+
+/* element types of tables / outputs */
+#define TDFO_F32   0
+#define TDFO_BF16  1
+
+/* pooling modes (torchrec PoolingType; NONE = EmbeddingCollection, one output row per id) */
+#define TDFO_POOL_SUM   0
+#define TDFO_POOL_MEAN  1
+#define TDFO_POOL_NONE  2
+
+/* fused optimizers (fbgemm_gpu EmbOptimType as selected at torchrec/train.py:191,195) */
+#define TDFO_OPT_SGD              0   /* EmbOptimType.SGD  (torchrec/train.py:195) */
+#define TDFO_OPT_ROWWISE_ADAGRAD  1   /* EmbOptimType.EXACT_ROWWISE_ADAGRAD (north star) */
+#define TDFO_OPT_ADAM             2   /* EmbOptimType.ADAM (torchrec/train.py:191) */
+
+/* bits of *err_flag */
+#define TDFO_FLAG_INDEX_OOB     1   /* an id was < 0 or >= rows of its table */
+#define TDFO_FLAG_SCAN_TIMEOUT  2   /* internal look-back watchdog fired (bug guard) */
+
+/* ------------------------------------------------------------------ misc */
+
+/* ABI version of the loaded library (== TDFO_ABI_VERSION it was built with). */
+int tdfo_abi_version(void);
+
+/* Thread-local message of the last failing call ("" if none). */
+const char* tdfo_last_error(void);
+
+/* Kernels launched by this library since it was loaded (host-side counter). */
+unsigned long long tdfo_launch_count(void);
+
+/* ------------------------------------------------------------------ KJT */
+
+/*
+ * lengths[n] -> offsets[n+1], complete cumulative sum.
+ * Replaces: KeyedJaggedTensor.from_lengths_sync(...) / .offsets()
+ *   (torchrec/train.py:38-40; upstream fbgemm asynchronous_complete_cumsum).
+ * scratch: tdfo_scan_scratch_bytes(n).
+ */
+size_t tdfo_scan_scratch_bytes(int64_t n);
+int tdfo_kjt_complete_cumsum(const int32_t* lengths, int64_t n, int64_t* offsets,
+                             void* scratch, size_t scratch_bytes, void* stream);
+
+/*
+ * Row-wise input dist, step 1: bucketise ids by destination rank.
+ * For feature f with `block_sizes[f]` rows per rank, id x goes to bucket
+ * x / block_sizes[f] and becomes x - bucket*block_sizes[f].  Output is laid
+ * out [bucket][feature][batch], stable inside each (bucket, f, b).
+ *   new_lengths  int32[world * F * B]
+ *   new_offsets  int64[world * F * B + 1]   (complete cumsum of new_lengths)
+ *   new_indices  int64[L]
+ *   new_weights  float[L] or NULL (iff weights == NULL)
+ *   unbucketize_permute int64[L] or NULL: position of original id p in new_indices
+ *   (needed by the sequence / EmbeddingCollection output dist).
+ * Replaces: the input_dist of the sharded EmbeddingCollection reached from
+ *   DMP(...) at torchrec/train.py:241-247 (upstream
+ *   fbgemm block_bucketize_sparse_features); the only explicit row partition in
+ *   the reference is MinSizePartitioner at tensorflow2/train_ps.py:55-61.
+ * Ids outside [0, world*block_size) set TDFO_FLAG_INDEX_OOB and go to the last bucket.
+ * scratch: tdfo_bucketize_scratch_bytes(F*B, world).
+ */
+size_t tdfo_bucketize_scratch_bytes(int64_t num_bags, int32_t world);
+int tdfo_kjt_bucketize_row_wise(const int32_t* lengths, const int64_t* offsets,
+                                const int64_t* indices, const float* weights,
+                                const int64_t* block_sizes /* [F] */,
+                                int32_t F, int64_t B, int32_t world,
+                                int32_t* new_lengths, int64_t* new_offsets,
+                                int64_t* new_indices, float* new_weights,
+                                int64_t* unbucketize_permute,
+                                int32_t* err_flag,
+                                void* scratch, size_t scratch_bytes, void* stream);
+
+/*
+ * Permute the (segment x batch) rows of a jagged 2-D layout:
+ *   out segment i = in segment permute[i]; every segment has B bags.
+ *   in_lengths int32[S_in*B], in_offsets int64[S_in*B+1]; out_* sized for S_out.
+ * Used after the input all-to-all to turn [src_rank][feature][batch] into
+ * [feature][src_rank][batch], and by KeyedJaggedTensor.permute().
+ * Replaces: upstream fbgemm permute_2D_sparse_data inside the same input_dist
+ *   (torchrec/train.py:98 -> DMP forward).
+ * scratch: tdfo_scan_scratch_bytes(S_out*B).
+ */
+int tdfo_kjt_permute_2d(const int32_t* permute /* [S_out] */, int32_t S_in, int32_t S_out, int64_t B,
+                        const int32_t* in_lengths, const int64_t* in_offsets,
+                        const int64_t* in_indices, const float* in_weights,
+                        int32_t* out_lengths, int64_t* out_offsets,
+                        int64_t* out_indices, float* out_weights,
+                        void* scratch, size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------ lookup */
+
+/*
+ * Embedding lookup over one storage group (all tables of one dim/dtype live in
+ * one [total_rows, D] buffer).  KJT layout: bag g = f*B + b, ids of bag g are
+ * indices[offsets[g] .. offsets[g+1]).
+ *   feat_row_base[f]  first row of feature f's table inside `weights`
+ *   feat_rows[f]      number of rows of that table (bounds check)
+ *   feat_out_col[f]   first output column of feature f (elements)
+ * Pooled (SUM/MEAN):  out is float[B, out_stride], bag (f,b) writes D floats at
+ *   out[b*out_stride + feat_out_col[f]].  MEAN divides by the bag length, an
+ *   empty bag yields zeros.  per_sample_weights (float[L]) may be NULL.
+ * Sequence (NONE):    out is float[L, D], out[p,:] = row of indices[p]
+ *   (out_stride, feat_out_col ignored).
+ * Accumulation is fp32 in bag order (deterministic).
+ * Replaces: `self.embed_collection(id_list_features)` torchrec/models.py:164
+ *   (EmbeddingCollection, upstream fbgemm TBE forward "nobag"), and the
+ *   EmbeddingBagCollection the BASELINE configs name (TBE pooled forward);
+ *   jax-flax/models.py:78-88 and tensorflow2/models.py:48-58 are the P=1 case.
+ */
+int tdfo_embedding_forward(const void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
+                           const int64_t* indices, const int64_t* offsets,
+                           const float* per_sample_weights,
+                           const int64_t* feat_row_base, const int64_t* feat_rows,
+                           const int64_t* feat_out_col,
+                           int32_t F, int64_t B, int64_t L /* used by POOL_NONE only */,
+                           int32_t pooling_mode,
+                           float* out, int64_t out_stride,
+                           int32_t* err_flag, void* stream);
+
+/* ------------------------------------------------------------------ backward */
+
+/*
+ * Stage 1 of the backward: linearise (feature, id) to a row of the storage
+ * group.  keys[p] = feat_row_base[f] + indices[p] (uint32; total_rows < 2^32),
+ * vals[p] = bag id g = f*B + b (uint32), or the position p itself when
+ * pooling_mode is TDFO_POOL_NONE.  Out-of-range ids get key `total_rows`
+ * (sorted last, skipped by the update) and set TDFO_FLAG_INDEX_OOB.
+ * Replaces: the linearize_cache_indices prologue of the fbgemm TBE backward
+ *   reached from loss.backward() at torchrec/train.py:104.
+ */
+int tdfo_linearize_indices(const int64_t* indices, const int64_t* offsets,
+                           const int64_t* feat_row_base, const int64_t* feat_rows,
+                           int32_t F, int64_t B, int64_t total_rows, int32_t pooling_mode,
+                           uint32_t* keys, uint32_t* vals,
+                           int32_t* err_flag, void* stream);
+
+/*
+ * Stage 2: stable LSD radix sort of n (key, val) uint32 pairs on the low
+ * `key_bits` bits of the key (1..32).  Result lands in keys_out / vals_out;
+ * keys_in / vals_in are clobbered (used as the ping-pong buffer).
+ * n < 2^30.  Bit-exact with a stable CPU sort.
+ * Replaces: cub::DeviceRadixSort::SortPairs in the upstream TBE backward
+ *   (torchrec/train.py:104).
+ * scratch: tdfo_radix_sort_scratch_bytes(n, key_bits).
+ */
+size_t tdfo_radix_sort_scratch_bytes(int64_t n, int32_t key_bits);
+int tdfo_radix_sort_pairs(uint32_t* keys_in, uint32_t* vals_in,
+                          uint32_t* keys_out, uint32_t* vals_out,
+                          int64_t n, int32_t key_bits,
+                          int32_t* err_flag,
+                          void* scratch, size_t scratch_bytes, void* stream);
+
+/*
+ * Stage 3: run-length encode sorted keys.
+ *   unique_keys uint32[n]     (first *num_unique entries valid)
+ *   seg_starts  uint32[n + 1] (seg_starts[u] = first sorted position of
+ *                              unique row u; seg_starts[*num_unique] = n)
+ *   num_unique  uint32[1]     device scalar
+ * Replaces: cub::DeviceRunLengthEncode in the upstream TBE backward.
+ * scratch: tdfo_scan_scratch_bytes(n).
+ */
+int tdfo_unique_segments(const uint32_t* sorted_keys, int64_t n,
+                         uint32_t* unique_keys, uint32_t* seg_starts, uint32_t* num_unique,
+                         int32_t* err_flag,
+                         void* scratch, size_t scratch_bytes, void* stream);
+
+/* Hyper-parameters of the fused optimizer (HOST struct, passed by pointer). */
+typedef struct tdfo_optimizer_args {
+    int32_t optimizer;      /* TDFO_OPT_* */
+    float   learning_rate;
+    float   eps;
+    float   weight_decay;   /* L2: g += weight_decay * w  (ADAM: decoupled into the step, as fbgemm) */
+    float   beta1, beta2;   /* ADAM */
+    int64_t step;           /* ADAM bias correction, 1-based iteration count */
+} tdfo_optimizer_args;
+
+/*
+ * Stage 4: per unique row, reduce the gradient rows of all its occurrences in
+ * sorted (= original) order in fp32 and apply the optimizer in place.  No dense
+ * [rows, D] gradient is ever formed.
+ *   grad_out   float[B, grad_stride]; bag (f,b) reads D floats at
+ *              grad_out[b*grad_stride + feat_out_col[f]]           (pooled)
+ *              float[L, D], occurrence p reads grad_out[p,:]        (POOL_NONE;
+ *              sorted_vals then hold positions p, see tdfo_embedding_backward_update)
+ *   offsets    int64[F*B+1] (MEAN scaling; may be NULL for SUM / NONE)
+ *   state0     ROWWISE_ADAGRAD: float[total_rows] sum of mean squared grads
+ *              ADAM: float[total_rows, D] first moment;  SGD: NULL
+ *   state1     ADAM: float[total_rows, D] second moment; else NULL
+ * ROWWISE_ADAGRAD: h += mean_d(g_d^2); w -= lr / (sqrt(h) + eps) * g.
+ * SGD: w -= lr * g.  bf16 tables: fp32 math, round-to-nearest-even on store.
+ * Replaces: upstream split_embedding_backward_codegen_{sgd,rowwise_adagrad,adam}
+ *   reached from loss.backward() (torchrec/train.py:104); optimizer.step()
+ *   (torchrec/train.py:105) is then a no-op for these rows.
+ */
+int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
+                       float* state0, float* state1,
+                       const float* grad_out, int64_t grad_stride,
+                       const uint32_t* sorted_vals,
+                       const uint32_t* unique_keys, const uint32_t* seg_starts,
+                       const uint32_t* num_unique,
+                       const int64_t* offsets, const int64_t* feat_out_col,
+                       int32_t F, int64_t B, int64_t L, int32_t pooling_mode,
+                       const tdfo_optimizer_args* opt /* HOST */,
+                       void* stream);
+
+/*
+ * The whole backward in one call: linearise -> sort -> unique -> update.
+ * Same arguments as the stages above.  On return (stream order) scratch holds,
+ * at the offsets reported by tdfo_backward_scratch_layout, the sorted keys,
+ * sorted vals, unique keys, segment starts and the unique count, so a caller
+ * (or a parity test) can read them.
+ * per_sample_weights must be NULL in this ABI version (weighted backward is
+ * TDFO_ERR_UNSUPPORTED).
+ * scratch: tdfo_backward_scratch_bytes(L, total_rows).
+ */
+typedef struct tdfo_backward_layout {
+    size_t sorted_keys, sorted_vals, unique_keys, seg_starts, num_unique; /* byte offsets */
+    size_t total_bytes;
+    int32_t key_bits;
+} tdfo_backward_layout;
+
+size_t tdfo_backward_scratch_bytes(int64_t L, int64_t total_rows);
+int tdfo_backward_scratch_layout(int64_t L, int64_t total_rows, tdfo_backward_layout* layout /* HOST */);
+int tdfo_embedding_backward_update(void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
+                                   float* state0, float* state1,
+                                   const float* grad_out, int64_t grad_stride,
+                                   const int64_t* indices, const int64_t* offsets,
+                                   const float* per_sample_weights,
+                                   const int64_t* feat_row_base, const int64_t* feat_rows,
+                                   const int64_t* feat_out_col,
+                                   int32_t F, int64_t B, int64_t L, int32_t pooling_mode,
+                                   const tdfo_optimizer_args* opt /* HOST */,
+                                   int32_t* err_flag,
+                                   void* scratch, size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------ jagged */
+
+/*
+ * values float[L, D], offsets int64[B+1] -> dense float[B, max_len, D];
+ * zero padded, rows beyond max_len dropped.
+ * Replaces: torch.ops.fbgemm.jagged_2d_to_dense at torchrec/models.py:168-172.
+ */
+int tdfo_jagged_2d_to_dense(const float* values, const int64_t* offsets,
+                            int64_t B, int32_t D, int64_t max_len,
+                            float* dense, void* stream);
+
+/*
+ * Gradient of the above: dense float[B, max_len, D] -> values float[L, D];
+ * rows that were dropped (position >= max_len) get zeros.
+ * Replaces: autograd of jagged_2d_to_dense (upstream fbgemm dense_to_jagged),
+ *   reached from loss.backward() at torchrec/train.py:104.
+ */
+int tdfo_dense_to_jagged(const float* dense, const int64_t* offsets,
+                         int64_t B, int32_t D, int64_t max_len, int64_t L,
+                         float* values, void* stream);
+
+/*
+ * values int64[L], offsets int64[B+1] -> dense int64[B, desired_length] padded
+ * with padding_value.
+ * Replaces: JaggedTensor.to_padded_dense at torchrec/models.py:210-212.
+ */
+int tdfo_jagged_1d_to_padded_dense(const int64_t* values, const int64_t* offsets,
+                                   int64_t B, int64_t desired_length, int64_t padding_value,
+                                   int64_t* dense, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TDFO_B200_H */

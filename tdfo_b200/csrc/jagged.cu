@@ -1,0 +1,315 @@
+// KeyedJaggedTensor routing kernels (row-wise bucketise, 2-D permute) and the
+// jagged <-> dense copies the reference model calls around the lookup.
+// All of it is integer / copy work bounded by HBM; results are bit-exact.
+#include "common.cuh"
+
+namespace tdfo {
+
+int complete_cumsum_impl(const int32_t* lengths, int64_t n, int64_t* offsets, void* scratch, cudaStream_t st);
+
+constexpr int kJagThreads = 256;
+constexpr int kMaxWorld = 32;
+
+// ---------------------------------------------------------------- bucketise
+// Pass 1: per (bucket, f, b) counts.  One warp per bag.
+__global__ void __launch_bounds__(kJagThreads)
+bucketize_count_kernel(const int64_t* __restrict__ offsets, const int64_t* __restrict__ indices,
+                       const int64_t* __restrict__ block_sizes, int64_t B, int64_t num_bags, int world,
+                       int32_t* __restrict__ new_lengths, int32_t* err_flag) {
+    const int64_t g = (int64_t)blockIdx.x * (kJagThreads / 32) + (threadIdx.x >> 5);
+    if (g >= num_bags) return;
+    const int lane = lane_id();
+    const int f = (int)(g / B);
+    const int64_t s = __ldg(offsets + g), e = __ldg(offsets + g + 1);
+    const int64_t bs = __ldg(block_sizes + f);
+    int my_count = 0;               // lane w counts bucket w
+    bool oob = false;
+    for (int64_t base = s; base < e; base += 32) {
+        int bucket = -1;
+        if (base + lane < e) {
+            const int64_t idx = __ldg(indices + base + lane);
+            int64_t q = idx / bs;
+            if (idx < 0 || q >= world) { oob = true; q = world - 1; }
+            bucket = (int)q;
+        }
+        for (int w = 0; w < world; ++w) {
+            const unsigned m = __ballot_sync(kFullMask, bucket == w);
+            if (lane == w) my_count += __popc(m);
+        }
+    }
+    if (lane < world) new_lengths[(int64_t)lane * num_bags + g] = my_count;
+    if (oob && err_flag) atomicOr(err_flag, TDFO_FLAG_INDEX_OOB);
+}
+
+// Pass 2: stable scatter into [bucket][f][b] order.
+__global__ void __launch_bounds__(kJagThreads)
+bucketize_scatter_kernel(const int64_t* __restrict__ offsets, const int64_t* __restrict__ indices,
+                         const float* __restrict__ weights, const int64_t* __restrict__ block_sizes,
+                         int64_t B, int64_t num_bags, int world,
+                         const int64_t* __restrict__ new_offsets, int64_t* __restrict__ new_indices,
+                         float* __restrict__ new_weights, int64_t* __restrict__ unbucketize_permute) {
+    const int64_t g = (int64_t)blockIdx.x * (kJagThreads / 32) + (threadIdx.x >> 5);
+    if (g >= num_bags) return;
+    const int lane = lane_id();
+    const int f = (int)(g / B);
+    const int64_t s = __ldg(offsets + g), e = __ldg(offsets + g + 1);
+    const int64_t bs = __ldg(block_sizes + f);
+    int64_t my_cursor = (lane < world) ? __ldg(new_offsets + (int64_t)lane * num_bags + g) : 0;
+    const unsigned lt = (1u << lane) - 1u;
+    for (int64_t base = s; base < e; base += 32) {
+        int bucket = -1;
+        int64_t idx = 0;
+        if (base + lane < e) {
+            idx = __ldg(indices + base + lane);
+            int64_t q = idx / bs;
+            if (idx < 0 || q >= world) q = world - 1;
+            bucket = (int)q;
+        }
+        int64_t pos = 0;
+        for (int w = 0; w < world; ++w) {
+            const unsigned m = __ballot_sync(kFullMask, bucket == w);
+            const int64_t cur = __shfl_sync(kFullMask, my_cursor, w);
+            if (bucket == w) pos = cur + __popc(m & lt);
+            if (lane == w) my_cursor += __popc(m);
+        }
+        if (bucket >= 0) {
+            new_indices[pos] = idx - (int64_t)bucket * bs;
+            if (weights) new_weights[pos] = __ldg(weights + base + lane);
+            if (unbucketize_permute) unbucketize_permute[base + lane] = pos;
+        }
+    }
+}
+
+// ---------------------------------------------------------------- permute 2-D
+__global__ void permute_lengths_kernel(const int32_t* __restrict__ permute, int64_t B, int64_t n_out,
+                                       const int32_t* __restrict__ in_lengths, int32_t* __restrict__ out_lengths) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_out) return;
+    const int64_t seg = i / B;
+    out_lengths[i] = in_lengths[(int64_t)__ldg(permute + seg) * B + (i - seg * B)];
+}
+
+__global__ void __launch_bounds__(kJagThreads)
+permute_data_kernel(const int32_t* __restrict__ permute, int64_t B, int64_t n_out,
+                    const int64_t* __restrict__ in_offsets, const int64_t* __restrict__ out_offsets,
+                    const int64_t* __restrict__ in_indices, const float* __restrict__ in_weights,
+                    int64_t* __restrict__ out_indices, float* __restrict__ out_weights) {
+    const int64_t g = (int64_t)blockIdx.x * (kJagThreads / 32) + (threadIdx.x >> 5);
+    if (g >= n_out) return;
+    const int lane = lane_id();
+    const int64_t seg = g / B;
+    const int64_t src = (int64_t)__ldg(permute + seg) * B + (g - seg * B);
+    const int64_t so = __ldg(in_offsets + src);
+    const int64_t len = __ldg(in_offsets + src + 1) - so;
+    const int64_t dofs = __ldg(out_offsets + g);
+    for (int64_t j = lane; j < len; j += 32) {
+        out_indices[dofs + j] = __ldg(in_indices + so + j);
+        if (in_weights) out_weights[dofs + j] = __ldg(in_weights + so + j);
+    }
+}
+
+// ---------------------------------------------------------------- jagged <-> dense
+// VEC floats per thread-chunk (4 when D % 4 == 0, else 1).
+template <int VEC>
+__global__ void jagged_2d_to_dense_kernel(const float* __restrict__ values, const int64_t* __restrict__ offsets,
+                                          int64_t B, int32_t D, int64_t max_len, float* __restrict__ dense) {
+    const int cpr = D / VEC;                                   // chunks per row
+    const int64_t total = B * max_len * cpr;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / cpr;
+        const int c = (int)(i - r * cpr);
+        const int64_t b = r / max_len;
+        const int64_t t = r - b * max_len;
+        const int64_t s = __ldg(offsets + b);
+        const int64_t len = __ldg(offsets + b + 1) - s;
+        if (VEC == 4) {
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (t < len) v = ldg_128(values + (size_t)(s + t) * D + (size_t)c * 4);
+            st_128(dense + (size_t)r * D + (size_t)c * 4, v);
+        } else {
+            dense[(size_t)r * D + c] = (t < len) ? __ldg(values + (size_t)(s + t) * D + c) : 0.f;
+        }
+    }
+}
+
+template <int VEC>
+__global__ void dense_to_jagged_kernel(const float* __restrict__ dense, const int64_t* __restrict__ offsets,
+                                       int64_t B, int32_t D, int64_t max_len, int64_t L,
+                                       float* __restrict__ values) {
+    const int cpr = D / VEC;
+    const int64_t total = L * cpr;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t p = i / cpr;
+        const int c = (int)(i - p * cpr);
+        int64_t lo = 0, hi = B;                                 // largest b with offsets[b] <= p
+        while (hi - lo > 1) {
+            const int64_t mid = (lo + hi) >> 1;
+            if (__ldg(offsets + mid) <= p) lo = mid; else hi = mid;
+        }
+        const int64_t t = p - __ldg(offsets + lo);
+        if (VEC == 4) {
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (t < max_len) v = ldg_128(dense + ((size_t)lo * max_len + t) * D + (size_t)c * 4);
+            st_128(values + (size_t)p * D + (size_t)c * 4, v);
+        } else {
+            values[(size_t)p * D + c] = (t < max_len) ? __ldg(dense + ((size_t)lo * max_len + t) * D + c) : 0.f;
+        }
+    }
+}
+
+__global__ void jagged_1d_to_padded_dense_kernel(const int64_t* __restrict__ values,
+                                                 const int64_t* __restrict__ offsets, int64_t B,
+                                                 int64_t desired_length, int64_t padding_value,
+                                                 int64_t* __restrict__ dense) {
+    const int64_t total = B * desired_length;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t b = i / desired_length;
+        const int64_t t = i - b * desired_length;
+        const int64_t s = __ldg(offsets + b);
+        const int64_t len = __ldg(offsets + b + 1) - s;
+        dense[i] = (t < len) ? __ldg(values + s + t) : padding_value;
+    }
+}
+
+static unsigned grid_for(int64_t items, int threads) {
+    int64_t blocks = (items + threads - 1) / threads;
+    const int64_t cap = (int64_t)kNumSMs * 32;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (unsigned)blocks;
+}
+
+}  // namespace tdfo
+
+using namespace tdfo;
+
+extern "C" size_t tdfo_bucketize_scratch_bytes(int64_t num_bags, int32_t world) {
+    if (num_bags < 0 || world < 1) return 256;
+    return tdfo_scan_scratch_bytes(num_bags * (int64_t)world);
+}
+
+extern "C" int tdfo_kjt_bucketize_row_wise(const int32_t* lengths, const int64_t* offsets,
+                                           const int64_t* indices, const float* weights,
+                                           const int64_t* block_sizes, int32_t F, int64_t B, int32_t world,
+                                           int32_t* new_lengths, int64_t* new_offsets,
+                                           int64_t* new_indices, float* new_weights,
+                                           int64_t* unbucketize_permute, int32_t* err_flag,
+                                           void* scratch, size_t scratch_bytes, void* stream) {
+    (void)lengths;
+    TDFO_CHECK_ARG(F >= 0 && B >= 0, "bucketize_row_wise: negative size");
+    TDFO_CHECK_ARG(world >= 1 && world <= kMaxWorld, "bucketize_row_wise: world must be in [1, %d]", kMaxWorld);
+    TDFO_CHECK_ARG(new_offsets != nullptr, "bucketize_row_wise: new_offsets is null");
+    TDFO_CHECK_ARG((weights == nullptr) == (new_weights == nullptr),
+                   "bucketize_row_wise: weights and new_weights must both be given or both be null");
+    const int64_t num_bags = (int64_t)F * B;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (num_bags == 0) {
+        TDFO_CUDA(cudaMemsetAsync(new_offsets, 0, sizeof(int64_t), st));
+        return TDFO_OK;
+    }
+    TDFO_CHECK_ARG(offsets && indices && block_sizes && new_lengths && new_indices,
+                   "bucketize_row_wise: null pointer");
+    const size_t need = tdfo_bucketize_scratch_bytes(num_bags, world);
+    if (!scratch || !aligned(scratch, 256) || scratch_bytes < need) {
+        set_error("bucketize_row_wise: scratch null, misaligned or smaller than %zu bytes", need);
+        return TDFO_ERR_SCRATCH;
+    }
+    const unsigned blocks = (unsigned)((num_bags + kJagThreads / 32 - 1) / (kJagThreads / 32));
+    bucketize_count_kernel<<<blocks, kJagThreads, 0, st>>>(offsets, indices, block_sizes, B, num_bags, world,
+                                                          new_lengths, err_flag);
+    count_launch();
+    TDFO_LAUNCH_CHECK("bucketize_count");
+    const int rc = complete_cumsum_impl(new_lengths, num_bags * world, new_offsets, scratch, st);
+    if (rc) return rc;
+    bucketize_scatter_kernel<<<blocks, kJagThreads, 0, st>>>(offsets, indices, weights, block_sizes, B, num_bags,
+                                                            world, new_offsets, new_indices, new_weights,
+                                                            unbucketize_permute);
+    count_launch();
+    TDFO_LAUNCH_CHECK("bucketize_scatter");
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_kjt_permute_2d(const int32_t* permute, int32_t S_in, int32_t S_out, int64_t B,
+                                   const int32_t* in_lengths, const int64_t* in_offsets,
+                                   const int64_t* in_indices, const float* in_weights,
+                                   int32_t* out_lengths, int64_t* out_offsets,
+                                   int64_t* out_indices, float* out_weights,
+                                   void* scratch, size_t scratch_bytes, void* stream) {
+    TDFO_CHECK_ARG(S_in >= 0 && S_out >= 0 && B >= 0, "permute_2d: negative size");
+    TDFO_CHECK_ARG(out_offsets != nullptr, "permute_2d: out_offsets is null");
+    TDFO_CHECK_ARG((in_weights == nullptr) == (out_weights == nullptr),
+                   "permute_2d: in_weights and out_weights must both be given or both be null");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int64_t n_out = (int64_t)S_out * B;
+    if (n_out == 0) {
+        TDFO_CUDA(cudaMemsetAsync(out_offsets, 0, sizeof(int64_t), st));
+        return TDFO_OK;
+    }
+    TDFO_CHECK_ARG(permute && in_lengths && in_offsets && out_lengths, "permute_2d: null pointer");
+    const size_t need = tdfo_scan_scratch_bytes(n_out);
+    if (!scratch || !aligned(scratch, 256) || scratch_bytes < need) {
+        set_error("permute_2d: scratch null, misaligned or smaller than %zu bytes", need);
+        return TDFO_ERR_SCRATCH;
+    }
+    permute_lengths_kernel<<<(unsigned)((n_out + 255) / 256), 256, 0, st>>>(permute, B, n_out, in_lengths, out_lengths);
+    count_launch();
+    TDFO_LAUNCH_CHECK("permute_lengths");
+    const int rc = complete_cumsum_impl(out_lengths, n_out, out_offsets, scratch, st);
+    if (rc) return rc;
+    if (in_indices && out_indices) {
+        const unsigned blocks = (unsigned)((n_out + kJagThreads / 32 - 1) / (kJagThreads / 32));
+        permute_data_kernel<<<blocks, kJagThreads, 0, st>>>(permute, B, n_out, in_offsets, out_offsets,
+                                                           in_indices, in_weights, out_indices, out_weights);
+        count_launch();
+        TDFO_LAUNCH_CHECK("permute_data");
+    }
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_jagged_2d_to_dense(const float* values, const int64_t* offsets, int64_t B, int32_t D,
+                                       int64_t max_len, float* dense, void* stream) {
+    TDFO_CHECK_ARG(B >= 0 && D > 0 && max_len >= 0, "jagged_2d_to_dense: bad size");
+    if (B == 0 || max_len == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(offsets && dense, "jagged_2d_to_dense: null pointer");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool vec = (D % 4 == 0) && aligned(values, 16) && aligned(dense, 16);
+    if (vec)
+        jagged_2d_to_dense_kernel<4><<<grid_for(B * max_len * (D / 4), 256), 256, 0, st>>>(values, offsets, B, D, max_len, dense);
+    else
+        jagged_2d_to_dense_kernel<1><<<grid_for(B * max_len * D, 256), 256, 0, st>>>(values, offsets, B, D, max_len, dense);
+    count_launch();
+    TDFO_LAUNCH_CHECK("jagged_2d_to_dense");
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_dense_to_jagged(const float* dense, const int64_t* offsets, int64_t B, int32_t D,
+                                    int64_t max_len, int64_t L, float* values, void* stream) {
+    TDFO_CHECK_ARG(B >= 0 && D > 0 && max_len >= 0 && L >= 0, "dense_to_jagged: bad size");
+    if (L == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(offsets && values && (dense || max_len == 0) && B > 0, "dense_to_jagged: null pointer");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool vec = (D % 4 == 0) && aligned(values, 16) && aligned(dense, 16);
+    if (vec)
+        dense_to_jagged_kernel<4><<<grid_for(L * (D / 4), 256), 256, 0, st>>>(dense, offsets, B, D, max_len, L, values);
+    else
+        dense_to_jagged_kernel<1><<<grid_for(L * D, 256), 256, 0, st>>>(dense, offsets, B, D, max_len, L, values);
+    count_launch();
+    TDFO_LAUNCH_CHECK("dense_to_jagged");
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_jagged_1d_to_padded_dense(const int64_t* values, const int64_t* offsets, int64_t B,
+                                              int64_t desired_length, int64_t padding_value,
+                                              int64_t* dense, void* stream) {
+    TDFO_CHECK_ARG(B >= 0 && desired_length >= 0, "jagged_1d_to_padded_dense: bad size");
+    if (B == 0 || desired_length == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(offsets && dense, "jagged_1d_to_padded_dense: null pointer");
+    jagged_1d_to_padded_dense_kernel<<<grid_for(B * desired_length, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        values, offsets, B, desired_length, padding_value, dense);
+    count_launch();
+    TDFO_LAUNCH_CHECK("jagged_1d_to_padded_dense");
+    return TDFO_OK;
+}

@@ -1,0 +1,183 @@
+// Single-pass device scans: lengths -> offsets (complete cumsum) and run-length
+// encoding of sorted row keys.  Both stream their input once (decoupled
+// look-back, tile ids from an atomic ticket) and are bandwidth-trivial next to
+// the gather; they exist so the step has no host round trip.
+#include "scan.cuh"
+
+namespace tdfo {
+
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 8;
+constexpr int kScanTile = kScanThreads * kScanItems;   // 2048
+
+static inline int64_t scan_tiles(int64_t n) { return (n + kScanTile - 1) / kScanTile; }
+
+// ---------------------------------------------------------------- cumsum
+__global__ void __launch_bounds__(kScanThreads)
+complete_cumsum_kernel(const int32_t* __restrict__ lengths, int64_t n, int64_t* __restrict__ offsets,
+                       ScanScratch* hdr, uint64_t* status) {
+    __shared__ uint64_t warp_totals[8];
+    __shared__ uint64_t s_prefix;
+    __shared__ int s_tile;
+    if (threadIdx.x == 0) s_tile = (int)atomicAdd(&hdr->ticket, 1u);
+    __syncthreads();
+    const int tile = s_tile;
+    const int64_t base = (int64_t)tile * kScanTile + (int64_t)threadIdx.x * kScanItems;
+    int64_t v[kScanItems];
+    uint64_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+        v[i] = (base + i < n) ? (int64_t)lengths[base + i] : 0;
+        sum += (uint64_t)v[i];
+    }
+    uint64_t total;
+    uint64_t excl = block_exclusive_scan_256<uint64_t>(sum, warp_totals, total);
+    if (threadIdx.x < 32) {
+        const uint64_t p = scan_lookback(status, tile, total, nullptr);
+        if (threadIdx.x == 0) s_prefix = p;
+    }
+    __syncthreads();
+    uint64_t run = s_prefix + excl;
+    if (tile == 0 && threadIdx.x == 0) offsets[0] = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+        run += (uint64_t)v[i];
+        if (base + i < n) offsets[base + i + 1] = (int64_t)run;
+    }
+}
+
+// ---------------------------------------------------------------- unique / RLE
+__global__ void __launch_bounds__(kScanThreads)
+unique_segments_kernel(const uint32_t* __restrict__ keys, int64_t n,
+                       uint32_t* __restrict__ unique_keys, uint32_t* __restrict__ seg_starts,
+                       uint32_t* __restrict__ num_unique, ScanScratch* hdr, uint64_t* status,
+                       int32_t* err_flag) {
+    __shared__ uint32_t warp_totals[8];
+    __shared__ uint32_t s_last[kScanThreads];
+    __shared__ uint64_t s_prefix;
+    __shared__ int s_tile;
+    if (threadIdx.x == 0) s_tile = (int)atomicAdd(&hdr->ticket, 1u);
+    __syncthreads();
+    const int tile = s_tile;
+    const int64_t base = (int64_t)tile * kScanTile + (int64_t)threadIdx.x * kScanItems;
+    uint32_t k[kScanItems];
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) k[i] = (base + i < n) ? keys[base + i] : 0u;
+    s_last[threadIdx.x] = k[kScanItems - 1];
+    __syncthreads();
+    uint32_t prev;
+    if (threadIdx.x > 0) prev = s_last[threadIdx.x - 1];
+    else prev = (base > 0) ? keys[base - 1] : 0u;
+    uint32_t heads = 0, count = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+        const bool valid = base + i < n;
+        const bool head = valid && ((base + i == 0) || k[i] != prev);
+        if (head) { heads |= 1u << i; ++count; }
+        prev = k[i];
+    }
+    uint32_t total;
+    uint32_t excl = block_exclusive_scan_256<uint32_t>(count, warp_totals, total);
+    if (threadIdx.x < 32) {
+        const uint64_t p = scan_lookback(status, tile, (uint64_t)total, err_flag);
+        if (threadIdx.x == 0) s_prefix = p;
+    }
+    __syncthreads();
+    uint32_t pos = (uint32_t)s_prefix + excl;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+        if (heads & (1u << i)) {
+            unique_keys[pos] = k[i];
+            seg_starts[pos] = (uint32_t)(base + i);
+            ++pos;
+        }
+    }
+    const int64_t last_tile = (n - 1) / kScanTile;
+    if (tile == last_tile && threadIdx.x == 0) {
+        const uint32_t u = (uint32_t)s_prefix + total;
+        *num_unique = u;
+        seg_starts[u] = (uint32_t)n;
+    }
+}
+
+static int check_scan_scratch(const char* who, int64_t n, void* scratch, size_t scratch_bytes) {
+    if (!scratch || !aligned(scratch, 256)) {
+        set_error("%s: scratch is null or not 256-byte aligned", who);
+        return TDFO_ERR_SCRATCH;
+    }
+    const size_t need = tdfo_scan_scratch_bytes(n);
+    if (scratch_bytes < need) {
+        set_error("%s: scratch has %zu bytes, needs %zu", who, scratch_bytes, need);
+        return TDFO_ERR_SCRATCH;
+    }
+    return TDFO_OK;
+}
+
+int complete_cumsum_impl(const int32_t* lengths, int64_t n, int64_t* offsets, void* scratch,
+                         cudaStream_t st) {
+    if (n == 0) {
+        TDFO_CUDA(cudaMemsetAsync(offsets, 0, sizeof(int64_t), st));
+        return TDFO_OK;
+    }
+    const size_t bytes = tdfo_scan_scratch_bytes(n);
+    TDFO_CUDA(cudaMemsetAsync(scratch, 0, bytes, st));
+    auto* hdr = static_cast<ScanScratch*>(scratch);
+    auto* status = reinterpret_cast<uint64_t*>(static_cast<char*>(scratch) + sizeof(ScanScratch));
+    complete_cumsum_kernel<<<(unsigned)scan_tiles(n), kScanThreads, 0, st>>>(lengths, n, offsets, hdr, status);
+    count_launch();
+    TDFO_LAUNCH_CHECK("complete_cumsum");
+    return TDFO_OK;
+}
+
+int unique_segments_impl(const uint32_t* sorted_keys, int64_t n, uint32_t* unique_keys,
+                         uint32_t* seg_starts, uint32_t* num_unique, int32_t* err_flag,
+                         void* scratch, cudaStream_t st) {
+    if (n == 0) {
+        TDFO_CUDA(cudaMemsetAsync(num_unique, 0, sizeof(uint32_t), st));
+        TDFO_CUDA(cudaMemsetAsync(seg_starts, 0, sizeof(uint32_t), st));
+        return TDFO_OK;
+    }
+    const size_t bytes = tdfo_scan_scratch_bytes(n);
+    TDFO_CUDA(cudaMemsetAsync(scratch, 0, bytes, st));
+    auto* hdr = static_cast<ScanScratch*>(scratch);
+    auto* status = reinterpret_cast<uint64_t*>(static_cast<char*>(scratch) + sizeof(ScanScratch));
+    unique_segments_kernel<<<(unsigned)scan_tiles(n), kScanThreads, 0, st>>>(
+        sorted_keys, n, unique_keys, seg_starts, num_unique, hdr, status, err_flag);
+    count_launch();
+    TDFO_LAUNCH_CHECK("unique_segments");
+    return TDFO_OK;
+}
+
+}  // namespace tdfo
+
+using namespace tdfo;
+
+extern "C" size_t tdfo_scan_scratch_bytes(int64_t n) {
+    if (n < 0) n = 0;
+    return align_up(sizeof(ScanScratch) + (size_t)scan_tiles(n) * sizeof(uint64_t), 256);
+}
+
+extern "C" int tdfo_kjt_complete_cumsum(const int32_t* lengths, int64_t n, int64_t* offsets,
+                                        void* scratch, size_t scratch_bytes, void* stream) {
+    TDFO_CHECK_ARG(n >= 0, "complete_cumsum: n < 0");
+    TDFO_CHECK_ARG(offsets && (lengths || n == 0), "complete_cumsum: null pointer");
+    if (n > 0) {
+        const int rc = check_scan_scratch("complete_cumsum", n, scratch, scratch_bytes);
+        if (rc) return rc;
+    }
+    return complete_cumsum_impl(lengths, n, offsets, scratch, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int tdfo_unique_segments(const uint32_t* sorted_keys, int64_t n, uint32_t* unique_keys,
+                                    uint32_t* seg_starts, uint32_t* num_unique, int32_t* err_flag,
+                                    void* scratch, size_t scratch_bytes, void* stream) {
+    TDFO_CHECK_ARG(n >= 0 && n < (1ll << 32) - 1, "unique_segments: n out of range");
+    TDFO_CHECK_ARG(seg_starts && num_unique && (n == 0 || (sorted_keys && unique_keys)),
+                   "unique_segments: null pointer");
+    if (n > 0) {
+        const int rc = check_scan_scratch("unique_segments", n, scratch, scratch_bytes);
+        if (rc) return rc;
+    }
+    return unique_segments_impl(sorted_keys, n, unique_keys, seg_starts, num_unique, err_flag, scratch,
+                                static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,443 @@
+// Backward of the embedding lookup with the optimizer fused in:
+//   linearise ids -> stable radix sort by row -> run-length encode ->
+//   per unique row: ordered fp32 reduction of its gradient rows + in-place update.
+// No dense [rows, D] gradient exists at any point.  HBM-bound: per unique row one
+// row read + one row write (+ optimizer state); gradient rows are re-read out of
+// L2 (sorted order walks the tables one after another, so the live gradient
+// slice is B*D*4 bytes per table, far below the 126 MB L2).
+#include "common.cuh"
+
+namespace tdfo {
+
+int radix_sort_impl(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int64_t n, int key_bits,
+                    int32_t* err_flag, void* scratch, cudaStream_t st, int* result_buf);
+size_t radix_sort_scratch_bytes_impl(int64_t n, int key_bits);
+int unique_segments_impl(const uint32_t* sorted_keys, int64_t n, uint32_t* unique_keys,
+                         uint32_t* seg_starts, uint32_t* num_unique, int32_t* err_flag,
+                         void* scratch, cudaStream_t st);
+
+constexpr int kUpdThreads = 256;
+
+// ---------------------------------------------------------------- linearise
+__global__ void __launch_bounds__(kUpdThreads)
+linearize_kernel(const int64_t* __restrict__ indices, const int64_t* __restrict__ offsets,
+                 const int64_t* __restrict__ feat_row_base, const int64_t* __restrict__ feat_rows,
+                 int64_t B, int64_t num_bags, uint32_t oob_key, int vals_are_positions,
+                 uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, int32_t* err_flag) {
+    const int64_t g = (int64_t)blockIdx.x * (kUpdThreads / 32) + (threadIdx.x >> 5);
+    if (g >= num_bags) return;
+    const int lane = lane_id();
+    const int f = (int)(g / B);
+    const int64_t s = __ldg(offsets + g), e = __ldg(offsets + g + 1);
+    const int64_t row_base = __ldg(feat_row_base + f);
+    const uint64_t rows = (uint64_t)__ldg(feat_rows + f);
+    bool oob = false;
+    for (int64_t p = s + lane; p < e; p += 32) {
+        const int64_t idx = __ldg(indices + p);
+        uint32_t k;
+        if ((uint64_t)idx < rows) k = (uint32_t)(row_base + idx);
+        else { k = oob_key; oob = true; }
+        keys[p] = k;
+        vals[p] = vals_are_positions ? (uint32_t)p : (uint32_t)g;
+    }
+    if (oob && err_flag) atomicOr(err_flag, TDFO_FLAG_INDEX_OOB);
+}
+
+// ---------------------------------------------------------------- update
+struct UpdateArgs {
+    void* weights;
+    float* state0;
+    float* state1;
+    const float* grad;
+    const uint32_t* sorted_vals;
+    const uint32_t* unique_keys;
+    const uint32_t* seg_starts;
+    const uint32_t* num_unique;
+    const int64_t* offsets;
+    const int64_t* feat_out_col;
+    int64_t grad_stride;
+    int64_t B;
+    uint32_t total_rows;
+    int32_t D;
+    int32_t nchunks;
+    int32_t pooling_mode;
+    float lr, eps, wd, beta1, beta2, bc1, bc2;   // bc = 1 - beta^step
+};
+
+template <typename T, int LPR, int CPL, int OPT>
+__global__ void __launch_bounds__(kUpdThreads)
+sparse_update_kernel(const UpdateArgs a) {
+    constexpr int E = Chunk<T>::kElems;
+    constexpr int GPB = kUpdThreads / LPR;         // row groups per block
+    const int sub = threadIdx.x % LPR;
+    // Row groups of one warp run different rows (and different trip counts): shuffles
+    // name only the lanes of their own group.
+    const unsigned gmask = (LPR == 32) ? kFullMask : (((1u << (LPR & 31)) - 1u) << ((lane_id() / LPR) * LPR));
+    const uint32_t nu = *a.num_unique;
+    uint4* __restrict__ wbase = reinterpret_cast<uint4*>(a.weights);
+
+    for (uint32_t u = blockIdx.x * GPB + threadIdx.x / LPR; u < nu; u += gridDim.x * GPB) {
+        const uint32_t row = __ldg(a.unique_keys + u);
+        if (row >= a.total_rows) continue;           // out-of-range marker, sorted last
+        const uint32_t s = __ldg(a.seg_starts + u), e = __ldg(a.seg_starts + u + 1);
+
+        float g[CPL][E];
+#pragma unroll
+        for (int k = 0; k < CPL; ++k)
+#pragma unroll
+            for (int i = 0; i < E; ++i) g[k][i] = 0.f;
+
+        // ordered reduction over the occurrences of this row
+        for (uint32_t i = s; i < e; ++i) {
+            const uint32_t v = __ldg(a.sorted_vals + i);
+            const float* grow;
+            float scale = 1.f;
+            if (a.pooling_mode == TDFO_POOL_NONE) {
+                grow = a.grad + (size_t)v * a.D;
+            } else {
+                const uint32_t f = v / (uint32_t)a.B;
+                const uint32_t b = v - f * (uint32_t)a.B;
+                grow = a.grad + (size_t)b * a.grad_stride + __ldg(a.feat_out_col + f);
+                if (a.pooling_mode == TDFO_POOL_MEAN) {
+                    const int64_t len = __ldg(a.offsets + v + 1) - __ldg(a.offsets + v);
+                    scale = 1.f / (float)len;
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < CPL; ++k) {
+                const int c = sub + k * LPR;
+                if (c < a.nchunks) {
+#pragma unroll
+                    for (int q = 0; q < E; q += 4) {
+                        const uint4 r = ldg_128(grow + (size_t)c * E + q);
+                        g[k][q]     = fmaf(scale, __uint_as_float(r.x), g[k][q]);
+                        g[k][q + 1] = fmaf(scale, __uint_as_float(r.y), g[k][q + 1]);
+                        g[k][q + 2] = fmaf(scale, __uint_as_float(r.z), g[k][q + 2]);
+                        g[k][q + 3] = fmaf(scale, __uint_as_float(r.w), g[k][q + 3]);
+                    }
+                }
+            }
+        }
+
+        // read the row once
+        float w[CPL][E];
+#pragma unroll
+        for (int k = 0; k < CPL; ++k) {
+            const int c = sub + k * LPR;
+            if (c < a.nchunks) Chunk<T>::unpack(ld_128(wbase + (size_t)row * a.nchunks + c), w[k]);
+            else {
+#pragma unroll
+                for (int i = 0; i < E; ++i) w[k][i] = 0.f;
+            }
+        }
+
+        if (OPT == TDFO_OPT_SGD) {
+#pragma unroll
+            for (int k = 0; k < CPL; ++k)
+#pragma unroll
+                for (int i = 0; i < E; ++i) {
+                    const float gi = fmaf(a.wd, w[k][i], g[k][i]);
+                    w[k][i] = fmaf(-a.lr, gi, w[k][i]);
+                }
+        } else if (OPT == TDFO_OPT_ROWWISE_ADAGRAD) {
+            float ss = 0.f;
+#pragma unroll
+            for (int k = 0; k < CPL; ++k)
+#pragma unroll
+                for (int i = 0; i < E; ++i) {
+                    g[k][i] = fmaf(a.wd, w[k][i], g[k][i]);
+                    ss = fmaf(g[k][i], g[k][i], ss);
+                }
+#pragma unroll
+            for (int o = 1; o < LPR; o <<= 1) ss += __shfl_xor_sync(gmask, ss, o);
+            const float h_old = a.state0[row];
+            __syncwarp(gmask);                       // every lane has read h before lane 0 overwrites it
+            const float h = h_old + ss / (float)a.D;
+            const float mult = a.lr / (sqrtf(h) + a.eps);
+            if (sub == 0) a.state0[row] = h;
+#pragma unroll
+            for (int k = 0; k < CPL; ++k)
+#pragma unroll
+                for (int i = 0; i < E; ++i) w[k][i] = fmaf(-mult, g[k][i], w[k][i]);
+        } else {   // ADAM
+#pragma unroll
+            for (int k = 0; k < CPL; ++k) {
+                const int c = sub + k * LPR;
+                if (c < a.nchunks) {
+                    float* m = a.state0 + (size_t)row * a.D + (size_t)c * E;
+                    float* v = a.state1 + (size_t)row * a.D + (size_t)c * E;
+#pragma unroll
+                    for (int q = 0; q < E; q += 4) {
+                        uint4 mr = ld_128(m + q), vr = ld_128(v + q);
+                        float mm[4] = {__uint_as_float(mr.x), __uint_as_float(mr.y), __uint_as_float(mr.z), __uint_as_float(mr.w)};
+                        float vv[4] = {__uint_as_float(vr.x), __uint_as_float(vr.y), __uint_as_float(vr.z), __uint_as_float(vr.w)};
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float gi = g[k][q + i];
+                            mm[i] = a.beta1 * mm[i] + (1.f - a.beta1) * gi;
+                            vv[i] = a.beta2 * vv[i] + (1.f - a.beta2) * gi * gi;
+                            const float mhat = mm[i] / a.bc1;
+                            const float vhat = vv[i] / a.bc2;
+                            w[k][q + i] -= a.lr * (mhat / (sqrtf(vhat) + a.eps) + a.wd * w[k][q + i]);
+                        }
+                        st_128(m + q, make_uint4(__float_as_uint(mm[0]), __float_as_uint(mm[1]), __float_as_uint(mm[2]), __float_as_uint(mm[3])));
+                        st_128(v + q, make_uint4(__float_as_uint(vv[0]), __float_as_uint(vv[1]), __float_as_uint(vv[2]), __float_as_uint(vv[3])));
+                    }
+                }
+            }
+        }
+
+#pragma unroll
+        for (int k = 0; k < CPL; ++k) {
+            const int c = sub + k * LPR;
+            if (c < a.nchunks) st_128(wbase + (size_t)row * a.nchunks + c, Chunk<T>::pack(w[k]));
+        }
+    }
+}
+
+template <typename T, int LPR, int CPL>
+static int launch_update(const UpdateArgs& a, int opt, int64_t max_unique, cudaStream_t st) {
+    constexpr int GPB = kUpdThreads / LPR;
+    int64_t blocks = (max_unique + GPB - 1) / GPB;
+    const int64_t cap = (int64_t)kNumSMs * 32;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    switch (opt) {
+        case TDFO_OPT_SGD:
+            sparse_update_kernel<T, LPR, CPL, TDFO_OPT_SGD><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
+        case TDFO_OPT_ROWWISE_ADAGRAD:
+            sparse_update_kernel<T, LPR, CPL, TDFO_OPT_ROWWISE_ADAGRAD><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
+        default:
+            sparse_update_kernel<T, LPR, CPL, TDFO_OPT_ADAM><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
+    }
+    count_launch();
+    TDFO_LAUNCH_CHECK("sparse_update");
+    return TDFO_OK;
+}
+
+template <typename T>
+static int dispatch_update(const UpdateArgs& a, int opt, int64_t max_unique, cudaStream_t st) {
+    const int n = a.nchunks;
+    if (n <= 1)   return launch_update<T, 1, 1>(a, opt, max_unique, st);
+    if (n <= 2)   return launch_update<T, 2, 1>(a, opt, max_unique, st);
+    if (n <= 4)   return launch_update<T, 4, 1>(a, opt, max_unique, st);
+    if (n <= 8)   return launch_update<T, 8, 1>(a, opt, max_unique, st);
+    if (n <= 16)  return launch_update<T, 16, 1>(a, opt, max_unique, st);
+    if (n <= 32)  return launch_update<T, 32, 1>(a, opt, max_unique, st);
+    if (n <= 64)  return launch_update<T, 32, 2>(a, opt, max_unique, st);
+    if (n <= 128) return launch_update<T, 32, 4>(a, opt, max_unique, st);
+    if (n <= 256) return launch_update<T, 32, 8>(a, opt, max_unique, st);
+    set_error("sparse_update: row of %d bytes exceeds the 4096-byte maximum", n * 16);
+    return TDFO_ERR_UNSUPPORTED;
+}
+
+static int key_bits_for(int64_t total_rows) {   // bits needed to hold the value total_rows itself
+    int b = 1;
+    while (b < 32 && (total_rows >> b) != 0) ++b;
+    return b;
+}
+
+static int check_common(const char* who, int32_t weights_dtype, int64_t total_rows, int32_t D) {
+    if (weights_dtype != TDFO_F32 && weights_dtype != TDFO_BF16) {
+        set_error("%s: unknown weights_dtype %d", who, weights_dtype);
+        return TDFO_ERR_INVALID_ARG;
+    }
+    const size_t esz = weights_dtype == TDFO_F32 ? 4 : 2;
+    if (D <= 0 || (D * esz) % 16 != 0) {
+        set_error("%s: row size D*elem = %zu bytes is not a positive multiple of 16", who, (size_t)D * esz);
+        return TDFO_ERR_INVALID_ARG;
+    }
+    if (total_rows < 0 || total_rows >= 0xffffffffll) {
+        set_error("%s: total_rows %lld must be < 2^32-1", who, (long long)total_rows);
+        return TDFO_ERR_INVALID_ARG;
+    }
+    return TDFO_OK;
+}
+
+static int check_opt(const char* who, const tdfo_optimizer_args* opt, const float* state0, const float* state1) {
+    if (!opt) { set_error("%s: optimizer args are null", who); return TDFO_ERR_INVALID_ARG; }
+    if (opt->optimizer < TDFO_OPT_SGD || opt->optimizer > TDFO_OPT_ADAM) {
+        set_error("%s: unknown optimizer %d", who, opt->optimizer);
+        return TDFO_ERR_INVALID_ARG;
+    }
+    if (opt->optimizer == TDFO_OPT_ROWWISE_ADAGRAD && !state0) {
+        set_error("%s: row-wise Adagrad needs state0 (float[total_rows])", who);
+        return TDFO_ERR_INVALID_ARG;
+    }
+    if (opt->optimizer == TDFO_OPT_ADAM && (!state0 || !state1 || opt->step < 1)) {
+        set_error("%s: ADAM needs state0, state1 (float[total_rows, D]) and step >= 1", who);
+        return TDFO_ERR_INVALID_ARG;
+    }
+    return TDFO_OK;
+}
+
+int sparse_update_impl(void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
+                       float* state0, float* state1, const float* grad_out, int64_t grad_stride,
+                       const uint32_t* sorted_vals, const uint32_t* unique_keys,
+                       const uint32_t* seg_starts, const uint32_t* num_unique,
+                       const int64_t* offsets, const int64_t* feat_out_col, int32_t F, int64_t B,
+                       int64_t L, int32_t pooling_mode, const tdfo_optimizer_args* opt, cudaStream_t st) {
+    if (L == 0) return TDFO_OK;
+    const size_t esz = weights_dtype == TDFO_F32 ? 4 : 2;
+    UpdateArgs a;
+    a.weights = weights; a.state0 = state0; a.state1 = state1; a.grad = grad_out;
+    a.sorted_vals = sorted_vals; a.unique_keys = unique_keys; a.seg_starts = seg_starts;
+    a.num_unique = num_unique; a.offsets = offsets; a.feat_out_col = feat_out_col;
+    a.grad_stride = grad_stride; a.B = B; a.total_rows = (uint32_t)total_rows; a.D = D;
+    a.nchunks = (int32_t)(D * esz / 16); a.pooling_mode = pooling_mode;
+    a.lr = opt->learning_rate; a.eps = opt->eps; a.wd = opt->weight_decay;
+    a.beta1 = opt->beta1; a.beta2 = opt->beta2;
+    a.bc1 = 1.f; a.bc2 = 1.f;
+    if (opt->optimizer == TDFO_OPT_ADAM) {
+        a.bc1 = (float)(1.0 - pow((double)opt->beta1, (double)opt->step));
+        a.bc2 = (float)(1.0 - pow((double)opt->beta2, (double)opt->step));
+    }
+    const int64_t max_unique = L < total_rows + 1 ? L : total_rows + 1;
+    (void)F;
+    return weights_dtype == TDFO_F32 ? dispatch_update<float>(a, opt->optimizer, max_unique, st)
+                                     : dispatch_update<__nv_bfloat16>(a, opt->optimizer, max_unique, st);
+}
+
+static size_t pair_array_bytes(int64_t L) { return align_up((size_t)(L + 1) * sizeof(uint32_t), 256); }
+
+}  // namespace tdfo
+
+using namespace tdfo;
+
+extern "C" int tdfo_linearize_indices(const int64_t* indices, const int64_t* offsets,
+                                      const int64_t* feat_row_base, const int64_t* feat_rows,
+                                      int32_t F, int64_t B, int64_t total_rows, int32_t pooling_mode,
+                                      uint32_t* keys, uint32_t* vals, int32_t* err_flag, void* stream) {
+    TDFO_CHECK_ARG(F >= 0 && B >= 0, "linearize_indices: negative size");
+    TDFO_CHECK_ARG(total_rows >= 0 && total_rows < 0xffffffffll, "linearize_indices: total_rows must be < 2^32-1");
+    TDFO_CHECK_ARG((int64_t)F * B < (1ll << 32), "linearize_indices: F*B must be < 2^32");
+    if (F == 0 || B == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(indices && offsets && feat_row_base && feat_rows && keys && vals, "linearize_indices: null pointer");
+    const int64_t num_bags = (int64_t)F * B;
+    const int64_t blocks = (num_bags + kUpdThreads / 32 - 1) / (kUpdThreads / 32);
+    linearize_kernel<<<(unsigned)blocks, kUpdThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        indices, offsets, feat_row_base, feat_rows, B, num_bags, (uint32_t)total_rows,
+        pooling_mode == TDFO_POOL_NONE, keys, vals, err_flag);
+    count_launch();
+    TDFO_LAUNCH_CHECK("linearize_indices");
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
+                                  float* state0, float* state1, const float* grad_out, int64_t grad_stride,
+                                  const uint32_t* sorted_vals, const uint32_t* unique_keys,
+                                  const uint32_t* seg_starts, const uint32_t* num_unique,
+                                  const int64_t* offsets, const int64_t* feat_out_col, int32_t F,
+                                  int64_t B, int64_t L, int32_t pooling_mode,
+                                  const tdfo_optimizer_args* opt, void* stream) {
+    int rc = check_common("sparse_update", weights_dtype, total_rows, D);
+    if (rc) return rc;
+    rc = check_opt("sparse_update", opt, state0, state1);
+    if (rc) return rc;
+    TDFO_CHECK_ARG(pooling_mode >= TDFO_POOL_SUM && pooling_mode <= TDFO_POOL_NONE, "sparse_update: unknown pooling_mode");
+    TDFO_CHECK_ARG(L >= 0 && L < (1ll << 30), "sparse_update: L must be in [0, 2^30)");
+    if (L == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(weights && grad_out && sorted_vals && unique_keys && seg_starts && num_unique, "sparse_update: null pointer");
+    TDFO_CHECK_ARG(aligned(weights, 16) && aligned(grad_out, 16), "sparse_update: weights/grad_out not 16-byte aligned");
+    if (pooling_mode != TDFO_POOL_NONE) {
+        TDFO_CHECK_ARG(feat_out_col != nullptr, "sparse_update: feat_out_col is null");
+        TDFO_CHECK_ARG(grad_stride % 4 == 0, "sparse_update: grad_stride not a multiple of 4");
+    }
+    TDFO_CHECK_ARG(pooling_mode != TDFO_POOL_MEAN || offsets, "sparse_update: MEAN pooling needs offsets");
+    return sparse_update_impl(weights, weights_dtype, total_rows, D, state0, state1, grad_out, grad_stride,
+                              sorted_vals, unique_keys, seg_starts, num_unique, offsets, feat_out_col,
+                              F, B, L, pooling_mode, opt, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int tdfo_backward_scratch_layout(int64_t L, int64_t total_rows, tdfo_backward_layout* layout) {
+    TDFO_CHECK_ARG(layout != nullptr, "backward_scratch_layout: null layout");
+    TDFO_CHECK_ARG(L >= 0 && L < (1ll << 30), "backward_scratch_layout: L must be in [0, 2^30)");
+    TDFO_CHECK_ARG(total_rows >= 0 && total_rows < 0xffffffffll, "backward_scratch_layout: total_rows must be < 2^32-1");
+    const int bits = key_bits_for(total_rows);
+    const size_t A = pair_array_bytes(L);
+    const int passes = (bits + 7) / 8;
+    const int res = passes & 1;               // buffer pair the sorted result lands in
+    layout->key_bits = bits;
+    layout->sorted_keys = (res ? 2 : 0) * A;
+    layout->sorted_vals = (res ? 3 : 1) * A;
+    layout->unique_keys = (res ? 0 : 2) * A;  // the other pair is free after the sort
+    layout->seg_starts  = (res ? 1 : 3) * A;
+    layout->num_unique = 4 * A;
+    const size_t sort_off = 4 * A + 256;
+    const size_t scan_off = sort_off + radix_sort_scratch_bytes_impl(L, bits);
+    layout->total_bytes = scan_off + tdfo_scan_scratch_bytes(L);
+    return TDFO_OK;
+}
+
+extern "C" size_t tdfo_backward_scratch_bytes(int64_t L, int64_t total_rows) {
+    tdfo_backward_layout lay;
+    if (tdfo_backward_scratch_layout(L, total_rows, &lay) != TDFO_OK) return 0;
+    return lay.total_bytes;
+}
+
+extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dtype, int64_t total_rows,
+                                              int32_t D, float* state0, float* state1,
+                                              const float* grad_out, int64_t grad_stride,
+                                              const int64_t* indices, const int64_t* offsets,
+                                              const float* per_sample_weights,
+                                              const int64_t* feat_row_base, const int64_t* feat_rows,
+                                              const int64_t* feat_out_col, int32_t F, int64_t B,
+                                              int64_t L, int32_t pooling_mode,
+                                              const tdfo_optimizer_args* opt, int32_t* err_flag,
+                                              void* scratch, size_t scratch_bytes, void* stream) {
+    int rc = check_common("embedding_backward_update", weights_dtype, total_rows, D);
+    if (rc) return rc;
+    rc = check_opt("embedding_backward_update", opt, state0, state1);
+    if (rc) return rc;
+    TDFO_CHECK_ARG(pooling_mode >= TDFO_POOL_SUM && pooling_mode <= TDFO_POOL_NONE,
+                   "embedding_backward_update: unknown pooling_mode");
+    TDFO_CHECK_ARG(F >= 0 && B >= 0 && L >= 0 && L < (1ll << 30), "embedding_backward_update: size out of range");
+    if (per_sample_weights) {
+        set_error("embedding_backward_update: per-sample weights are not supported in the backward yet");
+        return TDFO_ERR_UNSUPPORTED;
+    }
+    if (F == 0 || B == 0 || L == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(weights && grad_out && indices && offsets && feat_row_base && feat_rows,
+                   "embedding_backward_update: null pointer");
+    TDFO_CHECK_ARG(aligned(weights, 16) && aligned(grad_out, 16), "embedding_backward_update: weights/grad_out not 16-byte aligned");
+    if (pooling_mode != TDFO_POOL_NONE) {
+        TDFO_CHECK_ARG(feat_out_col != nullptr, "embedding_backward_update: feat_out_col is null");
+        TDFO_CHECK_ARG(grad_stride % 4 == 0, "embedding_backward_update: grad_stride not a multiple of 4");
+    }
+    tdfo_backward_layout lay;
+    rc = tdfo_backward_scratch_layout(L, total_rows, &lay);
+    if (rc) return rc;
+    if (!scratch || !aligned(scratch, 256) || scratch_bytes < lay.total_bytes) {
+        set_error("embedding_backward_update: scratch null, misaligned or smaller than %zu bytes", lay.total_bytes);
+        return TDFO_ERR_SCRATCH;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    char* base = static_cast<char*>(scratch);
+    const size_t A = pair_array_bytes(L);
+    uint32_t* k0 = reinterpret_cast<uint32_t*>(base);
+    uint32_t* v0 = reinterpret_cast<uint32_t*>(base + A);
+    uint32_t* k1 = reinterpret_cast<uint32_t*>(base + 2 * A);
+    uint32_t* v1 = reinterpret_cast<uint32_t*>(base + 3 * A);
+    uint32_t* num_unique = reinterpret_cast<uint32_t*>(base + lay.num_unique);
+    void* sort_scratch = base + 4 * A + 256;
+    void* scan_scratch = base + 4 * A + 256 + radix_sort_scratch_bytes_impl(L, lay.key_bits);
+
+    rc = tdfo_linearize_indices(indices, offsets, feat_row_base, feat_rows, F, B, total_rows, pooling_mode,
+                                k0, v0, err_flag, stream);
+    if (rc) return rc;
+    int where = 0;
+    rc = radix_sort_impl(k0, v0, k1, v1, L, lay.key_bits, err_flag, sort_scratch, st, &where);
+    if (rc) return rc;
+    uint32_t* sk = reinterpret_cast<uint32_t*>(base + lay.sorted_keys);
+    uint32_t* sv = reinterpret_cast<uint32_t*>(base + lay.sorted_vals);
+    uint32_t* uk = reinterpret_cast<uint32_t*>(base + lay.unique_keys);
+    uint32_t* ss = reinterpret_cast<uint32_t*>(base + lay.seg_starts);
+    if ((where ? k1 : k0) != sk) {
+        set_error("embedding_backward_update: internal layout mismatch");
+        return TDFO_ERR_INVALID_ARG;
+    }
+    rc = unique_segments_impl(sk, L, uk, ss, num_unique, err_flag, scan_scratch, st);
+    if (rc) return rc;
+    return sparse_update_impl(weights, weights_dtype, total_rows, D, state0, state1, grad_out, grad_stride,
+                              sv, uk, ss, num_unique, offsets, feat_out_col, F, B, L, pooling_mode, opt, st);
+}
