@@ -1,0 +1,133 @@
+"""The CPU oracle against the committed known answers (tests/golden/make_golden.py):
+torch.nn.EmbeddingBag / nn.Embedding, torch SGD / AdamW, FBGEMM's rowwise_sparse_adagrad_ref
+and the hand-computed routing cases.  This is what pins the oracle; the reference itself
+ships no vectors for this path."""
+import numpy as np
+
+import oracle as orc
+
+RTOL, ATOL = 1e-5, 1e-6   # north star: 1e-5 relative for fp32
+
+
+def test_forward_matches_embedding_bag(golden):
+    g = golden("fwd")
+    base, rows, col = g.table_meta()
+    for mode, psw, want in ((orc.POOL_SUM, None, g.out_sum), (orc.POOL_MEAN, None, g.out_mean),
+                            (orc.POOL_SUM, g.psw, g.out_wsum)):
+        out, oob = orc.embedding_forward(g.weights, g.D, g.indices, g.offsets, psw, base, rows, col,
+                                         g.F, g.B, mode)
+        assert not oob
+        np.testing.assert_allclose(out, want, rtol=RTOL, atol=ATOL)
+    out, oob = orc.embedding_forward(g.weights, g.D, g.indices, g.offsets, None, base, rows, None,
+                                     g.F, g.B, orc.POOL_NONE)
+    assert not oob
+    np.testing.assert_array_equal(out, g.out_seq)        # pure gather: bit-exact
+
+
+def test_empty_bags_are_zero(golden):
+    g = golden("fwd")
+    base, rows, col = g.table_meta()
+    out, _ = orc.embedding_forward(g.weights, g.D, g.indices, g.offsets, None, base, rows, col, g.F, g.B,
+                                   orc.POOL_MEAN)
+    lengths = g.lengths.reshape(g.F, g.B)
+    for f in range(g.F):
+        for b in range(g.B):
+            if lengths[f, b] == 0:
+                assert not out[b, f * g.D:(f + 1) * g.D].any()
+
+
+def test_sgd_matches_torch(golden):
+    g = golden("sgd")
+    base, rows, col = g.table_meta()
+    for mode, want in ((orc.POOL_SUM, g.weights_after_sum), (orc.POOL_MEAN, g.weights_after_mean)):
+        w = g.weights.copy()
+        orc.embedding_backward_update(w, g.D, None, None, g.grad_out, g.indices, g.offsets, base, rows, col,
+                                      g.F, g.B, mode, orc.OptArgs(orc.OPT_SGD, learning_rate=g.lr))
+        np.testing.assert_allclose(w, want, rtol=RTOL, atol=ATOL)
+
+
+def test_rowwise_adagrad_matches_fbgemm_ref(golden):
+    g = golden("rwa")
+    base, rows, col = g.table_meta()
+    for tag in ("nowd", "wd"):
+        w, h = g.weights.copy(), g.h0.copy()
+        opt = orc.OptArgs(orc.OPT_ROWWISE_ADAGRAD, learning_rate=g.lr, eps=g.eps,
+                          weight_decay=getattr(g, f"wd_{tag}"))
+        orc.embedding_backward_update(w, g.D, h, None, g.grad_out, g.indices, g.offsets, base, rows, col,
+                                      g.F, g.B, orc.POOL_SUM, opt)
+        np.testing.assert_allclose(w, getattr(g, f"weights_after_{tag}"), rtol=RTOL, atol=ATOL)
+        np.testing.assert_allclose(h, getattr(g, f"h_after_{tag}"), rtol=RTOL, atol=ATOL)
+
+
+def test_adam_matches_torch_adamw(golden):
+    g = golden("adam")
+    base, rows, col = g.table_meta()
+    for tag in ("nowd", "wd"):
+        w = g.weights.copy()
+        m, v = np.zeros_like(w), np.zeros_like(w)
+        for s in range(g.steps):
+            opt = orc.OptArgs(orc.OPT_ADAM, learning_rate=g.lr, eps=g.eps, weight_decay=getattr(g, f"wd_{tag}"),
+                              beta1=g.beta1, beta2=g.beta2, step=s + 1)
+            orc.embedding_backward_update(w, g.D, m, v, getattr(g, f"grad_out{s}"), getattr(g, f"indices{s}"),
+                                          getattr(g, f"offsets{s}"), base, rows, col, g.F, g.B, orc.POOL_SUM, opt)
+            np.testing.assert_allclose(w, getattr(g, f"weights_after_{tag}{s}"), rtol=RTOL, atol=ATOL)
+
+
+def test_bucketize_kat(golden):
+    g = golden("bucketize")
+    offsets = orc.complete_cumsum(g.lengths)
+    nl, no, ni, nw, perm, oob = orc.bucketize_row_wise(offsets, g.indices, g.weights, g.block_sizes,
+                                                       g.F, g.B, g.world)
+    assert not oob
+    np.testing.assert_array_equal(nl, g.new_lengths)
+    np.testing.assert_array_equal(no, orc.complete_cumsum(g.new_lengths))
+    np.testing.assert_array_equal(ni, g.new_indices)
+    np.testing.assert_array_equal(nw, g.new_weights)
+    np.testing.assert_array_equal(perm, g.unbucketize_permute)
+
+
+def test_permute_kat(golden):
+    g = golden("permute")
+    ol, oo, oi, _ = orc.permute_2d(g.permute, g.B, g.in_lengths, orc.complete_cumsum(g.in_lengths), g.in_indices)
+    np.testing.assert_array_equal(ol, g.out_lengths)
+    np.testing.assert_array_equal(oi, g.out_indices)
+    np.testing.assert_array_equal(oo, orc.complete_cumsum(g.out_lengths))
+
+
+def test_jagged_dense_kat(golden):
+    g = golden("jagged")
+    np.testing.assert_array_equal(orc.jagged_2d_to_dense(g.values, g.offsets, g.max_len), g.dense)
+    np.testing.assert_array_equal(orc.dense_to_jagged(g.dense, g.offsets), g.back)
+    np.testing.assert_array_equal(orc.jagged_1d_to_padded_dense(g.ids, g.offsets, g.desired, g.pad), g.padded)
+
+
+def test_sort_unique_against_numpy():
+    rng = np.random.default_rng(1)
+    keys = rng.integers(0, 50, size=1000).astype(np.uint32)
+    vals = np.arange(1000, dtype=np.uint32)
+    sk, sv = orc.sort_pairs_stable(keys, vals)
+    order = np.argsort(keys, kind="stable")
+    np.testing.assert_array_equal(sk, keys[order])
+    np.testing.assert_array_equal(sv, vals[order])
+    uk, ss, nu = orc.unique_segments(sk)
+    u, first = np.unique(sk, return_index=True)
+    assert nu == u.size
+    np.testing.assert_array_equal(uk, u)
+    np.testing.assert_array_equal(ss[:-1], first)
+    assert ss[-1] == 1000
+
+
+def test_out_of_range_ids_are_skipped_and_reported(golden):
+    g = golden("fwd")
+    base, rows, col = g.table_meta()
+    idx = g.indices.copy()
+    idx[0] = rows[0]          # one past the end of table 0
+    idx[2] = -1
+    out, oob = orc.embedding_forward(g.weights, g.D, idx, g.offsets, None, base, rows, col, g.F, g.B, orc.POOL_SUM)
+    assert oob
+    keep = np.ones(idx.size, bool); keep[[0, 2]] = False
+    # same as dropping those two ids from their bags
+    psw = keep.astype(np.float32)
+    idx2 = np.where(keep, idx, 0)
+    want, _ = orc.embedding_forward(g.weights, g.D, idx2, g.offsets, psw, base, rows, col, g.F, g.B, orc.POOL_SUM)
+    np.testing.assert_allclose(out, want, rtol=RTOL, atol=ATOL)
