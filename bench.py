@@ -1,0 +1,415 @@
+#!/usr/bin/env python
+"""bench.py — embedding lookups/sec (fwd + bwd + fused update) on BASELINE config 2.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One "step" = one pass of the hot path over one synthetic jagged batch:
+pooled lookup -> (synthetic upstream gradient) -> linearise -> radix sort -> unique ->
+fused row-wise Adagrad update.  Prints ONE JSON line (rank 0).
+
+* `value`     device-resident: ids / offsets / gradient already in HBM, timed with CUDA events
+              around exactly K steps on the launching stream, max over ranks.
+* `e2e`       the same metric through the public module API (KeyedJaggedTensor ->
+              EmbeddingBagCollection -> loss.backward()) with HOST (pinned) inputs: the per-step
+              host->device copy and a device->host read of the loss are inside the timed region.
+* `roofline`  the dominant kernel's algorithmic bytes / its CUDA-event time inside the timed region,
+              against the measured HBM copy bandwidth in MEASURED_PEAKS.json.
+* `cpu_baseline` / `--impl reference`: the CPU oracle (oracle/tdfo_oracle.c, OpenMP over all host
+              threads) on a bounded sample of the same workload.  The reference's own CPU kernels
+              (torchrec / fbgemm_gpu) are not installable here, hence kind = "port".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "embedding lookups/sec (fwd+bwd+update)"
+UNIT = "lookups/s"
+
+# BASELINE.json configs[1]
+CFG = dict(tables=26, rows=1_000_000, dim=128, pooling=20, batch=16384, lr=0.01, eps=1e-8)
+WORKLOAD = ("single-GPU EmbeddingBagCollection: 26 tables x 1M rows x dim 128 fp32, pooling factor 20, "
+            "batch 16384, uniform ids, SUM pooling, row-wise Adagrad")
+N_BATCHES = 4      # distinct id batches rotated through the timed region
+
+
+def measured_peak_gbs():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def algorithmic_bytes(L, bags, U, D, w=4, g=4, s=4):
+    """SURVEY.md §8(d) / BASELINE.md §3."""
+    fwd = L * (D * w + 8) + (bags + 1) * 8 + bags * D * g
+    upd_kernel = bags * D * g + U * (2 * D * w + 2 * s)      # the update kernel's own share
+    bwd = upd_kernel + L * 8                                  # + ids read by the linearise stage
+    return fwd, bwd, upd_kernel
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu_index, self.proc, self.path = gpu_index, None, f"/tmp/tdfo_clocks_{os.getpid()}.csv"
+
+    def start(self):
+        try:
+            self.fh = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu_index)], stdout=self.fh,
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.fh.close()
+        sm, smax, reasons = [], [], set()
+        for line in open(self.path):
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1])); smax.append(float(parts[2]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        try:
+            os.remove(self.path)
+        except OSError:
+            pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(smax), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- CPU arm (oracle port)
+def cpu_arm(steps: int, warmup: int, sample_batch: int, rows: int | None = None):
+    """Times oracle fwd + bwd/update (row-wise Adagrad) on the host.  Returns (lookups/s, info)."""
+    import oracle as orc
+    import psutil
+    F, D, P = CFG["tables"], CFG["dim"], CFG["pooling"]
+    rows = rows or CFG["rows"]
+    need = F * rows * D * 4
+    avail = psutil.virtual_memory().available
+    if need > 0.5 * avail:                               # keep tables <= half of free host RAM
+        rows = max(1000, int(0.5 * avail / (F * D * 4)))
+    B = sample_batch
+    cores = os.cpu_count() or 1
+    w = np.empty((F * rows, D), dtype=np.float32)
+    w.fill(0.01)
+    h = np.zeros(F * rows, dtype=np.float32)
+    rng = np.random.default_rng(42)
+    lengths = np.full(F * B, P, dtype=np.int32)
+    offsets = orc.complete_cumsum(lengths)
+    L = int(offsets[-1])
+    row_base = (np.arange(F) * rows).astype(np.int64)
+    frows = np.full(F, rows, dtype=np.int64)
+    col = (np.arange(F) * D).astype(np.int64)
+    grad = rng.normal(size=(B, F * D)).astype(np.float32)
+    opt = orc.OptArgs(orc.OPT_ROWWISE_ADAGRAD, CFG["lr"], CFG["eps"])
+    times = []
+    for i in range(warmup + steps):
+        idx = rng.integers(0, rows, size=L).astype(np.int64)
+        t0 = time.perf_counter()
+        orc.embedding_forward(w, D, idx, offsets, None, row_base, frows, col, F, B, orc.POOL_SUM)
+        orc.embedding_backward_update(w, D, h, None, grad, idx, offsets, row_base, frows, col, F, B, orc.POOL_SUM, opt)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    t = sum(times)
+    info = {"cores": cores, "kind": "port",
+            "sample": f"{steps} steps of batch {B} (1/{CFG['batch'] // B} of the workload batch, L={L} lookups/step), "
+                      f"{F} tables x {rows} rows x dim {D} fp32, oracle/tdfo_oracle.c with OpenMP"}
+    return L * steps / t, t / steps * 1e3, info
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    value, ms, info = cpu_arm(args.steps, min(args.warmup, 1), sample_batch=CFG["batch"] // 8)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": min(args.warmup, 1), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "note": "CPU arm: oracle port of the path on the host cores; the reference's own "
+                   "CPU kernels (torchrec/fbgemm_gpu) are not installable on this image"},
+        "cpu_baseline": {"value": value, "unit": UNIT, **info},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import tdfo_b200 as t
+    from tdfo_b200 import _lib, ops
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the tdfo_b200 path has no CPU fallback "
+                         "(use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=dev)
+
+    F, rows, D, P, B = CFG["tables"], CFG["rows"], CFG["dim"], CFG["pooling"], CFG["batch"]
+    gen = torch.Generator(device=dev).manual_seed(42 + rank)
+    bound = 1.0 / (rows ** 0.5)
+
+    tables = [t.EmbeddingBagConfig(num_embeddings=rows, embedding_dim=D, name=f"t{i}", feature_names=[f"f{i}"],
+                                   pooling=t.PoolingType.SUM) for i in range(F)]
+    ebc = t.EmbeddingBagCollection(tables, device=dev)
+    fused = ebc.set_fused_optimizer(t.EmbOptimType.EXACT_ROWWISE_ADAGRAD, learning_rate=CFG["lr"], eps=CFG["eps"])
+    ebc.train()
+    g0 = ebc._groups[0]
+    grp = ebc._table_group(g0, True)
+    keys = [f"f{i}" for i in range(F)]
+
+    lengths = torch.full((F * B,), P, dtype=torch.int32, device=dev)
+    offsets = ops.complete_cumsum(lengths)
+    L = int(offsets[-1].item())
+    bags = F * B
+    row_base = torch.arange(F, device=dev).repeat_interleave(B * P) * rows
+    batches, uniques = [], []
+    for _ in range(N_BATCHES):
+        idx = torch.randint(0, rows, (L,), device=dev, generator=gen)
+        batches.append(idx)
+        uniques.append(int(torch.unique(idx + row_base).numel()))
+    del row_base
+    grad_out = torch.randn((B, F * D), device=dev, generator=gen)
+    opt = ops.make_optimizer_args(_lib.OPT_ROWWISE_ADAGRAD, CFG["lr"], CFG["eps"])
+    lay = ops.backward_layout(L, F * rows)
+    scratch = torch.empty(lay.total_bytes, dtype=torch.uint8, device=dev)
+    out = torch.empty((B, F * D), dtype=torch.float32, device=dev)
+    stages = ["forward", "linearize", "sort", "unique", "update"]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_fused(i):
+        idx = batches[i % N_BATCHES]
+        ops.embedding_forward(grp, idx, offsets, B, _lib.POOL_SUM, out=out)
+        ops.embedding_backward_update(grp, grad_out, idx, offsets, B, _lib.POOL_SUM, opt, scratch=scratch)
+
+    def step_staged(i, ev):
+        """Same kernels, same order, one C-ABI call per stage so each can be bracketed by events."""
+        idx = batches[i % N_BATCHES]
+        ev[0].record()
+        ops.embedding_forward(grp, idx, offsets, B, _lib.POOL_SUM, out=out)
+        ev[1].record()
+        k, v = ops.linearize_indices(grp, idx, offsets, B, _lib.POOL_SUM)
+        ev[2].record()
+        sk, sv = ops.radix_sort_pairs(k, v, lay.key_bits, grp.err_flag)
+        ev[3].record()
+        uk, ss, nu = ops.unique_segments(sk, grp.err_flag)
+        ev[4].record()
+        ops.sparse_update(grp, grad_out, sv, uk, ss, nu, offsets, B, L, _lib.POOL_SUM, opt)
+        ev[5].record()
+
+    # ---------------- device-resident arm (`value`): the single-call product path
+    for i in range(args.warmup):
+        step_fused(i)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = ops.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        step_fused(args.warmup + i)
+    e1.record()
+    barrier()
+    launches = ops.launch_count() - launches0
+    ms_total = e0.elapsed_time(e1)
+
+    # ---------------- per-kernel timing with the same kernels staged (roofline of the dominant kernel)
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(6)] for _ in range(args.steps)]
+    for i in range(2):
+        step_staged(i, evs[0])
+    barrier()
+    for i in range(args.steps):
+        step_staged(args.warmup + i, evs[i])
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    stage_ms = {s: statistics.mean(evs[i][j].elapsed_time(evs[i][j + 1]) for i in range(args.steps))
+                for j, s in enumerate(stages)}
+    ops.check_error_flag(grp.err_flag, "bench")
+
+    if world > 1:
+        tt = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total = float(tt.item())
+    ms_step = ms_total / args.steps
+    value = L * world * args.steps / (ms_total * 1e-3)
+
+    U = statistics.mean(uniques)
+    fwd_b, bwd_b, upd_b = algorithmic_bytes(L, bags, U, D)
+    peak, peak_src = measured_peak_gbs()
+    kern_bytes = {"forward": fwd_b, "update": upd_b}
+    dominant = max(("forward", "update"), key=lambda s: stage_ms[s])
+    achieved = kern_bytes[dominant] / (stage_ms[dominant] * 1e-3) / 1e9
+    traffic = None
+    tp = ROOT / "profiles" / "ncu_traffic.json"
+    if tp.exists():
+        try:
+            traffic = json.loads(tp.read_text()).get(dominant)
+        except Exception:
+            traffic = None
+    roofline = {"bound": "hbm", "kernel": {"forward": "pooled_forward_kernel", "update": "sparse_update_kernel"}[dominant],
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                "peak_source": peak_src, "algorithmic_bytes_per_launch": kern_bytes[dominant],
+                "launch_ms": stage_ms[dominant]}
+    step_gbs = (fwd_b + bwd_b) / (ms_step * 1e-3) / 1e9
+    kernels = {s: {"ms": stage_ms[s]} for s in stages}
+    for s in ("forward", "update"):
+        kernels[s]["GB/s"] = kern_bytes[s] / (stage_ms[s] * 1e-3) / 1e9
+        kernels[s]["frac_of_peak"] = kernels[s]["GB/s"] / peak
+
+    # ---------------- end-to-end arm through the public module API with host buffers
+    e2e = run_e2e(args, t, ebc, keys, lengths, batches, grad_out, F, B, D, L, world, dev, barrier)
+
+    # ---------------- CPU baseline on rank 0 at N=1
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        del ebc, grp, scratch, out, batches
+        torch.cuda.empty_cache()
+        v, _, info = cpu_arm(steps=3, warmup=1, sample_batch=B // 8)
+        cpu = {"value": v, "unit": UNIT, **info}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "lookups_per_step_per_gpu": L, "unique_rows_per_step": U,
+                       "l2": f"inputs exceed L2: 13.3 GB of tables, {N_BATCHES} rotating id batches of {L * 8 >> 20} MiB",
+                       "parallelism": "1 GPU" if world == 1 else f"{world} independent table shards (no collective)",
+                       "optimizer": "row-wise Adagrad lr 0.01 eps 1e-8, fused into backward"},
+            "roofline": roofline,
+            "step_roofline": {"algorithmic_GB_per_step": (fwd_b + bwd_b) / 1e9, "achieved_GBps": step_gbs,
+                              "frac_of_measured_peak": step_gbs / peak, "frac_of_8TBps_spec": step_gbs / 8000.0},
+            "kernels": kernels,
+            "cpu_baseline": cpu,
+            "e2e": e2e,
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_e2e(args, t, ebc, keys, lengths_dev, batches, grad_out, F, B, D, L, world, dev, barrier):
+    """Public API, host inputs: pinned ids+lengths -> H2D (prefetched one step ahead on a copy stream,
+    as the reference's DataLoader(pin_memory)/prefetch_to_device does) -> KJT -> EBC -> loss ->
+    backward (fused update) -> loss.item()."""
+    import torch
+    import torch.distributed as dist
+    host_vals = [b.cpu().pin_memory() for b in batches]
+    host_lens = lengths_dev.cpu().pin_memory()
+    copy_stream = torch.cuda.Stream(device=dev)
+    slots = [dict(v=torch.empty(L, dtype=torch.int64, device=dev), l=torch.empty(F * B, dtype=torch.int32, device=dev),
+                  ev=torch.cuda.Event()) for _ in range(2)]
+    main = torch.cuda.current_stream(dev)
+
+    def prefetch(i):
+        s = slots[i % 2]
+        copy_stream.wait_stream(main)                       # slot reuse: previous consumer is done
+        with torch.cuda.stream(copy_stream):
+            s["v"].copy_(host_vals[i % len(host_vals)], non_blocking=True)
+            s["l"].copy_(host_lens, non_blocking=True)
+            s["ev"].record(copy_stream)
+
+    def step(i, n_total):
+        s = slots[i % 2]
+        main.wait_event(s["ev"])
+        if i + 1 < n_total:
+            prefetch(i + 1)
+        kjt = t.KeyedJaggedTensor.from_lengths_sync(keys, s["v"], s["l"])
+        kt = ebc(kjt)
+        loss = (kt.values() * grad_out).sum()
+        loss.backward()
+        return loss.item()                                   # D2H read of the step's result
+
+    n_w = max(args.warmup, 1)
+    prefetch(0)
+    for i in range(n_w):
+        step(i, n_w)
+    barrier()
+    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    prefetch(0)
+    for i in range(args.steps):
+        step(i, args.steps)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    ms = max(ms, 0.0)
+    if world > 1:
+        tt = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms = float(tt.item())
+    return {"value": L * world * args.steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / args.steps,
+            "wall_ms_per_step": wall_ms / args.steps,
+            "h2d_bytes_per_step": L * 8 + F * B * 4, "d2h_bytes_per_step": 4,
+            "api": "KeyedJaggedTensor.from_lengths_sync -> EmbeddingBagCollection.forward -> loss.backward() -> loss.item()"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        if args.warmup < 3:
+            args.warmup = 3
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

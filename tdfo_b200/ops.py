@@ -1,0 +1,331 @@
+"""Tensor-level wrappers over the C ABI (``include/tdfo_b200.h``).
+
+Torch is plumbing here: it owns device memory and streams; every op below is one
+call into ``libtdfo_b200.so`` with raw pointers on the current CUDA stream.
+CPU tensors are rejected — there is no fallback path.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass, field
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import (BF16, F32, OPT_ADAM, OPT_ROWWISE_ADAGRAD, OPT_SGD, POOL_MEAN, POOL_NONE, POOL_SUM,
+                   BackwardLayout, OptimizerArgs, check)
+
+__all__ = [
+    "TableGroup", "complete_cumsum", "embedding_forward", "embedding_backward_update", "linearize_indices",
+    "radix_sort_pairs", "unique_segments", "sparse_update", "jagged_2d_to_dense", "dense_to_jagged",
+    "jagged_1d_to_padded_dense", "bucketize_row_wise", "permute_2d", "launch_count", "check_error_flag",
+]
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _cuda(t: torch.Tensor, dtype: torch.dtype, name: str) -> torch.Tensor:
+    if not t.is_cuda:
+        raise RuntimeError(f"tdfo_b200: `{name}` must be a CUDA tensor (there is no CPU path), got {t.device}")
+    if t.dtype != dtype:
+        raise TypeError(f"tdfo_b200: `{name}` must be {dtype}, got {t.dtype}")
+    return t if t.is_contiguous() else t.contiguous()
+
+
+_scratch: dict = {}
+
+
+def _get_scratch(device: torch.device, nbytes: int) -> torch.Tensor:
+    """Per-(device, stream) workspace, grown geometrically; never shrinks."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(int(nbytes * 1.25), 1 << 16), dtype=torch.uint8, device=device)
+        _scratch[key] = buf
+    return buf
+
+
+def launch_count() -> int:
+    return int(_lib.load().tdfo_launch_count())
+
+
+def _wdtype(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise TypeError(f"tdfo_b200: tables must be float32 or bfloat16, got {t.dtype}")
+
+
+@dataclass
+class TableGroup:
+    """All tables of one (dim, dtype) in one ``[total_rows, D]`` buffer plus per-feature metadata.
+
+    ``feat_*`` are device int64 tensors of length F (features in KJT key order):
+    first row / row count of the feature's table in ``weights`` and the first output column.
+    """
+    weights: torch.Tensor
+    feat_row_base: torch.Tensor
+    feat_rows: torch.Tensor
+    feat_out_col: torch.Tensor
+    out_stride: int
+    state0: Optional[torch.Tensor] = None
+    state1: Optional[torch.Tensor] = None
+    err_flag: torch.Tensor = field(default=None)  # int32[1]
+
+    def __post_init__(self):
+        if self.err_flag is None:
+            self.err_flag = torch.zeros(1, dtype=torch.int32, device=self.weights.device)
+
+    @property
+    def D(self) -> int:
+        return self.weights.shape[1]
+
+    @property
+    def F(self) -> int:
+        return self.feat_row_base.numel()
+
+    @property
+    def total_rows(self) -> int:
+        return self.weights.shape[0]
+
+
+def check_error_flag(flag: torch.Tensor, what: str = "embedding lookup") -> None:
+    """Synchronising read of a device error word; raises like fbgemm's BoundsCheckMode.FATAL."""
+    v = int(flag.item())
+    if v & _lib.FLAG_SCAN_TIMEOUT:
+        raise RuntimeError(f"tdfo_b200: internal scan watchdog fired during {what}")
+    if v & _lib.FLAG_INDEX_OOB:
+        flag.zero_()
+        raise IndexError(f"tdfo_b200: an id was out of range of its table during {what}")
+
+
+# --------------------------------------------------------------------------- KJT
+def complete_cumsum(lengths: torch.Tensor) -> torch.Tensor:
+    lengths = _cuda(lengths, torch.int32, "lengths")
+    n = lengths.numel()
+    offsets = torch.empty(n + 1, dtype=torch.int64, device=lengths.device)
+    lib = _lib.load()
+    nb = lib.tdfo_scan_scratch_bytes(n)
+    scratch = _get_scratch(lengths.device, nb)
+    check(lib.tdfo_kjt_complete_cumsum(_ptr(lengths), n, _ptr(offsets), _ptr(scratch), scratch.numel(), _stream()))
+    return offsets
+
+
+def bucketize_row_wise(lengths, offsets, indices, weights, block_sizes, F, B, world, want_permute=False,
+                       err_flag=None):
+    indices = _cuda(indices, torch.int64, "indices")
+    offsets = _cuda(offsets, torch.int64, "offsets")
+    block_sizes = _cuda(block_sizes, torch.int64, "block_sizes")
+    if weights is not None:
+        weights = _cuda(weights, torch.float32, "weights")
+    dev = indices.device
+    bags, L = F * B, indices.numel()
+    new_lengths = torch.empty(bags * world, dtype=torch.int32, device=dev)
+    new_offsets = torch.empty(bags * world + 1, dtype=torch.int64, device=dev)
+    new_indices = torch.empty(L, dtype=torch.int64, device=dev)
+    new_weights = None if weights is None else torch.empty(L, dtype=torch.float32, device=dev)
+    perm = torch.empty(L, dtype=torch.int64, device=dev) if want_permute else None
+    lib = _lib.load()
+    scratch = _get_scratch(dev, lib.tdfo_bucketize_scratch_bytes(bags, world))
+    check(lib.tdfo_kjt_bucketize_row_wise(_ptr(lengths), _ptr(offsets), _ptr(indices), _ptr(weights),
+                                          _ptr(block_sizes), F, B, world, _ptr(new_lengths), _ptr(new_offsets),
+                                          _ptr(new_indices), _ptr(new_weights), _ptr(perm), _ptr(err_flag),
+                                          _ptr(scratch), scratch.numel(), _stream()))
+    return new_lengths, new_offsets, new_indices, new_weights, perm
+
+
+def permute_2d(permute, B, in_lengths, in_offsets, in_indices, in_weights=None, out_total: Optional[int] = None):
+    """``out_total``: number of ids the output holds, if the caller knows it (saves a sync);
+    otherwise it is read back from the computed offsets (one D2H sync)."""
+    permute = _cuda(permute, torch.int32, "permute")
+    in_lengths = _cuda(in_lengths, torch.int32, "in_lengths")
+    in_offsets = _cuda(in_offsets, torch.int64, "in_offsets")
+    in_indices = _cuda(in_indices, torch.int64, "in_indices")
+    dev = in_lengths.device
+    S_out = permute.numel()
+    S_in = in_lengths.numel() // B if B else 0
+    out_lengths = torch.empty(S_out * B, dtype=torch.int32, device=dev)
+    out_offsets = torch.empty(S_out * B + 1, dtype=torch.int64, device=dev)
+    lib = _lib.load()
+    scratch = _get_scratch(dev, lib.tdfo_scan_scratch_bytes(S_out * B))
+    if out_total is None:
+        # lengths first, then size the data buffers from the last offset
+        check(lib.tdfo_kjt_permute_2d(_ptr(permute), S_in, S_out, B, _ptr(in_lengths), _ptr(in_offsets), None, None,
+                                      _ptr(out_lengths), _ptr(out_offsets), None, None, _ptr(scratch),
+                                      scratch.numel(), _stream()))
+        out_total = int(out_offsets[-1].item())
+    out_indices = torch.empty(out_total, dtype=torch.int64, device=dev)
+    out_weights = None
+    if in_weights is not None:
+        in_weights = _cuda(in_weights, torch.float32, "in_weights")
+        out_weights = torch.empty(out_total, dtype=torch.float32, device=dev)
+    check(lib.tdfo_kjt_permute_2d(_ptr(permute), S_in, S_out, B, _ptr(in_lengths), _ptr(in_offsets),
+                                  _ptr(in_indices), _ptr(in_weights), _ptr(out_lengths), _ptr(out_offsets),
+                                  _ptr(out_indices), _ptr(out_weights), _ptr(scratch), scratch.numel(), _stream()))
+    return out_lengths, out_offsets, out_indices, out_weights
+
+
+# --------------------------------------------------------------------------- lookup
+def embedding_forward(group: TableGroup, indices: torch.Tensor, offsets: torch.Tensor, B: int, pooling_mode: int,
+                      per_sample_weights: Optional[torch.Tensor] = None,
+                      out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    indices = _cuda(indices, torch.int64, "indices")
+    offsets = _cuda(offsets, torch.int64, "offsets")
+    if per_sample_weights is not None:
+        per_sample_weights = _cuda(per_sample_weights, torch.float32, "per_sample_weights")
+    w = group.weights
+    if not w.is_cuda:
+        raise RuntimeError("tdfo_b200: embedding tables must live on a CUDA device (there is no CPU path)")
+    L = indices.numel()
+    if offsets.numel() != group.F * B + 1:
+        raise ValueError(f"offsets has {offsets.numel()} entries, expected F*B+1 = {group.F * B + 1}")
+    if out is None:
+        if pooling_mode == POOL_NONE:
+            out = torch.empty((L, group.D), dtype=torch.float32, device=w.device)
+        else:
+            out = torch.empty((B, group.out_stride), dtype=torch.float32, device=w.device)
+    check(_lib.load().tdfo_embedding_forward(
+        _ptr(w), _wdtype(w), group.total_rows, group.D, _ptr(indices), _ptr(offsets), _ptr(per_sample_weights),
+        _ptr(group.feat_row_base), _ptr(group.feat_rows), _ptr(group.feat_out_col), group.F, B, L, pooling_mode,
+        _ptr(out), group.out_stride, _ptr(group.err_flag), _stream()))
+    return out
+
+
+# --------------------------------------------------------------------------- backward
+def make_optimizer_args(optimizer: int, learning_rate: float, eps: float = 1e-8, weight_decay: float = 0.0,
+                        beta1: float = 0.9, beta2: float = 0.999, step: int = 1) -> OptimizerArgs:
+    return OptimizerArgs(optimizer, learning_rate, eps, weight_decay, beta1, beta2, step)
+
+
+def backward_layout(L: int, total_rows: int) -> BackwardLayout:
+    lay = BackwardLayout()
+    check(_lib.load().tdfo_backward_scratch_layout(L, total_rows, ctypes.byref(lay)))
+    return lay
+
+
+def embedding_backward_update(group: TableGroup, grad_out: torch.Tensor, indices: torch.Tensor,
+                              offsets: torch.Tensor, B: int, pooling_mode: int, opt: OptimizerArgs,
+                              scratch: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Fused backward + optimizer, in place on ``group.weights`` / state.  Returns the scratch buffer
+    (sorted keys / unique rows are readable at ``backward_layout`` offsets)."""
+    indices = _cuda(indices, torch.int64, "indices")
+    offsets = _cuda(offsets, torch.int64, "offsets")
+    grad_out = _cuda(grad_out, torch.float32, "grad_out")
+    w = group.weights
+    L = indices.numel()
+    lib = _lib.load()
+    nb = lib.tdfo_backward_scratch_bytes(L, group.total_rows)
+    if scratch is None:
+        scratch = _get_scratch(w.device, nb)
+    grad_stride = group.D if pooling_mode == POOL_NONE else grad_out.shape[-1]
+    check(lib.tdfo_embedding_backward_update(
+        _ptr(w), _wdtype(w), group.total_rows, group.D, _ptr(group.state0), _ptr(group.state1),
+        _ptr(grad_out), grad_stride, _ptr(indices), _ptr(offsets), None,
+        _ptr(group.feat_row_base), _ptr(group.feat_rows), _ptr(group.feat_out_col), group.F, B, L, pooling_mode,
+        ctypes.byref(opt), _ptr(group.err_flag), _ptr(scratch), scratch.numel(), _stream()))
+    return scratch
+
+
+def linearize_indices(group: TableGroup, indices, offsets, B, pooling_mode):
+    indices = _cuda(indices, torch.int64, "indices")
+    offsets = _cuda(offsets, torch.int64, "offsets")
+    L = indices.numel()
+    keys = torch.empty(L, dtype=torch.int32, device=indices.device)   # uint32 bit patterns
+    vals = torch.empty(L, dtype=torch.int32, device=indices.device)
+    check(_lib.load().tdfo_linearize_indices(_ptr(indices), _ptr(offsets), _ptr(group.feat_row_base),
+                                             _ptr(group.feat_rows), group.F, B, group.total_rows, pooling_mode,
+                                             _ptr(keys), _ptr(vals), _ptr(group.err_flag), _stream()))
+    return keys, vals
+
+
+def radix_sort_pairs(keys: torch.Tensor, vals: torch.Tensor, key_bits: int, err_flag=None):
+    """Stable sort of uint32 pairs held as int32 tensors; inputs are clobbered."""
+    keys = _cuda(keys, torch.int32, "keys")
+    vals = _cuda(vals, torch.int32, "vals")
+    n = keys.numel()
+    ko, vo = torch.empty_like(keys), torch.empty_like(vals)
+    lib = _lib.load()
+    scratch = _get_scratch(keys.device, lib.tdfo_radix_sort_scratch_bytes(n, key_bits))
+    check(lib.tdfo_radix_sort_pairs(_ptr(keys), _ptr(vals), _ptr(ko), _ptr(vo), n, key_bits, _ptr(err_flag),
+                                    _ptr(scratch), scratch.numel(), _stream()))
+    return ko, vo
+
+
+def unique_segments(sorted_keys: torch.Tensor, err_flag=None):
+    sorted_keys = _cuda(sorted_keys, torch.int32, "sorted_keys")
+    n = sorted_keys.numel()
+    dev = sorted_keys.device
+    uk = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    ss = torch.empty(n + 1, dtype=torch.int32, device=dev)
+    nu = torch.empty(1, dtype=torch.int32, device=dev)
+    lib = _lib.load()
+    scratch = _get_scratch(dev, lib.tdfo_scan_scratch_bytes(n))
+    check(lib.tdfo_unique_segments(_ptr(sorted_keys), n, _ptr(uk), _ptr(ss), _ptr(nu), _ptr(err_flag),
+                                   _ptr(scratch), scratch.numel(), _stream()))
+    return uk, ss, nu
+
+
+def sparse_update(group: TableGroup, grad_out, sorted_vals, unique_keys, seg_starts, num_unique, offsets, B, L,
+                  pooling_mode, opt: OptimizerArgs):
+    grad_out = _cuda(grad_out, torch.float32, "grad_out")
+    w = group.weights
+    grad_stride = group.D if pooling_mode == POOL_NONE else grad_out.shape[-1]
+    check(_lib.load().tdfo_sparse_update(
+        _ptr(w), _wdtype(w), group.total_rows, group.D, _ptr(group.state0), _ptr(group.state1), _ptr(grad_out),
+        grad_stride, _ptr(sorted_vals), _ptr(unique_keys), _ptr(seg_starts), _ptr(num_unique), _ptr(offsets),
+        _ptr(group.feat_out_col), group.F, B, L, pooling_mode, ctypes.byref(opt), _stream()))
+
+
+# --------------------------------------------------------------------------- jagged
+def _jagged_2d_to_dense_raw(values, offsets, max_len):
+    values = _cuda(values, torch.float32, "values")
+    offsets = _cuda(offsets, torch.int64, "offsets")
+    B, D = offsets.numel() - 1, values.shape[1]
+    dense = torch.empty((B, max_len, D), dtype=torch.float32, device=values.device)
+    check(_lib.load().tdfo_jagged_2d_to_dense(_ptr(values), _ptr(offsets), B, D, max_len, _ptr(dense), _stream()))
+    return dense
+
+
+def dense_to_jagged(dense, offsets, total_L: int):
+    dense = _cuda(dense, torch.float32, "dense")
+    offsets = _cuda(offsets, torch.int64, "offsets")
+    B, max_len, D = dense.shape
+    values = torch.empty((total_L, D), dtype=torch.float32, device=dense.device)
+    check(_lib.load().tdfo_dense_to_jagged(_ptr(dense), _ptr(offsets), B, D, max_len, total_L, _ptr(values), _stream()))
+    return values
+
+
+class _Jagged2DToDense(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, values, offsets, max_len):
+        ctx.save_for_backward(offsets)
+        ctx.total_L = values.shape[0]
+        return _jagged_2d_to_dense_raw(values, offsets, max_len)
+
+    @staticmethod
+    def backward(ctx, grad_dense):
+        (offsets,) = ctx.saved_tensors
+        return dense_to_jagged(grad_dense.contiguous(), offsets, ctx.total_L), None, None
+
+
+def jagged_2d_to_dense(values: torch.Tensor, offsets: torch.Tensor, max_sequence_length: int) -> torch.Tensor:
+    """Drop-in for ``torch.ops.fbgemm.jagged_2d_to_dense`` (torchrec/models.py:168-172), differentiable."""
+    return _Jagged2DToDense.apply(values, offsets, int(max_sequence_length))
+
+
+def jagged_1d_to_padded_dense(values, offsets, desired_length: int, padding_value: int):
+    values = _cuda(values, torch.int64, "values")
+    offsets = _cuda(offsets, torch.int64, "offsets")
+    B = offsets.numel() - 1
+    dense = torch.empty((B, desired_length), dtype=torch.int64, device=values.device)
+    check(_lib.load().tdfo_jagged_1d_to_padded_dense(_ptr(values), _ptr(offsets), B, desired_length,
+                                                     int(padding_value), _ptr(dense), _stream()))
+    return dense

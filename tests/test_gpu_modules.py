@@ -1,0 +1,158 @@
+"""The torchrec-shaped surface on the GPU: EmbeddingBagCollection / EmbeddingCollection through
+autograd with the fused optimizer, the reference's HistoryArch call pattern
+(torchrec/models.py:163-178), and size-independent properties at BASELINE config-2 scale."""
+import numpy as np
+import pytest
+import torch
+
+import oracle as orc
+from helpers import make_case
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def t():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import tdfo_b200
+    return tdfo_b200
+
+
+def test_ebc_forward_backward_matches_oracle(t):
+    c = make_case(seed=4, F=3, B=32, D=64, rows=[100, 40, 7], max_len=8)
+    tables = [t.EmbeddingBagConfig(num_embeddings=int(r), embedding_dim=c.D, name=f"t{i}", feature_names=[f"f{i}"],
+                                   pooling=t.PoolingType.SUM) for i, r in enumerate(c.rows)]
+    ebc = t.EmbeddingBagCollection(tables, device=torch.device("cuda"))
+    ebc.load_state_dict({f"embedding_bags.t{i}.weight": torch.from_numpy(
+        c.weights[c.row_base[i]:c.row_base[i] + c.rows[i]]) for i in range(c.F)})
+    fused = ebc.set_fused_optimizer(t.EmbOptimType.EXACT_ROWWISE_ADAGRAD, learning_rate=0.1, eps=1e-8)
+    assert not list(t.in_backward_optimizer_filter(ebc.named_parameters()))
+    kjt = t.KeyedJaggedTensor.from_lengths_sync([f"f{i}" for i in range(c.F)], torch.from_numpy(c.indices),
+                                                torch.from_numpy(c.lengths)).to("cuda")
+    ebc.train()
+    kt = ebc(kjt)
+    assert kt.keys() == ["f0", "f1", "f2"] and kt.values().shape == (c.B, c.F * c.D)
+    want, _ = orc.embedding_forward(c.weights, c.D, c.indices, c.offsets, None, c.row_base, c.rows, c.out_col,
+                                    c.F, c.B, orc.POOL_SUM)
+    np.testing.assert_allclose(kt.values().detach().cpu().numpy(), want, rtol=1e-5, atol=1e-5)
+    np.testing.assert_array_equal(kt["f1"].detach().cpu().numpy(), kt.values()[:, c.D:2 * c.D].detach().cpu().numpy())
+
+    proj = torch.randn(c.F * c.D, 1, device="cuda", requires_grad=True)
+    loss = (kt.values() @ proj).sum()
+    loss.backward()
+    fused.step(); fused.zero_grad()
+    grad_out = proj.detach().t().expand(c.B, -1).contiguous().cpu().numpy()
+    w_o, h_o = c.weights.copy(), np.zeros(c.total_rows, np.float32)
+    orc.embedding_backward_update(w_o, c.D, h_o, None, grad_out, c.indices, c.offsets, c.row_base, c.rows, c.out_col,
+                                  c.F, c.B, orc.POOL_SUM, orc.OptArgs(orc.OPT_ROWWISE_ADAGRAD, 0.1, 1e-8))
+    got = torch.cat([ebc.state_dict()[f"embedding_bags.t{i}.weight"] for i in range(c.F)]).cpu().numpy()
+    np.testing.assert_allclose(got, w_o, rtol=1e-5, atol=2e-6)
+    assert proj.grad is not None
+    ebc.check_errors()
+
+
+def test_ebc_mixed_dims_and_key_order(t):
+    rows, dims = [30, 20, 10], [16, 32, 16]
+    tables = [t.EmbeddingBagConfig(num_embeddings=r, embedding_dim=d, name=f"t{i}", feature_names=[f"f{i}"],
+                                   pooling=t.PoolingType.MEAN if i == 2 else t.PoolingType.SUM)
+              for i, (r, d) in enumerate(zip(rows, dims))]
+    ebc = t.EmbeddingBagCollection(tables, device=torch.device("cuda")).eval()
+    rng = np.random.default_rng(0)
+    B = 9
+    # KJT arrives in a different key order than the module's
+    order = ["f2", "f0", "f1"]
+    lens = {k: rng.integers(0, 5, size=B).astype(np.int32) for k in order}
+    ids = {k: rng.integers(0, rows[int(k[1])], size=int(lens[k].sum())) for k in order}
+    kjt = t.KeyedJaggedTensor.from_lengths_sync(order, torch.from_numpy(np.concatenate([ids[k] for k in order])),
+                                                torch.from_numpy(np.concatenate([lens[k] for k in order]))).to("cuda")
+    out = ebc(kjt)
+    sd = ebc.state_dict()
+    for i, k in enumerate(["f0", "f1", "f2"]):
+        w = sd[f"embedding_bags.t{i}.weight"].cpu().numpy()
+        off = orc.complete_cumsum(lens[k])
+        want, _ = orc.embedding_forward(np.ascontiguousarray(w), dims[i], ids[k], off, None, [0], [rows[i]], [0], 1, B,
+                                        orc.POOL_MEAN if i == 2 else orc.POOL_SUM)
+        np.testing.assert_allclose(out[k].cpu().numpy(), want, rtol=1e-5, atol=1e-6)
+
+
+def test_history_arch_pattern(t):
+    """EmbeddingCollection -> jagged_2d_to_dense -> loss -> backward, as torchrec/models.py:163-178
+    and torchrec/train.py:98-105 do, against the oracle's sequence path."""
+    V, D, B, T = 50, 16, 16, 20
+    ec = t.EmbeddingCollection([t.EmbeddingConfig(name="item_embedding", embedding_dim=D, num_embeddings=V,
+                                                  feature_names=["item"], weight_init_max=1.0, weight_init_min=-1.0)],
+                               device=torch.device("cuda"))
+    ec.set_fused_optimizer(t.EmbOptimType.SGD, learning_rate=3e-4, weight_decay=1e-4)
+    w0 = ec.state_dict()["embeddings.item_embedding.weight"].cpu().numpy().copy()
+    assert w0.min() >= -1 and w0.max() <= 1
+    rng = np.random.default_rng(1)
+    seqs = torch.from_numpy(rng.integers(0, V, size=(B, T)))
+    seqs_list = list(seqs)                                    # _to_kjt, torchrec/train.py:33-41
+    lengths = torch.IntTensor([v.size(0) for v in seqs_list])
+    kjt = t.KeyedJaggedTensor.from_lengths_sync(keys=["item"], values=torch.cat(seqs_list, dim=0),
+                                                lengths=lengths).to(torch.device("cuda"))
+    dense_ids = kjt["item"].to_padded_dense(desired_length=T, padding_value=0)
+    np.testing.assert_array_equal(dense_ids.cpu().numpy(), seqs.numpy())
+    ec.train()
+    jt = ec(kjt)
+    padded = t.jagged_2d_to_dense(values=jt["item"].values(), offsets=jt["item"].offsets(),
+                                  max_sequence_length=T).view(-1, T, D)
+    assert padded.shape == (kjt.stride(), T, D)
+    np.testing.assert_array_equal(padded.detach().cpu().numpy(), w0[seqs.numpy()])
+    target = torch.randn(B, T, D, device="cuda")
+    loss = ((padded - target) ** 2).sum()
+    loss.backward()
+    grad = (2 * (padded - target)).detach().view(-1, D).cpu().numpy()
+    w_o = w0.copy()
+    off = orc.complete_cumsum(lengths.numpy())
+    orc.embedding_backward_update(w_o, D, None, None, grad, seqs.numpy().ravel(), off, [0], [V], None, 1, B,
+                                  orc.POOL_NONE, orc.OptArgs(orc.OPT_SGD, 3e-4, weight_decay=1e-4))
+    np.testing.assert_allclose(ec.state_dict()["embeddings.item_embedding.weight"].cpu().numpy(), w_o,
+                               rtol=1e-5, atol=1e-6)
+
+
+def test_full_size_properties_config2(t):
+    """BASELINE config 2 (26 tables x 1M rows x D128 fp32, B=16384, pooling 20): properties that
+    do not need the oracle at this size.  Tables of ones => every pooled value is exactly the bag
+    length; SGD with lr=1 and unit gradients subtracts each row's occurrence count, so the total
+    decrement equals L*D exactly (small integers are exact in fp32)."""
+    free, _ = torch.cuda.mem_get_info()
+    if free < 40 << 30:
+        pytest.skip("needs 40 GB of free HBM")
+    ops = t.ops
+    F, rows, D, B, P = 26, 1_000_000, 128, 16384, 20
+    dev = torch.device("cuda")
+    w = torch.ones((F * rows, D), device=dev)
+    grp = ops.TableGroup(weights=w, feat_row_base=torch.arange(F, device=dev) * rows,
+                         feat_rows=torch.full((F,), rows, device=dev, dtype=torch.int64),
+                         feat_out_col=torch.arange(F, device=dev) * D, out_stride=F * D)
+    g = torch.Generator(device=dev).manual_seed(42)
+    lengths = torch.full((F * B,), P, dtype=torch.int32, device=dev)
+    lengths[::97] = 0                                     # some empty bags
+    lengths[5::1013] = 311                                # some long ones
+    offsets = ops.complete_cumsum(lengths)
+    assert torch.equal(offsets[1:], torch.cumsum(lengths.long(), 0))
+    L = int(offsets[-1].item())
+    idx = torch.randint(0, rows, (L,), device=dev, generator=g)
+    out = ops.embedding_forward(grp, idx, offsets, B, orc.POOL_SUM)
+    want = lengths.view(F, B).t().float()                 # [B, F]
+    assert torch.equal(out.view(B, F, D), want.unsqueeze(-1).expand(B, F, D))
+    grad = torch.ones((B, F * D), device=dev)
+    scratch = ops.embedding_backward_update(grp, grad, idx, offsets, B, orc.POOL_SUM,
+                                            ops.make_optimizer_args(orc.OPT_SGD, 1.0))
+    lay = ops.backward_layout(L, F * rows)
+    view = lambda off, n: scratch[off: off + 4 * n].view(torch.int32)
+    sk = view(lay.sorted_keys, L)
+    assert bool((sk[1:] >= sk[:-1]).all())                # sortedness (keys < 2^31 here)
+    nu = int(view(lay.num_unique, 1).item())
+    keys = (torch.arange(F, device=dev).repeat_interleave(lengths.view(F, B).sum(1).long()) * rows + idx)
+    assert nu == int(torch.unique(keys).numel())
+    ss = view(lay.seg_starts, nu + 1)
+    assert int(ss[0]) == 0 and int(ss[-1]) == L and bool((ss[1:] > ss[:-1]).all())
+    # the sorted payloads are a permutation of the bag ids
+    sv = view(lay.sorted_vals, L)
+    assert int(sv.long().sum()) == int(torch.arange(F * B, device=dev).repeat_interleave(lengths.long()).sum())
+    dec = float(F * rows) * D - w.sum(dtype=torch.float64).item()
+    assert dec == float(L) * D
+    assert int(grp.err_flag.item()) == 0

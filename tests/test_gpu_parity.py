@@ -1,0 +1,387 @@
+"""GPU parity: every C-ABI entry point of libtdfo_b200.so against the CPU oracle on the same
+seeded inputs, and against the committed golden vectors.
+
+Bars (BASELINE.json north_star): bit-exact for cumsum, bucketise, permute, linearise, sort,
+unique and the jagged copies; 1e-5 relative for fp32 pooled outputs and updated rows, 1e-2 for
+bf16 tables.
+"""
+import numpy as np
+import pytest
+import torch
+
+import oracle as orc
+from helpers import make_case
+
+pytestmark = pytest.mark.gpu
+
+FP32_RTOL, FP32_ATOL = 1e-5, 1e-6
+BF16_RTOL, BF16_ATOL = 1e-2, 1e-2
+
+
+@pytest.fixture(scope="module")
+def ops():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from tdfo_b200 import ops as _ops
+    return _ops
+
+
+def dev(a, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.cuda()
+
+
+def u32(t: torch.Tensor) -> np.ndarray:
+    return t.cpu().numpy().view(np.uint32)
+
+
+def group_for(ops, c, weights_t, pooled=True, state0=None, state1=None):
+    return ops.TableGroup(weights=weights_t, feat_row_base=dev(c.row_base), feat_rows=dev(c.rows),
+                          feat_out_col=dev(c.out_col), out_stride=(c.F * c.D if pooled else c.D),
+                          state0=state0, state1=state1)
+
+
+def oracle_weights(c, bf16):
+    return orc.bf16_bits(c.weights) if bf16 else c.weights.copy()
+
+
+def device_weights(c, bf16):
+    t = dev(c.weights)
+    return t.to(torch.bfloat16) if bf16 else t
+
+
+def table_to_f32(w_t: torch.Tensor) -> np.ndarray:
+    return w_t.float().cpu().numpy()
+
+
+def oracle_table_to_f32(w) -> np.ndarray:
+    return orc.bf16_to_f32(w) if w.dtype == np.uint16 else w
+
+
+# ----------------------------------------------------------------------------- cumsum
+@pytest.mark.parametrize("n", [0, 1, 31, 2047, 2048, 2049, 100_003, 1_500_000])
+def test_complete_cumsum_bit_exact(ops, n):
+    rng = np.random.default_rng(n)
+    lengths = rng.integers(0, 50, size=n).astype(np.int32)
+    got = ops.complete_cumsum(dev(lengths)).cpu().numpy()
+    np.testing.assert_array_equal(got, orc.complete_cumsum(lengths))
+
+
+# ----------------------------------------------------------------------------- forward
+def test_forward_golden(ops, golden):
+    g = golden("fwd")
+    base, rows, col = g.table_meta()
+    grp = ops.TableGroup(weights=dev(g.weights), feat_row_base=dev(base), feat_rows=dev(rows),
+                         feat_out_col=dev(col), out_stride=g.F * g.D)
+    idx, off = dev(g.indices), dev(g.offsets)
+    for mode, psw, want in ((orc.POOL_SUM, None, g.out_sum), (orc.POOL_MEAN, None, g.out_mean),
+                            (orc.POOL_SUM, dev(g.psw), g.out_wsum)):
+        out = ops.embedding_forward(grp, idx, off, g.B, mode, psw).cpu().numpy()
+        np.testing.assert_allclose(out, want, rtol=FP32_RTOL, atol=FP32_ATOL)
+    grp.out_stride = g.D
+    out = ops.embedding_forward(grp, idx, off, g.B, orc.POOL_NONE).cpu().numpy()
+    np.testing.assert_array_equal(out, g.out_seq)
+    assert int(grp.err_flag.item()) == 0
+
+
+@pytest.mark.parametrize("bf16", [False, True])
+@pytest.mark.parametrize("D", [4, 8, 16, 32, 64, 96, 128, 256, 512])
+@pytest.mark.parametrize("mode", [orc.POOL_SUM, orc.POOL_MEAN])
+def test_pooled_forward_vs_oracle(ops, D, mode, bf16):
+    if bf16 and D % 8:
+        pytest.skip("bf16 rows must be a multiple of 16 bytes")
+    c = make_case(seed=D * 7 + mode, F=5, B=37, D=D, max_len=9, long_bag=300)
+    w_o = oracle_weights(c, bf16)
+    want, oob = orc.embedding_forward(w_o, D, c.indices, c.offsets, None, c.row_base, c.rows, c.out_col,
+                                      c.F, c.B, mode)
+    assert not oob
+    grp = group_for(ops, c, device_weights(c, bf16))
+    got = ops.embedding_forward(grp, dev(c.indices), dev(c.offsets), c.B, mode).cpu().numpy()
+    # accumulation is fp32 in both; bf16 only changes the stored table, so the fp32 bar holds
+    np.testing.assert_allclose(got, want, rtol=FP32_RTOL, atol=1e-5)
+    assert int(grp.err_flag.item()) == 0
+
+
+def test_pooled_forward_d128_is_bit_exact_in_bag_order(ops):
+    # one lane per 16-byte chunk, rows added in bag order: same fp32 sequence as the oracle
+    c = make_case(seed=3, F=4, B=64, D=128, max_len=40)
+    want, _ = orc.embedding_forward(c.weights, 128, c.indices, c.offsets, None, c.row_base, c.rows, c.out_col,
+                                    c.F, c.B, orc.POOL_SUM)
+    got = ops.embedding_forward(group_for(ops, c, dev(c.weights)), dev(c.indices), dev(c.offsets), c.B,
+                                orc.POOL_SUM).cpu().numpy()
+    np.testing.assert_array_equal(got, want)
+
+
+def test_weighted_forward_vs_oracle(ops):
+    c = make_case(seed=11, F=3, B=50, D=64, max_len=12)
+    psw = np.random.default_rng(5).uniform(0.1, 2.0, size=c.L).astype(np.float32)
+    want, _ = orc.embedding_forward(c.weights, c.D, c.indices, c.offsets, psw, c.row_base, c.rows, c.out_col,
+                                    c.F, c.B, orc.POOL_SUM)
+    got = ops.embedding_forward(group_for(ops, c, dev(c.weights)), dev(c.indices), dev(c.offsets), c.B,
+                                orc.POOL_SUM, dev(psw)).cpu().numpy()
+    np.testing.assert_allclose(got, want, rtol=FP32_RTOL, atol=1e-5)
+
+
+@pytest.mark.parametrize("bf16", [False, True])
+@pytest.mark.parametrize("D", [8, 16, 128, 320])
+def test_sequence_forward_bit_exact(ops, D, bf16):
+    c = make_case(seed=D, F=3, B=21, D=D, max_len=7)
+    want, _ = orc.embedding_forward(oracle_weights(c, bf16), D, c.indices, c.offsets, None, c.row_base, c.rows,
+                                    None, c.F, c.B, orc.POOL_NONE)
+    grp = group_for(ops, c, device_weights(c, bf16), pooled=False)
+    got = ops.embedding_forward(grp, dev(c.indices), dev(c.offsets), c.B, orc.POOL_NONE).cpu().numpy()
+    np.testing.assert_array_equal(got, want)
+
+
+def test_all_bags_empty_and_zero_batch(ops):
+    c = make_case(seed=1, F=2, B=8, D=16, max_len=0)
+    assert c.L == 0
+    grp = group_for(ops, c, dev(c.weights))
+    out = ops.embedding_forward(grp, dev(c.indices), dev(c.offsets), c.B, orc.POOL_MEAN).cpu().numpy()
+    assert out.shape == (8, 32) and not out.any()
+
+
+def test_out_of_range_ids_flagged_and_skipped(ops):
+    c = make_case(seed=9, F=2, B=16, D=32, max_len=5, p_empty=0.0)
+    idx = c.indices.copy()
+    idx[0] = c.rows[0]
+    idx[3] = -7
+    want, oob = orc.embedding_forward(c.weights, c.D, idx, c.offsets, None, c.row_base, c.rows, c.out_col,
+                                      c.F, c.B, orc.POOL_SUM)
+    assert oob
+    grp = group_for(ops, c, dev(c.weights))
+    got = ops.embedding_forward(grp, dev(idx), dev(c.offsets), c.B, orc.POOL_SUM).cpu().numpy()
+    np.testing.assert_allclose(got, want, rtol=FP32_RTOL, atol=1e-6)
+    assert int(grp.err_flag.item()) & 1
+    with pytest.raises(IndexError):
+        ops.check_error_flag(grp.err_flag)
+
+
+# ----------------------------------------------------------------------------- sort / unique
+@pytest.mark.parametrize("n,bits", [(1, 1), (100, 7), (4095, 8), (4096, 9), (4097, 16), (50_000, 20),
+                                    (1_000_003, 25), (300_000, 32), (70_000, 3)])
+def test_radix_sort_bit_exact(ops, n, bits):
+    rng = np.random.default_rng(n + bits)
+    keys = rng.integers(0, 2 ** bits, size=n, dtype=np.uint64).astype(np.uint32)
+    vals = rng.integers(0, 2 ** 32, size=n, dtype=np.uint64).astype(np.uint32)
+    want_k, want_v = orc.sort_pairs_stable(keys, vals)
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ko, vo = ops.radix_sort_pairs(dev(keys.view(np.int32)), dev(vals.view(np.int32)), bits, flag)
+    np.testing.assert_array_equal(u32(ko), want_k)
+    np.testing.assert_array_equal(u32(vo), want_v)
+    assert int(flag.item()) == 0
+
+
+def test_radix_sort_skewed_keys(ops):
+    rng = np.random.default_rng(0)
+    n = 600_000
+    keys = np.minimum(rng.zipf(1.1, size=n), 2 ** 22 - 1).astype(np.uint32)
+    keys[: n // 3] = 12345                      # one very hot row
+    vals = np.arange(n, dtype=np.uint32)
+    want_k, want_v = orc.sort_pairs_stable(keys, vals)
+    ko, vo = ops.radix_sort_pairs(dev(keys.view(np.int32)), dev(vals.view(np.int32)), 22)
+    np.testing.assert_array_equal(u32(ko), want_k)
+    np.testing.assert_array_equal(u32(vo), want_v)
+
+
+@pytest.mark.parametrize("n,card", [(0, 1), (1, 1), (2048, 3), (2049, 5000), (777_777, 100_000), (10_000, 1)])
+def test_unique_segments_bit_exact(ops, n, card):
+    rng = np.random.default_rng(n)
+    keys = np.sort(rng.integers(0, card, size=n).astype(np.uint32))
+    uk_w, ss_w, nu_w = orc.unique_segments(keys)
+    uk, ss, nu = ops.unique_segments(dev(keys.view(np.int32)))
+    nu = int(nu.item())
+    assert nu == nu_w
+    np.testing.assert_array_equal(u32(uk)[:nu], uk_w)
+    np.testing.assert_array_equal(u32(ss)[: nu + 1], ss_w)
+
+
+def test_linearize_bit_exact(ops):
+    c = make_case(seed=21, F=6, B=33, D=16, max_len=8)
+    idx = c.indices.copy()
+    idx[5] = -1
+    for mode in (orc.POOL_SUM, orc.POOL_NONE):
+        wk, wv, oob = orc.linearize_indices(idx, c.offsets, c.row_base, c.rows, c.F, c.B, c.total_rows, mode)
+        grp = group_for(ops, c, dev(c.weights))
+        k, v = ops.linearize_indices(grp, dev(idx), dev(c.offsets), c.B, mode)
+        np.testing.assert_array_equal(u32(k), wk)
+        np.testing.assert_array_equal(u32(v), wv)
+        assert oob and int(grp.err_flag.item()) & 1
+
+
+# ----------------------------------------------------------------------------- backward + update
+def _run_backward_pair(ops, c, mode, optimizer, bf16, wd=0.0, steps=1, idx=None):
+    """Runs `steps` fused backward/update passes on oracle and GPU; returns both final states."""
+    idx = c.indices if idx is None else idx
+    rng = np.random.default_rng(99)
+    w_o = oracle_weights(c, bf16)
+    w_t = device_weights(c, bf16)
+    pooled = mode != orc.POOL_NONE
+    s0_o = s1_o = s0_t = s1_t = None
+    if optimizer == orc.OPT_ROWWISE_ADAGRAD:
+        s0_o = rng.uniform(0, 0.3, size=c.total_rows).astype(np.float32)
+        s0_t = dev(s0_o)
+    elif optimizer == orc.OPT_ADAM:
+        s0_o = np.zeros_like(c.weights); s1_o = np.zeros_like(c.weights)
+        s0_t = dev(s0_o); s1_t = dev(s1_o)
+    grp = group_for(ops, c, w_t, pooled=pooled, state0=s0_t, state1=s1_t)
+    routing = None
+    for step in range(1, steps + 1):
+        shape = (c.B, c.F * c.D) if pooled else (c.L, c.D)
+        grad = rng.normal(size=shape).astype(np.float32)
+        opt_o = orc.OptArgs(optimizer, learning_rate=0.05, eps=1e-8, weight_decay=wd, step=step)
+        routing = orc.embedding_backward_update(w_o, c.D, s0_o, s1_o, grad, idx, c.offsets, c.row_base, c.rows,
+                                                c.out_col, c.F, c.B, mode, opt_o, return_routing=True)
+        opt_t = ops.make_optimizer_args(optimizer, 0.05, 1e-8, wd, 0.9, 0.999, step)
+        scratch = ops.embedding_backward_update(grp, dev(grad), dev(idx), dev(c.offsets), c.B, mode, opt_t)
+    return w_o, s0_o, s1_o, grp, routing, scratch
+
+
+@pytest.mark.parametrize("bf16", [False, True])
+@pytest.mark.parametrize("optimizer", [orc.OPT_SGD, orc.OPT_ROWWISE_ADAGRAD, orc.OPT_ADAM])
+@pytest.mark.parametrize("mode", [orc.POOL_SUM, orc.POOL_MEAN, orc.POOL_NONE])
+@pytest.mark.parametrize("D", [16, 128])
+def test_backward_update_vs_oracle(ops, D, mode, optimizer, bf16):
+    c = make_case(seed=D + mode * 3 + optimizer, F=4, B=40, D=D, rows=[50, 7, 300, 19], max_len=10,
+                  long_bag=150, zipf=True)
+    w_o, s0_o, s1_o, grp, routing, scratch = _run_backward_pair(ops, c, mode, optimizer, bf16, wd=0.01, steps=2)
+    rtol, atol = (BF16_RTOL, BF16_ATOL) if bf16 else (FP32_RTOL, 2e-6)
+    np.testing.assert_allclose(table_to_f32(grp.weights), oracle_table_to_f32(w_o), rtol=rtol, atol=atol)
+    if s0_o is not None:
+        np.testing.assert_allclose(grp.state0.cpu().numpy(), s0_o, rtol=max(rtol, 2e-5), atol=atol)
+    if s1_o is not None:
+        np.testing.assert_allclose(grp.state1.cpu().numpy(), s1_o, rtol=max(rtol, 2e-5), atol=atol)
+    # routing produced on the way is bit-exact
+    lay = ops.backward_layout(c.L, c.total_rows)
+    raw = scratch.cpu().numpy()
+    take = lambda off, n: raw[off: off + 4 * n].view(np.uint32)
+    nu = int(take(lay.num_unique, 1)[0])
+    assert nu == routing["num_unique"]
+    np.testing.assert_array_equal(take(lay.sorted_keys, c.L), routing["sorted_keys"])
+    np.testing.assert_array_equal(take(lay.sorted_vals, c.L), routing["sorted_vals"])
+    np.testing.assert_array_equal(take(lay.unique_keys, nu), routing["unique_keys"])
+    np.testing.assert_array_equal(take(lay.seg_starts, nu + 1), routing["seg_starts"])
+    assert int(grp.err_flag.item()) == 0
+
+
+def test_backward_untouched_rows_unchanged_and_oob_skipped(ops):
+    c = make_case(seed=5, F=2, B=10, D=32, rows=[1000, 1000], max_len=3)
+    idx = c.indices.copy()
+    idx[0] = 5000                                     # out of range: must not update anything
+    w_o, _, _, grp, routing, _ = _run_backward_pair(ops, c, orc.POOL_SUM, orc.OPT_SGD, False, idx=idx)
+    got = table_to_f32(grp.weights)
+    np.testing.assert_allclose(got, w_o, rtol=FP32_RTOL, atol=1e-6)
+    touched = np.zeros(c.total_rows, bool)
+    touched[routing["unique_keys"][routing["unique_keys"] < c.total_rows]] = True
+    np.testing.assert_array_equal(got[~touched], c.weights[~touched])
+    assert int(grp.err_flag.item()) & 1
+
+
+def test_backward_golden(ops, golden):
+    g = golden("sgd")
+    base, rows, col = g.table_meta()
+    for mode, want in ((orc.POOL_SUM, g.weights_after_sum), (orc.POOL_MEAN, g.weights_after_mean)):
+        grp = ops.TableGroup(weights=dev(g.weights), feat_row_base=dev(base), feat_rows=dev(rows),
+                             feat_out_col=dev(col), out_stride=g.F * g.D)
+        ops.embedding_backward_update(grp, dev(g.grad_out), dev(g.indices), dev(g.offsets), g.B, mode,
+                                      ops.make_optimizer_args(orc.OPT_SGD, g.lr))
+        np.testing.assert_allclose(grp.weights.cpu().numpy(), want, rtol=FP32_RTOL, atol=1e-6)
+    g = golden("rwa")
+    base, rows, col = g.table_meta()
+    for tag in ("nowd", "wd"):
+        grp = ops.TableGroup(weights=dev(g.weights), feat_row_base=dev(base), feat_rows=dev(rows),
+                             feat_out_col=dev(col), out_stride=g.F * g.D, state0=dev(g.h0))
+        ops.embedding_backward_update(
+            grp, dev(g.grad_out), dev(g.indices), dev(g.offsets), g.B, orc.POOL_SUM,
+            ops.make_optimizer_args(orc.OPT_ROWWISE_ADAGRAD, g.lr, g.eps, getattr(g, f"wd_{tag}")))
+        np.testing.assert_allclose(grp.weights.cpu().numpy(), getattr(g, f"weights_after_{tag}"),
+                                   rtol=FP32_RTOL, atol=1e-6)
+        np.testing.assert_allclose(grp.state0.cpu().numpy(), getattr(g, f"h_after_{tag}"), rtol=FP32_RTOL, atol=1e-6)
+    g = golden("adam")
+    base, rows, col = g.table_meta()
+    for tag in ("nowd", "wd"):
+        grp = ops.TableGroup(weights=dev(g.weights), feat_row_base=dev(base), feat_rows=dev(rows),
+                             feat_out_col=dev(col), out_stride=g.F * g.D,
+                             state0=torch.zeros(g.weights.shape, device="cuda"),
+                             state1=torch.zeros(g.weights.shape, device="cuda"))
+        for s in range(g.steps):
+            ops.embedding_backward_update(
+                grp, dev(getattr(g, f"grad_out{s}")), dev(getattr(g, f"indices{s}")), dev(getattr(g, f"offsets{s}")),
+                g.B, orc.POOL_SUM,
+                ops.make_optimizer_args(orc.OPT_ADAM, g.lr, g.eps, getattr(g, f"wd_{tag}"), g.beta1, g.beta2, s + 1))
+            np.testing.assert_allclose(grp.weights.cpu().numpy(), getattr(g, f"weights_after_{tag}{s}"),
+                                       rtol=FP32_RTOL, atol=1e-6)
+
+
+# ----------------------------------------------------------------------------- routing
+def test_bucketize_golden_and_random(ops, golden):
+    g = golden("bucketize")
+    off = orc.complete_cumsum(g.lengths)
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    nl, no, ni, nw, perm = ops.bucketize_row_wise(dev(g.lengths), dev(off), dev(g.indices), dev(g.weights),
+                                                  dev(g.block_sizes), g.F, g.B, g.world, True, flag)
+    np.testing.assert_array_equal(nl.cpu().numpy(), g.new_lengths)
+    np.testing.assert_array_equal(ni.cpu().numpy(), g.new_indices)
+    np.testing.assert_array_equal(nw.cpu().numpy(), g.new_weights)
+    np.testing.assert_array_equal(perm.cpu().numpy(), g.unbucketize_permute)
+    np.testing.assert_array_equal(no.cpu().numpy(), orc.complete_cumsum(g.new_lengths))
+    for world in (1, 2, 4, 8):
+        c = make_case(seed=world, F=5, B=29, D=4, rows=[1000, 17, 64, 5, 333], max_len=70)
+        bs = (c.rows + world - 1) // world
+        w = np.random.default_rng(1).normal(size=c.L).astype(np.float32)
+        want = orc.bucketize_row_wise(c.offsets, c.indices, w, bs, c.F, c.B, world)
+        got = ops.bucketize_row_wise(dev(c.lengths), dev(c.offsets), dev(c.indices), dev(w), dev(bs), c.F, c.B,
+                                     world, True, flag)
+        for a, b in zip(got, want[:5]):
+            np.testing.assert_array_equal(a.cpu().numpy(), b)
+    assert int(flag.item()) == 0
+
+
+def test_permute_2d_golden_and_random(ops, golden):
+    g = golden("permute")
+    off = orc.complete_cumsum(g.in_lengths)
+    ol, oo, oi, _ = ops.permute_2d(dev(g.permute), g.B, dev(g.in_lengths), dev(off), dev(g.in_indices))
+    np.testing.assert_array_equal(ol.cpu().numpy(), g.out_lengths)
+    np.testing.assert_array_equal(oi.cpu().numpy(), g.out_indices)
+    c = make_case(seed=2, F=7, B=19, D=4, max_len=40)
+    perm = np.array([6, 0, 3, 3, 1, 5, 2, 4, 0], dtype=np.int32)
+    w = np.random.default_rng(3).normal(size=c.L).astype(np.float32)
+    want = orc.permute_2d(perm, c.B, c.lengths, c.offsets, c.indices, w)
+    got = ops.permute_2d(dev(perm), c.B, dev(c.lengths), dev(c.offsets), dev(c.indices), dev(w))
+    for a, b in zip(got, want):
+        np.testing.assert_array_equal(a.cpu().numpy(), b)
+
+
+# ----------------------------------------------------------------------------- jagged
+def test_jagged_dense_golden_and_random(ops, golden):
+    g = golden("jagged")
+    np.testing.assert_array_equal(
+        ops._jagged_2d_to_dense_raw(dev(g.values), dev(g.offsets), g.max_len).cpu().numpy(), g.dense)
+    np.testing.assert_array_equal(ops.dense_to_jagged(dev(g.dense), dev(g.offsets), 4).cpu().numpy(), g.back)
+    np.testing.assert_array_equal(
+        ops.jagged_1d_to_padded_dense(dev(g.ids), dev(g.offsets), g.desired, g.pad).cpu().numpy(), g.padded)
+    rng = np.random.default_rng(0)
+    for D in (3, 16, 20):
+        lengths = rng.integers(0, 30, size=200).astype(np.int32)
+        off = orc.complete_cumsum(lengths)
+        vals = rng.normal(size=(int(off[-1]), D)).astype(np.float32)
+        for max_len in (1, 20, 35):
+            dense = orc.jagged_2d_to_dense(vals, off, max_len)
+            np.testing.assert_array_equal(ops._jagged_2d_to_dense_raw(dev(vals), dev(off), max_len).cpu().numpy(), dense)
+            np.testing.assert_array_equal(ops.dense_to_jagged(dev(dense), dev(off), int(off[-1])).cpu().numpy(),
+                                          orc.dense_to_jagged(dense, off))
+    ids = rng.integers(0, 1000, size=int(off[-1]))
+    np.testing.assert_array_equal(ops.jagged_1d_to_padded_dense(dev(ids), dev(off), 20, 0).cpu().numpy(),
+                                  orc.jagged_1d_to_padded_dense(ids, off, 20, 0))
+
+
+# ----------------------------------------------------------------------------- argument checking through the C ABI
+def test_c_abi_rejects_bad_arguments(ops):
+    from tdfo_b200._lib import TdfoError
+    c = make_case(seed=1, F=2, B=4, D=6, max_len=3)          # 6 floats = 24 B, not a multiple of 16
+    with pytest.raises(TdfoError, match="multiple of 16"):
+        ops.embedding_forward(group_for(ops, c, dev(c.weights)), dev(c.indices), dev(c.offsets), c.B, orc.POOL_SUM)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        ops.complete_cumsum(torch.zeros(4, dtype=torch.int32))
