@@ -159,7 +159,7 @@ int tdfo_embedding_forward(const void* weights, int32_t weights_dtype, int64_t t
                            const float* per_sample_weights,
                            const int64_t* feat_row_base, const int64_t* feat_rows,
                            const int64_t* feat_out_col,
-                           int32_t F, int64_t B, int64_t L /* used by POOL_NONE only */,
+                           int32_t F, int64_t B, int64_t L /* number of ids == offsets[F*B] */,
                            int32_t pooling_mode,
                            float* out, int64_t out_stride,
                            int32_t* err_flag, void* stream);

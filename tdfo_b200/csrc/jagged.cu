@@ -210,8 +210,8 @@ extern "C" int tdfo_kjt_bucketize_row_wise(const int32_t* lengths, const int64_t
         TDFO_CUDA(cudaMemsetAsync(new_offsets, 0, sizeof(int64_t), st));
         return TDFO_OK;
     }
-    TDFO_CHECK_ARG(offsets && indices && block_sizes && new_lengths && new_indices,
-                   "bucketize_row_wise: null pointer");
+    // indices / new_indices may be null when every bag is empty
+    TDFO_CHECK_ARG(offsets && block_sizes && new_lengths, "bucketize_row_wise: null pointer");
     const size_t need = tdfo_bucketize_scratch_bytes(num_bags, world);
     if (!scratch || !aligned(scratch, 256) || scratch_bytes < need) {
         set_error("bucketize_row_wise: scratch null, misaligned or smaller than %zu bytes", need);

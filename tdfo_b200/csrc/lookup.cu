@@ -236,7 +236,7 @@ extern "C" int tdfo_embedding_forward(const void* weights, int32_t weights_dtype
     TDFO_CHECK_ARG(total_rows >= 0 && total_rows < 0xffffffffll,
                    "embedding_forward: total_rows %lld must be < 2^32-1", (long long)total_rows);
     if (F == 0 || B == 0) return TDFO_OK;
-    TDFO_CHECK_ARG(weights && indices && offsets && feat_row_base && feat_rows && out,
+    TDFO_CHECK_ARG(weights && (indices || L == 0) && offsets && feat_row_base && feat_rows && out,
                    "embedding_forward: null pointer");
     TDFO_CHECK_ARG(aligned(weights, 16) && aligned(out, 16), "embedding_forward: weights/out not 16-byte aligned");
     if (pooling_mode != TDFO_POOL_NONE) {

@@ -312,7 +312,8 @@ extern "C" int tdfo_linearize_indices(const int64_t* indices, const int64_t* off
     TDFO_CHECK_ARG(total_rows >= 0 && total_rows < 0xffffffffll, "linearize_indices: total_rows must be < 2^32-1");
     TDFO_CHECK_ARG((int64_t)F * B < (1ll << 32), "linearize_indices: F*B must be < 2^32");
     if (F == 0 || B == 0) return TDFO_OK;
-    TDFO_CHECK_ARG(indices && offsets && feat_row_base && feat_rows && keys && vals, "linearize_indices: null pointer");
+    // indices / keys / vals may be null when every bag is empty
+    TDFO_CHECK_ARG(offsets && feat_row_base && feat_rows, "linearize_indices: null pointer");
     const int64_t num_bags = (int64_t)F * B;
     const int64_t blocks = (num_bags + kUpdThreads / 32 - 1) / (kUpdThreads / 32);
     linearize_kernel<<<(unsigned)blocks, kUpdThreads, 0, static_cast<cudaStream_t>(stream)>>>(
