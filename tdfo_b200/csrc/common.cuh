@@ -49,25 +49,28 @@ inline void count_launch(int n = 1) { g_launch_count += (unsigned long long)n; }
 // ---------------------------------------------------------------- device side
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 
-// 128-bit streaming load of table rows: read-only path, do not pollute L1.
+// Memory access flavours.  These are compiler intrinsics on purpose: an `asm volatile` load
+// inside a `cond ? load : 0` makes ptxas wait for each load before issuing the next one
+// (seen in SASS as one destination register reused by every LDG), which serialises a gather.
+// Table rows are read once per step: streaming (evict-first), no reuse expected.
 __device__ __forceinline__ uint4 ldg_stream_128(const void* p) {
-    uint4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-    return r;
+    return __ldcs(reinterpret_cast<const uint4*>(p));
 }
 // 128-bit load that may hit in L1/L2 (gradient rows re-read by several rows).
 __device__ __forceinline__ uint4 ldg_128(const void* p) {
     return __ldg(reinterpret_cast<const uint4*>(p));
 }
-// Plain (coherent) 128-bit load for read-modify-write rows.
+// Plain (coherent) 128-bit load.
 __device__ __forceinline__ uint4 ld_128(const void* p) {
     return *reinterpret_cast<const uint4*>(p);
 }
+// Read-modify-write rows: coherent, cached in L2 only (each row is touched once per step).
+__device__ __forceinline__ uint4 ld_row_128(const void* p) {
+    return __ldcg(reinterpret_cast<const uint4*>(p));
+}
 // Streaming store (written once, not re-read by this kernel).
 __device__ __forceinline__ void st_stream_128(void* p, uint4 v) {
-    asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};"
-                 :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+    __stcs(reinterpret_cast<uint4*>(p), v);
 }
 __device__ __forceinline__ void st_128(void* p, uint4 v) {
     *reinterpret_cast<uint4*>(p) = v;

@@ -57,176 +57,274 @@ struct UpdateArgs {
     const int64_t* feat_out_col;
     int64_t grad_stride;
     int64_t B;
+    uint64_t B_magic;    // ceil(2^64 / B): bag id / B == __umul64hi(id, B_magic) for every 32-bit id (B > 1)
     uint32_t total_rows;
+    uint32_t L;
     int32_t D;
     int32_t nchunks;
     int32_t pooling_mode;
     float lr, eps, wd, beta1, beta2, bc1, bc2;   // bc = 1 - beta^step
+    float inv_D;
 };
 
-template <typename T, int LPR, int CPL, int OPT>
-__global__ void __launch_bounds__(kUpdThreads)
+constexpr int kUpdBlocksPerSM = 2;     // persistent grid: 148 x 2 CTAs of 8 warps (<= 128 registers)
+
+// Metadata of a tile of 32 consecutive unique rows, one row per lane.
+struct TileMeta {
+    uint32_t key, s, e;
+};
+
+__device__ __forceinline__ TileMeta load_tile_meta(const UpdateArgs& a, uint32_t tile, uint32_t nu, int lane) {
+    TileMeta m;
+    const uint32_t u = tile * 32u + (uint32_t)lane;
+    if (u < nu) {
+        m.key = __ldg(a.unique_keys + u);
+        m.s = __ldg(a.seg_starts + u);
+        m.e = __ldg(a.seg_starts + u + 1);
+    } else {
+        m.key = 0xffffffffu;
+        m.s = m.e = a.L;
+    }
+    return m;
+}
+
+// Gradient row of one occurrence (payload v) and its scale.
+template <int POOL_RUNTIME = 0>
+__device__ __forceinline__ const float* grad_row_of(const UpdateArgs& a, uint32_t v, float& scale) {
+    scale = 1.f;
+    if (a.pooling_mode == TDFO_POOL_NONE) return a.grad + (size_t)v * a.D;
+    const uint32_t f = a.B_magic ? (uint32_t)__umul64hi((uint64_t)v, a.B_magic) : v;
+    const uint32_t b = v - f * (uint32_t)a.B;
+    if (a.pooling_mode == TDFO_POOL_MEAN)
+        scale = 1.f / (float)(__ldg(a.offsets + v + 1) - __ldg(a.offsets + v));
+    return a.grad + (size_t)b * a.grad_stride + __ldg(a.feat_out_col + f);
+}
+
+// Persistent warps over tiles of 32 unique rows.  Per tile the row keys, segment bounds and
+// the first 32 payloads are fetched with three coalesced loads (prefetched one / two tiles
+// ahead), then the rows are processed UR at a time per LPR-lane group: weight row, first
+// gradient row and optimizer state are all requested before any of them is consumed, so
+// each warp keeps 2*UR (+state) independent 128-bit row requests in flight.
+template <typename T, int LPR, int CPL, int UR, int OPT>
+__global__ void __launch_bounds__(kUpdThreads, kUpdBlocksPerSM)
 sparse_update_kernel(const UpdateArgs a) {
     constexpr int E = Chunk<T>::kElems;
-    constexpr int GPB = kUpdThreads / LPR;         // row groups per block
-    const int sub = threadIdx.x % LPR;
-    // Row groups of one warp run different rows (and different trip counts): shuffles
-    // name only the lanes of their own group.
-    const unsigned gmask = (LPR == 32) ? kFullMask : (((1u << (LPR & 31)) - 1u) << ((lane_id() / LPR) * LPR));
+    constexpr int RPW = 32 / LPR;                  // rows processed in parallel by one warp
+    static_assert(RPW * UR <= 32, "a step may not cover more than the 32 rows of a tile");
+    constexpr int GQ = E / 4;                      // 16-byte gradient loads per table chunk
+    const int lane = lane_id();
+    const int sub = lane % LPR;
+    const int grp = lane / LPR;
+    // Row groups of one warp run different rows (and different trip counts): group-level
+    // shuffles name only the lanes of their own group.
+    const unsigned gmask = (LPR == 32) ? kFullMask : (((1u << (LPR & 31)) - 1u) << (grp * LPR));
     const uint32_t nu = *a.num_unique;
+    const uint32_t ntiles = (nu + 31u) / 32u;
+    const uint32_t nwarps = gridDim.x * (kUpdThreads / 32);
+    uint32_t tile = blockIdx.x * (kUpdThreads / 32) + (threadIdx.x >> 5);
+    if (tile >= ntiles) return;
     uint4* __restrict__ wbase = reinterpret_cast<uint4*>(a.weights);
 
-    for (uint32_t u = blockIdx.x * GPB + threadIdx.x / LPR; u < nu; u += gridDim.x * GPB) {
-        const uint32_t row = __ldg(a.unique_keys + u);
-        if (row >= a.total_rows) continue;           // out-of-range marker, sorted last
-        const uint32_t s = __ldg(a.seg_starts + u), e = __ldg(a.seg_starts + u + 1);
+    TileMeta cur = load_tile_meta(a, tile, nu, lane);
+    TileMeta nxt = load_tile_meta(a, tile + nwarps, nu, lane);     // past-the-end tiles come back empty
+    uint32_t cur_s0 = __shfl_sync(kFullMask, cur.s, 0);
+    uint32_t cur_val = (cur_s0 + lane < __shfl_sync(kFullMask, cur.e, 31)) ? __ldg(a.sorted_vals + cur_s0 + lane) : 0u;
 
-        float g[CPL][E];
-#pragma unroll
-        for (int k = 0; k < CPL; ++k)
-#pragma unroll
-            for (int i = 0; i < E; ++i) g[k][i] = 0.f;
+    while (tile < ntiles) {
+        // prefetch: metadata two tiles ahead, payloads one tile ahead
+        const TileMeta nn = load_tile_meta(a, tile + 2u * nwarps, nu, lane);
+        const uint32_t nxt_s0 = __shfl_sync(kFullMask, nxt.s, 0);
+        const uint32_t nxt_val = (nxt_s0 + lane < __shfl_sync(kFullMask, nxt.e, 31)) ? __ldg(a.sorted_vals + nxt_s0 + lane) : 0u;
 
-        // ordered reduction over the occurrences of this row
-        for (uint32_t i = s; i < e; ++i) {
-            const uint32_t v = __ldg(a.sorted_vals + i);
-            const float* grow;
-            float scale = 1.f;
-            if (a.pooling_mode == TDFO_POOL_NONE) {
-                grow = a.grad + (size_t)v * a.D;
-            } else {
-                const uint32_t f = v / (uint32_t)a.B;
-                const uint32_t b = v - f * (uint32_t)a.B;
-                grow = a.grad + (size_t)b * a.grad_stride + __ldg(a.feat_out_col + f);
-                if (a.pooling_mode == TDFO_POOL_MEAN) {
-                    const int64_t len = __ldg(a.offsets + v + 1) - __ldg(a.offsets + v);
-                    scale = 1.f / (float)len;
+        for (int j0 = 0; j0 < 32; j0 += RPW * UR) {
+            uint32_t row[UR], s[UR], e[UR];
+            bool valid[UR];
+            uint4 wv[UR][CPL];
+            uint4 gv[UR][CPL][GQ];
+            float scale[UR];
+            float h_old[UR];
+            // ---- issue every independent request of this step.  All loads are unconditional:
+            // rows / payloads that do not exist are redirected to element 0 and masked below.
+#pragma unroll
+            for (int q = 0; q < UR; ++q) {
+                const int r = j0 + q * RPW + grp;
+                row[q] = __shfl_sync(kFullMask, cur.key, r);
+                s[q] = __shfl_sync(kFullMask, cur.s, r);
+                e[q] = __shfl_sync(kFullMask, cur.e, r);
+                valid[q] = row[q] < a.total_rows;              // padding lanes and the out-of-range marker fail this
+                const uint32_t pos = s[q] - cur_s0;
+                uint32_t v0 = __shfl_sync(kFullMask, cur_val, pos & 31u);
+                if (valid[q] && pos >= 32u) v0 = __ldg(a.sorted_vals + s[q]);
+                if (!valid[q]) v0 = 0u;
+                const float* grow = grad_row_of(a, v0, scale[q]);
+                const size_t wrow = (size_t)(valid[q] ? row[q] : 0u) * a.nchunks;
+#pragma unroll
+                for (int k = 0; k < CPL; ++k) {
+                    const int c = min(sub + k * LPR, a.nchunks - 1);
+                    wv[q][k] = ld_row_128(wbase + wrow + c);
+#pragma unroll
+                    for (int t = 0; t < GQ; ++t) gv[q][k][t] = ldg_128(grow + (size_t)c * E + 4 * t);
                 }
+                h_old[q] = 0.f;
+                if (OPT == TDFO_OPT_ROWWISE_ADAGRAD) h_old[q] = __ldcg(a.state0 + (valid[q] ? row[q] : 0u));
             }
+            // ---- consume
 #pragma unroll
-            for (int k = 0; k < CPL; ++k) {
-                const int c = sub + k * LPR;
-                if (c < a.nchunks) {
+            for (int q = 0; q < UR; ++q) {
+                float g[CPL][E], w[CPL][E];
 #pragma unroll
-                    for (int q = 0; q < E; q += 4) {
-                        const uint4 r = ldg_128(grow + (size_t)c * E + q);
-                        g[k][q]     = fmaf(scale, __uint_as_float(r.x), g[k][q]);
-                        g[k][q + 1] = fmaf(scale, __uint_as_float(r.y), g[k][q + 1]);
-                        g[k][q + 2] = fmaf(scale, __uint_as_float(r.z), g[k][q + 2]);
-                        g[k][q + 3] = fmaf(scale, __uint_as_float(r.w), g[k][q + 3]);
+                for (int k = 0; k < CPL; ++k) {
+#pragma unroll
+                    for (int t = 0; t < GQ; ++t) {
+                        g[k][4 * t]     = scale[q] * __uint_as_float(gv[q][k][t].x);
+                        g[k][4 * t + 1] = scale[q] * __uint_as_float(gv[q][k][t].y);
+                        g[k][4 * t + 2] = scale[q] * __uint_as_float(gv[q][k][t].z);
+                        g[k][4 * t + 3] = scale[q] * __uint_as_float(gv[q][k][t].w);
                     }
+                    Chunk<T>::unpack(wv[q][k], w[k]);
                 }
-            }
-        }
-
-        // read the row once
-        float w[CPL][E];
+                // further occurrences of the row, in sorted (= original) order
+                if (valid[q]) {
+                    for (uint32_t i = s[q] + 1; i < e[q]; ++i) {
+                        float sc;
+                        const float* grow = grad_row_of(a, __ldg(a.sorted_vals + i), sc);
 #pragma unroll
-        for (int k = 0; k < CPL; ++k) {
-            const int c = sub + k * LPR;
-            if (c < a.nchunks) Chunk<T>::unpack(ld_128(wbase + (size_t)row * a.nchunks + c), w[k]);
-            else {
+                        for (int k = 0; k < CPL; ++k) {
+                            const int c = sub + k * LPR;
+                            if (c < a.nchunks) {
 #pragma unroll
-                for (int i = 0; i < E; ++i) w[k][i] = 0.f;
-            }
-        }
-
-        if (OPT == TDFO_OPT_SGD) {
-#pragma unroll
-            for (int k = 0; k < CPL; ++k)
-#pragma unroll
-                for (int i = 0; i < E; ++i) {
-                    const float gi = fmaf(a.wd, w[k][i], g[k][i]);
-                    w[k][i] = fmaf(-a.lr, gi, w[k][i]);
-                }
-        } else if (OPT == TDFO_OPT_ROWWISE_ADAGRAD) {
-            float ss = 0.f;
-#pragma unroll
-            for (int k = 0; k < CPL; ++k)
-#pragma unroll
-                for (int i = 0; i < E; ++i) {
-                    g[k][i] = fmaf(a.wd, w[k][i], g[k][i]);
-                    ss = fmaf(g[k][i], g[k][i], ss);
-                }
-#pragma unroll
-            for (int o = 1; o < LPR; o <<= 1) ss += __shfl_xor_sync(gmask, ss, o);
-            const float h_old = a.state0[row];
-            __syncwarp(gmask);                       // every lane has read h before lane 0 overwrites it
-            const float h = h_old + ss / (float)a.D;
-            const float mult = a.lr / (sqrtf(h) + a.eps);
-            if (sub == 0) a.state0[row] = h;
-#pragma unroll
-            for (int k = 0; k < CPL; ++k)
-#pragma unroll
-                for (int i = 0; i < E; ++i) w[k][i] = fmaf(-mult, g[k][i], w[k][i]);
-        } else {   // ADAM
-#pragma unroll
-            for (int k = 0; k < CPL; ++k) {
-                const int c = sub + k * LPR;
-                if (c < a.nchunks) {
-                    float* m = a.state0 + (size_t)row * a.D + (size_t)c * E;
-                    float* v = a.state1 + (size_t)row * a.D + (size_t)c * E;
-#pragma unroll
-                    for (int q = 0; q < E; q += 4) {
-                        uint4 mr = ld_128(m + q), vr = ld_128(v + q);
-                        float mm[4] = {__uint_as_float(mr.x), __uint_as_float(mr.y), __uint_as_float(mr.z), __uint_as_float(mr.w)};
-                        float vv[4] = {__uint_as_float(vr.x), __uint_as_float(vr.y), __uint_as_float(vr.z), __uint_as_float(vr.w)};
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            const float gi = g[k][q + i];
-                            mm[i] = a.beta1 * mm[i] + (1.f - a.beta1) * gi;
-                            vv[i] = a.beta2 * vv[i] + (1.f - a.beta2) * gi * gi;
-                            const float mhat = mm[i] / a.bc1;
-                            const float vhat = vv[i] / a.bc2;
-                            w[k][q + i] -= a.lr * (mhat / (sqrtf(vhat) + a.eps) + a.wd * w[k][q + i]);
+                                for (int t = 0; t < GQ; ++t) {
+                                    const uint4 x = ldg_128(grow + (size_t)c * E + 4 * t);
+                                    g[k][4 * t]     = fmaf(sc, __uint_as_float(x.x), g[k][4 * t]);
+                                    g[k][4 * t + 1] = fmaf(sc, __uint_as_float(x.y), g[k][4 * t + 1]);
+                                    g[k][4 * t + 2] = fmaf(sc, __uint_as_float(x.z), g[k][4 * t + 2]);
+                                    g[k][4 * t + 3] = fmaf(sc, __uint_as_float(x.w), g[k][4 * t + 3]);
+                                }
+                            }
                         }
-                        st_128(m + q, make_uint4(__float_as_uint(mm[0]), __float_as_uint(mm[1]), __float_as_uint(mm[2]), __float_as_uint(mm[3])));
-                        st_128(v + q, make_uint4(__float_as_uint(vv[0]), __float_as_uint(vv[1]), __float_as_uint(vv[2]), __float_as_uint(vv[3])));
+                    }
+                }
+
+                if (OPT == TDFO_OPT_SGD) {
+#pragma unroll
+                    for (int k = 0; k < CPL; ++k)
+#pragma unroll
+                        for (int i = 0; i < E; ++i) {
+                            const float gi = fmaf(a.wd, w[k][i], g[k][i]);
+                            w[k][i] = fmaf(-a.lr, gi, w[k][i]);
+                        }
+                } else if (OPT == TDFO_OPT_ROWWISE_ADAGRAD) {
+                    float ss = 0.f;
+#pragma unroll
+                    for (int k = 0; k < CPL; ++k)
+#pragma unroll
+                        for (int i = 0; i < E; ++i) {
+                            g[k][i] = fmaf(a.wd, w[k][i], g[k][i]);
+                            ss = fmaf(g[k][i], g[k][i], ss);
+                        }
+#pragma unroll
+                    for (int o = 1; o < LPR; o <<= 1) ss += __shfl_xor_sync(gmask, ss, o);
+                    const float h = h_old[q] + ss * a.inv_D;
+                    // sqrt / divide through the SFU (2-3 ulp, far inside the 1e-5 parity bar)
+                    const float sq = h > 0.f ? h * rsqrtf(h) : 0.f;
+                    const float mult = __fdividef(a.lr, sq + a.eps);
+                    if (valid[q] && sub == 0) a.state0[row[q]] = h;
+#pragma unroll
+                    for (int k = 0; k < CPL; ++k)
+#pragma unroll
+                        for (int i = 0; i < E; ++i) w[k][i] = fmaf(-mult, g[k][i], w[k][i]);
+                } else if (valid[q]) {   // ADAM
+#pragma unroll
+                    for (int k = 0; k < CPL; ++k) {
+                        const int c = sub + k * LPR;
+                        if (c < a.nchunks) {
+                            float* m = a.state0 + (size_t)row[q] * a.D + (size_t)c * E;
+                            float* v = a.state1 + (size_t)row[q] * a.D + (size_t)c * E;
+#pragma unroll
+                            for (int t = 0; t < E; t += 4) {
+                                uint4 mr = ld_128(m + t), vr = ld_128(v + t);
+                                float mm[4] = {__uint_as_float(mr.x), __uint_as_float(mr.y), __uint_as_float(mr.z), __uint_as_float(mr.w)};
+                                float vv[4] = {__uint_as_float(vr.x), __uint_as_float(vr.y), __uint_as_float(vr.z), __uint_as_float(vr.w)};
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) {
+                                    const float gi = g[k][t + i];
+                                    mm[i] = a.beta1 * mm[i] + (1.f - a.beta1) * gi;
+                                    vv[i] = a.beta2 * vv[i] + (1.f - a.beta2) * gi * gi;
+                                    const float mhat = mm[i] / a.bc1;
+                                    const float vhat = vv[i] / a.bc2;
+                                    w[k][t + i] -= a.lr * (mhat / (sqrtf(vhat) + a.eps) + a.wd * w[k][t + i]);
+                                }
+                                st_128(m + t, make_uint4(__float_as_uint(mm[0]), __float_as_uint(mm[1]), __float_as_uint(mm[2]), __float_as_uint(mm[3])));
+                                st_128(v + t, make_uint4(__float_as_uint(vv[0]), __float_as_uint(vv[1]), __float_as_uint(vv[2]), __float_as_uint(vv[3])));
+                            }
+                        }
+                    }
+                }
+
+                if (valid[q]) {
+#pragma unroll
+                    for (int k = 0; k < CPL; ++k) {
+                        const int c = sub + k * LPR;
+                        if (c < a.nchunks) st_128(wbase + (size_t)row[q] * a.nchunks + c, Chunk<T>::pack(w[k]));
                     }
                 }
             }
         }
-
-#pragma unroll
-        for (int k = 0; k < CPL; ++k) {
-            const int c = sub + k * LPR;
-            if (c < a.nchunks) st_128(wbase + (size_t)row * a.nchunks + c, Chunk<T>::pack(w[k]));
-        }
+        tile += nwarps;
+        cur = nxt; cur_s0 = nxt_s0; cur_val = nxt_val;
+        nxt = nn;
     }
 }
 
-template <typename T, int LPR, int CPL>
+template <typename T, int LPR, int CPL, int UR>
 static int launch_update(const UpdateArgs& a, int opt, int64_t max_unique, cudaStream_t st) {
-    constexpr int GPB = kUpdThreads / LPR;
-    int64_t blocks = (max_unique + GPB - 1) / GPB;
-    const int64_t cap = (int64_t)kNumSMs * 32;
+    const int64_t tiles = (max_unique + 31) / 32;                 // one warp per tile of 32 unique rows
+    int64_t blocks = (tiles + kUpdThreads / 32 - 1) / (kUpdThreads / 32);
+    const int64_t cap = (int64_t)kNumSMs * kUpdBlocksPerSM;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     switch (opt) {
         case TDFO_OPT_SGD:
-            sparse_update_kernel<T, LPR, CPL, TDFO_OPT_SGD><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
+            sparse_update_kernel<T, LPR, CPL, UR, TDFO_OPT_SGD><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
         case TDFO_OPT_ROWWISE_ADAGRAD:
-            sparse_update_kernel<T, LPR, CPL, TDFO_OPT_ROWWISE_ADAGRAD><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
+            sparse_update_kernel<T, LPR, CPL, UR, TDFO_OPT_ROWWISE_ADAGRAD><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
         default:
-            sparse_update_kernel<T, LPR, CPL, TDFO_OPT_ADAM><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
+            sparse_update_kernel<T, LPR, CPL, UR, TDFO_OPT_ADAM><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
     }
     count_launch();
     TDFO_LAUNCH_CHECK("sparse_update");
     return TDFO_OK;
 }
 
+// Few lanes per row on purpose: the per-row bookkeeping (metadata shuffles, gradient address,
+// optimizer scalar math) is replicated in every lane of the row's group, so a group of 8 lanes
+// with 4 chunks each spends a quarter of the issue slots per row that 32 lanes x 1 chunk would,
+// and a warp keeps RPW * UR rows (weight + gradient) in flight.
 template <typename T>
 static int dispatch_update(const UpdateArgs& a, int opt, int64_t max_unique, cudaStream_t st) {
     const int n = a.nchunks;
-    if (n <= 1)   return launch_update<T, 1, 1>(a, opt, max_unique, st);
-    if (n <= 2)   return launch_update<T, 2, 1>(a, opt, max_unique, st);
-    if (n <= 4)   return launch_update<T, 4, 1>(a, opt, max_unique, st);
-    if (n <= 8)   return launch_update<T, 8, 1>(a, opt, max_unique, st);
-    if (n <= 16)  return launch_update<T, 16, 1>(a, opt, max_unique, st);
-    if (n <= 32)  return launch_update<T, 32, 1>(a, opt, max_unique, st);
-    if (n <= 64)  return launch_update<T, 32, 2>(a, opt, max_unique, st);
-    if (n <= 128) return launch_update<T, 32, 4>(a, opt, max_unique, st);
-    if (n <= 256) return launch_update<T, 32, 8>(a, opt, max_unique, st);
+    constexpr bool kWide = sizeof(T) == 4;          // fp32: 4 chunks per lane; bf16 (8 elems / chunk): 2
+    if (kWide) {
+        if (n <= 1)   return launch_update<T, 1, 1, 1>(a, opt, max_unique, st);
+        if (n <= 2)   return launch_update<T, 1, 2, 1>(a, opt, max_unique, st);
+        if (n <= 4)   return launch_update<T, 1, 4, 1>(a, opt, max_unique, st);
+        if (n <= 8)   return launch_update<T, 2, 4, 2>(a, opt, max_unique, st);
+        if (n <= 16)  return launch_update<T, 4, 4, 2>(a, opt, max_unique, st);
+        if (n <= 32)  return launch_update<T, 8, 4, 2>(a, opt, max_unique, st);
+        if (n <= 64)  return launch_update<T, 16, 4, 2>(a, opt, max_unique, st);
+        if (n <= 128) return launch_update<T, 32, 4, 1>(a, opt, max_unique, st);
+        if (n <= 256) return launch_update<T, 32, 8, 1>(a, opt, max_unique, st);
+    } else {
+        if (n <= 1)   return launch_update<T, 1, 1, 1>(a, opt, max_unique, st);
+        if (n <= 2)   return launch_update<T, 1, 2, 1>(a, opt, max_unique, st);
+        if (n <= 4)   return launch_update<T, 2, 2, 2>(a, opt, max_unique, st);
+        if (n <= 8)   return launch_update<T, 4, 2, 2>(a, opt, max_unique, st);
+        if (n <= 16)  return launch_update<T, 8, 2, 2>(a, opt, max_unique, st);
+        if (n <= 32)  return launch_update<T, 16, 2, 2>(a, opt, max_unique, st);
+        if (n <= 64)  return launch_update<T, 32, 2, 1>(a, opt, max_unique, st);
+        if (n <= 128) return launch_update<T, 32, 4, 1>(a, opt, max_unique, st);
+        if (n <= 256) return launch_update<T, 32, 8, 1>(a, opt, max_unique, st);
+    }
     set_error("sparse_update: row of %d bytes exceeds the 4096-byte maximum", n * 16);
     return TDFO_ERR_UNSUPPORTED;
 }
@@ -283,8 +381,10 @@ int sparse_update_impl(void* weights, int32_t weights_dtype, int64_t total_rows,
     a.weights = weights; a.state0 = state0; a.state1 = state1; a.grad = grad_out;
     a.sorted_vals = sorted_vals; a.unique_keys = unique_keys; a.seg_starts = seg_starts;
     a.num_unique = num_unique; a.offsets = offsets; a.feat_out_col = feat_out_col;
-    a.grad_stride = grad_stride; a.B = B; a.total_rows = (uint32_t)total_rows; a.D = D;
+    a.grad_stride = grad_stride; a.B = B;
+    a.B_magic = B > 1 ? (~0ull / (uint64_t)B + 1ull) : 0ull; a.total_rows = (uint32_t)total_rows; a.L = (uint32_t)L; a.D = D;
     a.nchunks = (int32_t)(D * esz / 16); a.pooling_mode = pooling_mode;
+    a.inv_D = 1.f / (float)D;
     a.lr = opt->learning_rate; a.eps = opt->eps; a.wd = opt->weight_decay;
     a.beta1 = opt->beta1; a.beta2 = opt->beta2;
     a.bc1 = 1.f; a.bc2 = 1.f;
