@@ -225,8 +225,10 @@ def run_ours(args):
 
     def step_fused(i):
         idx = batches[i % N_BATCHES]
-        ops.embedding_forward(grp, idx, offsets, B, _lib.POOL_SUM, out=out)
-        ops.embedding_backward_update(grp, grad_out, idx, offsets, B, _lib.POOL_SUM, opt, scratch=scratch)
+        # the forward also emits the (row, bag) pairs the backward sorts (linearise stage fused away)
+        ops.embedding_forward(grp, idx, offsets, B, _lib.POOL_SUM, out=out, backward_scratch=scratch)
+        ops.embedding_backward_update(grp, grad_out, idx, offsets, B, _lib.POOL_SUM, opt, scratch=scratch,
+                                      keys_in_scratch=True)
 
     def step_staged(i, ev):
         """Same kernels, same order, one C-ABI call per stage so each can be bracketed by events."""

@@ -149,6 +149,11 @@ int tdfo_kjt_permute_2d(const int32_t* permute /* [S_out] */, int32_t S_in, int3
  * Sequence (NONE):    out is float[L, D], out[p,:] = row of indices[p]
  *   (out_stride, feat_out_col ignored).
  * Accumulation is fp32 in bag order (deterministic).
+ * sort_keys / sort_vals (uint32[L], both or neither): when given, the kernel also
+ *   writes the (row key, payload) pair of every id exactly as tdfo_linearize_indices
+ *   would, while the ids are in registers.  Pointing them at the input_keys /
+ *   input_vals slots of the backward scratch (tdfo_backward_scratch_layout) lets
+ *   tdfo_embedding_backward_update(keys_in_scratch = 1) skip its linearise stage.
  * Replaces: `self.embed_collection(id_list_features)` torchrec/models.py:164
  *   (EmbeddingCollection, upstream fbgemm TBE forward "nobag"), and the
  *   EmbeddingBagCollection the BASELINE configs name (TBE pooled forward);
@@ -162,6 +167,7 @@ int tdfo_embedding_forward(const void* weights, int32_t weights_dtype, int64_t t
                            int32_t F, int64_t B, int64_t L /* number of ids == offsets[F*B] */,
                            int32_t pooling_mode,
                            float* out, int64_t out_stride,
+                           uint32_t* sort_keys, uint32_t* sort_vals,
                            int32_t* err_flag, void* stream);
 
 /* ------------------------------------------------------------------ backward */
@@ -256,11 +262,15 @@ int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t total_rows,
  * at the offsets reported by tdfo_backward_scratch_layout, the sorted keys,
  * sorted vals, unique keys, segment starts and the unique count, so a caller
  * (or a parity test) can read them.
+ * keys_in_scratch != 0: the caller already had tdfo_embedding_forward write the
+ * linearised pairs for these same indices / offsets into the input_keys /
+ * input_vals slots of `scratch`; the linearise stage is skipped.
  * per_sample_weights must be NULL in this ABI version (weighted backward is
  * TDFO_ERR_UNSUPPORTED).
  * scratch: tdfo_backward_scratch_bytes(L, total_rows).
  */
 typedef struct tdfo_backward_layout {
+    size_t input_keys, input_vals;   /* where linearised pairs go in (clobbered by the sort) */
     size_t sorted_keys, sorted_vals, unique_keys, seg_starts, num_unique; /* byte offsets */
     size_t total_bytes;
     int32_t key_bits;
@@ -277,6 +287,7 @@ int tdfo_embedding_backward_update(void* weights, int32_t weights_dtype, int64_t
                                    const int64_t* feat_out_col,
                                    int32_t F, int64_t B, int64_t L, int32_t pooling_mode,
                                    const tdfo_optimizer_args* opt /* HOST */,
+                                   int32_t keys_in_scratch,
                                    int32_t* err_flag,
                                    void* scratch, size_t scratch_bytes, void* stream);
 

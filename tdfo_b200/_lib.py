@@ -25,7 +25,7 @@ class OptimizerArgs(Structure):
 
 
 class BackwardLayout(Structure):
-    _fields_ = [("sorted_keys", c_size_t), ("sorted_vals", c_size_t), ("unique_keys", c_size_t),
+    _fields_ = [("input_keys", c_size_t), ("input_vals", c_size_t), ("sorted_keys", c_size_t), ("sorted_vals", c_size_t), ("unique_keys", c_size_t),
                 ("seg_starts", c_size_t), ("num_unique", c_size_t), ("total_bytes", c_size_t),
                 ("key_bits", c_int32)]
 
@@ -41,7 +41,7 @@ _SIGNATURES = {
     "tdfo_kjt_bucketize_row_wise": (c_int, [P, P, P, P, P, c_int32, c_int64, c_int32, P, P, P, P, P, P, P, c_size_t, P]),
     "tdfo_kjt_permute_2d": (c_int, [P, c_int32, c_int32, c_int64, P, P, P, P, P, P, P, P, P, c_size_t, P]),
     "tdfo_embedding_forward": (c_int, [P, c_int32, c_int64, c_int32, P, P, P, P, P, P, c_int32, c_int64, c_int64,
-                                       c_int32, P, c_int64, P, P]),
+                                       c_int32, P, c_int64, P, P, P, P]),
     "tdfo_linearize_indices": (c_int, [P, P, P, P, c_int32, c_int64, c_int64, c_int32, P, P, P, P]),
     "tdfo_radix_sort_scratch_bytes": (c_size_t, [c_int64, c_int32]),
     "tdfo_radix_sort_pairs": (c_int, [P, P, P, P, c_int64, c_int32, P, P, c_size_t, P]),
@@ -51,8 +51,8 @@ _SIGNATURES = {
     "tdfo_backward_scratch_bytes": (c_size_t, [c_int64, c_int64]),
     "tdfo_backward_scratch_layout": (c_int, [c_int64, c_int64, POINTER(BackwardLayout)]),
     "tdfo_embedding_backward_update": (c_int, [P, c_int32, c_int64, c_int32, P, P, P, c_int64, P, P, P, P, P, P,
-                                               c_int32, c_int64, c_int64, c_int32, POINTER(OptimizerArgs), P, P,
-                                               c_size_t, P]),
+                                               c_int32, c_int64, c_int64, c_int32, POINTER(OptimizerArgs), c_int32,
+                                               P, P, c_size_t, P]),
     "tdfo_jagged_2d_to_dense": (c_int, [P, P, c_int64, c_int32, c_int64, P, P]),
     "tdfo_dense_to_jagged": (c_int, [P, P, c_int64, c_int32, c_int64, c_int64, P, P]),
     "tdfo_jagged_1d_to_padded_dense": (c_int, [P, P, c_int64, c_int64, c_int64, P, P]),

@@ -19,6 +19,8 @@ struct LookupArgs {
     const int64_t* feat_rows;
     const int64_t* feat_out_col;
     float* out;
+    uint32_t* sort_keys;   // optional: backward's (row key, payload) pairs, emitted while the ids are in registers
+    uint32_t* sort_vals;
     int32_t* err_flag;
     int64_t B;
     int64_t num_bags;     // F * B
@@ -27,6 +29,7 @@ struct LookupArgs {
     int32_t F;
     int32_t nchunks;      // 16-byte chunks per row
     int32_t mean;
+    uint32_t oob_key;     // key given to out-of-range ids (== total_rows)
 };
 
 constexpr int kFwdThreads = 256;
@@ -54,6 +57,10 @@ __device__ __forceinline__ BagHead load_bag_head(const LookupArgs& a, int64_t g,
         if ((uint64_t)idx < (uint64_t)__ldg(a.feat_rows + f)) h.row = (uint32_t)(__ldg(a.feat_row_base + f) + idx);
         else h.oob = true;
         if (a.psw) h.w = __ldg(a.psw + h.s + lane);
+        if (a.sort_keys) {
+            a.sort_keys[h.s + lane] = h.oob ? a.oob_key : h.row;
+            a.sort_vals[h.s + lane] = (uint32_t)g;
+        }
     }
     return h;
 }
@@ -148,6 +155,10 @@ pooled_forward_kernel(const LookupArgs a) {
                         my_row = (uint32_t)(__ldg(a.feat_row_base + f) + idx);
                     else oob = true;
                     if (WEIGHTED) my_w = __ldg(a.psw + base + lane);
+                    if (a.sort_keys) {
+                        a.sort_keys[base + lane] = (my_row == 0xffffffffu) ? a.oob_key : my_row;
+                        a.sort_vals[base + lane] = (uint32_t)g;
+                    }
                 }
             }
             // full batches of U rows per sub-group, then one shorter batch for the tail
@@ -225,6 +236,10 @@ sequence_forward_kernel(const LookupArgs a) {
         const bool valid = (uint64_t)idx < (uint64_t)__ldg(a.feat_rows + lo);
         if (!valid) oob = true;
         const size_t row = (size_t)(__ldg(a.feat_row_base + lo) + idx);
+        if (a.sort_keys && sub == 0) {
+            a.sort_keys[p] = valid ? (uint32_t)row : a.oob_key;
+            a.sort_vals[p] = (uint32_t)p;
+        }
         float* orow = a.out + (size_t)p * a.nchunks * E;
 #pragma unroll
         for (int k = 0; k < CPL; ++k) {
@@ -294,6 +309,7 @@ extern "C" int tdfo_embedding_forward(const void* weights, int32_t weights_dtype
                                       const int64_t* feat_row_base, const int64_t* feat_rows,
                                       const int64_t* feat_out_col, int32_t F, int64_t B, int64_t L,
                                       int32_t pooling_mode, float* out, int64_t out_stride,
+                                      uint32_t* sort_keys, uint32_t* sort_vals,
                                       int32_t* err_flag, void* stream) {
     TDFO_CHECK_ARG(weights_dtype == TDFO_F32 || weights_dtype == TDFO_BF16,
                    "embedding_forward: unknown weights_dtype %d", weights_dtype);
@@ -320,7 +336,11 @@ extern "C" int tdfo_embedding_forward(const void* weights, int32_t weights_dtype
     LookupArgs a;
     a.weights = weights; a.indices = indices; a.offsets = offsets; a.psw = per_sample_weights;
     a.feat_row_base = feat_row_base; a.feat_rows = feat_rows; a.feat_out_col = feat_out_col;
-    a.out = out; a.err_flag = err_flag; a.B = B; a.num_bags = (int64_t)F * B; a.L = L;
+    TDFO_CHECK_ARG((sort_keys == nullptr) == (sort_vals == nullptr),
+                   "embedding_forward: sort_keys and sort_vals must both be given or both be null");
+    TDFO_CHECK_ARG(sort_keys == nullptr || ((int64_t)F * B < (1ll << 32) && L < (1ll << 32)),
+                   "embedding_forward: sort keys need F*B and L below 2^32");
+    a.out = out; a.sort_keys = sort_keys; a.sort_vals = sort_vals; a.oob_key = (uint32_t)total_rows; a.err_flag = err_flag; a.B = B; a.num_bags = (int64_t)F * B; a.L = L;
     a.out_stride = out_stride; a.F = F; a.nchunks = (int32_t)(D * esz / 16);
     a.mean = pooling_mode == TDFO_POOL_MEAN;
     cudaStream_t st = static_cast<cudaStream_t>(stream);

@@ -11,7 +11,9 @@ namespace tdfo {
 constexpr int kSortThreads = 256;
 constexpr int kSortItems = 16;
 constexpr int kSortTile = kSortThreads * kSortItems;    // 4096 pairs per tile
-constexpr int kRadix = 256;                             // max bins per pass (<= 8 bits)
+constexpr int kRadixLog = 9;                            // up to 9 bits per pass
+constexpr int kRadix = 1 << kRadixLog;                  // bins per pass (lookback / histogram row stride)
+constexpr int kBinsPerThread = kRadix / kSortThreads;   // 2
 constexpr int kMaxPasses = 4;
 
 constexpr uint32_t kLbAgg  = 1u << 30;
@@ -28,7 +30,7 @@ struct SortPlan {
 
 static SortPlan make_sort_plan(int64_t n, int key_bits) {
     SortPlan p{};
-    p.passes = (key_bits + 7) / 8;
+    p.passes = (key_bits + kRadixLog - 1) / kRadixLog;
     const int per = (key_bits + p.passes - 1) / p.passes;
     int s = 0;
     for (int i = 0; i < p.passes; ++i) {
@@ -76,7 +78,7 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __re
                       const uint32_t* __restrict__ ghist,   // [kRadix] counts of this pass
                       uint32_t* lookback,                   // [tiles][kRadix], zeroed
                       unsigned int* ticket, int32_t* err_flag) {
-    __shared__ uint32_t s_warp_hist[kSortThreads / 32][kRadix];
+    __shared__ uint16_t s_warp_hist[kSortThreads / 32][kRadix];   // counts <= 4096 fit 16 bits
     __shared__ uint32_t s_keys[kSortTile];
     __shared__ uint32_t s_vals[kSortTile];
     __shared__ uint32_t s_tile_start[kRadix];   // first slot of digit d in the tile-sorted order
@@ -91,7 +93,8 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __re
     const int nbins = 1 << bits;
 
     if (tid == 0) s_tile = (int)atomicAdd(ticket, 1u);
-    for (int i = tid; i < (kSortThreads / 32) * kRadix; i += kSortThreads) (&s_warp_hist[0][0])[i] = 0;
+    for (int i = tid; i < (kSortThreads / 32) * kRadix / 2; i += kSortThreads)
+        reinterpret_cast<uint32_t*>(&s_warp_hist[0][0])[i] = 0;
     __syncthreads();
     const int tile = s_tile;
     const int64_t tile_base = (int64_t)tile * kSortTile;
@@ -122,7 +125,7 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __re
         uint32_t pre = 0;
         if (lane == leader && d < (uint32_t)kRadix) {
             pre = s_warp_hist[warp][d];
-            s_warp_hist[warp][d] = pre + __popc(peers);
+            s_warp_hist[warp][d] = (uint16_t)(pre + __popc(peers));
         }
         pre = __shfl_sync(kFullMask, pre, leader);
         rank[i] = (uint16_t)(pre + __popc(peers & lt_mask));
@@ -130,41 +133,58 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __re
     }
     __syncthreads();
 
-    // ---- per digit: prefix over warps, tile count, publish, look back
-    uint32_t tile_count = 0;
-    if (tid < nbins) {
+    // ---- per digit (kBinsPerThread digits per thread, digit = tid*kBinsPerThread + j so that a
+    // thread's digits are adjacent): prefix over warps, tile count, publish, look back
+    uint32_t tile_count[kBinsPerThread];
+    uint32_t pair_count = 0, gpair = 0;
+    uint32_t gcount[kBinsPerThread];
 #pragma unroll
-        for (int w = 0; w < kSortThreads / 32; ++w) {
-            const uint32_t c = s_warp_hist[w][tid];
-            s_warp_hist[w][tid] = tile_count;
-            tile_count += c;
+    for (int j = 0; j < kBinsPerThread; ++j) {
+        const int d = tid * kBinsPerThread + j;
+        tile_count[j] = 0;
+        gcount[j] = 0;
+        if (d < nbins) {
+#pragma unroll
+            for (int w = 0; w < kSortThreads / 32; ++w) {
+                const uint32_t c = s_warp_hist[w][d];
+                s_warp_hist[w][d] = (uint16_t)tile_count[j];
+                tile_count[j] += c;
+            }
+            st_relaxed_u32(lookback + (size_t)tile * kRadix + d, (tile == 0 ? kLbIncl : kLbAgg) | tile_count[j]);
+            gcount[j] = ghist[d];
         }
-        st_relaxed_u32(lookback + (size_t)tile * kRadix + tid, (tile == 0 ? kLbIncl : kLbAgg) | tile_count);
+        pair_count += tile_count[j];
+        gpair += gcount[j];
     }
     uint32_t total;
-    const uint32_t tile_start = block_exclusive_scan_256<uint32_t>(tile_count, s_scan, total);
-    const uint32_t gcount = (tid < nbins) ? ghist[tid] : 0u;
-    const uint32_t gstart = block_exclusive_scan_256<uint32_t>(gcount, s_scan, total);
-    if (tid < nbins) {
-        uint32_t excl = 0;
-        int spins = 0;
-        for (int t = tile - 1; t >= 0; --t) {
-            uint32_t w = ld_relaxed_u32(lookback + (size_t)t * kRadix + tid);
-            while ((w >> 30) == 0) {
-                if (++spins > kScanWatchdog) {
-                    if (err_flag) atomicOr(err_flag, TDFO_FLAG_SCAN_TIMEOUT);
-                    w = kLbIncl;
-                    break;
+    uint32_t tile_start = block_exclusive_scan_256<uint32_t>(pair_count, s_scan, total);
+    uint32_t gstart = block_exclusive_scan_256<uint32_t>(gpair, s_scan, total);
+#pragma unroll
+    for (int j = 0; j < kBinsPerThread; ++j) {
+        const int d = tid * kBinsPerThread + j;
+        if (d < nbins) {
+            uint32_t excl = 0;
+            int spins = 0;
+            for (int t = tile - 1; t >= 0; --t) {
+                uint32_t w = ld_relaxed_u32(lookback + (size_t)t * kRadix + d);
+                while ((w >> 30) == 0) {
+                    if (++spins > kScanWatchdog) {
+                        if (err_flag) atomicOr(err_flag, TDFO_FLAG_SCAN_TIMEOUT);
+                        w = kLbIncl;
+                        break;
+                    }
+                    w = ld_relaxed_u32(lookback + (size_t)t * kRadix + d);
                 }
-                w = ld_relaxed_u32(lookback + (size_t)t * kRadix + tid);
+                excl += w & kLbMask;
+                if ((w >> 30) == 2) break;
             }
-            excl += w & kLbMask;
-            if ((w >> 30) == 2) break;
+            if (tile > 0)
+                st_relaxed_u32(lookback + (size_t)tile * kRadix + d, kLbIncl | ((excl + tile_count[j]) & kLbMask));
+            s_tile_start[d] = tile_start;
+            s_out_base[d] = gstart + excl - tile_start;
         }
-        if (tile > 0)
-            st_relaxed_u32(lookback + (size_t)tile * kRadix + tid, kLbIncl | ((excl + tile_count) & kLbMask));
-        s_tile_start[tid] = tile_start;
-        s_out_base[tid] = gstart + excl - tile_start;
+        tile_start += tile_count[j];
+        gstart += gcount[j];
     }
     __syncthreads();
 
@@ -227,6 +247,8 @@ int radix_sort_impl(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int6
     *result_buf = p.passes & 1;
     return TDFO_OK;
 }
+
+int radix_sort_passes_impl(int key_bits) { return (key_bits + kRadixLog - 1) / kRadixLog; }
 
 size_t radix_sort_scratch_bytes_impl(int64_t n, int key_bits) {
     if (n <= 0) return 256;

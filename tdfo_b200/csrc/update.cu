@@ -6,12 +6,14 @@
 // L2 (sorted order walks the tables one after another, so the live gradient
 // slice is B*D*4 bytes per table, far below the 126 MB L2).
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace tdfo {
 
 int radix_sort_impl(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int64_t n, int key_bits,
                     int32_t* err_flag, void* scratch, cudaStream_t st, int* result_buf);
 size_t radix_sort_scratch_bytes_impl(int64_t n, int key_bits);
+int radix_sort_passes_impl(int key_bits);
 int unique_segments_impl(const uint32_t* sorted_keys, int64_t n, uint32_t* unique_keys,
                          uint32_t* seg_starts, uint32_t* num_unique, int32_t* err_flag,
                          void* scratch, cudaStream_t st);
@@ -105,8 +107,8 @@ __device__ __forceinline__ const float* grad_row_of(const UpdateArgs& a, uint32_
 // ahead), then the rows are processed UR at a time per LPR-lane group: weight row, first
 // gradient row and optimizer state are all requested before any of them is consumed, so
 // each warp keeps 2*UR (+state) independent 128-bit row requests in flight.
-template <typename T, int LPR, int CPL, int UR, int OPT>
-__global__ void __launch_bounds__(kUpdThreads, kUpdBlocksPerSM)
+template <typename T, int LPR, int CPL, int UR, int MINB, int OPT>
+__global__ void __launch_bounds__(kUpdThreads, MINB)
 sparse_update_kernel(const UpdateArgs a) {
     constexpr int E = Chunk<T>::kElems;
     constexpr int RPW = 32 / LPR;                  // rows processed in parallel by one warp
@@ -276,20 +278,20 @@ sparse_update_kernel(const UpdateArgs a) {
     }
 }
 
-template <typename T, int LPR, int CPL, int UR>
+template <typename T, int LPR, int CPL, int UR, int MINB = 2>
 static int launch_update(const UpdateArgs& a, int opt, int64_t max_unique, cudaStream_t st) {
     const int64_t tiles = (max_unique + 31) / 32;                 // one warp per tile of 32 unique rows
     int64_t blocks = (tiles + kUpdThreads / 32 - 1) / (kUpdThreads / 32);
-    const int64_t cap = (int64_t)kNumSMs * kUpdBlocksPerSM;
+    const int64_t cap = (int64_t)kNumSMs * MINB;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     switch (opt) {
         case TDFO_OPT_SGD:
-            sparse_update_kernel<T, LPR, CPL, UR, TDFO_OPT_SGD><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
+            sparse_update_kernel<T, LPR, CPL, UR, MINB, TDFO_OPT_SGD><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
         case TDFO_OPT_ROWWISE_ADAGRAD:
-            sparse_update_kernel<T, LPR, CPL, UR, TDFO_OPT_ROWWISE_ADAGRAD><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
+            sparse_update_kernel<T, LPR, CPL, UR, MINB, TDFO_OPT_ROWWISE_ADAGRAD><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
         default:
-            sparse_update_kernel<T, LPR, CPL, UR, TDFO_OPT_ADAM><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
+            sparse_update_kernel<T, LPR, CPL, UR, MINB, TDFO_OPT_ADAM><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
     }
     count_launch();
     TDFO_LAUNCH_CHECK("sparse_update");
@@ -310,7 +312,19 @@ static int dispatch_update(const UpdateArgs& a, int opt, int64_t max_unique, cud
         if (n <= 4)   return launch_update<T, 1, 4, 1>(a, opt, max_unique, st);
         if (n <= 8)   return launch_update<T, 2, 4, 2>(a, opt, max_unique, st);
         if (n <= 16)  return launch_update<T, 4, 4, 2>(a, opt, max_unique, st);
-        if (n <= 32)  return launch_update<T, 8, 4, 2>(a, opt, max_unique, st);
+        if (n <= 32) {
+            const char* v = getenv("TDFO_UPD_VARIANT");          // TUNING ONLY
+            const int vi = v ? atoi(v) : 0;
+            if (vi == 1) return launch_update<T, 8, 4, 1, 3>(a, opt, max_unique, st);
+            if (vi == 2) return launch_update<T, 8, 4, 1, 4>(a, opt, max_unique, st);
+            if (vi == 3) return launch_update<T, 16, 2, 2, 3>(a, opt, max_unique, st);
+            if (vi == 4) return launch_update<T, 16, 2, 1, 4>(a, opt, max_unique, st);
+            if (vi == 5) return launch_update<T, 16, 2, 1, 5>(a, opt, max_unique, st);
+            if (vi == 6) return launch_update<T, 8, 4, 2, 3>(a, opt, max_unique, st);
+            if (vi == 7) return launch_update<T, 32, 1, 2, 4>(a, opt, max_unique, st);
+            if (vi == 8) return launch_update<T, 32, 1, 4, 3>(a, opt, max_unique, st);
+            return launch_update<T, 8, 4, 1, 3>(a, opt, max_unique, st);
+        }
         if (n <= 64)  return launch_update<T, 16, 4, 2>(a, opt, max_unique, st);
         if (n <= 128) return launch_update<T, 32, 4, 1>(a, opt, max_unique, st);
         if (n <= 256) return launch_update<T, 32, 8, 1>(a, opt, max_unique, st);
@@ -456,13 +470,15 @@ extern "C" int tdfo_backward_scratch_layout(int64_t L, int64_t total_rows, tdfo_
     TDFO_CHECK_ARG(total_rows >= 0 && total_rows < 0xffffffffll, "backward_scratch_layout: total_rows must be < 2^32-1");
     const int bits = key_bits_for(total_rows);
     const size_t A = pair_array_bytes(L);
-    const int passes = (bits + 7) / 8;
+    const int passes = radix_sort_passes_impl(bits);
     const int res = passes & 1;               // buffer pair the sorted result lands in
     layout->key_bits = bits;
     layout->sorted_keys = (res ? 2 : 0) * A;
     layout->sorted_vals = (res ? 3 : 1) * A;
     layout->unique_keys = (res ? 0 : 2) * A;  // the other pair is free after the sort
     layout->seg_starts  = (res ? 1 : 3) * A;
+    layout->input_keys = 0;
+    layout->input_vals = A;
     layout->num_unique = 4 * A;
     const size_t sort_off = 4 * A + 256;
     const size_t scan_off = sort_off + radix_sort_scratch_bytes_impl(L, bits);
@@ -484,7 +500,8 @@ extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dty
                                               const int64_t* feat_row_base, const int64_t* feat_rows,
                                               const int64_t* feat_out_col, int32_t F, int64_t B,
                                               int64_t L, int32_t pooling_mode,
-                                              const tdfo_optimizer_args* opt, int32_t* err_flag,
+                                              const tdfo_optimizer_args* opt, int32_t keys_in_scratch,
+                                              int32_t* err_flag,
                                               void* scratch, size_t scratch_bytes, void* stream) {
     int rc = check_common("embedding_backward_update", weights_dtype, total_rows, D);
     if (rc) return rc;
@@ -523,9 +540,11 @@ extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dty
     void* sort_scratch = base + 4 * A + 256;
     void* scan_scratch = base + 4 * A + 256 + radix_sort_scratch_bytes_impl(L, lay.key_bits);
 
-    rc = tdfo_linearize_indices(indices, offsets, feat_row_base, feat_rows, F, B, total_rows, pooling_mode,
-                                k0, v0, err_flag, stream);
-    if (rc) return rc;
+    if (!keys_in_scratch) {
+        rc = tdfo_linearize_indices(indices, offsets, feat_row_base, feat_rows, F, B, total_rows, pooling_mode,
+                                    k0, v0, err_flag, stream);
+        if (rc) return rc;
+    }
     int where = 0;
     rc = radix_sort_impl(k0, v0, k1, v1, L, lay.key_bits, err_flag, sort_scratch, st, &where);
     if (rc) return rc;

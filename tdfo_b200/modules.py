@@ -88,12 +88,14 @@ class _LookupFn(torch.autograd.Function):
     def forward(ctx, anchor, module, values, offsets, B, psw):
         ctx.module, ctx.B = module, B
         ctx.save_for_backward(values, offsets)
-        return module._forward_impl(values, offsets, B, psw)
+        out = module._forward_impl(values, offsets, B, psw, emit_keys=True)
+        ctx.keys_token = module._keys_token
+        return out
 
     @staticmethod
     def backward(ctx, grad_out):
         values, offsets = ctx.saved_tensors
-        ctx.module._backward_impl(grad_out.contiguous(), values, offsets, ctx.B)
+        ctx.module._backward_impl(grad_out.contiguous(), values, offsets, ctx.B, ctx.keys_token)
         return None, None, None, None, None, None
 
 
@@ -165,6 +167,10 @@ class _FusedEmbeddingBase(nn.Module):
         self.register_buffer("_err_flag", torch.zeros(1, dtype=torch.int32, device=device), persistent=False)
         self._anchor: Optional[torch.Tensor] = None
         self._fused: Optional[FusedOptimizer] = None
+        # Backward workspace.  In training the forward kernel already writes the (row, bag) pairs the
+        # backward sorts into it; `_keys_token` says which forward call they belong to.
+        self._bw_scratch: Optional[torch.Tensor] = None
+        self._keys_token = 0
         self.set_fused_optimizer(EmbOptimType.EXACT_SGD, learning_rate=0.01)
 
     # ------------------------------------------------------------------ optimizer
@@ -210,19 +216,31 @@ class _FusedEmbeddingBase(nn.Module):
             state0=s0, state1=s1, err_flag=self._err_flag)
 
     # ------------------------------------------------------------------ compute
-    def _forward_impl(self, values, offsets, B, psw):
+    def _scratch_for(self, L: int, total_rows: int, device) -> torch.Tensor:
+        need = ops.backward_layout(L, total_rows).total_bytes
+        if self._bw_scratch is None or self._bw_scratch.numel() < need or self._bw_scratch.device != device:
+            self._bw_scratch = torch.empty(int(need * 1.1) + 256, dtype=torch.uint8, device=device)
+        return self._bw_scratch
+
+    def _forward_impl(self, values, offsets, B, psw, emit_keys: bool = False):
         dev = values.device
+        scratch = None
+        if emit_keys and len(self._groups) == 1 and values.numel() > 0:
+            scratch = self._scratch_for(values.numel(), self._groups[0].total_rows, dev)
+            self._keys_token += 1
         if self._sequence:
             g = self._groups[0]
-            return ops.embedding_forward(self._table_group(g, False), values, offsets, B, _lib.POOL_NONE)
+            return ops.embedding_forward(self._table_group(g, False), values, offsets, B, _lib.POOL_NONE,
+                                         backward_scratch=scratch)
         out = torch.empty((B, self._total_D), dtype=torch.float32, device=dev)
         for g in self._groups:
             F = len(g.features)
             off = offsets[g.f0 * B:(g.f0 + F) * B + 1]
-            ops.embedding_forward(self._table_group(g, False), values, off, B, g.pooling, psw, out=out)
+            ops.embedding_forward(self._table_group(g, False), values, off, B, g.pooling, psw, out=out,
+                                  backward_scratch=scratch)
         return out
 
-    def _backward_impl(self, grad_out, values, offsets, B):
+    def _backward_impl(self, grad_out, values, offsets, B, keys_token: int = -1):
         self._fused.iteration += 1
         opt = self._fused.args()
         for g in self._groups:
@@ -231,7 +249,12 @@ class _FusedEmbeddingBase(nn.Module):
             # group-local ids only: the kernels index `values` by absolute offsets, and
             # L bounds the sort, so pass the slice this group's offsets cover
             if len(self._groups) == 1:
-                ops.embedding_backward_update(self._table_group(g, True), grad_out, values, off, B, g.pooling, opt)
+                scratch = self._scratch_for(values.numel(), g.total_rows, values.device)
+                # the pairs in `scratch` are still this call's unless another forward ran in between
+                fused = keys_token == self._keys_token and values.numel() > 0
+                ops.embedding_backward_update(self._table_group(g, True), grad_out, values, off, B, g.pooling, opt,
+                                              scratch=scratch, keys_in_scratch=fused)
+                self._keys_token += 1          # the sort consumed them
             else:
                 lo, hi = self._group_bounds(offsets, g, B)
                 ops.embedding_backward_update(self._table_group(g, True), grad_out, values[lo:hi], off - lo, B,

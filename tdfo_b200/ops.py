@@ -176,7 +176,11 @@ def permute_2d(permute, B, in_lengths, in_offsets, in_indices, in_weights=None, 
 # --------------------------------------------------------------------------- lookup
 def embedding_forward(group: TableGroup, indices: torch.Tensor, offsets: torch.Tensor, B: int, pooling_mode: int,
                       per_sample_weights: Optional[torch.Tensor] = None,
-                      out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                      out: Optional[torch.Tensor] = None,
+                      backward_scratch: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``backward_scratch``: a buffer of ``backward_layout(L, rows).total_bytes`` bytes; when given, the
+    kernel also writes the linearised (row key, payload) pairs the backward sorts into it, so
+    ``embedding_backward_update(..., keys_in_scratch=True)`` can skip its linearise stage."""
     indices = _cuda(indices, torch.int64, "indices")
     offsets = _cuda(offsets, torch.int64, "offsets")
     if per_sample_weights is not None:
@@ -192,10 +196,17 @@ def embedding_forward(group: TableGroup, indices: torch.Tensor, offsets: torch.T
             out = torch.empty((L, group.D), dtype=torch.float32, device=w.device)
         else:
             out = torch.empty((B, group.out_stride), dtype=torch.float32, device=w.device)
+    sk = sv = None
+    if backward_scratch is not None and L > 0:
+        lay = backward_layout(L, group.total_rows)
+        if backward_scratch.numel() < lay.total_bytes:
+            raise ValueError(f"backward_scratch has {backward_scratch.numel()} bytes, needs {lay.total_bytes}")
+        sk = ctypes.c_void_p(backward_scratch.data_ptr() + lay.input_keys)
+        sv = ctypes.c_void_p(backward_scratch.data_ptr() + lay.input_vals)
     check(_lib.load().tdfo_embedding_forward(
         _ptr(w), _wdtype(w), group.total_rows, group.D, _ptr(indices), _ptr(offsets), _ptr(per_sample_weights),
         _ptr(group.feat_row_base), _ptr(group.feat_rows), _ptr(group.feat_out_col), group.F, B, L, pooling_mode,
-        _ptr(out), group.out_stride, _ptr(group.err_flag), _stream()))
+        _ptr(out), group.out_stride, sk, sv, _ptr(group.err_flag), _stream()))
     return out
 
 
@@ -213,7 +224,7 @@ def backward_layout(L: int, total_rows: int) -> BackwardLayout:
 
 def embedding_backward_update(group: TableGroup, grad_out: torch.Tensor, indices: torch.Tensor,
                               offsets: torch.Tensor, B: int, pooling_mode: int, opt: OptimizerArgs,
-                              scratch: Optional[torch.Tensor] = None) -> torch.Tensor:
+                              scratch: Optional[torch.Tensor] = None, keys_in_scratch: bool = False) -> torch.Tensor:
     """Fused backward + optimizer, in place on ``group.weights`` / state.  Returns the scratch buffer
     (sorted keys / unique rows are readable at ``backward_layout`` offsets)."""
     indices = _cuda(indices, torch.int64, "indices")
@@ -230,7 +241,8 @@ def embedding_backward_update(group: TableGroup, grad_out: torch.Tensor, indices
         _ptr(w), _wdtype(w), group.total_rows, group.D, _ptr(group.state0), _ptr(group.state1),
         _ptr(grad_out), grad_stride, _ptr(indices), _ptr(offsets), None,
         _ptr(group.feat_row_base), _ptr(group.feat_rows), _ptr(group.feat_out_col), group.F, B, L, pooling_mode,
-        ctypes.byref(opt), _ptr(group.err_flag), _ptr(scratch), scratch.numel(), _stream()))
+        ctypes.byref(opt), 1 if keys_in_scratch else 0, _ptr(group.err_flag), _ptr(scratch), scratch.numel(),
+        _stream()))
     return scratch
 
 

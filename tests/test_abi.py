@@ -57,7 +57,8 @@ def test_host_only_helpers(lib):
 
 def test_argument_errors_without_touching_the_gpu(lib):
     # rejected by host-side validation before any CUDA call
-    rc = lib.tdfo_embedding_forward(None, 7, 10, 128, None, None, None, None, None, None, 1, 1, 0, 0, None, 128, None, None)
+    rc = lib.tdfo_embedding_forward(None, 7, 10, 128, None, None, None, None, None, None, 1, 1, 0, 0, None, 128, None, None,
+                                    None, None)
     assert rc == -1 and b"weights_dtype" in lib.tdfo_last_error()
     rc = lib.tdfo_radix_sort_pairs(None, None, None, None, 10, 40, None, None, 0, None)
     assert rc == -1 and b"key_bits" in lib.tdfo_last_error()

@@ -385,3 +385,28 @@ def test_c_abi_rejects_bad_arguments(ops):
         ops.embedding_forward(group_for(ops, c, dev(c.weights)), dev(c.indices), dev(c.offsets), c.B, orc.POOL_SUM)
     with pytest.raises(RuntimeError, match="no CPU path"):
         ops.complete_cumsum(torch.zeros(4, dtype=torch.int32))
+
+
+def test_forward_emits_the_backward_pairs(ops):
+    """tdfo_embedding_forward(sort_keys, sort_vals) == tdfo_linearize_indices, and the fused
+    backward that consumes them matches the unfused one bit for bit."""
+    for mode in (orc.POOL_SUM, orc.POOL_NONE):
+        c = make_case(seed=31 + mode, F=4, B=50, D=32, rows=[64, 9, 500, 33], max_len=45, long_bag=90)
+        idx = c.indices.copy()
+        idx[7] = 10 ** 9                                      # out of range
+        pooled = mode != orc.POOL_NONE
+        wk, wv, _ = orc.linearize_indices(idx, c.offsets, c.row_base, c.rows, c.F, c.B, c.total_rows, mode)
+        grp = group_for(ops, c, dev(c.weights), pooled=pooled)
+        lay = ops.backward_layout(c.L, c.total_rows)
+        scratch = torch.zeros(lay.total_bytes, dtype=torch.uint8, device="cuda")
+        ops.embedding_forward(grp, dev(idx), dev(c.offsets), c.B, mode, backward_scratch=scratch)
+        raw = scratch.cpu().numpy()
+        np.testing.assert_array_equal(raw[lay.input_keys: lay.input_keys + 4 * c.L].view(np.uint32), wk)
+        np.testing.assert_array_equal(raw[lay.input_vals: lay.input_vals + 4 * c.L].view(np.uint32), wv)
+        grad = np.random.default_rng(0).normal(size=(c.B, c.F * c.D) if pooled else (c.L, c.D)).astype(np.float32)
+        opt = ops.make_optimizer_args(orc.OPT_SGD, 0.1)
+        ops.embedding_backward_update(grp, dev(grad), dev(idx), dev(c.offsets), c.B, mode, opt, scratch=scratch,
+                                      keys_in_scratch=True)
+        grp2 = group_for(ops, c, dev(c.weights), pooled=pooled)
+        ops.embedding_backward_update(grp2, dev(grad), dev(idx), dev(c.offsets), c.B, mode, opt)
+        assert torch.equal(grp.weights, grp2.weights)

@@ -34,9 +34,9 @@ int main(int argc, char** argv) {
         float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= 10;
         printf("%-44s %8.3f ms  %7.1f GB/s\n", name, ms, bytes / ms / 1e6);
     };
-    timeit("lib forward, out [B, F*D]", [&] { TK(tdfo_embedding_forward(w, TDFO_F32, rows, 128, idx, off, nullptr, base, frows, col, F, B, L, TDFO_POOL_SUM, out, F * 128, flag, nullptr)); });
+    timeit("lib forward, out [B, F*D]", [&] { TK(tdfo_embedding_forward(w, TDFO_F32, rows, 128, idx, off, nullptr, base, frows, col, F, B, L, TDFO_POOL_SUM, out, F * 128, nullptr, nullptr, flag, nullptr)); });
     // same work as ONE feature over F*B bags: contiguous output rows, no per-feature division effects
     { int64_t one_rows = rows; int64_t zero = 0; CK(cudaMemcpy(frows, &one_rows, 8, cudaMemcpyHostToDevice)); CK(cudaMemcpy(col, &zero, 8, cudaMemcpyHostToDevice)); }
-    timeit("lib forward, 1 feature, out [F*B, D]", [&] { TK(tdfo_embedding_forward(w, TDFO_F32, rows, 128, idx, off, nullptr, base, frows, col, 1, bags, L, TDFO_POOL_SUM, out, 128, flag, nullptr)); });
+    timeit("lib forward, 1 feature, out [F*B, D]", [&] { TK(tdfo_embedding_forward(w, TDFO_F32, rows, 128, idx, off, nullptr, base, frows, col, 1, bags, L, TDFO_POOL_SUM, out, 128, nullptr, nullptr, flag, nullptr)); });
     return 0;
 }
