@@ -240,9 +240,9 @@ def run_ours(args):
         ev[2].record()
         sk, sv = ops.radix_sort_pairs(k, v, lay.key_bits, grp.err_flag)
         ev[3].record()
-        uk, ss, nu = ops.unique_segments(sk, grp.err_flag)
+        uk, ss, nu, fv = ops.unique_segments(sk, grp.err_flag, sv)
         ev[4].record()
-        ops.sparse_update(grp, grad_out, sv, uk, ss, nu, offsets, B, L, _lib.POOL_SUM, opt)
+        ops.sparse_update(grp, grad_out, sv, uk, ss, fv, nu, offsets, B, L, _lib.POOL_SUM, opt)
         ev[5].record()
 
     # ---------------- device-resident arm (`value`): the single-call product path

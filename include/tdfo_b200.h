@@ -208,12 +208,16 @@ int tdfo_radix_sort_pairs(uint32_t* keys_in, uint32_t* vals_in,
  *   unique_keys uint32[n]     (first *num_unique entries valid)
  *   seg_starts  uint32[n + 1] (seg_starts[u] = first sorted position of
  *                              unique row u; seg_starts[*num_unique] = n)
+ *   first_vals  uint32[n]     optional (needs sorted_vals): payload of the first occurrence
+ *                             of unique row u, i.e. sorted_vals[seg_starts[u]] -- lets the
+ *                             update kernel find a row's first gradient without a dependent load
  *   num_unique  uint32[1]     device scalar
  * Replaces: cub::DeviceRunLengthEncode in the upstream TBE backward.
  * scratch: tdfo_scan_scratch_bytes(n).
  */
-int tdfo_unique_segments(const uint32_t* sorted_keys, int64_t n,
-                         uint32_t* unique_keys, uint32_t* seg_starts, uint32_t* num_unique,
+int tdfo_unique_segments(const uint32_t* sorted_keys, const uint32_t* sorted_vals, int64_t n,
+                         uint32_t* unique_keys, uint32_t* seg_starts, uint32_t* first_vals,
+                         uint32_t* num_unique,
                          int32_t* err_flag,
                          void* scratch, size_t scratch_bytes, void* stream);
 
@@ -250,7 +254,7 @@ int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t total_rows,
                        const float* grad_out, int64_t grad_stride,
                        const uint32_t* sorted_vals,
                        const uint32_t* unique_keys, const uint32_t* seg_starts,
-                       const uint32_t* num_unique,
+                       const uint32_t* first_vals, const uint32_t* num_unique,
                        const int64_t* offsets, const int64_t* feat_out_col,
                        int32_t F, int64_t B, int64_t L, int32_t pooling_mode,
                        const tdfo_optimizer_args* opt /* HOST */,
@@ -271,7 +275,7 @@ int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t total_rows,
  */
 typedef struct tdfo_backward_layout {
     size_t input_keys, input_vals;   /* where linearised pairs go in (clobbered by the sort) */
-    size_t sorted_keys, sorted_vals, unique_keys, seg_starts, num_unique; /* byte offsets */
+    size_t sorted_keys, sorted_vals, unique_keys, seg_starts, first_vals, num_unique; /* byte offsets */
     size_t total_bytes;
     int32_t key_bits;
 } tdfo_backward_layout;

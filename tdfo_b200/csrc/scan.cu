@@ -48,9 +48,9 @@ complete_cumsum_kernel(const int32_t* __restrict__ lengths, int64_t n, int64_t* 
 
 // ---------------------------------------------------------------- unique / RLE
 __global__ void __launch_bounds__(kScanThreads)
-unique_segments_kernel(const uint32_t* __restrict__ keys, int64_t n,
+unique_segments_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t n,
                        uint32_t* __restrict__ unique_keys, uint32_t* __restrict__ seg_starts,
-                       uint32_t* __restrict__ num_unique, ScanScratch* hdr, uint64_t* status,
+                       uint32_t* __restrict__ first_vals, uint32_t* __restrict__ num_unique, ScanScratch* hdr, uint64_t* status,
                        int32_t* err_flag) {
     __shared__ uint32_t warp_totals[8];
     __shared__ uint32_t s_last[kScanThreads];
@@ -89,6 +89,7 @@ unique_segments_kernel(const uint32_t* __restrict__ keys, int64_t n,
         if (heads & (1u << i)) {
             unique_keys[pos] = k[i];
             seg_starts[pos] = (uint32_t)(base + i);
+            if (first_vals) first_vals[pos] = vals[base + i];
             ++pos;
         }
     }
@@ -129,9 +130,9 @@ int complete_cumsum_impl(const int32_t* lengths, int64_t n, int64_t* offsets, vo
     return TDFO_OK;
 }
 
-int unique_segments_impl(const uint32_t* sorted_keys, int64_t n, uint32_t* unique_keys,
-                         uint32_t* seg_starts, uint32_t* num_unique, int32_t* err_flag,
-                         void* scratch, cudaStream_t st) {
+int unique_segments_impl(const uint32_t* sorted_keys, const uint32_t* sorted_vals, int64_t n,
+                         uint32_t* unique_keys, uint32_t* seg_starts, uint32_t* first_vals,
+                         uint32_t* num_unique, int32_t* err_flag, void* scratch, cudaStream_t st) {
     if (n == 0) {
         TDFO_CUDA(cudaMemsetAsync(num_unique, 0, sizeof(uint32_t), st));
         TDFO_CUDA(cudaMemsetAsync(seg_starts, 0, sizeof(uint32_t), st));
@@ -142,7 +143,7 @@ int unique_segments_impl(const uint32_t* sorted_keys, int64_t n, uint32_t* uniqu
     auto* hdr = static_cast<ScanScratch*>(scratch);
     auto* status = reinterpret_cast<uint64_t*>(static_cast<char*>(scratch) + sizeof(ScanScratch));
     unique_segments_kernel<<<(unsigned)scan_tiles(n), kScanThreads, 0, st>>>(
-        sorted_keys, n, unique_keys, seg_starts, num_unique, hdr, status, err_flag);
+        sorted_keys, sorted_vals, n, unique_keys, seg_starts, first_vals, num_unique, hdr, status, err_flag);
     count_launch();
     TDFO_LAUNCH_CHECK("unique_segments");
     return TDFO_OK;
@@ -168,16 +169,19 @@ extern "C" int tdfo_kjt_complete_cumsum(const int32_t* lengths, int64_t n, int64
     return complete_cumsum_impl(lengths, n, offsets, scratch, static_cast<cudaStream_t>(stream));
 }
 
-extern "C" int tdfo_unique_segments(const uint32_t* sorted_keys, int64_t n, uint32_t* unique_keys,
-                                    uint32_t* seg_starts, uint32_t* num_unique, int32_t* err_flag,
+extern "C" int tdfo_unique_segments(const uint32_t* sorted_keys, const uint32_t* sorted_vals, int64_t n,
+                                    uint32_t* unique_keys, uint32_t* seg_starts, uint32_t* first_vals,
+                                    uint32_t* num_unique, int32_t* err_flag,
                                     void* scratch, size_t scratch_bytes, void* stream) {
     TDFO_CHECK_ARG(n >= 0 && n < (1ll << 32) - 1, "unique_segments: n out of range");
     TDFO_CHECK_ARG(seg_starts && num_unique && (n == 0 || (sorted_keys && unique_keys)),
                    "unique_segments: null pointer");
+    TDFO_CHECK_ARG(first_vals == nullptr || sorted_vals != nullptr || n == 0,
+                   "unique_segments: first_vals needs sorted_vals");
     if (n > 0) {
         const int rc = check_scan_scratch("unique_segments", n, scratch, scratch_bytes);
         if (rc) return rc;
     }
-    return unique_segments_impl(sorted_keys, n, unique_keys, seg_starts, num_unique, err_flag, scratch,
-                                static_cast<cudaStream_t>(stream));
+    return unique_segments_impl(sorted_keys, sorted_vals, n, unique_keys, seg_starts, first_vals, num_unique,
+                                err_flag, scratch, static_cast<cudaStream_t>(stream));
 }

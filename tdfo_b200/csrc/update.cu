@@ -6,7 +6,6 @@
 // L2 (sorted order walks the tables one after another, so the live gradient
 // slice is B*D*4 bytes per table, far below the 126 MB L2).
 #include "common.cuh"
-#include <stdlib.h>
 
 namespace tdfo {
 
@@ -14,11 +13,11 @@ int radix_sort_impl(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int6
                     int32_t* err_flag, void* scratch, cudaStream_t st, int* result_buf);
 size_t radix_sort_scratch_bytes_impl(int64_t n, int key_bits);
 int radix_sort_passes_impl(int key_bits);
-int unique_segments_impl(const uint32_t* sorted_keys, int64_t n, uint32_t* unique_keys,
-                         uint32_t* seg_starts, uint32_t* num_unique, int32_t* err_flag,
-                         void* scratch, cudaStream_t st);
+int unique_segments_impl(const uint32_t* sorted_keys, const uint32_t* sorted_vals, int64_t n,
+                         uint32_t* unique_keys, uint32_t* seg_starts, uint32_t* first_vals,
+                         uint32_t* num_unique, int32_t* err_flag, void* scratch, cudaStream_t st);
 
-constexpr int kUpdThreads = 256;
+constexpr int kUpdThreads = 256;    // linearise kernel
 
 // ---------------------------------------------------------------- linearise
 __global__ void __launch_bounds__(kUpdThreads)
@@ -54,6 +53,7 @@ struct UpdateArgs {
     const uint32_t* sorted_vals;
     const uint32_t* unique_keys;
     const uint32_t* seg_starts;
+    const uint32_t* first_vals;
     const uint32_t* num_unique;
     const int64_t* offsets;
     const int64_t* feat_out_col;
@@ -69,29 +69,29 @@ struct UpdateArgs {
     float inv_D;
 };
 
-constexpr int kUpdBlocksPerSM = 2;     // persistent grid: 148 x 2 CTAs of 8 warps (<= 128 registers)
+// Launch shape of the update kernel: 8 warps per CTA, persistent grid of 148 x MINB CTAs.
+constexpr int kUpdCtaThreads = 256;
 
-// Metadata of a tile of 32 consecutive unique rows, one row per lane.
-struct TileMeta {
-    uint32_t key, s, e;
+// Per unique row: key, first / one-past-last sorted position, payload of the first occurrence.
+struct RowMeta {
+    uint32_t key, s, e, v0;
 };
 
-__device__ __forceinline__ TileMeta load_tile_meta(const UpdateArgs& a, uint32_t tile, uint32_t nu, int lane) {
-    TileMeta m;
-    const uint32_t u = tile * 32u + (uint32_t)lane;
+__device__ __forceinline__ RowMeta load_row_meta(const UpdateArgs& a, uint32_t u, uint32_t nu) {
+    RowMeta m;
     if (u < nu) {
         m.key = __ldg(a.unique_keys + u);
         m.s = __ldg(a.seg_starts + u);
         m.e = __ldg(a.seg_starts + u + 1);
+        m.v0 = __ldg(a.first_vals + u);
     } else {
         m.key = 0xffffffffu;
-        m.s = m.e = a.L;
+        m.s = m.e = m.v0 = 0u;
     }
     return m;
 }
 
 // Gradient row of one occurrence (payload v) and its scale.
-template <int POOL_RUNTIME = 0>
 __device__ __forceinline__ const float* grad_row_of(const UpdateArgs& a, uint32_t v, float& scale) {
     scale = 1.f;
     if (a.pooling_mode == TDFO_POOL_NONE) return a.grad + (size_t)v * a.D;
@@ -102,18 +102,26 @@ __device__ __forceinline__ const float* grad_row_of(const UpdateArgs& a, uint32_
     return a.grad + (size_t)b * a.grad_stride + __ldg(a.feat_out_col + f);
 }
 
-// Persistent warps over tiles of 32 unique rows.  Per tile the row keys, segment bounds and
-// the first 32 payloads are fetched with three coalesced loads (prefetched one / two tiles
-// ahead), then the rows are processed UR at a time per LPR-lane group: weight row, first
-// gradient row and optimizer state are all requested before any of them is consumed, so
-// each warp keeps 2*UR (+state) independent 128-bit row requests in flight.
-template <typename T, int LPR, int CPL, int UR, int MINB, int OPT>
-__global__ void __launch_bounds__(kUpdThreads, MINB)
+// Persistent warps; a warp works on RPW*UR consecutive unique rows per step, one row per
+// LPR-lane group and unroll slot.  Under load a B200 memory round trip takes ~3 us, so the
+// kernel is built to keep as many independent 128-bit row requests in flight per SM as the
+// register file allows (tools/rmw2_micro.cu: 32 warps x 4 rows x (weight + gradient) reach
+// 5.6 TB/s of row read+write traffic, 93 % of the pure read-modify-write ceiling):
+//   * the four metadata words of the NEXT step's rows are requested before this step's rows
+//     are consumed (the unique pass also emits each row's first payload, so finding the first
+//     gradient row needs no dependent load);
+//   * per step every lane requests its chunks of the weight row, of the first gradient row and
+//     the row state before consuming any of them; all of these loads are unconditional (rows
+//     that do not exist are redirected to row 0 and masked) so ptxas issues them back to back;
+//   * few lanes per row (LPR 8 x 4 chunks for a 512 B row): per-row bookkeeping is replicated
+//     in every lane of a group, so narrow groups spend a quarter of the issue slots per row.
+template <typename T, int LPR, int CPL, int UR, int MINB, int OPT, bool PREFETCH = true>
+__global__ void __launch_bounds__(kUpdCtaThreads, MINB)
 sparse_update_kernel(const UpdateArgs a) {
     constexpr int E = Chunk<T>::kElems;
     constexpr int RPW = 32 / LPR;                  // rows processed in parallel by one warp
-    static_assert(RPW * UR <= 32, "a step may not cover more than the 32 rows of a tile");
-    constexpr int GQ = E / 4;                      // 16-byte gradient loads per table chunk
+    constexpr int STEP = RPW * UR;                 // rows per warp step
+    constexpr int GQ = E / 4;                      // 16-byte gradient pieces per table chunk
     const int lane = lane_id();
     const int sub = lane % LPR;
     const int grp = lane / LPR;
@@ -121,223 +129,200 @@ sparse_update_kernel(const UpdateArgs a) {
     // shuffles name only the lanes of their own group.
     const unsigned gmask = (LPR == 32) ? kFullMask : (((1u << (LPR & 31)) - 1u) << (grp * LPR));
     const uint32_t nu = *a.num_unique;
-    const uint32_t ntiles = (nu + 31u) / 32u;
-    const uint32_t nwarps = gridDim.x * (kUpdThreads / 32);
-    uint32_t tile = blockIdx.x * (kUpdThreads / 32) + (threadIdx.x >> 5);
-    if (tile >= ntiles) return;
+    const uint32_t stride = gridDim.x * (kUpdCtaThreads / 32) * STEP;
+    uint32_t u0 = (blockIdx.x * (kUpdCtaThreads / 32) + (threadIdx.x >> 5)) * STEP;
+    if (u0 >= nu) return;
     uint4* __restrict__ wbase = reinterpret_cast<uint4*>(a.weights);
 
-    TileMeta cur = load_tile_meta(a, tile, nu, lane);
-    TileMeta nxt = load_tile_meta(a, tile + nwarps, nu, lane);     // past-the-end tiles come back empty
-    uint32_t cur_s0 = __shfl_sync(kFullMask, cur.s, 0);
-    uint32_t cur_val = (cur_s0 + lane < __shfl_sync(kFullMask, cur.e, 31)) ? __ldg(a.sorted_vals + cur_s0 + lane) : 0u;
+    RowMeta cur[UR];
+#pragma unroll
+    for (int q = 0; q < UR; ++q) cur[q] = load_row_meta(a, u0 + q * RPW + grp, nu);
 
-    while (tile < ntiles) {
-        // prefetch: metadata two tiles ahead, payloads one tile ahead
-        const TileMeta nn = load_tile_meta(a, tile + 2u * nwarps, nu, lane);
-        const uint32_t nxt_s0 = __shfl_sync(kFullMask, nxt.s, 0);
-        const uint32_t nxt_val = (nxt_s0 + lane < __shfl_sync(kFullMask, nxt.e, 31)) ? __ldg(a.sorted_vals + nxt_s0 + lane) : 0u;
+    while (u0 < nu) {
+        RowMeta nxt[UR];                            // on their way while this step's rows are processed
+        if (PREFETCH) {
+#pragma unroll
+            for (int q = 0; q < UR; ++q) nxt[q] = load_row_meta(a, u0 + stride + q * RPW + grp, nu);
+        }
 
-        for (int j0 = 0; j0 < 32; j0 += RPW * UR) {
-            uint32_t row[UR], s[UR], e[UR];
-            bool valid[UR];
-            uint4 wv[UR][CPL];
-            uint4 gv[UR][CPL][GQ];
-            float scale[UR];
-            float h_old[UR];
-            // ---- issue every independent request of this step.  All loads are unconditional:
-            // rows / payloads that do not exist are redirected to element 0 and masked below.
+        bool valid[UR];
+        float scale[UR], h_old[UR];
+        uint4 wv[UR][CPL];
+        uint4 gv[UR][CPL][GQ];
+        // ---- issue every request of this step
 #pragma unroll
-            for (int q = 0; q < UR; ++q) {
-                const int r = j0 + q * RPW + grp;
-                row[q] = __shfl_sync(kFullMask, cur.key, r);
-                s[q] = __shfl_sync(kFullMask, cur.s, r);
-                e[q] = __shfl_sync(kFullMask, cur.e, r);
-                valid[q] = row[q] < a.total_rows;              // padding lanes and the out-of-range marker fail this
-                const uint32_t pos = s[q] - cur_s0;
-                uint32_t v0 = __shfl_sync(kFullMask, cur_val, pos & 31u);
-                if (valid[q] && pos >= 32u) v0 = __ldg(a.sorted_vals + s[q]);
-                if (!valid[q]) v0 = 0u;
-                const float* grow = grad_row_of(a, v0, scale[q]);
-                const size_t wrow = (size_t)(valid[q] ? row[q] : 0u) * a.nchunks;
+        for (int q = 0; q < UR; ++q) {
+            valid[q] = cur[q].key < a.total_rows;      // padding rows and the out-of-range marker fail this
+            const float* grow = grad_row_of(a, valid[q] ? cur[q].v0 : 0u, scale[q]);
+            const size_t wrow = (size_t)(valid[q] ? cur[q].key : 0u) * a.nchunks;
 #pragma unroll
-                for (int k = 0; k < CPL; ++k) {
-                    const int c = min(sub + k * LPR, a.nchunks - 1);
-                    wv[q][k] = ld_row_128(wbase + wrow + c);
+            for (int k = 0; k < CPL; ++k) {
+                const int c = min(sub + k * LPR, a.nchunks - 1);
+                wv[q][k] = ld_row_128(wbase + wrow + c);
 #pragma unroll
-                    for (int t = 0; t < GQ; ++t) gv[q][k][t] = ldg_128(grow + (size_t)c * E + 4 * t);
-                }
-                h_old[q] = 0.f;
-                if (OPT == TDFO_OPT_ROWWISE_ADAGRAD) h_old[q] = __ldcg(a.state0 + (valid[q] ? row[q] : 0u));
+                for (int t = 0; t < GQ; ++t) gv[q][k][t] = ldg_128(grow + (size_t)c * E + 4 * t);
             }
-            // ---- consume
+            h_old[q] = 0.f;
+            if (OPT == TDFO_OPT_ROWWISE_ADAGRAD) h_old[q] = __ldcg(a.state0 + (valid[q] ? cur[q].key : 0u));
+        }
+        // ---- reduce, update, store
 #pragma unroll
-            for (int q = 0; q < UR; ++q) {
-                float g[CPL][E], w[CPL][E];
+        for (int q = 0; q < UR; ++q) {
+            const uint32_t row = cur[q].key;
+            float g[CPL][E], w[CPL][E];
 #pragma unroll
-                for (int k = 0; k < CPL; ++k) {
+            for (int k = 0; k < CPL; ++k) {
 #pragma unroll
-                    for (int t = 0; t < GQ; ++t) {
-                        g[k][4 * t]     = scale[q] * __uint_as_float(gv[q][k][t].x);
-                        g[k][4 * t + 1] = scale[q] * __uint_as_float(gv[q][k][t].y);
-                        g[k][4 * t + 2] = scale[q] * __uint_as_float(gv[q][k][t].z);
-                        g[k][4 * t + 3] = scale[q] * __uint_as_float(gv[q][k][t].w);
-                    }
-                    Chunk<T>::unpack(wv[q][k], w[k]);
+                for (int t = 0; t < GQ; ++t) {
+                    g[k][4 * t]     = scale[q] * __uint_as_float(gv[q][k][t].x);
+                    g[k][4 * t + 1] = scale[q] * __uint_as_float(gv[q][k][t].y);
+                    g[k][4 * t + 2] = scale[q] * __uint_as_float(gv[q][k][t].z);
+                    g[k][4 * t + 3] = scale[q] * __uint_as_float(gv[q][k][t].w);
                 }
-                // further occurrences of the row, in sorted (= original) order
-                if (valid[q]) {
-                    for (uint32_t i = s[q] + 1; i < e[q]; ++i) {
-                        float sc;
-                        const float* grow = grad_row_of(a, __ldg(a.sorted_vals + i), sc);
-#pragma unroll
-                        for (int k = 0; k < CPL; ++k) {
-                            const int c = sub + k * LPR;
-                            if (c < a.nchunks) {
-#pragma unroll
-                                for (int t = 0; t < GQ; ++t) {
-                                    const uint4 x = ldg_128(grow + (size_t)c * E + 4 * t);
-                                    g[k][4 * t]     = fmaf(sc, __uint_as_float(x.x), g[k][4 * t]);
-                                    g[k][4 * t + 1] = fmaf(sc, __uint_as_float(x.y), g[k][4 * t + 1]);
-                                    g[k][4 * t + 2] = fmaf(sc, __uint_as_float(x.z), g[k][4 * t + 2]);
-                                    g[k][4 * t + 3] = fmaf(sc, __uint_as_float(x.w), g[k][4 * t + 3]);
-                                }
-                            }
-                        }
-                    }
-                }
-
-                if (OPT == TDFO_OPT_SGD) {
-#pragma unroll
-                    for (int k = 0; k < CPL; ++k)
-#pragma unroll
-                        for (int i = 0; i < E; ++i) {
-                            const float gi = fmaf(a.wd, w[k][i], g[k][i]);
-                            w[k][i] = fmaf(-a.lr, gi, w[k][i]);
-                        }
-                } else if (OPT == TDFO_OPT_ROWWISE_ADAGRAD) {
-                    float ss = 0.f;
-#pragma unroll
-                    for (int k = 0; k < CPL; ++k)
-#pragma unroll
-                        for (int i = 0; i < E; ++i) {
-                            g[k][i] = fmaf(a.wd, w[k][i], g[k][i]);
-                            ss = fmaf(g[k][i], g[k][i], ss);
-                        }
-#pragma unroll
-                    for (int o = 1; o < LPR; o <<= 1) ss += __shfl_xor_sync(gmask, ss, o);
-                    const float h = h_old[q] + ss * a.inv_D;
-                    // sqrt / divide through the SFU (2-3 ulp, far inside the 1e-5 parity bar)
-                    const float sq = h > 0.f ? h * rsqrtf(h) : 0.f;
-                    const float mult = __fdividef(a.lr, sq + a.eps);
-                    if (valid[q] && sub == 0) a.state0[row[q]] = h;
-#pragma unroll
-                    for (int k = 0; k < CPL; ++k)
-#pragma unroll
-                        for (int i = 0; i < E; ++i) w[k][i] = fmaf(-mult, g[k][i], w[k][i]);
-                } else if (valid[q]) {   // ADAM
+                Chunk<T>::unpack(wv[q][k], w[k]);
+            }
+            // further occurrences of the row, in sorted (= original) order
+            if (valid[q]) {
+                for (uint32_t i = cur[q].s + 1; i < cur[q].e; ++i) {
+                    float sc;
+                    const float* grow = grad_row_of(a, __ldg(a.sorted_vals + i), sc);
 #pragma unroll
                     for (int k = 0; k < CPL; ++k) {
                         const int c = sub + k * LPR;
                         if (c < a.nchunks) {
-                            float* m = a.state0 + (size_t)row[q] * a.D + (size_t)c * E;
-                            float* v = a.state1 + (size_t)row[q] * a.D + (size_t)c * E;
 #pragma unroll
-                            for (int t = 0; t < E; t += 4) {
-                                uint4 mr = ld_128(m + t), vr = ld_128(v + t);
-                                float mm[4] = {__uint_as_float(mr.x), __uint_as_float(mr.y), __uint_as_float(mr.z), __uint_as_float(mr.w)};
-                                float vv[4] = {__uint_as_float(vr.x), __uint_as_float(vr.y), __uint_as_float(vr.z), __uint_as_float(vr.w)};
-#pragma unroll
-                                for (int i = 0; i < 4; ++i) {
-                                    const float gi = g[k][t + i];
-                                    mm[i] = a.beta1 * mm[i] + (1.f - a.beta1) * gi;
-                                    vv[i] = a.beta2 * vv[i] + (1.f - a.beta2) * gi * gi;
-                                    const float mhat = mm[i] / a.bc1;
-                                    const float vhat = vv[i] / a.bc2;
-                                    w[k][t + i] -= a.lr * (mhat / (sqrtf(vhat) + a.eps) + a.wd * w[k][t + i]);
-                                }
-                                st_128(m + t, make_uint4(__float_as_uint(mm[0]), __float_as_uint(mm[1]), __float_as_uint(mm[2]), __float_as_uint(mm[3])));
-                                st_128(v + t, make_uint4(__float_as_uint(vv[0]), __float_as_uint(vv[1]), __float_as_uint(vv[2]), __float_as_uint(vv[3])));
+                            for (int t = 0; t < GQ; ++t) {
+                                const uint4 x = ldg_128(grow + (size_t)c * E + 4 * t);
+                                g[k][4 * t]     = fmaf(sc, __uint_as_float(x.x), g[k][4 * t]);
+                                g[k][4 * t + 1] = fmaf(sc, __uint_as_float(x.y), g[k][4 * t + 1]);
+                                g[k][4 * t + 2] = fmaf(sc, __uint_as_float(x.z), g[k][4 * t + 2]);
+                                g[k][4 * t + 3] = fmaf(sc, __uint_as_float(x.w), g[k][4 * t + 3]);
                             }
                         }
                     }
                 }
+            }
 
-                if (valid[q]) {
+            if (OPT == TDFO_OPT_SGD) {
 #pragma unroll
-                    for (int k = 0; k < CPL; ++k) {
-                        const int c = sub + k * LPR;
-                        if (c < a.nchunks) st_128(wbase + (size_t)row[q] * a.nchunks + c, Chunk<T>::pack(w[k]));
+                for (int k = 0; k < CPL; ++k)
+#pragma unroll
+                    for (int i = 0; i < E; ++i) {
+                        const float gi = fmaf(a.wd, w[k][i], g[k][i]);
+                        w[k][i] = fmaf(-a.lr, gi, w[k][i]);
+                    }
+            } else if (OPT == TDFO_OPT_ROWWISE_ADAGRAD) {
+                float ss = 0.f;
+#pragma unroll
+                for (int k = 0; k < CPL; ++k)
+#pragma unroll
+                    for (int i = 0; i < E; ++i) {
+                        g[k][i] = fmaf(a.wd, w[k][i], g[k][i]);
+                        if (sub + k * LPR >= a.nchunks) g[k][i] = 0.f;       // lanes past the row end
+                        ss = fmaf(g[k][i], g[k][i], ss);
+                    }
+#pragma unroll
+                for (int o = 1; o < LPR; o <<= 1) ss += __shfl_xor_sync(gmask, ss, o);
+                const float h = h_old[q] + ss * a.inv_D;
+                // sqrt / divide through the SFU (2-3 ulp, far inside the 1e-5 parity bar)
+                const float sq = h > 0.f ? h * rsqrtf(h) : 0.f;
+                const float mult = __fdividef(a.lr, sq + a.eps);
+                if (valid[q] && sub == 0) a.state0[row] = h;
+#pragma unroll
+                for (int k = 0; k < CPL; ++k)
+#pragma unroll
+                    for (int i = 0; i < E; ++i) w[k][i] = fmaf(-mult, g[k][i], w[k][i]);
+            } else if (valid[q]) {   // ADAM
+#pragma unroll
+                for (int k = 0; k < CPL; ++k) {
+                    const int c = sub + k * LPR;
+                    if (c < a.nchunks) {
+                        float* m = a.state0 + (size_t)row * a.D + (size_t)c * E;
+                        float* v = a.state1 + (size_t)row * a.D + (size_t)c * E;
+#pragma unroll
+                        for (int t = 0; t < E; t += 4) {
+                            uint4 mr = ld_128(m + t), vr = ld_128(v + t);
+                            float mm[4] = {__uint_as_float(mr.x), __uint_as_float(mr.y), __uint_as_float(mr.z), __uint_as_float(mr.w)};
+                            float vv[4] = {__uint_as_float(vr.x), __uint_as_float(vr.y), __uint_as_float(vr.z), __uint_as_float(vr.w)};
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                const float gi = g[k][t + i];
+                                mm[i] = a.beta1 * mm[i] + (1.f - a.beta1) * gi;
+                                vv[i] = a.beta2 * vv[i] + (1.f - a.beta2) * gi * gi;
+                                const float mhat = mm[i] / a.bc1;
+                                const float vhat = vv[i] / a.bc2;
+                                w[k][t + i] -= a.lr * (mhat / (sqrtf(vhat) + a.eps) + a.wd * w[k][t + i]);
+                            }
+                            st_128(m + t, make_uint4(__float_as_uint(mm[0]), __float_as_uint(mm[1]), __float_as_uint(mm[2]), __float_as_uint(mm[3])));
+                            st_128(v + t, make_uint4(__float_as_uint(vv[0]), __float_as_uint(vv[1]), __float_as_uint(vv[2]), __float_as_uint(vv[3])));
+                        }
                     }
                 }
             }
+
+            if (valid[q]) {
+#pragma unroll
+                for (int k = 0; k < CPL; ++k) {
+                    const int c = sub + k * LPR;
+                    if (c < a.nchunks) st_128(wbase + (size_t)row * a.nchunks + c, Chunk<T>::pack(w[k]));
+                }
+            }
         }
-        tile += nwarps;
-        cur = nxt; cur_s0 = nxt_s0; cur_val = nxt_val;
-        nxt = nn;
+        u0 += stride;
+#pragma unroll
+        for (int q = 0; q < UR; ++q) cur[q] = PREFETCH ? nxt[q] : load_row_meta(a, u0 + q * RPW + grp, nu);
     }
 }
 
-template <typename T, int LPR, int CPL, int UR, int MINB = 2>
+template <typename T, int LPR, int CPL, int UR, int MINB, bool PREFETCH = true>
 static int launch_update(const UpdateArgs& a, int opt, int64_t max_unique, cudaStream_t st) {
-    const int64_t tiles = (max_unique + 31) / 32;                 // one warp per tile of 32 unique rows
-    int64_t blocks = (tiles + kUpdThreads / 32 - 1) / (kUpdThreads / 32);
+    constexpr int STEP = (32 / LPR) * UR;
+    const int64_t steps = (max_unique + STEP - 1) / STEP;             // one warp step per STEP rows
+    int64_t blocks = (steps + kUpdCtaThreads / 32 - 1) / (kUpdCtaThreads / 32);
     const int64_t cap = (int64_t)kNumSMs * MINB;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     switch (opt) {
         case TDFO_OPT_SGD:
-            sparse_update_kernel<T, LPR, CPL, UR, MINB, TDFO_OPT_SGD><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
+            sparse_update_kernel<T, LPR, CPL, UR, MINB, TDFO_OPT_SGD, PREFETCH><<<(unsigned)blocks, kUpdCtaThreads, 0, st>>>(a); break;
         case TDFO_OPT_ROWWISE_ADAGRAD:
-            sparse_update_kernel<T, LPR, CPL, UR, MINB, TDFO_OPT_ROWWISE_ADAGRAD><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
+            sparse_update_kernel<T, LPR, CPL, UR, MINB, TDFO_OPT_ROWWISE_ADAGRAD, PREFETCH><<<(unsigned)blocks, kUpdCtaThreads, 0, st>>>(a); break;
         default:
-            sparse_update_kernel<T, LPR, CPL, UR, MINB, TDFO_OPT_ADAM><<<(unsigned)blocks, kUpdThreads, 0, st>>>(a); break;
+            sparse_update_kernel<T, LPR, CPL, UR, MINB, TDFO_OPT_ADAM, PREFETCH><<<(unsigned)blocks, kUpdCtaThreads, 0, st>>>(a); break;
     }
     count_launch();
     TDFO_LAUNCH_CHECK("sparse_update");
     return TDFO_OK;
 }
 
-// Few lanes per row on purpose: the per-row bookkeeping (metadata shuffles, gradient address,
-// optimizer scalar math) is replicated in every lane of the row's group, so a group of 8 lanes
-// with 4 chunks each spends a quarter of the issue slots per row that 32 lanes x 1 chunk would,
-// and a warp keeps RPW * UR rows (weight + gradient) in flight.
+// Shapes measured on B200 (tools/tune_update.py, BASELINE config 2): 8 lanes x 4 chunks per
+// 512 B row, one row per group per step, 3 CTAs / SM (80 registers, no spills) = 1.46 ms;
+// anything that spills, or 32 lanes per row, is 15-60 % slower.  Few lanes per row matter:
+// per-row bookkeeping is replicated in every lane of the group.
 template <typename T>
 static int dispatch_update(const UpdateArgs& a, int opt, int64_t max_unique, cudaStream_t st) {
     const int n = a.nchunks;
     constexpr bool kWide = sizeof(T) == 4;          // fp32: 4 chunks per lane; bf16 (8 elems / chunk): 2
     if (kWide) {
-        if (n <= 1)   return launch_update<T, 1, 1, 1>(a, opt, max_unique, st);
-        if (n <= 2)   return launch_update<T, 1, 2, 1>(a, opt, max_unique, st);
-        if (n <= 4)   return launch_update<T, 1, 4, 1>(a, opt, max_unique, st);
-        if (n <= 8)   return launch_update<T, 2, 4, 2>(a, opt, max_unique, st);
-        if (n <= 16)  return launch_update<T, 4, 4, 2>(a, opt, max_unique, st);
-        if (n <= 32) {
-            const char* v = getenv("TDFO_UPD_VARIANT");          // TUNING ONLY
-            const int vi = v ? atoi(v) : 0;
-            if (vi == 1) return launch_update<T, 8, 4, 1, 3>(a, opt, max_unique, st);
-            if (vi == 2) return launch_update<T, 8, 4, 1, 4>(a, opt, max_unique, st);
-            if (vi == 3) return launch_update<T, 16, 2, 2, 3>(a, opt, max_unique, st);
-            if (vi == 4) return launch_update<T, 16, 2, 1, 4>(a, opt, max_unique, st);
-            if (vi == 5) return launch_update<T, 16, 2, 1, 5>(a, opt, max_unique, st);
-            if (vi == 6) return launch_update<T, 8, 4, 2, 3>(a, opt, max_unique, st);
-            if (vi == 7) return launch_update<T, 32, 1, 2, 4>(a, opt, max_unique, st);
-            if (vi == 8) return launch_update<T, 32, 1, 4, 3>(a, opt, max_unique, st);
-            return launch_update<T, 8, 4, 1, 3>(a, opt, max_unique, st);
-        }
-        if (n <= 64)  return launch_update<T, 16, 4, 2>(a, opt, max_unique, st);
-        if (n <= 128) return launch_update<T, 32, 4, 1>(a, opt, max_unique, st);
-        if (n <= 256) return launch_update<T, 32, 8, 1>(a, opt, max_unique, st);
+        if (n <= 1)   return launch_update<T, 1, 1, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 2)   return launch_update<T, 1, 2, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 4)   return launch_update<T, 1, 4, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 8)   return launch_update<T, 2, 4, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 16)  return launch_update<T, 4, 4, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 32)  return launch_update<T, 8, 4, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 64)  return launch_update<T, 16, 4, 1, 2, false>(a, opt, max_unique, st);
+        if (n <= 128) return launch_update<T, 32, 4, 1, 2, false>(a, opt, max_unique, st);
+        if (n <= 256) return launch_update<T, 32, 8, 1, 2, false>(a, opt, max_unique, st);
     } else {
-        if (n <= 1)   return launch_update<T, 1, 1, 1>(a, opt, max_unique, st);
-        if (n <= 2)   return launch_update<T, 1, 2, 1>(a, opt, max_unique, st);
-        if (n <= 4)   return launch_update<T, 2, 2, 2>(a, opt, max_unique, st);
-        if (n <= 8)   return launch_update<T, 4, 2, 2>(a, opt, max_unique, st);
-        if (n <= 16)  return launch_update<T, 8, 2, 2>(a, opt, max_unique, st);
-        if (n <= 32)  return launch_update<T, 16, 2, 2>(a, opt, max_unique, st);
-        if (n <= 64)  return launch_update<T, 32, 2, 1>(a, opt, max_unique, st);
-        if (n <= 128) return launch_update<T, 32, 4, 1>(a, opt, max_unique, st);
-        if (n <= 256) return launch_update<T, 32, 8, 1>(a, opt, max_unique, st);
+        if (n <= 1)   return launch_update<T, 1, 1, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 2)   return launch_update<T, 1, 2, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 4)   return launch_update<T, 2, 2, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 8)   return launch_update<T, 4, 2, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 16)  return launch_update<T, 8, 2, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 32)  return launch_update<T, 16, 2, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 64)  return launch_update<T, 32, 2, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 128) return launch_update<T, 32, 4, 1, 2, false>(a, opt, max_unique, st);
+        if (n <= 256) return launch_update<T, 32, 8, 1, 2, false>(a, opt, max_unique, st);
     }
     set_error("sparse_update: row of %d bytes exceeds the 4096-byte maximum", n * 16);
     return TDFO_ERR_UNSUPPORTED;
@@ -386,14 +371,14 @@ static int check_opt(const char* who, const tdfo_optimizer_args* opt, const floa
 int sparse_update_impl(void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
                        float* state0, float* state1, const float* grad_out, int64_t grad_stride,
                        const uint32_t* sorted_vals, const uint32_t* unique_keys,
-                       const uint32_t* seg_starts, const uint32_t* num_unique,
+                       const uint32_t* seg_starts, const uint32_t* first_vals, const uint32_t* num_unique,
                        const int64_t* offsets, const int64_t* feat_out_col, int32_t F, int64_t B,
                        int64_t L, int32_t pooling_mode, const tdfo_optimizer_args* opt, cudaStream_t st) {
     if (L == 0) return TDFO_OK;
     const size_t esz = weights_dtype == TDFO_F32 ? 4 : 2;
     UpdateArgs a;
     a.weights = weights; a.state0 = state0; a.state1 = state1; a.grad = grad_out;
-    a.sorted_vals = sorted_vals; a.unique_keys = unique_keys; a.seg_starts = seg_starts;
+    a.sorted_vals = sorted_vals; a.unique_keys = unique_keys; a.seg_starts = seg_starts; a.first_vals = first_vals;
     a.num_unique = num_unique; a.offsets = offsets; a.feat_out_col = feat_out_col;
     a.grad_stride = grad_stride; a.B = B;
     a.B_magic = B > 1 ? (~0ull / (uint64_t)B + 1ull) : 0ull; a.total_rows = (uint32_t)total_rows; a.L = (uint32_t)L; a.D = D;
@@ -441,7 +426,7 @@ extern "C" int tdfo_linearize_indices(const int64_t* indices, const int64_t* off
 extern "C" int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
                                   float* state0, float* state1, const float* grad_out, int64_t grad_stride,
                                   const uint32_t* sorted_vals, const uint32_t* unique_keys,
-                                  const uint32_t* seg_starts, const uint32_t* num_unique,
+                                  const uint32_t* seg_starts, const uint32_t* first_vals, const uint32_t* num_unique,
                                   const int64_t* offsets, const int64_t* feat_out_col, int32_t F,
                                   int64_t B, int64_t L, int32_t pooling_mode,
                                   const tdfo_optimizer_args* opt, void* stream) {
@@ -452,7 +437,8 @@ extern "C" int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t 
     TDFO_CHECK_ARG(pooling_mode >= TDFO_POOL_SUM && pooling_mode <= TDFO_POOL_NONE, "sparse_update: unknown pooling_mode");
     TDFO_CHECK_ARG(L >= 0 && L < (1ll << 30), "sparse_update: L must be in [0, 2^30)");
     if (L == 0) return TDFO_OK;
-    TDFO_CHECK_ARG(weights && grad_out && sorted_vals && unique_keys && seg_starts && num_unique, "sparse_update: null pointer");
+    TDFO_CHECK_ARG(weights && grad_out && sorted_vals && unique_keys && seg_starts && first_vals && num_unique,
+                   "sparse_update: null pointer");
     TDFO_CHECK_ARG(aligned(weights, 16) && aligned(grad_out, 16), "sparse_update: weights/grad_out not 16-byte aligned");
     if (pooling_mode != TDFO_POOL_NONE) {
         TDFO_CHECK_ARG(feat_out_col != nullptr, "sparse_update: feat_out_col is null");
@@ -460,7 +446,7 @@ extern "C" int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t 
     }
     TDFO_CHECK_ARG(pooling_mode != TDFO_POOL_MEAN || offsets, "sparse_update: MEAN pooling needs offsets");
     return sparse_update_impl(weights, weights_dtype, total_rows, D, state0, state1, grad_out, grad_stride,
-                              sorted_vals, unique_keys, seg_starts, num_unique, offsets, feat_out_col,
+                              sorted_vals, unique_keys, seg_starts, first_vals, num_unique, offsets, feat_out_col,
                               F, B, L, pooling_mode, opt, static_cast<cudaStream_t>(stream));
 }
 
@@ -477,10 +463,11 @@ extern "C" int tdfo_backward_scratch_layout(int64_t L, int64_t total_rows, tdfo_
     layout->sorted_vals = (res ? 3 : 1) * A;
     layout->unique_keys = (res ? 0 : 2) * A;  // the other pair is free after the sort
     layout->seg_starts  = (res ? 1 : 3) * A;
+    layout->first_vals  = 4 * A;
     layout->input_keys = 0;
     layout->input_vals = A;
-    layout->num_unique = 4 * A;
-    const size_t sort_off = 4 * A + 256;
+    layout->num_unique = 5 * A;
+    const size_t sort_off = 5 * A + 256;
     const size_t scan_off = sort_off + radix_sort_scratch_bytes_impl(L, bits);
     layout->total_bytes = scan_off + tdfo_scan_scratch_bytes(L);
     return TDFO_OK;
@@ -537,8 +524,8 @@ extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dty
     uint32_t* k1 = reinterpret_cast<uint32_t*>(base + 2 * A);
     uint32_t* v1 = reinterpret_cast<uint32_t*>(base + 3 * A);
     uint32_t* num_unique = reinterpret_cast<uint32_t*>(base + lay.num_unique);
-    void* sort_scratch = base + 4 * A + 256;
-    void* scan_scratch = base + 4 * A + 256 + radix_sort_scratch_bytes_impl(L, lay.key_bits);
+    void* sort_scratch = base + 5 * A + 256;
+    void* scan_scratch = base + 5 * A + 256 + radix_sort_scratch_bytes_impl(L, lay.key_bits);
 
     if (!keys_in_scratch) {
         rc = tdfo_linearize_indices(indices, offsets, feat_row_base, feat_rows, F, B, total_rows, pooling_mode,
@@ -556,8 +543,9 @@ extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dty
         set_error("embedding_backward_update: internal layout mismatch");
         return TDFO_ERR_INVALID_ARG;
     }
-    rc = unique_segments_impl(sk, L, uk, ss, num_unique, err_flag, scan_scratch, st);
+    uint32_t* fv = reinterpret_cast<uint32_t*>(base + lay.first_vals);
+    rc = unique_segments_impl(sk, sv, L, uk, ss, fv, num_unique, err_flag, scan_scratch, st);
     if (rc) return rc;
     return sparse_update_impl(weights, weights_dtype, total_rows, D, state0, state1, grad_out, grad_stride,
-                              sv, uk, ss, num_unique, offsets, feat_out_col, F, B, L, pooling_mode, opt, st);
+                              sv, uk, ss, fv, num_unique, offsets, feat_out_col, F, B, L, pooling_mode, opt, st);
 }

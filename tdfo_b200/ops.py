@@ -271,7 +271,8 @@ def radix_sort_pairs(keys: torch.Tensor, vals: torch.Tensor, key_bits: int, err_
     return ko, vo
 
 
-def unique_segments(sorted_keys: torch.Tensor, err_flag=None):
+def unique_segments(sorted_keys: torch.Tensor, err_flag=None, sorted_vals: Optional[torch.Tensor] = None):
+    """Returns (unique_keys, seg_starts, num_unique[, first_vals if ``sorted_vals`` is given])."""
     sorted_keys = _cuda(sorted_keys, torch.int32, "sorted_keys")
     n = sorted_keys.numel()
     dev = sorted_keys.device
@@ -280,19 +281,21 @@ def unique_segments(sorted_keys: torch.Tensor, err_flag=None):
     nu = torch.empty(1, dtype=torch.int32, device=dev)
     lib = _lib.load()
     scratch = _get_scratch(dev, lib.tdfo_scan_scratch_bytes(n))
-    check(lib.tdfo_unique_segments(_ptr(sorted_keys), n, _ptr(uk), _ptr(ss), _ptr(nu), _ptr(err_flag),
-                                   _ptr(scratch), scratch.numel(), _stream()))
-    return uk, ss, nu
+    fv = None if sorted_vals is None else torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    check(lib.tdfo_unique_segments(_ptr(sorted_keys), _ptr(sorted_vals), n, _ptr(uk), _ptr(ss), _ptr(fv), _ptr(nu),
+                                   _ptr(err_flag), _ptr(scratch), scratch.numel(), _stream()))
+    return (uk, ss, nu) if sorted_vals is None else (uk, ss, nu, fv)
 
 
-def sparse_update(group: TableGroup, grad_out, sorted_vals, unique_keys, seg_starts, num_unique, offsets, B, L,
-                  pooling_mode, opt: OptimizerArgs):
+def sparse_update(group: TableGroup, grad_out, sorted_vals, unique_keys, seg_starts, first_vals, num_unique, offsets,
+                  B, L, pooling_mode, opt: OptimizerArgs):
     grad_out = _cuda(grad_out, torch.float32, "grad_out")
     w = group.weights
     grad_stride = group.D if pooling_mode == POOL_NONE else grad_out.shape[-1]
     check(_lib.load().tdfo_sparse_update(
         _ptr(w), _wdtype(w), group.total_rows, group.D, _ptr(group.state0), _ptr(group.state1), _ptr(grad_out),
-        grad_stride, _ptr(sorted_vals), _ptr(unique_keys), _ptr(seg_starts), _ptr(num_unique), _ptr(offsets),
+        grad_stride, _ptr(sorted_vals), _ptr(unique_keys), _ptr(seg_starts), _ptr(first_vals), _ptr(num_unique),
+        _ptr(offsets),
         _ptr(group.feat_out_col), group.F, B, L, pooling_mode, ctypes.byref(opt), _stream()))
 
 

@@ -191,11 +191,13 @@ def test_unique_segments_bit_exact(ops, n, card):
     rng = np.random.default_rng(n)
     keys = np.sort(rng.integers(0, card, size=n).astype(np.uint32))
     uk_w, ss_w, nu_w = orc.unique_segments(keys)
-    uk, ss, nu = ops.unique_segments(dev(keys.view(np.int32)))
+    vals = rng.integers(0, 2 ** 32, size=n, dtype=np.uint64).astype(np.uint32)
+    uk, ss, nu, fv = ops.unique_segments(dev(keys.view(np.int32)), sorted_vals=dev(vals.view(np.int32)))
     nu = int(nu.item())
     assert nu == nu_w
     np.testing.assert_array_equal(u32(uk)[:nu], uk_w)
     np.testing.assert_array_equal(u32(ss)[: nu + 1], ss_w)
+    np.testing.assert_array_equal(u32(fv)[:nu], vals[ss_w[:-1]])         # payload of each row's first occurrence
 
 
 def test_linearize_bit_exact(ops):

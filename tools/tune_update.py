@@ -32,8 +32,8 @@ def run(tag, n=10):
         e[0].record(); ops.embedding_forward(grp, idx, offsets, B, 0, out=out)
         e[1].record(); k, v = ops.linearize_indices(grp, idx, offsets, B, 0)
         e[2].record(); sk, sv = ops.radix_sort_pairs(k, v, lay.key_bits, grp.err_flag)
-        e[3].record(); uk, ss, nu = ops.unique_segments(sk, grp.err_flag)
-        e[4].record(); ops.sparse_update(grp, grad, sv, uk, ss, nu, offsets, B, L, 0, opt)
+        e[3].record(); uk, ss, nu, fv = ops.unique_segments(sk, grp.err_flag, sv)
+        e[4].record(); ops.sparse_update(grp, grad, sv, uk, ss, fv, nu, offsets, B, L, 0, opt)
         e[5].record()
     torch.cuda.synchronize()
     ms = [statistics.mean(ev[i][j].elapsed_time(ev[i][j + 1]) for i in range(n)) for j in range(5)]
