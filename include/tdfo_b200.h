@@ -89,6 +89,34 @@ int tdfo_kjt_complete_cumsum(const int32_t* lengths, int64_t n, int64_t* offsets
                              void* scratch, size_t scratch_bytes, void* stream);
 
 /*
+ * The same lengths -> offsets scan for callers that cannot hand over device scratch because
+ * they cannot allocate any: a plug-in running inside a framework that has already claimed
+ * nearly all of HBM for its own pool (XLA and TensorFlow do this by default, and those are
+ * the runtimes behind the reference's jax-flax and tensorflow2 trainers), where a cudaMalloc
+ * from the plug-in fails or eats into the host framework's budget; or a serving loop that
+ * must not hit the device-wide synchronisation cudaMalloc / cudaFree imply.  This entry point
+ * has no counterpart in the reference.
+ *
+ * The workspace is a fixed array inside the library image (about 16 KB per GPU that loads the
+ * library, held until process exit), which is why the input is limited to
+ * TDFO_CUMSUM_STATIC_MAX_N lengths; larger n returns TDFO_ERR_SCRATCH and the message names
+ * the limit.  The call performs no cudaMalloc / cudaFree and calls nothing that allocates;
+ * `lengths` and `offsets` are still the caller's buffers.
+ *
+ *  - The first call on each device looks up the array's device address
+ *    (cudaGetSymbolAddress, with that device current).  Make that first call before starting
+ *    any stream capture on the device.
+ *  - All calls on a device share the one array, and it still holds the previous call's
+ *    contents; each call re-zeroes the words it needs on `stream` before its kernel runs.
+ *    Two calls whose GPU work can overlap (different streams without an ordering between them,
+ *    or several host threads) race on it: order them, or use tdfo_kjt_complete_cumsum with
+ *    separate scratch buffers.
+ * Results are identical to tdfo_kjt_complete_cumsum.
+ */
+#define TDFO_CUMSUM_STATIC_MAX_N (1 << 22)   /* 4 194 304 lengths, e.g. 256 features x batch 16 384 */
+int tdfo_kjt_complete_cumsum_static(const int32_t* lengths, int64_t n, int64_t* offsets, void* stream);
+
+/*
  * Row-wise input dist, step 1: bucketise ids by destination rank.
  * For feature f with `block_sizes[f]` rows per rank, id x goes to bucket
  * x / block_sizes[f] and becomes x - bucket*block_sizes[f].  Output is laid

@@ -17,6 +17,7 @@ POOL_SUM, POOL_MEAN, POOL_NONE = 0, 1, 2
 OPT_SGD, OPT_ROWWISE_ADAGRAD, OPT_ADAM = 0, 1, 2
 FLAG_INDEX_OOB, FLAG_SCAN_TIMEOUT = 1, 2
 ABI_VERSION = 1
+CUMSUM_STATIC_MAX_N = 1 << 22
 
 
 class OptimizerArgs(Structure):
@@ -37,6 +38,7 @@ _SIGNATURES = {
     "tdfo_launch_count": (c_ulonglong, []),
     "tdfo_scan_scratch_bytes": (c_size_t, [c_int64]),
     "tdfo_kjt_complete_cumsum": (c_int, [P, c_int64, P, P, c_size_t, P]),
+    "tdfo_kjt_complete_cumsum_static": (c_int, [P, c_int64, P, P]),
     "tdfo_bucketize_scratch_bytes": (c_size_t, [c_int64, c_int32]),
     "tdfo_kjt_bucketize_row_wise": (c_int, [P, P, P, P, P, c_int32, c_int64, c_int32, P, P, P, P, P, P, P, c_size_t, P]),
     "tdfo_kjt_permute_2d": (c_int, [P, c_int32, c_int32, c_int64, P, P, P, P, P, P, P, P, P, c_size_t, P]),

@@ -3,6 +3,7 @@
 // look-back, tile ids from an atomic ticket) and are bandwidth-trivial next to
 // the gather; they exist so the step has no host round trip.
 #include "scan.cuh"
+#include <mutex>
 
 namespace tdfo {
 
@@ -184,4 +185,63 @@ extern "C" int tdfo_unique_segments(const uint32_t* sorted_keys, const uint32_t*
     }
     return unique_segments_impl(sorted_keys, sorted_vals, n, unique_keys, seg_starts, first_vals, num_unique,
                                 err_flag, scratch, static_cast<cudaStream_t>(stream));
+}
+
+
+// ---------------------------------------------------------------- cumsum without caller scratch
+//
+// Workspace for tdfo_kjt_complete_cumsum_static: the ticket word and one look-back status word
+// per 2048-length tile, for up to TDFO_CUMSUM_STATIC_MAX_N lengths.  It lives in the library
+// image, so every GPU that loads the library carries these ~16 KB until the process exits.
+namespace tdfo {
+constexpr size_t kStaticScanBytes =
+    sizeof(ScanScratch) + (size_t)(TDFO_CUMSUM_STATIC_MAX_N / kScanTile) * sizeof(uint64_t);
+static_assert(TDFO_CUMSUM_STATIC_MAX_N % kScanTile == 0, "maximum must be a whole number of scan tiles");
+static_assert(kStaticScanBytes % 256 == 0, "keep the workspace a multiple of its alignment");
+}  // namespace tdfo
+
+static __device__ __align__(256) unsigned char g_static_scan_scratch[tdfo::kStaticScanBytes];
+
+namespace tdfo {
+constexpr int kMaxDevices = 64;
+static void* g_static_scan_ptr[kMaxDevices] = {};     // device address of the array, per device
+static std::mutex g_static_scan_mutex;
+
+// In host code `g_static_scan_scratch` is only a handle for the symbol, not something a kernel
+// can dereference: the address on the current device has to be asked for, once per device.
+static int static_scan_scratch(void** out) {
+    int dev = -1;
+    TDFO_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) {
+        set_error("complete_cumsum_static: device ordinal %d is outside [0, %d)", dev, kMaxDevices);
+        return TDFO_ERR_UNSUPPORTED;
+    }
+    std::lock_guard<std::mutex> lock(g_static_scan_mutex);
+    if (g_static_scan_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        TDFO_CUDA(cudaGetSymbolAddress(&p, g_static_scan_scratch));
+        g_static_scan_ptr[dev] = p;
+    }
+    *out = g_static_scan_ptr[dev];
+    return TDFO_OK;
+}
+}  // namespace tdfo
+
+extern "C" int tdfo_kjt_complete_cumsum_static(const int32_t* lengths, int64_t n, int64_t* offsets,
+                                               void* stream) {
+    TDFO_CHECK_ARG(n >= 0, "complete_cumsum_static: n < 0");
+    TDFO_CHECK_ARG(offsets && (lengths || n == 0), "complete_cumsum_static: null pointer");
+    if (n > (int64_t)TDFO_CUMSUM_STATIC_MAX_N) {
+        set_error("complete_cumsum_static: n = %lld exceeds the built-in workspace (at most %lld lengths); "
+                  "use tdfo_kjt_complete_cumsum with caller scratch for larger inputs",
+                  (long long)n, (long long)TDFO_CUMSUM_STATIC_MAX_N);
+        return TDFO_ERR_SCRATCH;
+    }
+    void* scratch = nullptr;
+    const int rc = static_scan_scratch(&scratch);
+    if (rc) return rc;
+    // Same kernel as tdfo_kjt_complete_cumsum.  complete_cumsum_impl first zeroes the part of the
+    // workspace this n uses (ticket + status words) on `stream`: the previous call's look-back
+    // words are still in there and would otherwise be read as finished prefixes.
+    return complete_cumsum_impl(lengths, n, offsets, scratch, static_cast<cudaStream_t>(stream));
 }
