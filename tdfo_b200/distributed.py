@@ -1,0 +1,438 @@
+"""Sharded embedding path: table-wise / row-wise / mixed sharding of an EmbeddingBagCollection
+over the GPUs of one box, one process per GPU.
+
+This is the part of the reference that `DistributedModelParallel(module, device, sharders=[...])`
+(torchrec/train.py:241-247) delegates to torchrec's sharded modules (SURVEY.md §8 a10, a11, a13,
+§8e).  Per step and rank:
+
+  input dist   TW features are permuted into owner order, RW features are bucketised by row
+               block (`tdfo_kjt_bucketize_row_wise`); lengths, then ids, are exchanged with two
+               all-to-alls; the received [src][feature][batch] layout is permuted to
+               [feature][src][batch] (`tdfo_kjt_permute_2d`) so each local feature sees the
+               global batch W*B.
+  lookup       `tdfo_embedding_forward` over the local storage (whole TW tables, row blocks of RW
+               tables).
+  output dist  TW: all-to-all of pooled rows back to the rank that owns the samples;
+               RW: partial sums are exchanged and added in source-rank order (a reduce-scatter
+               with a fixed, reproducible order).
+  backward     the reverse exchanges (all-to-all of gradients for TW, all-gather for RW), then the
+               fused sort/unique/update kernels on the local storage.
+
+torch.distributed is the plumbing (NCCL over NVLink on the GPU box, gloo in the CPU tests).  The
+compute steps go through a small `KernelOps` table whose only implementation in this package is
+the CUDA one; the CPU tests in `tests/` inject their own checker-backed table to exercise the
+routing logic without a GPU.
+"""
+from __future__ import annotations
+
+import enum
+import zlib
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from . import _lib
+from .modules import EmbeddingBagConfig, PoolingType
+from .optim import EmbOptimType, FusedOptimizer
+from .sparse import KeyedJaggedTensor, KeyedTensor
+
+
+class ShardingType(enum.Enum):
+    TABLE_WISE = "table_wise"
+    ROW_WISE = "row_wise"
+
+
+@dataclass
+class ParameterSharding:
+    sharding_type: ShardingType
+    rank: Optional[int] = None          # owner for TABLE_WISE
+
+
+def table_wise(rank: int) -> ParameterSharding:
+    return ParameterSharding(ShardingType.TABLE_WISE, rank)
+
+
+def row_wise() -> ParameterSharding:
+    return ParameterSharding(ShardingType.ROW_WISE)
+
+
+def balanced_table_wise_plan(tables: Sequence[EmbeddingBagConfig], world: int) -> Dict[str, ParameterSharding]:
+    """Greedy size-balanced table -> rank assignment (largest table first onto the lightest rank)."""
+    load = [0] * world
+    plan: Dict[str, ParameterSharding] = {}
+    for t in sorted(tables, key=lambda t: -t.num_embeddings * t.embedding_dim):
+        r = min(range(world), key=lambda i: (load[i], i))
+        plan[t.name] = table_wise(r)
+        load[r] += t.num_embeddings * t.embedding_dim
+    return plan
+
+
+class CudaKernelOps:
+    """The compute steps of the sharded path, on the sm_100a kernels (the only shipped table)."""
+
+    def __init__(self):
+        from . import ops
+        self._ops = ops
+
+    def make_group(self, weights, feat_row_base, feat_rows, feat_out_col, out_stride, state0, state1, err_flag):
+        return self._ops.TableGroup(weights=weights, feat_row_base=feat_row_base, feat_rows=feat_rows,
+                                    feat_out_col=feat_out_col, out_stride=out_stride, state0=state0,
+                                    state1=state1, err_flag=err_flag)
+
+    def complete_cumsum(self, lengths):
+        return self._ops.complete_cumsum(lengths)
+
+    def bucketize_row_wise(self, lengths, offsets, indices, block_sizes, F, B, world, err_flag):
+        nl, no, ni, _, _ = self._ops.bucketize_row_wise(lengths, offsets, indices, None, block_sizes, F, B, world,
+                                                        False, err_flag)
+        return nl, no, ni
+
+    def permute_2d(self, permute, B, lengths, offsets, indices, out_total):
+        ol, oo, oi, _ = self._ops.permute_2d(permute, B, lengths, offsets, indices, None, out_total=out_total)
+        return ol, oo, oi
+
+    def embedding_forward(self, group, indices, offsets, B, pooling_mode, out):
+        return self._ops.embedding_forward(group, indices, offsets, B, pooling_mode, out=out)
+
+    def embedding_backward_update(self, group, grad_out, indices, offsets, B, pooling_mode, opt):
+        self._ops.embedding_backward_update(group, grad_out, indices, offsets, B, pooling_mode, opt)
+
+
+class _Shard:
+    """Local storage of one sharding flavour (all TW tables this rank owns, or all RW row blocks)."""
+
+    def __init__(self):
+        self.tables: List[EmbeddingBagConfig] = []
+        self.local_rows: List[int] = []
+        self.row0: List[int] = []
+        self.features: List[int] = []        # global feature indices served, in local order
+        self.feat_table: List[int] = []
+        self.total_rows = 0
+
+    def add(self, table: EmbeddingBagConfig, rows: int, feature_ids: List[int]):
+        self.row0.append(self.total_rows)
+        self.tables.append(table)
+        self.local_rows.append(rows)
+        self.total_rows += rows
+        for f in feature_ids:
+            self.features.append(f)
+            self.feat_table.append(len(self.tables) - 1)
+
+
+class _ShardedLookupFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, anchor, module, values, lengths, B):
+        out, saved = module._forward_impl(values, lengths, B)
+        ctx.module, ctx.saved, ctx.B = module, saved, B
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        ctx.module._backward_impl(grad_out.contiguous(), ctx.saved, ctx.B)
+        return None, None, None, None, None
+
+
+class ShardedEmbeddingBagCollection(nn.Module):
+    """`EmbeddingBagCollection` whose tables are spread over the ranks of `process_group`.
+
+    `plan` maps table name -> `table_wise(rank)` / `row_wise()`.  Every rank feeds its own local
+    batch (same batch size B on every rank) and gets back the pooled embeddings of ITS samples,
+    exactly what the unsharded module would return for them.
+    All tables must share embedding_dim, data_type and pooling in this version.
+    """
+
+    def __init__(self, tables: List[EmbeddingBagConfig], plan: Dict[str, ParameterSharding],
+                 device: torch.device, process_group: Optional[dist.ProcessGroup] = None,
+                 kernel_ops=None, init_seed: int = 0, init_on_device: bool = False):
+        super().__init__()
+        self._pg = process_group
+        self._world = dist.get_world_size(process_group)
+        self._rank = dist.get_rank(process_group)
+        self._ops = kernel_ops if kernel_ops is not None else CudaKernelOps()
+        self._configs = list(tables)
+        W, r = self._world, self._rank
+        dims = {t.embedding_dim for t in tables}
+        kinds = {(t.data_type, t.pooling) for t in tables}
+        if len(dims) != 1 or len(kinds) != 1:
+            raise ValueError("sharded tables must share embedding_dim, data_type and pooling in this version")
+        self._D = tables[0].embedding_dim
+        self._pooling = _lib.POOL_MEAN if tables[0].pooling == PoolingType.MEAN else _lib.POOL_SUM
+        if self._pooling == _lib.POOL_MEAN and any(plan[t.name].sharding_type == ShardingType.ROW_WISE for t in tables):
+            raise ValueError("row-wise sharding supports SUM pooling only (a bag's length is split across ranks)")
+        dtype = torch.float32 if tables[0].data_type.value == "FP32" else torch.bfloat16
+        device = torch.device(device)
+
+        self._feature_names: List[str] = [f for t in tables for f in t.feature_names]
+        F_total = len(self._feature_names)
+        feat_ids: Dict[str, List[int]] = {}
+        k = 0
+        for t in tables:
+            feat_ids[t.name] = list(range(k, k + len(t.feature_names)))
+            k += len(t.feature_names)
+
+        # who serves which feature
+        self._tw_feats: List[List[int]] = [[] for _ in range(W)]   # per owner rank, module order
+        self._rw_feats: List[int] = []
+        self._rw_block: List[int] = []                             # block size per RW feature
+        self._tw, self._rw = _Shard(), _Shard()
+        for t in tables:
+            ps = plan[t.name]
+            if ps.sharding_type == ShardingType.TABLE_WISE:
+                if ps.rank is None or not 0 <= ps.rank < W:
+                    raise ValueError(f"table {t.name}: table-wise owner rank {ps.rank} outside [0, {W})")
+                self._tw_feats[ps.rank] += feat_ids[t.name]
+                if ps.rank == r:
+                    self._tw.add(t, t.num_embeddings, feat_ids[t.name])
+            else:
+                bs = (t.num_embeddings + W - 1) // W
+                self._rw_feats += feat_ids[t.name]
+                self._rw_block += [bs] * len(t.feature_names)
+                self._rw.add(t, max(0, min(bs, t.num_embeddings - r * bs)), feat_ids[t.name])
+        self._F_total = F_total
+        self._n_tw = [len(x) for x in self._tw_feats]
+        self._n_rw = len(self._rw_feats)
+        self._F_local = self._n_tw[r] + self._n_rw
+
+        # storage: identical initial values to an unsharded module built with the same seed would
+        # need a shared generator; each table is drawn from its own seeded stream instead.
+        for name, sh in (("tw", self._tw), ("rw", self._rw)):
+            w = torch.empty((max(sh.total_rows, 1), self._D), dtype=dtype, device=device)
+            for t, r0, rows in zip(sh.tables, sh.row0, sh.local_rows):
+                if init_on_device:          # large tables: draw the local rows in place (not rank-consistent)
+                    w[r0:r0 + rows].uniform_(t.get_weight_init_min(), t.get_weight_init_max())
+                    continue
+                full = self.initial_table(t, init_seed)
+                lo = 0 if sh is self._tw else r * ((t.num_embeddings + W - 1) // W)
+                w[r0:r0 + rows].copy_(full[lo:lo + rows].to(dtype))
+            p = nn.Parameter(w, requires_grad=False)
+            self.register_parameter(f"_{name}_weight", p)
+            n_f = len(sh.features)
+            self.register_buffer(f"_{name}_row_base", torch.tensor([sh.row0[ti] for ti in sh.feat_table] or [0],
+                                                                    dtype=torch.int64, device=device)[:max(n_f, 0)],
+                                 persistent=False)
+            self.register_buffer(f"_{name}_rows", torch.tensor([sh.local_rows[ti] for ti in sh.feat_table] or [0],
+                                                                dtype=torch.int64, device=device)[:max(n_f, 0)],
+                                 persistent=False)
+            self.register_buffer(f"_{name}_out_col", (torch.arange(max(n_f, 1), device=device) * self._D)[:n_f],
+                                 persistent=False)
+        self.register_buffer("_rw_block_sizes", torch.tensor(self._rw_block or [1], dtype=torch.int64, device=device),
+                             persistent=False)
+        self.register_buffer("_err_flag", torch.zeros(1, dtype=torch.int32, device=device), persistent=False)
+
+        # static permutes
+        tw_order = [f for d in range(W) for f in self._tw_feats[d]]
+        self.register_buffer("_tw_send_perm", torch.tensor(tw_order or [0], dtype=torch.int32, device=device),
+                             persistent=False)
+        self.register_buffer("_rw_select_perm", torch.tensor(self._rw_feats or [0], dtype=torch.int32, device=device),
+                             persistent=False)
+        Fl = self._F_local
+        recv_perm = [s * Fl + f for f in range(Fl) for s in range(W)]       # [src][f][b] -> [f][src][b]
+        self.register_buffer("_recv_perm", torch.tensor(recv_perm or [0], dtype=torch.int32, device=device),
+                             persistent=False)
+        self._anchor: Optional[torch.Tensor] = None
+        self._fused: Optional[FusedOptimizer] = None
+        self.set_fused_optimizer(EmbOptimType.EXACT_SGD, learning_rate=0.01)
+
+    # ------------------------------------------------------------------ optimizer
+    def set_fused_optimizer(self, optimizer=EmbOptimType.EXACT_SGD, learning_rate=0.01, eps=1e-8, weight_decay=0.0,
+                            beta1=0.9, beta2=0.999) -> FusedOptimizer:
+        params = {"_tw_weight": self._tw_weight, "_rw_weight": self._rw_weight}
+        self._fused = FusedOptimizer(params, optimizer, learning_rate, eps, weight_decay, beta1, beta2)
+        for p in params.values():
+            p._in_backward_optimizers = [self._fused]
+        return self._fused
+
+    @property
+    def fused_optimizer(self) -> FusedOptimizer:
+        return self._fused
+
+    def _state_for(self, name: str, rows: int):
+        code = self._fused.optimizer.code()
+        w = getattr(self, f"_{name}_weight")
+        st = self._fused.state
+        k0, k1 = f"_{name}_weight.state0", f"_{name}_weight.state1"
+        if code == _lib.OPT_SGD:
+            return None, None
+        if code == _lib.OPT_ROWWISE_ADAGRAD:
+            if k0 not in st:
+                st[k0] = torch.zeros(w.shape[0], dtype=torch.float32, device=w.device)
+            return st[k0], None
+        for k in (k0, k1):
+            if k not in st:
+                st[k] = torch.zeros(tuple(w.shape), dtype=torch.float32, device=w.device)
+        return st[k0], st[k1]
+
+    def _group(self, name: str, with_state: bool):
+        sh = self._tw if name == "tw" else self._rw
+        s0, s1 = self._state_for(name, sh.total_rows) if with_state else (None, None)
+        return self._ops.make_group(getattr(self, f"_{name}_weight").data, getattr(self, f"_{name}_row_base"),
+                                    getattr(self, f"_{name}_rows"), getattr(self, f"_{name}_out_col"),
+                                    len(sh.features) * self._D, s0, s1, self._err_flag)
+
+    # ------------------------------------------------------------------ collectives (plumbing)
+    def _a2a(self, send: torch.Tensor, send_splits: Optional[List[int]], recv_splits: Optional[List[int]],
+             recv_shape_tail=()) -> torch.Tensor:
+        n = sum(recv_splits) if recv_splits is not None else send.shape[0]
+        recv = torch.empty((n, *recv_shape_tail), dtype=send.dtype, device=send.device)
+        dist.all_to_all_single(recv, send.contiguous(), recv_splits, send_splits, group=self._pg)
+        return recv
+
+    # ------------------------------------------------------------------ forward
+    def _forward_impl(self, values, lengths, B):
+        W, r, D, ops = self._world, self._rank, self._D, self._ops
+        dev = values.device
+        offsets = ops.complete_cumsum(lengths)
+        Fl, n_rw = self._F_local, self._n_rw
+
+        # ---- input dist: per-destination blocks  [tw features of d | rw bucket d]
+        len_parts: List[List[torch.Tensor]] = [[] for _ in range(W)]
+        val_parts: List[List[torch.Tensor]] = [[] for _ in range(W)]
+        n_tw_all = sum(self._n_tw)
+        if n_tw_all:
+            tl, to, tv = ops.permute_2d(self._tw_send_perm[:n_tw_all], B, lengths, offsets, values, values.numel())
+            f0 = 0
+            bounds = to[:: max(B, 1)] if B else to
+            for d in range(W):
+                f1 = f0 + self._n_tw[d]
+                len_parts[d].append(tl[f0 * B:f1 * B])
+                val_parts[d].append((tv, bounds, f0, f1))
+                f0 = f1
+        if n_rw:
+            rl, ro, rv = ops.permute_2d(self._rw_select_perm[:n_rw], B, lengths, offsets, values, values.numel())
+            bl, bo, bv = ops.bucketize_row_wise(rl, ro, rv, self._rw_block_sizes[:n_rw], n_rw, B, W, self._err_flag)
+            bbounds = bo[:: max(n_rw * B, 1)]
+            for d in range(W):
+                len_parts[d].append(bl[d * n_rw * B:(d + 1) * n_rw * B])
+                val_parts[d].append((bv, bbounds, d, d + 1))
+        send_lengths = torch.cat([p for d in range(W) for p in len_parts[d]])
+        # value split sizes need host ints: one small device->host read per step
+        bound_list = []
+        for d in range(W):
+            for (_, bnd, i0, i1) in val_parts[d]:
+                bound_list += [bnd[i0], bnd[i1]]
+        b_host = torch.stack(bound_list).tolist() if bound_list else []
+        send_vals, send_splits, k = [], [0] * W, 0
+        for d in range(W):
+            for (buf, _, _, _) in val_parts[d]:
+                lo, hi = b_host[k], b_host[k + 1]
+                k += 2
+                send_vals.append(buf[lo:hi])
+                send_splits[d] += hi - lo
+        send_values = torch.cat(send_vals) if send_vals else values[:0]
+
+        len_send_splits = [(self._n_tw[d] + n_rw) * B for d in range(W)]
+        recv_lengths = self._a2a(send_lengths, len_send_splits, [Fl * B] * W)
+        n_tw_r = self._n_tw[r]
+        if Fl * B:
+            rl3 = recv_lengths.view(W, Fl, B)
+            # per-source id counts and the id count of the TW part: one device->host read
+            host = torch.cat([rl3.sum(dim=(1, 2), dtype=torch.int64),
+                              rl3[:, :n_tw_r].sum(dtype=torch.int64).view(1)]).tolist()
+            recv_splits, tw_total = host[:W], host[W]
+        else:
+            recv_splits, tw_total = [0] * W, 0
+        recv_values = self._a2a(send_values, send_splits, recv_splits)
+
+        # ---- [src][f][b] -> [f][src][b]
+        if Fl:
+            recv_offsets = ops.complete_cumsum(recv_lengths)
+            ll, lo_, lv = ops.permute_2d(self._recv_perm[:Fl * W], B, recv_lengths, recv_offsets, recv_values,
+                                         int(sum(recv_splits)))
+        else:
+            ll = recv_lengths
+            lo_ = torch.zeros(1, dtype=torch.int64, device=dev)
+            lv = recv_values
+        GB = W * B                                            # global batch seen by each local feature
+
+        # ---- lookup on the local storage
+        out = torch.empty((B, self._F_total * D), dtype=torch.float32, device=dev)
+        out3 = out.view(B, self._F_total, D)
+        if n_tw_all:
+            send_rows = None
+            if n_tw_r:
+                tw_out = torch.empty((GB, n_tw_r * D), dtype=torch.float32, device=dev)
+                ops.embedding_forward(self._group("tw", False), lv[:tw_total], lo_[: n_tw_r * GB + 1], GB,
+                                      self._pooling, tw_out)
+                send_rows = tw_out
+            else:
+                send_rows = torch.empty((0,), dtype=torch.float32, device=dev)
+            # output dist TW: rank d returns B rows of n_tw[d]*D floats to every source rank
+            send_flat = send_rows.reshape(-1)
+            recv_flat = self._a2a(send_flat, [B * n_tw_r * D] * W, [B * self._n_tw[d] * D for d in range(W)])
+            pos = 0
+            for d in range(W):
+                n = self._n_tw[d]
+                if n:
+                    out3[:, self._tw_feats[d], :] = recv_flat[pos:pos + B * n * D].view(B, n, D)
+                    pos += B * n * D
+        if n_rw:
+            rw_off = lo_[n_tw_r * GB:] - tw_total if n_tw_r else lo_
+            rw_vals = lv[tw_total:]
+            rw_out = torch.empty((GB, n_rw * D), dtype=torch.float32, device=dev)
+            ops.embedding_forward(self._group("rw", False), rw_vals, rw_off, GB, _lib.POOL_SUM, rw_out)
+            # output dist RW: exchange partial sums, add them in source-rank order
+            recv_flat = self._a2a(rw_out.reshape(-1), [B * n_rw * D] * W, [B * n_rw * D] * W)
+            parts = recv_flat.view(W, B, n_rw, D)
+            acc = parts[0].clone()
+            for s in range(1, W):
+                acc += parts[s]
+            out3[:, self._rw_feats, :] = acc
+            saved_rw = (rw_vals, rw_off)
+        else:
+            saved_rw = None
+        # the TW part of the local ids only: the backward sorts exactly the ids it is given
+        saved = dict(lv=lv[:tw_total], lo=lo_, n_tw_r=n_tw_r, GB=GB, rw=saved_rw)
+        return out, saved
+
+    # ------------------------------------------------------------------ backward
+    def _backward_impl(self, grad_out, saved, B):
+        W, D, ops = self._world, self._D, self._ops
+        self._fused.iteration += 1
+        opt = self._fused.args()
+        g3 = grad_out.view(B, self._F_total, D)
+        GB, n_tw_r, n_rw = saved["GB"], saved["n_tw_r"], self._n_rw
+        if sum(self._n_tw):
+            # reverse all-to-all: the owner of a TW feature gets the gradient rows of every rank's samples
+            send = torch.cat([g3[:, self._tw_feats[d], :].reshape(-1) for d in range(W)])
+            recv = self._a2a(send, [B * self._n_tw[d] * D for d in range(W)], [B * n_tw_r * D] * W)
+            if n_tw_r:
+                ops.embedding_backward_update(self._group("tw", True), recv.view(GB, n_tw_r * D), saved["lv"],
+                                              saved["lo"][: n_tw_r * GB + 1], GB, self._pooling, opt)
+        if n_rw:
+            mine = g3[:, self._rw_feats, :].reshape(B, n_rw * D).contiguous()
+            full = torch.empty((GB, n_rw * D), dtype=torch.float32, device=grad_out.device)
+            dist.all_gather_into_tensor(full, mine, group=self._pg)
+            rw_vals, rw_off = saved["rw"]
+            ops.embedding_backward_update(self._group("rw", True), full, rw_vals, rw_off, GB, _lib.POOL_SUM, opt)
+
+    def forward(self, features: KeyedJaggedTensor) -> KeyedTensor:
+        if list(features.keys()) != self._feature_names:
+            keys = list(features.keys())
+            features = features.permute([keys.index(k) for k in self._feature_names])
+        values, lengths, B = features.values(), features.lengths(), features.stride()
+        if self.training and torch.is_grad_enabled():
+            if self._anchor is None or self._anchor.device != values.device:
+                self._anchor = torch.zeros(1, device=values.device, requires_grad=True)
+            out = _ShardedLookupFn.apply(self._anchor, self, values, lengths, B)
+        else:
+            out, _ = self._forward_impl(values, lengths, B)
+        return KeyedTensor(self._feature_names, [self._D] * self._F_total, out)
+
+    # ------------------------------------------------------------------ inspection helpers
+    def local_table(self, name: str) -> torch.Tensor:
+        """This rank's rows of table `name` (whole table for TW on the owner, the row block for RW)."""
+        for shn, sh in (("tw", self._tw), ("rw", self._rw)):
+            for t, r0, rows in zip(sh.tables, sh.row0, sh.local_rows):
+                if t.name == name:
+                    return getattr(self, f"_{shn}_weight")[r0:r0 + rows]
+        return torch.empty((0, self._D))
+
+    @staticmethod
+    def initial_table(table: EmbeddingBagConfig, init_seed: int = 0) -> torch.Tensor:
+        """The full initial value of `table` as every rank draws it (for tests / checkpoints)."""
+        g = torch.Generator(device="cpu").manual_seed(init_seed * 1_000_003 + zlib.crc32(table.name.encode()) % 1_000_003)
+        return torch.empty((table.num_embeddings, table.embedding_dim), dtype=torch.float32).uniform_(
+            table.get_weight_init_min(), table.get_weight_init_max(), generator=g)

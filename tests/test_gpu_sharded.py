@@ -1,0 +1,85 @@
+"""The sharded path on real GPUs (needs >= 2): same invariant as tests/test_sharded_gloo.py, but
+with the CUDA kernels and NCCL.  Skipped on a single-GPU box."""
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import oracle as orc
+from test_sharded_gloo import B, D, W, free_port, global_batch, local_batch, make_tables
+
+pytestmark = pytest.mark.gpu
+
+
+def run_rank(rank, port, plan_kind, results):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=W, device_id=dev)
+    try:
+        import tdfo_b200 as t
+        from tdfo_b200 import distributed as td
+        tables = make_tables(t)
+        rows = [c.num_embeddings for c in tables]
+        plan = {"tw": {"t0": td.table_wise(0), "t1": td.table_wise(1), "t2": td.table_wise(0), "t3": td.table_wise(1),
+                       "t4": td.table_wise(1)},
+                "rw": {c.name: td.row_wise() for c in tables},
+                "mixed": {"t0": td.table_wise(1), "t1": td.row_wise(), "t2": td.table_wise(0), "t3": td.row_wise(),
+                          "t4": td.table_wise(1)}}[plan_kind]
+        m = td.ShardedEmbeddingBagCollection(tables, plan, dev, init_seed=3)
+        m.set_fused_optimizer(t.EmbOptimType.EXACT_ROWWISE_ADAGRAD, learning_rate=0.05, eps=1e-8)
+        m.train()
+        lengths, idx, grad = local_batch(rank, rows)
+        kjt = t.KeyedJaggedTensor.from_lengths_sync([f"f{i}" for i in range(len(rows))], torch.from_numpy(idx),
+                                                    torch.from_numpy(lengths)).to(dev)
+        out = m(kjt).values()
+        (out * torch.from_numpy(grad).to(dev)).sum().backward()
+        torch.cuda.synchronize()
+        assert int(m._err_flag.item()) == 0
+
+        full = np.concatenate([td.ShardedEmbeddingBagCollection.initial_table(c, 3).numpy() for c in tables])
+        base = np.concatenate([[0], np.cumsum(rows)[:-1]]).astype(np.int64)
+        col = (np.arange(len(rows)) * D).astype(np.int64)
+        want, _ = orc.embedding_forward(full, D, idx, orc.complete_cumsum(lengths), None, base, rows, col,
+                                        len(rows), B, orc.POOL_SUM)
+        np.testing.assert_allclose(out.detach().cpu().numpy(), want, rtol=1e-5, atol=1e-6)
+        g_len, g_idx, g_grad = global_batch(rows)
+        w_ref, h_ref = full.copy(), np.zeros(sum(rows), np.float32)
+        orc.embedding_backward_update(w_ref, D, h_ref, None, g_grad, g_idx, orc.complete_cumsum(g_len), base, rows, col,
+                                      len(rows), W * B, orc.POOL_SUM, orc.OptArgs(orc.OPT_ROWWISE_ADAGRAD, 0.05, 1e-8))
+        mine = {c.name: m.local_table(c.name).detach().cpu().numpy().copy() for c in tables}
+        gathered = [None] * W
+        dist.all_gather_object(gathered, mine)
+        for i, c in enumerate(tables):
+            ps = plan[c.name]
+            got = gathered[ps.rank][c.name] if ps.sharding_type == td.ShardingType.TABLE_WISE else \
+                np.concatenate([gathered[r][c.name] for r in range(W)])
+            np.testing.assert_allclose(got, w_ref[base[i]:base[i] + rows[i]], rtol=1e-5, atol=2e-6,
+                                       err_msg=f"table {c.name} ({plan_kind})")
+        results[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("plan_kind", ["tw", "rw", "mixed"])
+def test_sharded_equals_unsharded_on_2_gpus(plan_kind):
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    port = free_port()
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        results = mgr.dict()
+        procs = [ctx.Process(target=run_rank, args=(r, port, plan_kind, results)) for r in range(W)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=300)
+        for p in procs:
+            if p.is_alive():
+                p.terminate()
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        assert dict(results) == {0: "ok", 1: "ok"}

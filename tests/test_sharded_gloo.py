@@ -1,0 +1,136 @@
+"""World-size-2 (gloo, CPU) test of the sharded path's host logic: input dist (permute /
+bucketise / two all-to-alls / recv permute), output dist (all-to-all for table-wise, ordered
+partial-sum exchange for row-wise) and the reverse exchanges in backward.
+
+Invariant (the one torchrec's own sharding tests use): every rank's sharded
+output equals the unsharded lookup of its local batch, and after one backward the gathered
+shards equal the unsharded fused update applied to the global batch.  The compute kernels are
+replaced by the oracle-backed table from tests/oracle_ops.py, so this covers routing only;
+the same test runs the CUDA kernels on 2 GPUs in tests/test_gpu_sharded.py."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import oracle as orc
+
+W, B, D = 2, 6, 8
+
+
+def free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def make_tables(t):
+    cfg = lambda name, rows, feats: t.EmbeddingBagConfig(num_embeddings=rows, embedding_dim=D, name=name,
+                                                         feature_names=feats, pooling=t.PoolingType.SUM)
+    return [cfg("t0", 50, ["f0"]), cfg("t1", 41, ["f1"]), cfg("t2", 30, ["f2"]), cfg("t3", 17, ["f3"]),
+            cfg("t4", 9, ["f4"])]
+
+
+def local_batch(rank, rows):
+    rng = np.random.default_rng(100 + rank)
+    F = len(rows)
+    lengths = rng.integers(0, 5, size=F * B).astype(np.int32)
+    lengths[rank::7] = 0
+    offsets = orc.complete_cumsum(lengths)
+    idx = np.concatenate([rng.integers(0, rows[f], size=int(offsets[(f + 1) * B] - offsets[f * B])) for f in range(F)])
+    grad = rng.normal(size=(B, F * D)).astype(np.float32)
+    return lengths, idx.astype(np.int64), grad
+
+
+def global_batch(rows):
+    """Concatenate the ranks' batches per feature: sample index = rank * B + b."""
+    F = len(rows)
+    per = [local_batch(r, rows) for r in range(W)]
+    lengths = np.concatenate([per[r][0].reshape(F, B)[f] for f in range(F) for r in range(W)]).astype(np.int32)
+    idx_parts = []
+    for f in range(F):
+        for r in range(W):
+            off = orc.complete_cumsum(per[r][0])
+            idx_parts.append(per[r][1][off[f * B]:off[(f + 1) * B]])
+    grad = np.concatenate([per[r][2] for r in range(W)], axis=0)
+    return lengths, np.concatenate(idx_parts), grad
+
+
+def run_rank(rank, port, plan_kind, optimizer_name, results):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=W)
+    try:
+        import tdfo_b200 as t
+        from tdfo_b200 import distributed as td
+        from oracle_ops import OracleKernelOps
+        tables = make_tables(t)
+        rows = [c.num_embeddings for c in tables]
+        if plan_kind == "tw":
+            plan = {"t0": td.table_wise(0), "t1": td.table_wise(1), "t2": td.table_wise(0), "t3": td.table_wise(1),
+                    "t4": td.table_wise(1)}
+        elif plan_kind == "rw":
+            plan = {c.name: td.row_wise() for c in tables}
+        else:
+            plan = {"t0": td.table_wise(1), "t1": td.row_wise(), "t2": td.table_wise(0), "t3": td.row_wise(),
+                    "t4": td.table_wise(1)}
+        m = td.ShardedEmbeddingBagCollection(tables, plan, torch.device("cpu"), kernel_ops=OracleKernelOps(), init_seed=3)
+        opt_type = getattr(t.EmbOptimType, optimizer_name)
+        m.set_fused_optimizer(opt_type, learning_rate=0.05, eps=1e-8)
+        m.train()
+        lengths, idx, grad = local_batch(rank, rows)
+        kjt = t.KeyedJaggedTensor.from_lengths_sync([f"f{i}" for i in range(len(rows))], torch.from_numpy(idx),
+                                                    torch.from_numpy(lengths))
+        out = m(kjt).values()
+        (out * torch.from_numpy(grad)).sum().backward()
+
+        # ---- unsharded oracle on the same data
+        full = np.concatenate([td.ShardedEmbeddingBagCollection.initial_table(c, 3).numpy() for c in tables])
+        base = np.concatenate([[0], np.cumsum(rows)[:-1]]).astype(np.int64)
+        col = (np.arange(len(rows)) * D).astype(np.int64)
+        want, _ = orc.embedding_forward(full, D, idx, orc.complete_cumsum(lengths), None, base, rows, col,
+                                        len(rows), B, orc.POOL_SUM)
+        np.testing.assert_allclose(out.detach().numpy(), want, rtol=1e-5, atol=1e-6)
+
+        g_len, g_idx, g_grad = global_batch(rows)
+        w_ref = full.copy()
+        code = {"EXACT_SGD": orc.OPT_SGD, "EXACT_ROWWISE_ADAGRAD": orc.OPT_ROWWISE_ADAGRAD}[optimizer_name]
+        h_ref = np.zeros(sum(rows), np.float32)
+        orc.embedding_backward_update(w_ref, D, h_ref, None, g_grad, g_idx, orc.complete_cumsum(g_len), base, rows, col,
+                                      len(rows), W * B, orc.POOL_SUM, orc.OptArgs(code, 0.05, 1e-8))
+        mine = {c.name: m.local_table(c.name).detach().numpy().copy() for c in tables}
+        gathered = [None] * W
+        dist.all_gather_object(gathered, mine)
+        for i, c in enumerate(tables):
+            ps = plan[c.name]
+            if ps.sharding_type == td.ShardingType.TABLE_WISE:
+                got = gathered[ps.rank][c.name]
+            else:
+                got = np.concatenate([gathered[r][c.name] for r in range(W)])
+            np.testing.assert_allclose(got, w_ref[base[i]:base[i] + rows[i]], rtol=1e-5, atol=1e-6,
+                                       err_msg=f"table {c.name} ({plan_kind})")
+        results[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("plan_kind,optimizer_name", [("tw", "EXACT_SGD"), ("rw", "EXACT_ROWWISE_ADAGRAD"),
+                                                      ("mixed", "EXACT_ROWWISE_ADAGRAD")])
+def test_sharded_equals_unsharded_world2(plan_kind, optimizer_name):
+    port = free_port()
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        results = mgr.dict()
+        procs = [ctx.Process(target=run_rank, args=(r, port, plan_kind, optimizer_name, results)) for r in range(W)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=180)
+        for p in procs:
+            if p.is_alive():
+                p.terminate()
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        assert dict(results) == {0: "ok", 1: "ok"}
