@@ -198,6 +198,27 @@ int tdfo_embedding_forward(const void* weights, int32_t weights_dtype, int64_t t
                            uint32_t* sort_keys, uint32_t* sort_vals,
                            int32_t* err_flag, void* stream);
 
+/*
+ * Pooled lookup with the table-wise output dist fused in: the B bags of every local feature
+ * cover the GLOBAL batch (world * peer_batch samples, source-rank major), and the pooled row of
+ * sample b is stored straight into the output buffer of its source rank b / peer_batch:
+ *   peer_out[src] + (b % peer_batch) * out_stride + feat_out_col[f]
+ * peer_out is a device array of `B / peer_batch` base addresses (as uint64), one per source rank,
+ * pointing into NVLink peer memory (e.g. a torch symmetric-memory buffer); the caller puts a
+ * barrier between this call and the readers.  Everything else as tdfo_embedding_forward.
+ * Replaces: TBE forward + PooledEmbeddingsAllToAll of the sharded module DMP builds
+ *   (torchrec/train.py:241-247, 98).
+ */
+int tdfo_embedding_forward_peer(const void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
+                                const int64_t* indices, const int64_t* offsets,
+                                const float* per_sample_weights,
+                                const int64_t* feat_row_base, const int64_t* feat_rows,
+                                const int64_t* feat_out_col,
+                                int32_t F, int64_t B, int64_t L, int32_t pooling_mode,
+                                const uint64_t* peer_out, int64_t peer_batch, int64_t out_stride,
+                                uint32_t* sort_keys, uint32_t* sort_vals,
+                                int32_t* err_flag, void* stream);
+
 /* ------------------------------------------------------------------ backward */
 
 /*
@@ -322,6 +343,19 @@ int tdfo_embedding_backward_update(void* weights, int32_t weights_dtype, int64_t
                                    int32_t keys_in_scratch,
                                    int32_t* err_flag,
                                    void* scratch, size_t scratch_bytes, void* stream);
+
+/*
+ * Output dist helper: move pooled rows between the per-rank exchange layout
+ * ([rank][batch][features of that rank * D]) and the KeyedTensor layout ([batch][all features * D]).
+ * Slot j copies B rows of D floats: src[src_off[j] + b*src_stride[j] ..] -> dst[dst_off[j] + b*dst_stride[j] ..].
+ * meta = device int64[4*nslots] = src_off | src_stride | dst_off | dst_stride (elements; multiples of 4).
+ * With dst == NULL the dst_off entries are absolute addresses divided by 4, so different slots can
+ * target different buffers, including NVLink peer memory (gradient rows pushed to the table owners).
+ * Replaces: the column permute after PooledEmbeddingsAllToAll in the sharded module DMP builds
+ *   (torchrec/train.py:241-247), and its gradient.
+ */
+int tdfo_copy_feature_blocks(const float* src, float* dst, int64_t B, int32_t D, int32_t nslots,
+                             const int64_t* meta, void* stream);
 
 /* ------------------------------------------------------------------ jagged */
 

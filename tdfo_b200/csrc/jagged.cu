@@ -174,6 +174,24 @@ __global__ void jagged_1d_to_padded_dense_kernel(const int64_t* __restrict__ val
     }
 }
 
+// Strided block copy used around the pooled-output exchanges: slot j moves B rows of D floats
+// from src + src_off[j] (+ b * src_stride[j]) to dst + dst_off[j] (+ b * dst_stride[j]).
+__global__ void copy_feature_blocks_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t B,
+                                           int32_t D4, int32_t nslots, const int64_t* __restrict__ meta) {
+    const int64_t total = (int64_t)nslots * B * D4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i % D4);
+        const int64_t rb = i / D4;
+        const int j = (int)(rb % nslots);
+        const int64_t b = rb / nslots;
+        const int64_t so = __ldg(meta + j), ss = __ldg(meta + nslots + j);
+        const int64_t dof = __ldg(meta + 2 * nslots + j), ds = __ldg(meta + 3 * nslots + j);
+        const uint4 v = __ldcs(reinterpret_cast<const uint4*>(src + so + b * ss) + c);
+        __stcs(reinterpret_cast<uint4*>(dst + dof + b * ds) + c, v);
+    }
+}
+
 static unsigned grid_for(int64_t items, int threads) {
     int64_t blocks = (items + threads - 1) / threads;
     const int64_t cap = (int64_t)kNumSMs * 32;
@@ -311,5 +329,18 @@ extern "C" int tdfo_jagged_1d_to_padded_dense(const int64_t* values, const int64
         values, offsets, B, desired_length, padding_value, dense);
     count_launch();
     TDFO_LAUNCH_CHECK("jagged_1d_to_padded_dense");
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_copy_feature_blocks(const float* src, float* dst, int64_t B, int32_t D, int32_t nslots,
+                                        const int64_t* meta, void* stream) {
+    TDFO_CHECK_ARG(B >= 0 && D > 0 && D % 4 == 0 && nslots >= 0, "copy_feature_blocks: bad size (D must be a multiple of 4)");
+    if (B == 0 || nslots == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(src && meta, "copy_feature_blocks: null pointer");   // dst == NULL: absolute destinations
+    TDFO_CHECK_ARG(aligned(src, 16) && aligned(dst, 16), "copy_feature_blocks: buffers not 16-byte aligned");
+    copy_feature_blocks_kernel<<<grid_for((int64_t)nslots * B * (D / 4), 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        src, dst, B, D / 4, nslots, meta);
+    count_launch();
+    TDFO_LAUNCH_CHECK("copy_feature_blocks");
     return TDFO_OK;
 }

@@ -19,6 +19,8 @@ struct LookupArgs {
     const int64_t* feat_rows;
     const int64_t* feat_out_col;
     float* out;
+    const uint64_t* peer_out;   // optional: out base pointer of every source rank (NVLink peer memory)
+    int64_t peer_batch;         // samples per source rank when peer_out is set
     uint32_t* sort_keys;   // optional: backward's (row key, payload) pairs, emitted while the ids are in registers
     uint32_t* sort_vals;
     int32_t* err_flag;
@@ -187,7 +189,17 @@ pooled_forward_kernel(const LookupArgs a) {
 
         if (grp == 0) {
             const float scale = (a.mean && cur.e > cur.s) ? 1.f / (float)(cur.e - cur.s) : 1.f;
-            float* orow = a.out + b * a.out_stride + __ldg(a.feat_out_col + f);
+            // Sharded table-wise output dist fused into the lookup: sample b of the global batch
+            // belongs to source rank b / peer_batch, and its pooled row is stored straight into
+            // that rank's output buffer over NVLink instead of going through an all-to-all.
+            float* obase = a.out;
+            int64_t brow = b;
+            if (a.peer_out) {
+                const int64_t src = b / a.peer_batch;
+                brow = b - src * a.peer_batch;
+                obase = reinterpret_cast<float*>(__ldg(a.peer_out + src));
+            }
+            float* orow = obase + brow * a.out_stride + __ldg(a.feat_out_col + f);
 #pragma unroll
             for (int k = 0; k < CPL; ++k) {
                 const int c = sub + k * LPR;
@@ -303,14 +315,15 @@ static int dispatch_forward(const LookupArgs& a, int pooling_mode, cudaStream_t 
 
 using namespace tdfo;
 
-extern "C" int tdfo_embedding_forward(const void* weights, int32_t weights_dtype, int64_t total_rows,
-                                      int32_t D, const int64_t* indices, const int64_t* offsets,
-                                      const float* per_sample_weights,
-                                      const int64_t* feat_row_base, const int64_t* feat_rows,
-                                      const int64_t* feat_out_col, int32_t F, int64_t B, int64_t L,
-                                      int32_t pooling_mode, float* out, int64_t out_stride,
-                                      uint32_t* sort_keys, uint32_t* sort_vals,
-                                      int32_t* err_flag, void* stream) {
+static int embedding_forward_impl(const void* weights, int32_t weights_dtype, int64_t total_rows,
+                                  int32_t D, const int64_t* indices, const int64_t* offsets,
+                                  const float* per_sample_weights,
+                                  const int64_t* feat_row_base, const int64_t* feat_rows,
+                                  const int64_t* feat_out_col, int32_t F, int64_t B, int64_t L,
+                                  int32_t pooling_mode, float* out, int64_t out_stride,
+                                  const uint64_t* peer_out, int64_t peer_batch,
+                                  uint32_t* sort_keys, uint32_t* sort_vals,
+                                  int32_t* err_flag, void* stream) {
     TDFO_CHECK_ARG(weights_dtype == TDFO_F32 || weights_dtype == TDFO_BF16,
                    "embedding_forward: unknown weights_dtype %d", weights_dtype);
     TDFO_CHECK_ARG(pooling_mode >= TDFO_POOL_SUM && pooling_mode <= TDFO_POOL_NONE,
@@ -323,9 +336,15 @@ extern "C" int tdfo_embedding_forward(const void* weights, int32_t weights_dtype
                    "embedding_forward: total_rows %lld must be < 2^32-1", (long long)total_rows);
     if (F == 0 || B == 0 || L == 0 && pooling_mode == TDFO_POOL_NONE) return TDFO_OK;
     TDFO_CHECK_ARG(total_rows >= 1, "embedding_forward: the storage group has no rows");
-    TDFO_CHECK_ARG(weights && (indices || L == 0) && offsets && feat_row_base && feat_rows && out,
+    TDFO_CHECK_ARG(weights && (indices || L == 0) && offsets && feat_row_base && feat_rows && (out || peer_out),
                    "embedding_forward: null pointer");
     TDFO_CHECK_ARG(aligned(weights, 16) && aligned(out, 16), "embedding_forward: weights/out not 16-byte aligned");
+    if (peer_out) {
+        TDFO_CHECK_ARG(pooling_mode != TDFO_POOL_NONE, "embedding_forward_peer: pooled modes only");
+        TDFO_CHECK_ARG(peer_batch > 0 && B % peer_batch == 0,
+                       "embedding_forward_peer: batch %lld is not a multiple of the per-rank batch %lld",
+                       (long long)B, (long long)peer_batch);
+    }
     if (pooling_mode != TDFO_POOL_NONE) {
         TDFO_CHECK_ARG(feat_out_col != nullptr, "embedding_forward: feat_out_col is null");
         TDFO_CHECK_ARG(out_stride % 4 == 0, "embedding_forward: out_stride %lld not a multiple of 4",
@@ -340,10 +359,40 @@ extern "C" int tdfo_embedding_forward(const void* weights, int32_t weights_dtype
                    "embedding_forward: sort_keys and sort_vals must both be given or both be null");
     TDFO_CHECK_ARG(sort_keys == nullptr || ((int64_t)F * B < (1ll << 32) && L < (1ll << 32)),
                    "embedding_forward: sort keys need F*B and L below 2^32");
-    a.out = out; a.sort_keys = sort_keys; a.sort_vals = sort_vals; a.oob_key = (uint32_t)total_rows; a.err_flag = err_flag; a.B = B; a.num_bags = (int64_t)F * B; a.L = L;
+    a.out = out; a.peer_out = peer_out; a.peer_batch = peer_batch; a.sort_keys = sort_keys; a.sort_vals = sort_vals; a.oob_key = (uint32_t)total_rows; a.err_flag = err_flag; a.B = B; a.num_bags = (int64_t)F * B; a.L = L;
     a.out_stride = out_stride; a.F = F; a.nchunks = (int32_t)(D * esz / 16);
     a.mean = pooling_mode == TDFO_POOL_MEAN;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     return weights_dtype == TDFO_F32 ? dispatch_forward<float>(a, pooling_mode, st)
                                      : dispatch_forward<__nv_bfloat16>(a, pooling_mode, st);
+}
+
+extern "C" int tdfo_embedding_forward(const void* weights, int32_t weights_dtype, int64_t total_rows,
+                                      int32_t D, const int64_t* indices, const int64_t* offsets,
+                                      const float* per_sample_weights,
+                                      const int64_t* feat_row_base, const int64_t* feat_rows,
+                                      const int64_t* feat_out_col, int32_t F, int64_t B, int64_t L,
+                                      int32_t pooling_mode, float* out, int64_t out_stride,
+                                      uint32_t* sort_keys, uint32_t* sort_vals,
+                                      int32_t* err_flag, void* stream) {
+    return embedding_forward_impl(weights, weights_dtype, total_rows, D, indices, offsets, per_sample_weights,
+                                  feat_row_base, feat_rows, feat_out_col, F, B, L, pooling_mode, out, out_stride,
+                                  nullptr, 0, sort_keys, sort_vals, err_flag, stream);
+}
+
+extern "C" int tdfo_embedding_forward_peer(const void* weights, int32_t weights_dtype, int64_t total_rows,
+                                           int32_t D, const int64_t* indices, const int64_t* offsets,
+                                           const float* per_sample_weights,
+                                           const int64_t* feat_row_base, const int64_t* feat_rows,
+                                           const int64_t* feat_out_col, int32_t F, int64_t B, int64_t L,
+                                           int32_t pooling_mode, const uint64_t* peer_out, int64_t peer_batch,
+                                           int64_t out_stride, uint32_t* sort_keys, uint32_t* sort_vals,
+                                           int32_t* err_flag, void* stream) {
+    if (!peer_out) {
+        set_error("embedding_forward_peer: peer_out is null");
+        return TDFO_ERR_INVALID_ARG;
+    }
+    return embedding_forward_impl(weights, weights_dtype, total_rows, D, indices, offsets, per_sample_weights,
+                                  feat_row_base, feat_rows, feat_out_col, F, B, L, pooling_mode, nullptr, out_stride,
+                                  peer_out, peer_batch, sort_keys, sort_vals, err_flag, stream);
 }

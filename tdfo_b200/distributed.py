@@ -94,11 +94,22 @@ class CudaKernelOps:
         ol, oo, oi, _ = self._ops.permute_2d(permute, B, lengths, offsets, indices, None, out_total=out_total)
         return ol, oo, oi
 
-    def embedding_forward(self, group, indices, offsets, B, pooling_mode, out):
-        return self._ops.embedding_forward(group, indices, offsets, B, pooling_mode, out=out)
+    def embedding_forward(self, group, indices, offsets, B, pooling_mode, out, backward_scratch=None):
+        return self._ops.embedding_forward(group, indices, offsets, B, pooling_mode, out=out,
+                                           backward_scratch=backward_scratch)
 
-    def embedding_backward_update(self, group, grad_out, indices, offsets, B, pooling_mode, opt):
-        self._ops.embedding_backward_update(group, grad_out, indices, offsets, B, pooling_mode, opt)
+    def embedding_backward_update(self, group, grad_out, indices, offsets, B, pooling_mode, opt, scratch=None,
+                                  keys_in_scratch=False):
+        self._ops.embedding_backward_update(group, grad_out, indices, offsets, B, pooling_mode, opt, scratch=scratch,
+                                            keys_in_scratch=keys_in_scratch)
+
+    def embedding_forward_peer(self, group, indices, offsets, B, pooling_mode, peer_out, peer_batch,
+                               backward_scratch=None):
+        self._ops.embedding_forward_peer(group, indices, offsets, B, pooling_mode, peer_out, peer_batch,
+                                         backward_scratch=backward_scratch)
+
+    def copy_feature_blocks(self, src, dst, B, D, meta):
+        self._ops.copy_feature_blocks(src, dst, B, D, meta)
 
 
 class _Shard:
@@ -120,6 +131,33 @@ class _Shard:
         for f in feature_ids:
             self.features.append(f)
             self.feat_table.append(len(self.tables) - 1)
+
+
+class _PeerExchange:
+    """Symmetric (NVLink peer-mapped) buffers of one sharded module for a given local batch size:
+    two rotating output buffers [B, F_total*D] that the owners of table-wise features store pooled
+    rows into, and one gradient landing buffer per rank that the sample owners push gradient rows
+    into.  Barriers are the symmetric-memory signal-pad barriers, enqueued on the current stream."""
+
+    def __init__(self, pg, device, B: int, F_total: int, D: int, n_tw: List[int]):
+        import torch.distributed._symmetric_memory as symm
+        W = len(n_tw)
+        group = pg if pg is not None else dist.group.WORLD
+        try:
+            symm.enable_symm_mem_for_group(group.group_name)
+        except Exception:
+            pass
+        self.B = B
+        self.out = [symm.empty(B * F_total * D, dtype=torch.float32, device=device) for _ in range(2)]
+        self.out_hdl = [symm.rendezvous(t_, group) for t_ in self.out]
+        self.out_ptrs = [torch.tensor(list(h.buffer_ptrs), dtype=torch.int64, device=device) for h in self.out_hdl]
+        self.grad = symm.empty(max(W * B * max(n_tw) * D, 4), dtype=torch.float32, device=device)
+        self.grad_hdl = symm.rendezvous(self.grad, group)
+        self.grad_ptrs = list(self.grad_hdl.buffer_ptrs)
+        self.step = 0
+
+    def barrier(self):
+        self.grad_hdl.barrier(channel=0)
 
 
 class _ShardedLookupFn(torch.autograd.Function):
@@ -146,7 +184,8 @@ class ShardedEmbeddingBagCollection(nn.Module):
 
     def __init__(self, tables: List[EmbeddingBagConfig], plan: Dict[str, ParameterSharding],
                  device: torch.device, process_group: Optional[dist.ProcessGroup] = None,
-                 kernel_ops=None, init_seed: int = 0, init_on_device: bool = False):
+                 kernel_ops=None, init_seed: int = 0, init_on_device: bool = False,
+                 peer_memory: Optional[bool] = None):
         super().__init__()
         self._pg = process_group
         self._world = dist.get_world_size(process_group)
@@ -232,9 +271,68 @@ class ShardedEmbeddingBagCollection(nn.Module):
         recv_perm = [s * Fl + f for f in range(Fl) for s in range(W)]       # [src][f][b] -> [f][src][b]
         self.register_buffer("_recv_perm", torch.tensor(recv_perm or [0], dtype=torch.int32, device=device),
                              persistent=False)
+        # strided-copy tables between the exchange layout [rank d][B][n_tw[d]*D] and the output
+        # [B][F_total*D]; slots = TW features in owner order
+        D_ = self._D
+        so, ss, do, ds = [], [], [], []
+        self._tw_block_off: List[int] = []          # element offset of rank d's block for batch size 1
+        acc = 0
+        for d in range(W):
+            self._tw_block_off.append(acc)
+            acc += self._n_tw[d] * D_
+        self._tw_cols_total = acc
+        self._unpack_slots = [(d, j, f) for d in range(W) for j, f in enumerate(self._tw_feats[d])]
         self._anchor: Optional[torch.Tensor] = None
         self._fused: Optional[FusedOptimizer] = None
+        self._meta_cache: Dict[tuple, torch.Tensor] = {}
+        self._scratch: Dict[str, torch.Tensor] = {}
+        self._emit_keys = False                      # set per forward: training with the CUDA kernel table
+        self._fwd_token = 0
+        # Table-wise output dist / gradient return through NVLink peer memory instead of NCCL
+        # all-to-alls (needs the CUDA kernels and symmetric memory; on by default when available).
+        if peer_memory is None:
+            peer_memory = (isinstance(self._ops, CudaKernelOps) and W > 1 and device.type == "cuda"
+                           and sum(self._n_tw) > 0)
+        self._use_peer = bool(peer_memory)
+        self._peer: Optional[_PeerExchange] = None
+        self.register_buffer("_tw_global_col", torch.tensor([f * self._D for f in self._tw.features] or [0],
+                                                            dtype=torch.int64, device=device)[:len(self._tw.features)],
+                             persistent=False)
         self.set_fused_optimizer(EmbOptimType.EXACT_SGD, learning_rate=0.01)
+
+    def _tw_meta(self, B: int, to_output: bool, device) -> torch.Tensor:
+        """Copy table for batch size B: exchange layout <-> KeyedTensor layout (cached per B)."""
+        key = (B, to_output, str(device))
+        m = self._meta_cache.get(key)
+        if m is None:
+            D_, Ft = self._D, self._F_total
+            ex_off, ex_stride, kt_off, kt_stride = [], [], [], []
+            for (d, j, f) in self._unpack_slots:
+                ex_off.append(self._tw_block_off[d] * B + j * D_)
+                ex_stride.append(self._n_tw[d] * D_)
+                kt_off.append(f * D_)
+                kt_stride.append(Ft * D_)
+            rows = [ex_off, ex_stride, kt_off, kt_stride] if to_output else [kt_off, kt_stride, ex_off, ex_stride]
+            m = torch.tensor(rows, dtype=torch.int64, device=device).reshape(-1)
+            self._meta_cache[key] = m
+        return m
+
+    def _peer_grad_meta(self, B: int, device) -> torch.Tensor:
+        """Copy table: my gradient columns -> rows [rank*B, rank*B + B) of each owner's landing buffer."""
+        key = (B, "peer_grad", str(device))
+        m = self._meta_cache.get(key)
+        if m is None:
+            D_, Ft, r = self._D, self._F_total, self._rank
+            so, ss, do, ds = [], [], [], []
+            for (d, j, f) in self._unpack_slots:
+                n = self._n_tw[d]
+                so.append(f * D_)
+                ss.append(Ft * D_)
+                do.append(self._peer.grad_ptrs[d] // 4 + r * B * n * D_ + j * D_)     # absolute address / 4
+                ds.append(n * D_)
+            m = torch.tensor([so, ss, do, ds], dtype=torch.int64, device=device).reshape(-1)
+            self._meta_cache[key] = m
+        return m
 
     # ------------------------------------------------------------------ optimizer
     def set_fused_optimizer(self, optimizer=EmbOptimType.EXACT_SGD, learning_rate=0.01, eps=1e-8, weight_decay=0.0,
@@ -350,29 +448,43 @@ class ShardedEmbeddingBagCollection(nn.Module):
         # ---- lookup on the local storage
         out = torch.empty((B, self._F_total * D), dtype=torch.float32, device=dev)
         out3 = out.view(B, self._F_total, D)
-        if n_tw_all:
+        peer = None
+        if n_tw_all and self._use_peer:
+            if self._peer is None or self._peer.B != B:
+                self._peer = _PeerExchange(self._pg, dev, B, self._F_total, D, self._n_tw)
+            peer = self._peer
+            k = peer.step % 2
+            peer.step += 1
+            out = peer.out[k].view(B, self._F_total * D)
+            out3 = out.view(B, self._F_total, D)
+            # every rank is past all readers of this buffer's previous contents before anyone writes
+            peer.barrier()
+            if n_tw_r:
+                grp = self._group("tw", False)
+                grp.feat_out_col = self._tw_global_col        # columns of the final [B, F_total*D] layout
+                grp.out_stride = self._F_total * D
+                self._ops.embedding_forward_peer(grp, lv[:tw_total], lo_[: n_tw_r * GB + 1], GB, self._pooling,
+                                                 peer.out_ptrs[k], B, self._bw_scratch("tw", tw_total, dev))
+            peer.barrier()                                    # all pooled rows have landed
+        elif n_tw_all:
             send_rows = None
             if n_tw_r:
                 tw_out = torch.empty((GB, n_tw_r * D), dtype=torch.float32, device=dev)
                 ops.embedding_forward(self._group("tw", False), lv[:tw_total], lo_[: n_tw_r * GB + 1], GB,
-                                      self._pooling, tw_out)
+                                      self._pooling, tw_out, self._bw_scratch("tw", tw_total, dev))
                 send_rows = tw_out
             else:
                 send_rows = torch.empty((0,), dtype=torch.float32, device=dev)
             # output dist TW: rank d returns B rows of n_tw[d]*D floats to every source rank
             send_flat = send_rows.reshape(-1)
             recv_flat = self._a2a(send_flat, [B * n_tw_r * D] * W, [B * self._n_tw[d] * D for d in range(W)])
-            pos = 0
-            for d in range(W):
-                n = self._n_tw[d]
-                if n:
-                    out3[:, self._tw_feats[d], :] = recv_flat[pos:pos + B * n * D].view(B, n, D)
-                    pos += B * n * D
+            ops.copy_feature_blocks(recv_flat, out, B, D, self._tw_meta(B, True, dev))
         if n_rw:
             rw_off = lo_[n_tw_r * GB:] - tw_total if n_tw_r else lo_
             rw_vals = lv[tw_total:]
             rw_out = torch.empty((GB, n_rw * D), dtype=torch.float32, device=dev)
-            ops.embedding_forward(self._group("rw", False), rw_vals, rw_off, GB, _lib.POOL_SUM, rw_out)
+            ops.embedding_forward(self._group("rw", False), rw_vals, rw_off, GB, _lib.POOL_SUM, rw_out,
+                                  self._bw_scratch("rw", rw_vals.numel(), dev))
             # output dist RW: exchange partial sums, add them in source-rank order
             recv_flat = self._a2a(rw_out.reshape(-1), [B * n_rw * D] * W, [B * n_rw * D] * W)
             parts = recv_flat.view(W, B, n_rw, D)
@@ -384,29 +496,57 @@ class ShardedEmbeddingBagCollection(nn.Module):
         else:
             saved_rw = None
         # the TW part of the local ids only: the backward sorts exactly the ids it is given
-        saved = dict(lv=lv[:tw_total], lo=lo_, n_tw_r=n_tw_r, GB=GB, rw=saved_rw)
+        self._fwd_token += 1
+        saved = dict(lv=lv[:tw_total], lo=lo_, n_tw_r=n_tw_r, GB=GB, rw=saved_rw, fused=self._emit_keys,
+                     token=self._fwd_token)
         return out, saved
+
+    def _bw_scratch(self, name: str, L: int, device):
+        """Backward workspace of a shard; the forward writes the sort pairs into it when training."""
+        if not self._emit_keys or L == 0:
+            return None
+        from . import ops as _o
+        sh = self._tw if name == "tw" else self._rw
+        need = _o.backward_layout(L, max(sh.total_rows, 1)).total_bytes
+        buf = self._scratch.get(name)
+        if buf is None or buf.numel() < need or buf.device != device:
+            buf = torch.empty(int(need * 1.1) + 256, dtype=torch.uint8, device=device)
+            self._scratch[name] = buf
+        return buf
 
     # ------------------------------------------------------------------ backward
     def _backward_impl(self, grad_out, saved, B):
         W, D, ops = self._world, self._D, self._ops
+        if saved["token"] != self._fwd_token:
+            saved = dict(saved, fused=False)          # another forward reused the workspace since
         self._fused.iteration += 1
         opt = self._fused.args()
         g3 = grad_out.view(B, self._F_total, D)
         GB, n_tw_r, n_rw = saved["GB"], saved["n_tw_r"], self._n_rw
         if sum(self._n_tw):
             # reverse all-to-all: the owner of a TW feature gets the gradient rows of every rank's samples
-            send = torch.cat([g3[:, self._tw_feats[d], :].reshape(-1) for d in range(W)])
-            recv = self._a2a(send, [B * self._n_tw[d] * D for d in range(W)], [B * n_tw_r * D] * W)
+            if self._use_peer and self._peer is not None:
+                # push every gradient row into the landing buffer of the feature's owner over NVLink
+                ops.copy_feature_blocks(grad_out, None, B, D, self._peer_grad_meta(B, grad_out.device))
+                self._peer.barrier()
+                recv = self._peer.grad[: GB * n_tw_r * D]
+            else:
+                send = torch.empty(B * self._tw_cols_total, dtype=torch.float32, device=grad_out.device)
+                ops.copy_feature_blocks(grad_out, send, B, D, self._tw_meta(B, False, grad_out.device))
+                recv = self._a2a(send, [B * self._n_tw[d] * D for d in range(W)], [B * n_tw_r * D] * W)
             if n_tw_r:
+                sc = self._scratch.get("tw") if saved["fused"] else None
                 ops.embedding_backward_update(self._group("tw", True), recv.view(GB, n_tw_r * D), saved["lv"],
-                                              saved["lo"][: n_tw_r * GB + 1], GB, self._pooling, opt)
+                                              saved["lo"][: n_tw_r * GB + 1], GB, self._pooling, opt,
+                                              scratch=sc, keys_in_scratch=sc is not None and saved["lv"].numel() > 0)
         if n_rw:
             mine = g3[:, self._rw_feats, :].reshape(B, n_rw * D).contiguous()
             full = torch.empty((GB, n_rw * D), dtype=torch.float32, device=grad_out.device)
             dist.all_gather_into_tensor(full, mine, group=self._pg)
             rw_vals, rw_off = saved["rw"]
-            ops.embedding_backward_update(self._group("rw", True), full, rw_vals, rw_off, GB, _lib.POOL_SUM, opt)
+            sc = self._scratch.get("rw") if saved["fused"] else None
+            ops.embedding_backward_update(self._group("rw", True), full, rw_vals, rw_off, GB, _lib.POOL_SUM, opt,
+                                          scratch=sc, keys_in_scratch=sc is not None and rw_vals.numel() > 0)
 
     def forward(self, features: KeyedJaggedTensor) -> KeyedTensor:
         if list(features.keys()) != self._feature_names:
@@ -416,8 +556,10 @@ class ShardedEmbeddingBagCollection(nn.Module):
         if self.training and torch.is_grad_enabled():
             if self._anchor is None or self._anchor.device != values.device:
                 self._anchor = torch.zeros(1, device=values.device, requires_grad=True)
+            self._emit_keys = isinstance(self._ops, CudaKernelOps)
             out = _ShardedLookupFn.apply(self._anchor, self, values, lengths, B)
         else:
+            self._emit_keys = False
             out, _ = self._forward_impl(values, lengths, B)
         return KeyedTensor(self._feature_names, [self._D] * self._F_total, out)
 

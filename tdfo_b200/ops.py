@@ -210,6 +210,29 @@ def embedding_forward(group: TableGroup, indices: torch.Tensor, offsets: torch.T
     return out
 
 
+def embedding_forward_peer(group: TableGroup, indices: torch.Tensor, offsets: torch.Tensor, B: int, pooling_mode: int,
+                           peer_out: torch.Tensor, peer_batch: int,
+                           backward_scratch: Optional[torch.Tensor] = None) -> None:
+    """Pooled lookup whose rows are stored into the output buffers of the samples' source ranks
+    (``peer_out``: int64 device tensor of base addresses, one per source rank)."""
+    indices = _cuda(indices, torch.int64, "indices")
+    offsets = _cuda(offsets, torch.int64, "offsets")
+    peer_out = _cuda(peer_out, torch.int64, "peer_out")
+    w = group.weights
+    L = indices.numel()
+    sk = sv = None
+    if backward_scratch is not None and L > 0:
+        lay = backward_layout(L, group.total_rows)
+        if backward_scratch.numel() < lay.total_bytes:
+            raise ValueError(f"backward_scratch has {backward_scratch.numel()} bytes, needs {lay.total_bytes}")
+        sk = ctypes.c_void_p(backward_scratch.data_ptr() + lay.input_keys)
+        sv = ctypes.c_void_p(backward_scratch.data_ptr() + lay.input_vals)
+    check(_lib.load().tdfo_embedding_forward_peer(
+        _ptr(w), _wdtype(w), group.total_rows, group.D, _ptr(indices), _ptr(offsets), None,
+        _ptr(group.feat_row_base), _ptr(group.feat_rows), _ptr(group.feat_out_col), group.F, B, L, pooling_mode,
+        _ptr(peer_out), peer_batch, group.out_stride, sk, sv, _ptr(group.err_flag), _stream()))
+
+
 # --------------------------------------------------------------------------- backward
 def make_optimizer_args(optimizer: int, learning_rate: float, eps: float = 1e-8, weight_decay: float = 0.0,
                         beta1: float = 0.9, beta2: float = 0.999, step: int = 1) -> OptimizerArgs:
@@ -297,6 +320,14 @@ def sparse_update(group: TableGroup, grad_out, sorted_vals, unique_keys, seg_sta
         grad_stride, _ptr(sorted_vals), _ptr(unique_keys), _ptr(seg_starts), _ptr(first_vals), _ptr(num_unique),
         _ptr(offsets),
         _ptr(group.feat_out_col), group.F, B, L, pooling_mode, ctypes.byref(opt), _stream()))
+
+
+def copy_feature_blocks(src: torch.Tensor, dst: torch.Tensor, B: int, D: int, meta: torch.Tensor) -> None:
+    """meta: int64[4*nslots] on the device = src_off | src_stride | dst_off | dst_stride (elements)."""
+    src = _cuda(src, torch.float32, "src")
+    if dst is not None and not (dst.is_cuda and dst.dtype == torch.float32 and dst.is_contiguous()):
+        raise TypeError("dst must be a contiguous float32 CUDA tensor (or None for absolute destinations)")
+    check(_lib.load().tdfo_copy_feature_blocks(_ptr(src), _ptr(dst), B, D, meta.numel() // 4, _ptr(meta), _stream()))
 
 
 # --------------------------------------------------------------------------- jagged

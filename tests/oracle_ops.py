@@ -34,7 +34,7 @@ class OracleKernelOps:
         ol, oo, oi, _ = orc.permute_2d(_np(permute), B, _np(lengths), _np(offsets), _np(indices))
         return torch.from_numpy(ol), torch.from_numpy(oo), torch.from_numpy(oi)
 
-    def embedding_forward(self, group, indices, offsets, B, pooling_mode, out):
+    def embedding_forward(self, group, indices, offsets, B, pooling_mode, out, backward_scratch=None):
         F = group.feat_row_base.numel()
         w = np.ascontiguousarray(_np(group.weights))
         res, oob = orc.embedding_forward(w, w.shape[1], _np(indices), _np(offsets), None, _np(group.feat_row_base),
@@ -45,7 +45,8 @@ class OracleKernelOps:
             group.err_flag |= 1
         return out
 
-    def embedding_backward_update(self, group, grad_out, indices, offsets, B, pooling_mode, opt):
+    def embedding_backward_update(self, group, grad_out, indices, offsets, B, pooling_mode, opt, scratch=None,
+                                  keys_in_scratch=False):
         F = group.feat_row_base.numel()
         w = group.weights.numpy()                       # shares memory with the parameter
         o = orc.OptArgs(opt.optimizer, opt.learning_rate, opt.eps, opt.weight_decay, opt.beta1, opt.beta2, opt.step)
@@ -53,3 +54,11 @@ class OracleKernelOps:
                                       None if group.state1 is None else group.state1.numpy(), _np(grad_out),
                                       _np(indices), _np(offsets), _np(group.feat_row_base), _np(group.feat_rows),
                                       _np(group.feat_out_col), F, B, pooling_mode, o)
+
+    def copy_feature_blocks(self, src, dst, B, D, meta):
+        m = _np(meta).reshape(4, -1)
+        s, d = src.reshape(-1), dst.reshape(-1)
+        for j in range(m.shape[1]):
+            so, ss, do, ds = (int(x) for x in m[:, j])
+            for b in range(B):
+                d[do + b * ds: do + b * ds + D] = s[so + b * ss: so + b * ss + D]

@@ -14,7 +14,7 @@ from test_sharded_gloo import B, D, W, free_port, global_batch, local_batch, mak
 pytestmark = pytest.mark.gpu
 
 
-def run_rank(rank, port, plan_kind, results):
+def run_rank(rank, port, plan_kind, peer, results):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -30,13 +30,14 @@ def run_rank(rank, port, plan_kind, results):
                 "rw": {c.name: td.row_wise() for c in tables},
                 "mixed": {"t0": td.table_wise(1), "t1": td.row_wise(), "t2": td.table_wise(0), "t3": td.row_wise(),
                           "t4": td.table_wise(1)}}[plan_kind]
-        m = td.ShardedEmbeddingBagCollection(tables, plan, dev, init_seed=3)
+        m = td.ShardedEmbeddingBagCollection(tables, plan, dev, init_seed=3, peer_memory=peer)
         m.set_fused_optimizer(t.EmbOptimType.EXACT_ROWWISE_ADAGRAD, learning_rate=0.05, eps=1e-8)
         m.train()
         lengths, idx, grad = local_batch(rank, rows)
         kjt = t.KeyedJaggedTensor.from_lengths_sync([f"f{i}" for i in range(len(rows))], torch.from_numpy(idx),
                                                     torch.from_numpy(lengths)).to(dev)
         out = m(kjt).values()
+        out_host = out.detach().cpu().numpy().copy()
         (out * torch.from_numpy(grad).to(dev)).sum().backward()
         torch.cuda.synchronize()
         assert int(m._err_flag.item()) == 0
@@ -46,7 +47,7 @@ def run_rank(rank, port, plan_kind, results):
         col = (np.arange(len(rows)) * D).astype(np.int64)
         want, _ = orc.embedding_forward(full, D, idx, orc.complete_cumsum(lengths), None, base, rows, col,
                                         len(rows), B, orc.POOL_SUM)
-        np.testing.assert_allclose(out.detach().cpu().numpy(), want, rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(out_host, want, rtol=1e-5, atol=1e-6)
         g_len, g_idx, g_grad = global_batch(rows)
         w_ref, h_ref = full.copy(), np.zeros(sum(rows), np.float32)
         orc.embedding_backward_update(w_ref, D, h_ref, None, g_grad, g_idx, orc.complete_cumsum(g_len), base, rows, col,
@@ -65,15 +66,18 @@ def run_rank(rank, port, plan_kind, results):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("plan_kind", ["tw", "rw", "mixed"])
-def test_sharded_equals_unsharded_on_2_gpus(plan_kind):
+@pytest.mark.parametrize("plan_kind,peer", [("tw", False), ("tw", True), ("rw", False), ("mixed", False),
+                                            ("mixed", True)])
+def test_sharded_equals_unsharded_on_2_gpus(plan_kind, peer):
+    """peer=True: table-wise pooled rows and gradient rows travel through NVLink peer memory written
+    by the kernels themselves; peer=False: NCCL all-to-alls."""
     if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     port = free_port()
     ctx = mp.get_context("spawn")
     with ctx.Manager() as mgr:
         results = mgr.dict()
-        procs = [ctx.Process(target=run_rank, args=(r, port, plan_kind, results)) for r in range(W)]
+        procs = [ctx.Process(target=run_rank, args=(r, port, plan_kind, peer, results)) for r in range(W)]
         for p in procs:
             p.start()
         for p in procs:
