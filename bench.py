@@ -463,6 +463,11 @@ def run_e2e(args, t, ebc, keys, lengths_dev, batches, grad_out, F, B, D, L, worl
             s["l"].copy_(host_lens, non_blocking=True)
             s["ev"].record(copy_stream)
 
+    loss_host = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+    loss_ev = [torch.cuda.Event() for _ in range(2)]
+    grad_flat = grad_out.view(-1)
+    losses = []
+
     def step(i, n_total):
         s = slots[i % 2]
         main.wait_event(s["ev"])
@@ -470,9 +475,18 @@ def run_e2e(args, t, ebc, keys, lengths_dev, batches, grad_out, F, B, D, L, worl
             prefetch(i + 1)
         kjt = t.KeyedJaggedTensor.from_lengths_sync(keys, s["v"], s["l"])
         kt = ebc(kjt)
-        loss = (kt.values() * grad_out).sum()
+        loss = torch.dot(kt.values().view(-1), grad_flat)     # scalar loss; d(loss)/d(pooled) = grad_out
         loss.backward()
-        return loss.item()                                   # D2H read of the step's result
+        # device->host read of the step's loss: asynchronous copy into pinned memory, consumed one step
+        # later (logging lags by a step, the GPU never waits for the host)
+        loss_host[i % 2].copy_(loss.detach().view(1), non_blocking=True)
+        loss_ev[i % 2].record(main)
+        if i > 0:
+            loss_ev[(i - 1) % 2].synchronize()
+            losses.append(float(loss_host[(i - 1) % 2][0]))
+        if i + 1 == n_total:
+            loss_ev[i % 2].synchronize()
+            losses.append(float(loss_host[i % 2][0]))
 
     n_w = max(args.warmup, 1)
     prefetch(0)
@@ -497,13 +511,14 @@ def run_e2e(args, t, ebc, keys, lengths_dev, batches, grad_out, F, B, D, L, worl
     return {"value": L * world * args.steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / args.steps,
             "wall_ms_per_step": wall_ms / args.steps,
             "h2d_bytes_per_step": L * 8 + F * B * 4, "d2h_bytes_per_step": 4,
-            "api": "KeyedJaggedTensor.from_lengths_sync -> EmbeddingBagCollection.forward -> loss.backward() -> loss.item()"}
+            "losses_read": len(losses),
+            "api": "pinned ids/lengths -> H2D -> KeyedJaggedTensor.from_lengths_sync -> EmbeddingBagCollection.forward -> "
+                   "loss.backward() (fused update) -> loss D2H"}
 
 
 def main():
     # keep stdout to the one JSON line: NCCL prints its version banner there at NCCL_DEBUG=VERSION
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-        os.environ["NCCL_DEBUG"] = "WARN"
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
