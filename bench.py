@@ -361,7 +361,7 @@ def run_ours_sharded(args):
     gen = torch.Generator(device=dev).manual_seed(42 + rank)
     tables = [t.EmbeddingBagConfig(num_embeddings=rows, embedding_dim=D, name=f"t{i}", feature_names=[f"f{i}"],
                                    pooling=t.PoolingType.SUM) for i in range(F)]
-    n_tw = (F // world) * world
+    n_tw = F if args.plan == "tw" else (F // world) * world
     plan = {f"t{i}": (td.table_wise(i % world) if i < n_tw else td.row_wise()) for i in range(F)}
     m = td.ShardedEmbeddingBagCollection(tables, plan, dev, init_on_device=True)
     m.set_fused_optimizer(t.EmbOptimType.EXACT_ROWWISE_ADAGRAD, learning_rate=CFG["lr"], eps=CFG["eps"])
@@ -525,6 +525,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--plan", choices=["tw", "mixed"], default="mixed",
+                    help="N>1: all tables table-wise (round-robin), or the remainder row-wise for balance")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

@@ -64,6 +64,7 @@ extern "C" {
 /* bits of *err_flag */
 #define TDFO_FLAG_INDEX_OOB     1   /* an id was < 0 or >= rows of its table */
 #define TDFO_FLAG_SCAN_TIMEOUT  2   /* internal look-back watchdog fired (bug guard) */
+#define TDFO_FLAG_RECV_OVERFLOW 4   /* a peer's id receive buffer was too small for this batch */
 
 /* ------------------------------------------------------------------ misc */
 
@@ -161,6 +162,27 @@ int tdfo_kjt_permute_2d(const int32_t* permute /* [S_out] */, int32_t S_in, int3
                         int32_t* out_lengths, int64_t* out_offsets,
                         int64_t* out_indices, float* out_weights,
                         void* scratch, size_t scratch_bytes, void* stream);
+
+/*
+ * Input dist over NVLink peer memory (no all-to-all, no host round trip for split sizes).
+ * Every feature segment (the B bags of one feature, or of one (bucket, feature) after
+ * tdfo_kjt_bucketize_row_wise) is contiguous at the sender and, in the owner's
+ * [feature][source rank][batch] layout, contiguous at the receiver.
+ *
+ * tdfo_kjt_push_lengths: slot j copies B lengths, lengths[src_off[j] .. +B) -> *(int32*)dst_addr[j].
+ *   meta = device int64[2*nslots] = src_off (elements) | dst_addr (absolute, peer memory).
+ * (barrier; the owner runs tdfo_kjt_complete_cumsum over what it received; barrier)
+ * tdfo_kjt_push_ids: slot j sends segment seg[j] = values[offsets[seg*B] .. offsets[(seg+1)*B])
+ *   to ids_base[j] + *(int64*)off_addr[j], where off_addr[j] points at the owner's offset word for
+ *   this (feature, source rank) (read remotely), ids_base[j] at its id buffer.
+ *   meta = device int64[3*nslots] = seg | off_addr | ids_base.  A segment that would run past
+ *   `capacity` ids is dropped and TDFO_FLAG_RECV_OVERFLOW is set.
+ * Replaces: KJTAllToAll (two all_to_all_single + permute_2D_sparse_data) in the input_dist of the
+ *   sharded module DMP builds (torchrec/train.py:241-247, 98).
+ */
+int tdfo_kjt_push_lengths(const int32_t* lengths, int64_t B, int32_t nslots, const int64_t* meta, void* stream);
+int tdfo_kjt_push_ids(const int64_t* values, const int64_t* offsets, int64_t B, int32_t nslots,
+                      const int64_t* meta, int64_t capacity, int32_t* err_flag, void* stream);
 
 /* ------------------------------------------------------------------ lookup */
 

@@ -15,7 +15,7 @@ LIB_PATH = Path(__file__).resolve().parent / "libtdfo_b200.so"
 F32, BF16 = 0, 1
 POOL_SUM, POOL_MEAN, POOL_NONE = 0, 1, 2
 OPT_SGD, OPT_ROWWISE_ADAGRAD, OPT_ADAM = 0, 1, 2
-FLAG_INDEX_OOB, FLAG_SCAN_TIMEOUT = 1, 2
+FLAG_INDEX_OOB, FLAG_SCAN_TIMEOUT, FLAG_RECV_OVERFLOW = 1, 2, 4
 ABI_VERSION = 1
 CUMSUM_STATIC_MAX_N = 1 << 22
 
@@ -42,6 +42,8 @@ _SIGNATURES = {
     "tdfo_bucketize_scratch_bytes": (c_size_t, [c_int64, c_int32]),
     "tdfo_kjt_bucketize_row_wise": (c_int, [P, P, P, P, P, c_int32, c_int64, c_int32, P, P, P, P, P, P, P, c_size_t, P]),
     "tdfo_kjt_permute_2d": (c_int, [P, c_int32, c_int32, c_int64, P, P, P, P, P, P, P, P, P, c_size_t, P]),
+    "tdfo_kjt_push_lengths": (c_int, [P, c_int64, c_int32, P, P]),
+    "tdfo_kjt_push_ids": (c_int, [P, P, c_int64, c_int32, P, c_int64, P, P]),
     "tdfo_embedding_forward": (c_int, [P, c_int32, c_int64, c_int32, P, P, P, P, P, P, c_int32, c_int64, c_int64,
                                        c_int32, P, c_int64, P, P, P, P]),
     "tdfo_embedding_forward_peer": (c_int, [P, c_int32, c_int64, c_int32, P, P, P, P, P, P, c_int32, c_int64, c_int64,

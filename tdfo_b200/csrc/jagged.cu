@@ -192,6 +192,44 @@ __global__ void copy_feature_blocks_kernel(const float* __restrict__ src, float*
     }
 }
 
+// ---------------------------------------------------------------- input dist over peer memory
+// Slot j copies B lengths from src + src_off[j] to the absolute address dst_addr[j]
+// (a peer rank's receive buffer, already in its final [feature][source rank][batch] layout).
+__global__ void push_lengths_kernel(const int32_t* __restrict__ src, int64_t B, int32_t nslots,
+                                    const int64_t* __restrict__ meta) {
+    const int64_t total = (int64_t)nslots * B;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int j = (int)(i / B);
+        const int64_t b = i - (int64_t)j * B;
+        int32_t* dst = reinterpret_cast<int32_t*>(__ldg(meta + nslots + j));
+        dst[b] = __ldg(src + __ldg(meta + j) + b);
+    }
+}
+
+// Slot j moves the ids of one whole feature segment (B consecutive bags, contiguous on both
+// sides) to the owner rank: the destination offset is read from the owner's offsets array
+// (one remote 8-byte load per slot), the ids are then streamed over NVLink with plain stores.
+// blockIdx.y = slot; blockIdx.x strides over the segment.
+__global__ void __launch_bounds__(256)
+push_ids_kernel(const int64_t* __restrict__ values, const int64_t* __restrict__ offsets, int64_t B,
+                const int64_t* __restrict__ meta, int32_t nslots, int64_t capacity, int32_t* err_flag) {
+    const int j = blockIdx.y;
+    const int64_t seg = __ldg(meta + j);
+    const int64_t s0 = __ldg(offsets + seg * B), s1 = __ldg(offsets + (seg + 1) * B);
+    const int64_t n = s1 - s0;
+    if (n <= 0) return;
+    const int64_t dst_off = *reinterpret_cast<const volatile int64_t*>(__ldg(meta + nslots + j));
+    if (dst_off < 0 || dst_off + n > capacity) {
+        if (err_flag && threadIdx.x == 0 && blockIdx.x == 0) atomicOr(err_flag, TDFO_FLAG_RECV_OVERFLOW);
+        return;
+    }
+    int64_t* dst = reinterpret_cast<int64_t*>(__ldg(meta + 2 * nslots + j)) + dst_off;
+    const int64_t* src = values + s0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        dst[i] = __ldg(src + i);
+}
+
 static unsigned grid_for(int64_t items, int threads) {
     int64_t blocks = (items + threads - 1) / threads;
     const int64_t cap = (int64_t)kNumSMs * 32;
@@ -342,5 +380,31 @@ extern "C" int tdfo_copy_feature_blocks(const float* src, float* dst, int64_t B,
         src, dst, B, D / 4, nslots, meta);
     count_launch();
     TDFO_LAUNCH_CHECK("copy_feature_blocks");
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_kjt_push_lengths(const int32_t* lengths, int64_t B, int32_t nslots, const int64_t* meta,
+                                     void* stream) {
+    TDFO_CHECK_ARG(B >= 0 && nslots >= 0, "kjt_push_lengths: negative size");
+    if (B == 0 || nslots == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(lengths && meta, "kjt_push_lengths: null pointer");
+    push_lengths_kernel<<<grid_for((int64_t)nslots * B, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        lengths, B, nslots, meta);
+    count_launch();
+    TDFO_LAUNCH_CHECK("kjt_push_lengths");
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_kjt_push_ids(const int64_t* values, const int64_t* offsets, int64_t B, int32_t nslots,
+                                 const int64_t* meta, int64_t capacity, int32_t* err_flag, void* stream) {
+    TDFO_CHECK_ARG(B >= 0 && nslots >= 0 && capacity >= 0, "kjt_push_ids: negative size");
+    TDFO_CHECK_ARG(nslots <= 65535, "kjt_push_ids: at most 65535 segments per call");
+    if (B == 0 || nslots == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(offsets && meta, "kjt_push_ids: null pointer");
+    dim3 grid(64, (unsigned)nslots);          // 64 x 256 threads stream one segment
+    push_ids_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(values, offsets, B, meta, nslots, capacity,
+                                                                        err_flag);
+    count_launch();
+    TDFO_LAUNCH_CHECK("kjt_push_ids");
     return TDFO_OK;
 }

@@ -111,6 +111,15 @@ class CudaKernelOps:
     def copy_feature_blocks(self, src, dst, B, D, meta):
         self._ops.copy_feature_blocks(src, dst, B, D, meta)
 
+    def push_lengths(self, lengths, B, meta):
+        self._ops.push_lengths(lengths, B, meta)
+
+    def push_ids(self, values, offsets, B, meta, capacity, err_flag):
+        self._ops.push_ids(values, offsets, B, meta, capacity, err_flag)
+
+    def complete_cumsum_into(self, lengths, out):
+        return self._ops.complete_cumsum(lengths, out=out)
+
 
 class _Shard:
     """Local storage of one sharding flavour (all TW tables this rank owns, or all RW row blocks)."""
@@ -139,15 +148,22 @@ class _PeerExchange:
     rows into, and one gradient landing buffer per rank that the sample owners push gradient rows
     into.  Barriers are the symmetric-memory signal-pad barriers, enqueued on the current stream."""
 
-    def __init__(self, pg, device, B: int, F_total: int, D: int, n_tw: List[int]):
+    def __init__(self, pg, device, B: int, F_total: int, D: int, n_tw: List[int], n_rw: int, ids_capacity: int):
         import torch.distributed._symmetric_memory as symm
         W = len(n_tw)
         group = pg if pg is not None else dist.group.WORLD
-        try:
-            symm.enable_symm_mem_for_group(group.group_name)
-        except Exception:
-            pass
         self.B = B
+        # input dist landing zones, already in the [feature][source rank][batch] layout
+        fl_max = max(n_tw) + n_rw
+        self.capacity = int(ids_capacity)
+        self.len_x = symm.empty(max(fl_max * W * B, 4), dtype=torch.int32, device=device)
+        self.off_x = symm.empty(fl_max * W * B + 4, dtype=torch.int64, device=device)
+        self.ids_x = symm.empty(max(self.capacity, 4), dtype=torch.int64, device=device)
+        self.len_ptrs = list(symm.rendezvous(self.len_x, group).buffer_ptrs)
+        self.off_ptrs = list(symm.rendezvous(self.off_x, group).buffer_ptrs)
+        self.ids_ptrs = list(symm.rendezvous(self.ids_x, group).buffer_ptrs)
+        self.counts_host = torch.zeros(2, dtype=torch.int64).pin_memory()
+        self.counts_event = torch.cuda.Event()
         self.out = [symm.empty(B * F_total * D, dtype=torch.float32, device=device) for _ in range(2)]
         self.out_hdl = [symm.rendezvous(t_, group) for t_ in self.out]
         self.out_ptrs = [torch.tensor(list(h.buffer_ptrs), dtype=torch.int64, device=device) for h in self.out_hdl]
@@ -185,7 +201,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
     def __init__(self, tables: List[EmbeddingBagConfig], plan: Dict[str, ParameterSharding],
                  device: torch.device, process_group: Optional[dist.ProcessGroup] = None,
                  kernel_ops=None, init_seed: int = 0, init_on_device: bool = False,
-                 peer_memory: Optional[bool] = None):
+                 peer_memory: Optional[bool] = None, max_ids_per_rank: Optional[int] = None):
         super().__init__()
         self._pg = process_group
         self._world = dist.get_world_size(process_group)
@@ -294,6 +310,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
             peer_memory = (isinstance(self._ops, CudaKernelOps) and W > 1 and device.type == "cuda"
                            and sum(self._n_tw) > 0)
         self._use_peer = bool(peer_memory)
+        self._max_ids_per_rank = max_ids_per_rank
         self._peer: Optional[_PeerExchange] = None
         self.register_buffer("_tw_global_col", torch.tensor([f * self._D for f in self._tw.features] or [0],
                                                             dtype=torch.int64, device=device)[:len(self._tw.features)],
@@ -385,121 +402,180 @@ class ShardedEmbeddingBagCollection(nn.Module):
         offsets = ops.complete_cumsum(lengths)
         Fl, n_rw = self._F_local, self._n_rw
 
-        # ---- input dist: per-destination blocks  [tw features of d | rw bucket d]
-        len_parts: List[List[torch.Tensor]] = [[] for _ in range(W)]
-        val_parts: List[List[torch.Tensor]] = [[] for _ in range(W)]
         n_tw_all = sum(self._n_tw)
-        if n_tw_all:
-            tl, to, tv = ops.permute_2d(self._tw_send_perm[:n_tw_all], B, lengths, offsets, values, values.numel())
-            f0 = 0
-            bounds = to[:: max(B, 1)] if B else to
-            for d in range(W):
-                f1 = f0 + self._n_tw[d]
-                len_parts[d].append(tl[f0 * B:f1 * B])
-                val_parts[d].append((tv, bounds, f0, f1))
-                f0 = f1
-        if n_rw:
-            rl, ro, rv = ops.permute_2d(self._rw_select_perm[:n_rw], B, lengths, offsets, values, values.numel())
-            bl, bo, bv = ops.bucketize_row_wise(rl, ro, rv, self._rw_block_sizes[:n_rw], n_rw, B, W, self._err_flag)
-            bbounds = bo[:: max(n_rw * B, 1)]
-            for d in range(W):
-                len_parts[d].append(bl[d * n_rw * B:(d + 1) * n_rw * B])
-                val_parts[d].append((bv, bbounds, d, d + 1))
-        send_lengths = torch.cat([p for d in range(W) for p in len_parts[d]])
-        # value split sizes need host ints: one small device->host read per step
-        bound_list = []
-        for d in range(W):
-            for (_, bnd, i0, i1) in val_parts[d]:
-                bound_list += [bnd[i0], bnd[i1]]
-        b_host = torch.stack(bound_list).tolist() if bound_list else []
-        send_vals, send_splits, k = [], [0] * W, 0
-        for d in range(W):
-            for (buf, _, _, _) in val_parts[d]:
-                lo, hi = b_host[k], b_host[k + 1]
-                k += 2
-                send_vals.append(buf[lo:hi])
-                send_splits[d] += hi - lo
-        send_values = torch.cat(send_vals) if send_vals else values[:0]
-
-        len_send_splits = [(self._n_tw[d] + n_rw) * B for d in range(W)]
-        recv_lengths = self._a2a(send_lengths, len_send_splits, [Fl * B] * W)
         n_tw_r = self._n_tw[r]
-        if Fl * B:
-            rl3 = recv_lengths.view(W, Fl, B)
-            # per-source id counts and the id count of the TW part: one device->host read
-            host = torch.cat([rl3.sum(dim=(1, 2), dtype=torch.int64),
-                              rl3[:, :n_tw_r].sum(dtype=torch.int64).view(1)]).tolist()
-            recv_splits, tw_total = host[:W], host[W]
+        peer = None
+        if self._use_peer:
+            # ---- input dist through NVLink peer memory: lengths, then ids, are stored by the senders
+            # directly where the owner's lookup reads them; no all-to-all, no split sizes on the host
+            if self._peer is None or self._peer.B != B:
+                cap = self._max_ids_per_rank or int(1.5 * W * max(values.numel(), 1)) + 1024
+                self._peer = _PeerExchange(self._pg, dev, B, self._F_total, D, self._n_tw, n_rw, cap)
+                self._meta_cache.clear()
+            peer = self._peer
+            peer.barrier()                 # everyone is done reading last step's landing zones / outputs
+            if n_tw_all:
+                ops.push_lengths(lengths, B, self._peer_meta("len_tw", B, dev))
+            if n_rw:
+                rl, ro, rv = ops.permute_2d(self._rw_select_perm[:n_rw], B, lengths, offsets, values, values.numel())
+                bl, bo, bv = ops.bucketize_row_wise(rl, ro, rv, self._rw_block_sizes[:n_rw], n_rw, B, W, self._err_flag)
+                ops.push_lengths(bl, B, self._peer_meta("len_rw", B, dev))
+            peer.barrier()                 # lengths have landed
+            lo_ = peer.off_x[: Fl * W * B + 1]
+            ops.complete_cumsum_into(peer.len_x[: Fl * W * B], lo_)
+            peer.counts_host.copy_(torch.stack([lo_[n_tw_r * W * B], lo_[Fl * W * B]]), non_blocking=True)
+            peer.counts_event.record()
+            peer.barrier()                 # every owner's offsets are readable
+            if n_tw_all:
+                ops.push_ids(values, offsets, B, self._peer_meta("ids_tw", B, dev), peer.capacity, self._err_flag)
+            if n_rw:
+                ops.push_ids(bv, bo, B, self._peer_meta("ids_rw", B, dev), peer.capacity, self._err_flag)
+            peer.barrier()                 # ids have landed
+            lv = peer.ids_x
+            tw_total = None                # known on the host only later (counts_event)
         else:
-            recv_splits, tw_total = [0] * W, 0
-        recv_values = self._a2a(send_values, send_splits, recv_splits)
+            # ---- input dist: per-destination blocks  [tw features of d | rw bucket d]
+            len_parts: List[List[torch.Tensor]] = [[] for _ in range(W)]
+            val_parts: List[List[torch.Tensor]] = [[] for _ in range(W)]
+            n_tw_all = sum(self._n_tw)
+            if n_tw_all:
+                tl, to, tv = ops.permute_2d(self._tw_send_perm[:n_tw_all], B, lengths, offsets, values, values.numel())
+                f0 = 0
+                bounds = to[:: max(B, 1)] if B else to
+                for d in range(W):
+                    f1 = f0 + self._n_tw[d]
+                    len_parts[d].append(tl[f0 * B:f1 * B])
+                    val_parts[d].append((tv, bounds, f0, f1))
+                    f0 = f1
+            if n_rw:
+                rl, ro, rv = ops.permute_2d(self._rw_select_perm[:n_rw], B, lengths, offsets, values, values.numel())
+                bl, bo, bv = ops.bucketize_row_wise(rl, ro, rv, self._rw_block_sizes[:n_rw], n_rw, B, W, self._err_flag)
+                bbounds = bo[:: max(n_rw * B, 1)]
+                for d in range(W):
+                    len_parts[d].append(bl[d * n_rw * B:(d + 1) * n_rw * B])
+                    val_parts[d].append((bv, bbounds, d, d + 1))
+            send_lengths = torch.cat([p for d in range(W) for p in len_parts[d]])
+            # value split sizes need host ints: one small device->host read per step
+            bound_list = []
+            for d in range(W):
+                for (_, bnd, i0, i1) in val_parts[d]:
+                    bound_list += [bnd[i0], bnd[i1]]
+            b_host = torch.stack(bound_list).tolist() if bound_list else []
+            send_vals, send_splits, k = [], [0] * W, 0
+            for d in range(W):
+                for (buf, _, _, _) in val_parts[d]:
+                    lo, hi = b_host[k], b_host[k + 1]
+                    k += 2
+                    send_vals.append(buf[lo:hi])
+                    send_splits[d] += hi - lo
+            send_values = torch.cat(send_vals) if send_vals else values[:0]
 
-        # ---- [src][f][b] -> [f][src][b]
-        if Fl:
-            recv_offsets = ops.complete_cumsum(recv_lengths)
-            ll, lo_, lv = ops.permute_2d(self._recv_perm[:Fl * W], B, recv_lengths, recv_offsets, recv_values,
-                                         int(sum(recv_splits)))
-        else:
-            ll = recv_lengths
-            lo_ = torch.zeros(1, dtype=torch.int64, device=dev)
-            lv = recv_values
+            len_send_splits = [(self._n_tw[d] + n_rw) * B for d in range(W)]
+            recv_lengths = self._a2a(send_lengths, len_send_splits, [Fl * B] * W)
+            n_tw_r = self._n_tw[r]
+            if Fl * B:
+                rl3 = recv_lengths.view(W, Fl, B)
+                # per-source id counts and the id count of the TW part: one device->host read
+                host = torch.cat([rl3.sum(dim=(1, 2), dtype=torch.int64),
+                                  rl3[:, :n_tw_r].sum(dtype=torch.int64).view(1)]).tolist()
+                recv_splits, tw_total = host[:W], host[W]
+            else:
+                recv_splits, tw_total = [0] * W, 0
+            recv_values = self._a2a(send_values, send_splits, recv_splits)
+
+            # ---- [src][f][b] -> [f][src][b]
+            if Fl:
+                recv_offsets = ops.complete_cumsum(recv_lengths)
+                ll, lo_, lv = ops.permute_2d(self._recv_perm[:Fl * W], B, recv_lengths, recv_offsets, recv_values,
+                                             int(sum(recv_splits)))
+            else:
+                ll = recv_lengths
+                lo_ = torch.zeros(1, dtype=torch.int64, device=dev)
+                lv = recv_values
         GB = W * B                                            # global batch seen by each local feature
 
         # ---- lookup on the local storage
-        out = torch.empty((B, self._F_total * D), dtype=torch.float32, device=dev)
-        out3 = out.view(B, self._F_total, D)
-        peer = None
-        if n_tw_all and self._use_peer:
-            if self._peer is None or self._peer.B != B:
-                self._peer = _PeerExchange(self._pg, dev, B, self._F_total, D, self._n_tw)
-            peer = self._peer
+        self._fwd_token += 1
+        if peer is not None:
             k = peer.step % 2
             peer.step += 1
-            out = peer.out[k].view(B, self._F_total * D)
+            out = peer.out[k].view(B, self._F_total * D)     # valid until the forward after next
             out3 = out.view(B, self._F_total, D)
-            # every rank is past all readers of this buffer's previous contents before anyone writes
-            peer.barrier()
             if n_tw_r:
+                # pooled rows go straight into the output buffer of the rank that owns the sample
                 grp = self._group("tw", False)
                 grp.feat_out_col = self._tw_global_col        # columns of the final [B, F_total*D] layout
                 grp.out_stride = self._F_total * D
-                self._ops.embedding_forward_peer(grp, lv[:tw_total], lo_[: n_tw_r * GB + 1], GB, self._pooling,
-                                                 peer.out_ptrs[k], B, self._bw_scratch("tw", tw_total, dev))
+                ops.embedding_forward_peer(grp, lv, lo_[: n_tw_r * GB + 1], GB, self._pooling, peer.out_ptrs[k], B)
             peer.barrier()                                    # all pooled rows have landed
-        elif n_tw_all:
-            send_rows = None
+            if n_rw:
+                rw_out = torch.empty((GB, n_rw * D), dtype=torch.float32, device=dev)
+                ops.embedding_forward(self._group("rw", False), lv, lo_[n_tw_r * GB: Fl * GB + 1], GB, _lib.POOL_SUM,
+                                      rw_out)
+                out3[:, self._rw_feats, :] = self._exchange_partial_sums(rw_out, B, n_rw)
+            return out, dict(peer=True, lo=lo_, n_tw_r=n_tw_r, GB=GB, token=self._fwd_token, fused=False)
+
+        out = torch.empty((B, self._F_total * D), dtype=torch.float32, device=dev)
+        out3 = out.view(B, self._F_total, D)
+        if n_tw_all:
             if n_tw_r:
                 tw_out = torch.empty((GB, n_tw_r * D), dtype=torch.float32, device=dev)
                 ops.embedding_forward(self._group("tw", False), lv[:tw_total], lo_[: n_tw_r * GB + 1], GB,
                                       self._pooling, tw_out, self._bw_scratch("tw", tw_total, dev))
-                send_rows = tw_out
             else:
-                send_rows = torch.empty((0,), dtype=torch.float32, device=dev)
+                tw_out = torch.empty((0,), dtype=torch.float32, device=dev)
             # output dist TW: rank d returns B rows of n_tw[d]*D floats to every source rank
-            send_flat = send_rows.reshape(-1)
-            recv_flat = self._a2a(send_flat, [B * n_tw_r * D] * W, [B * self._n_tw[d] * D for d in range(W)])
+            recv_flat = self._a2a(tw_out.reshape(-1), [B * n_tw_r * D] * W, [B * self._n_tw[d] * D for d in range(W)])
             ops.copy_feature_blocks(recv_flat, out, B, D, self._tw_meta(B, True, dev))
+        saved_rw = None
         if n_rw:
             rw_off = lo_[n_tw_r * GB:] - tw_total if n_tw_r else lo_
             rw_vals = lv[tw_total:]
             rw_out = torch.empty((GB, n_rw * D), dtype=torch.float32, device=dev)
             ops.embedding_forward(self._group("rw", False), rw_vals, rw_off, GB, _lib.POOL_SUM, rw_out,
                                   self._bw_scratch("rw", rw_vals.numel(), dev))
-            # output dist RW: exchange partial sums, add them in source-rank order
-            recv_flat = self._a2a(rw_out.reshape(-1), [B * n_rw * D] * W, [B * n_rw * D] * W)
-            parts = recv_flat.view(W, B, n_rw, D)
-            acc = parts[0].clone()
-            for s in range(1, W):
-                acc += parts[s]
-            out3[:, self._rw_feats, :] = acc
+            out3[:, self._rw_feats, :] = self._exchange_partial_sums(rw_out, B, n_rw)
             saved_rw = (rw_vals, rw_off)
-        else:
-            saved_rw = None
         # the TW part of the local ids only: the backward sorts exactly the ids it is given
-        self._fwd_token += 1
-        saved = dict(lv=lv[:tw_total], lo=lo_, n_tw_r=n_tw_r, GB=GB, rw=saved_rw, fused=self._emit_keys,
+        saved = dict(peer=False, lv=lv[:tw_total], lo=lo_, n_tw_r=n_tw_r, GB=GB, rw=saved_rw, fused=self._emit_keys,
                      token=self._fwd_token)
         return out, saved
+
+    def _exchange_partial_sums(self, rw_out: torch.Tensor, B: int, n_rw: int) -> torch.Tensor:
+        """Row-wise output dist: every rank holds partial sums for all W*B samples; exchange them and
+        add in source-rank order (a reduce-scatter with a fixed, reproducible order)."""
+        W, D = self._world, self._D
+        recv_flat = self._a2a(rw_out.reshape(-1), [B * n_rw * D] * W, [B * n_rw * D] * W)
+        parts = recv_flat.view(W, B, n_rw, D)
+        acc = parts[0].clone()
+        for s_ in range(1, W):
+            acc += parts[s_]
+        return acc
+
+    def _peer_meta(self, kind: str, B: int, device) -> torch.Tensor:
+        """Push tables for the peer-memory input dist (cached per batch size)."""
+        key = (B, kind, str(device))
+        m = self._meta_cache.get(key)
+        if m is not None:
+            return m
+        W, r, n_rw, p = self._world, self._rank, self._n_rw, self._peer
+        rows: List[List[int]] = []
+        if kind in ("len_tw", "ids_tw"):
+            slots = [(d, j, f) for d in range(W) for j, f in enumerate(self._tw_feats[d])]
+            seg = [f for (_, _, f) in slots]                               # segment = original feature
+            word = [(j * W + r) * B for (_, j, _) in slots]                # (feature j, source r, batch 0) on owner d
+        else:
+            slots = [(d, self._n_tw[d] + k_, None) for d in range(W) for k_ in range(n_rw)]
+            seg = [d * n_rw + k_ for d in range(W) for k_ in range(n_rw)]  # segment of the bucketised layout
+            word = [(j * W + r) * B for (_, j, _) in slots]
+        dsts = [d for (d, _, _) in slots]
+        if kind.startswith("len"):
+            rows = [[sg * B for sg in seg], [p.len_ptrs[d] + 4 * w_ for d, w_ in zip(dsts, word)]]
+        else:
+            rows = [seg, [p.off_ptrs[d] + 8 * w_ for d, w_ in zip(dsts, word)], [p.ids_ptrs[d] for d in dsts]]
+        m = torch.tensor(rows, dtype=torch.int64, device=device).reshape(-1)
+        self._meta_cache[key] = m
+        return m
 
     def _bw_scratch(self, name: str, L: int, device):
         """Backward workspace of a shard; the forward writes the sort pairs into it when training."""
@@ -517,15 +593,28 @@ class ShardedEmbeddingBagCollection(nn.Module):
     # ------------------------------------------------------------------ backward
     def _backward_impl(self, grad_out, saved, B):
         W, D, ops = self._world, self._D, self._ops
-        if saved["token"] != self._fwd_token:
-            saved = dict(saved, fused=False)          # another forward reused the workspace since
+        stale = saved["token"] != self._fwd_token          # another forward ran since
         self._fused.iteration += 1
         opt = self._fused.args()
-        g3 = grad_out.view(B, self._F_total, D)
         GB, n_tw_r, n_rw = saved["GB"], saved["n_tw_r"], self._n_rw
+        Fl = self._F_local
+        if saved["peer"]:
+            if stale:
+                raise RuntimeError("tdfo_b200: with peer-memory exchange, backward must run before the next forward "
+                                   "(the received ids live in the shared landing buffers)")
+            peer = self._peer
+            peer.counts_event.synchronize()                 # counts were copied during the forward: no stall
+            tw_total, total = (int(x) for x in peer.counts_host.tolist())
+            lo_ = saved["lo"]
+            lv_tw, lo_tw = peer.ids_x[:tw_total], lo_[: n_tw_r * GB + 1]
+            rw = (peer.ids_x[tw_total:total], lo_[n_tw_r * GB: Fl * GB + 1] - tw_total) if n_rw else None
+            fused = False
+        else:
+            lv_tw, lo_tw, rw = saved["lv"], saved["lo"][: n_tw_r * GB + 1], saved["rw"]
+            fused = saved["fused"] and not stale
         if sum(self._n_tw):
-            # reverse all-to-all: the owner of a TW feature gets the gradient rows of every rank's samples
-            if self._use_peer and self._peer is not None:
+            # the owner of a TW feature needs the gradient rows of every rank's samples
+            if saved["peer"]:
                 # push every gradient row into the landing buffer of the feature's owner over NVLink
                 ops.copy_feature_blocks(grad_out, None, B, D, self._peer_grad_meta(B, grad_out.device))
                 self._peer.barrier()
@@ -535,16 +624,17 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 ops.copy_feature_blocks(grad_out, send, B, D, self._tw_meta(B, False, grad_out.device))
                 recv = self._a2a(send, [B * self._n_tw[d] * D for d in range(W)], [B * n_tw_r * D] * W)
             if n_tw_r:
-                sc = self._scratch.get("tw") if saved["fused"] else None
-                ops.embedding_backward_update(self._group("tw", True), recv.view(GB, n_tw_r * D), saved["lv"],
-                                              saved["lo"][: n_tw_r * GB + 1], GB, self._pooling, opt,
-                                              scratch=sc, keys_in_scratch=sc is not None and saved["lv"].numel() > 0)
+                sc = self._scratch.get("tw") if fused else None
+                ops.embedding_backward_update(self._group("tw", True), recv.view(GB, n_tw_r * D), lv_tw, lo_tw, GB,
+                                              self._pooling, opt, scratch=sc,
+                                              keys_in_scratch=sc is not None and lv_tw.numel() > 0)
         if n_rw:
+            g3 = grad_out.view(B, self._F_total, D)
             mine = g3[:, self._rw_feats, :].reshape(B, n_rw * D).contiguous()
             full = torch.empty((GB, n_rw * D), dtype=torch.float32, device=grad_out.device)
             dist.all_gather_into_tensor(full, mine, group=self._pg)
-            rw_vals, rw_off = saved["rw"]
-            sc = self._scratch.get("rw") if saved["fused"] else None
+            rw_vals, rw_off = rw
+            sc = self._scratch.get("rw") if fused else None
             ops.embedding_backward_update(self._group("rw", True), full, rw_vals, rw_off, GB, _lib.POOL_SUM, opt,
                                           scratch=sc, keys_in_scratch=sc is not None and rw_vals.numel() > 0)
 

@@ -102,16 +102,22 @@ def check_error_flag(flag: torch.Tensor, what: str = "embedding lookup") -> None
     v = int(flag.item())
     if v & _lib.FLAG_SCAN_TIMEOUT:
         raise RuntimeError(f"tdfo_b200: internal scan watchdog fired during {what}")
+    if v & _lib.FLAG_RECV_OVERFLOW:
+        flag.zero_()
+        raise RuntimeError(f"tdfo_b200: a rank received more ids than its exchange buffer holds during {what}; "
+                           "raise max_ids_per_rank")
     if v & _lib.FLAG_INDEX_OOB:
         flag.zero_()
         raise IndexError(f"tdfo_b200: an id was out of range of its table during {what}")
 
 
 # --------------------------------------------------------------------------- KJT
-def complete_cumsum(lengths: torch.Tensor) -> torch.Tensor:
+def complete_cumsum(lengths: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     lengths = _cuda(lengths, torch.int32, "lengths")
     n = lengths.numel()
-    offsets = torch.empty(n + 1, dtype=torch.int64, device=lengths.device)
+    offsets = out if out is not None else torch.empty(n + 1, dtype=torch.int64, device=lengths.device)
+    if offsets.numel() < n + 1 or offsets.dtype != torch.int64 or not offsets.is_contiguous():
+        raise ValueError("complete_cumsum: `out` must be a contiguous int64 tensor with n+1 entries")
     lib = _lib.load()
     nb = lib.tdfo_scan_scratch_bytes(n)
     scratch = _get_scratch(lengths.device, nb)
@@ -140,6 +146,18 @@ def bucketize_row_wise(lengths, offsets, indices, weights, block_sizes, F, B, wo
                                           _ptr(new_indices), _ptr(new_weights), _ptr(perm), _ptr(err_flag),
                                           _ptr(scratch), scratch.numel(), _stream()))
     return new_lengths, new_offsets, new_indices, new_weights, perm
+
+
+def push_lengths(lengths: torch.Tensor, B: int, meta: torch.Tensor) -> None:
+    lengths = _cuda(lengths, torch.int32, "lengths")
+    check(_lib.load().tdfo_kjt_push_lengths(_ptr(lengths), B, meta.numel() // 2, _ptr(meta), _stream()))
+
+
+def push_ids(values: torch.Tensor, offsets: torch.Tensor, B: int, meta: torch.Tensor, capacity: int, err_flag) -> None:
+    values = _cuda(values, torch.int64, "values")
+    offsets = _cuda(offsets, torch.int64, "offsets")
+    check(_lib.load().tdfo_kjt_push_ids(_ptr(values), _ptr(offsets), B, meta.numel() // 3, _ptr(meta), capacity,
+                                        _ptr(err_flag), _stream()))
 
 
 def permute_2d(permute, B, in_lengths, in_offsets, in_indices, in_weights=None, out_total: Optional[int] = None):
