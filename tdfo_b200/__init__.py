@@ -11,9 +11,14 @@ from .optim import (CombinedOptimizer, EmbOptimType, FusedOptimizer, KeyedOptimi
                     in_backward_optimizer_filter)
 from .ops import jagged_2d_to_dense
 from .sparse import JaggedTensor, KeyedJaggedTensor, KeyedTensor
+from .distributed import (DistributedModelParallel, EmbeddingBagCollectionSharder, EmbeddingCollectionSharder,
+                          ParameterSharding, ShardedEmbeddingBagCollection, ShardingType, balanced_table_wise_plan,
+                          row_wise, table_wise)
 
 __all__ = [
     "ops", "DataType", "EmbeddingBagCollection", "EmbeddingBagConfig", "EmbeddingCollection", "EmbeddingConfig",
     "PoolingType", "CombinedOptimizer", "EmbOptimType", "FusedOptimizer", "KeyedOptimizerWrapper",
     "in_backward_optimizer_filter", "jagged_2d_to_dense", "JaggedTensor", "KeyedJaggedTensor", "KeyedTensor",
+    "DistributedModelParallel", "EmbeddingBagCollectionSharder", "EmbeddingCollectionSharder", "ParameterSharding",
+    "ShardedEmbeddingBagCollection", "ShardingType", "balanced_table_wise_plan", "row_wise", "table_wise",
 ]

@@ -668,3 +668,101 @@ class ShardedEmbeddingBagCollection(nn.Module):
         g = torch.Generator(device="cpu").manual_seed(init_seed * 1_000_003 + zlib.crc32(table.name.encode()) % 1_000_003)
         return torch.empty((table.num_embeddings, table.embedding_dim), dtype=torch.float32).uniform_(
             table.get_weight_init_min(), table.get_weight_init_max(), generator=g)
+
+
+# --------------------------------------------------------------------------- DMP-style wrapper
+class _Sharder:
+    """`EmbeddingCollectionSharder(fused_params)` / `EmbeddingBagCollectionSharder(fused_params)`:
+    carries the fused-optimizer settings exactly as the reference passes them
+    (torchrec/train.py:236-245): {"optimizer": EmbOptimType, "learning_rate": float,
+    "weight_decay": float, optional "eps", "beta1", "beta2"}."""
+
+    module_kind: str = ""
+
+    def __init__(self, fused_params: Optional[Dict[str, object]] = None):
+        self.fused_params = dict(fused_params or {})
+
+    def optimizer_kwargs(self) -> Dict[str, object]:
+        fp = self.fused_params
+        kw: Dict[str, object] = {}
+        if "optimizer" in fp:
+            kw["optimizer"] = fp["optimizer"]
+        for src, dst in (("learning_rate", "learning_rate"), ("weight_decay", "weight_decay"), ("eps", "eps"),
+                         ("beta1", "beta1"), ("beta2", "beta2")):
+            if src in fp:
+                kw[dst] = fp[src]
+        return kw
+
+
+class EmbeddingCollectionSharder(_Sharder):
+    module_kind = "EmbeddingCollection"
+
+
+class EmbeddingBagCollectionSharder(_Sharder):
+    module_kind = "EmbeddingBagCollection"
+
+
+class DistributedModelParallel(nn.Module):
+    """`DMP(module=model, device=device, sharders=[...])` as at torchrec/train.py:241-247.
+
+    * every EmbeddingBagCollection / EmbeddingCollection inside `module` gets the sharder's fused
+      optimizer (the update then happens inside backward; `fused_optimizer` is the handle the
+      reference puts into `CombinedOptimizer`);
+    * with more than one rank, EmbeddingBagCollections are replaced by
+      `ShardedEmbeddingBagCollection` (plan: `plan[table_name]`, default size-balanced table-wise)
+      and the remaining (dense) parameters are wrapped in DistributedDataParallel.
+      Sharding an EmbeddingCollection (sequence output) across ranks is not built yet.
+    """
+
+    def __init__(self, module: nn.Module, device: Optional[torch.device] = None,
+                 sharders: Optional[List[_Sharder]] = None, plan: Optional[Dict[str, ParameterSharding]] = None,
+                 init_data_parallel: bool = True, process_group: Optional[dist.ProcessGroup] = None):
+        super().__init__()
+        from .modules import EmbeddingBagCollection, EmbeddingCollection
+        from .optim import CombinedFusedOptimizer
+        device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
+        by_kind = {s.module_kind: s for s in (sharders or [])}
+        fused: List[FusedOptimizer] = []
+
+        def convert(parent: nn.Module):
+            for name, child in list(parent.named_children()):
+                if isinstance(child, EmbeddingBagCollection):
+                    kw = by_kind["EmbeddingBagCollection"].optimizer_kwargs() if "EmbeddingBagCollection" in by_kind else {}
+                    if world > 1:
+                        tables = child.embedding_bag_configs()
+                        p = plan or balanced_table_wise_plan(tables, world)
+                        new = ShardedEmbeddingBagCollection(tables, p, device, process_group)
+                        setattr(parent, name, new)
+                        child = new
+                    else:
+                        child.to(device)
+                    fused.append(child.set_fused_optimizer(**kw) if kw else child.fused_optimizer)
+                elif isinstance(child, EmbeddingCollection):
+                    if world > 1:
+                        raise NotImplementedError("sharding an EmbeddingCollection (sequence embeddings) over several "
+                                                  "ranks is not built yet; use EmbeddingBagCollection or one rank")
+                    kw = by_kind["EmbeddingCollection"].optimizer_kwargs() if "EmbeddingCollection" in by_kind else {}
+                    child.to(device)
+                    fused.append(child.set_fused_optimizer(**kw) if kw else child.fused_optimizer)
+                else:
+                    convert(child)
+
+        holder = nn.ModuleDict({"m": module})
+        convert(holder)
+        module = holder["m"]
+        module.to(device)
+        self._fused_optimizer = CombinedFusedOptimizer(fused)
+        dense = [p for p in module.parameters() if p.requires_grad]
+        if world > 1 and init_data_parallel and dense:
+            from torch.nn.parallel import DistributedDataParallel as DDP
+            module = DDP(module, device_ids=[device.index] if device.type == "cuda" else None,
+                         process_group=process_group)
+        self.module = module
+
+    @property
+    def fused_optimizer(self):
+        return self._fused_optimizer
+
+    def forward(self, *args, **kwargs):
+        return self.module(*args, **kwargs)

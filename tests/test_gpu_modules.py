@@ -156,3 +156,54 @@ def test_full_size_properties_config2(t):
     dec = float(F * rows) * D - w.sum(dtype=torch.float64).item()
     assert dec == float(L) * D
     assert int(grp.err_flag.item()) == 0
+
+
+def test_train_py_model_parallel_block(t):
+    """The model-parallel block of the reference's main() (torchrec/train.py:235-254) and one step of
+    its training loop (:97-106), with a small stand-in for Bert4Rec around the same HistoryArch calls."""
+    import torch.nn as nn
+    import torch.optim as optim
+    V, D, T, B = 64, 16, 20, 8
+    dev = torch.device("cuda")
+
+    class Tiny(nn.Module):                                     # HistoryArch + output layer
+        def __init__(self):
+            super().__init__()
+            self.embed_collection = t.EmbeddingCollection(
+                tables=[t.EmbeddingConfig(name="item_embedding", embedding_dim=D, num_embeddings=V,
+                                          feature_names=["item"], weight_init_max=1.0, weight_init_min=-1.0)],
+                device=dev)
+            self.out = nn.Linear(D, V, device=dev)
+
+        def forward(self, kjt):
+            jt = self.embed_collection(kjt)
+            padded = [t.jagged_2d_to_dense(values=jt[e].values(), offsets=jt[e].offsets(),
+                                           max_sequence_length=T).view(-1, T, D) for e in kjt.keys()]
+            return self.out(torch.cat(padded, dim=1))
+
+    fused_params = {"optimizer": t.EmbOptimType.ADAM, "learning_rate": 3e-4, "weight_decay": 1e-4}
+    model = t.DistributedModelParallel(module=Tiny(), device=dev, sharders=[t.EmbeddingCollectionSharder(fused_params)])
+    dense_optimizer = t.KeyedOptimizerWrapper(
+        dict(t.in_backward_optimizer_filter(model.named_parameters())),
+        lambda params: optim.Adam(params, lr=3e-4, weight_decay=1e-4))
+    optimizer = t.CombinedOptimizer([model.fused_optimizer, dense_optimizer])
+    assert sorted(dense_optimizer.params) == ["module.out.bias", "module.out.weight"]
+    table0 = model.state_dict()["module.embed_collection.embeddings.item_embedding.weight"].clone()
+    dense0 = model.module.out.weight.detach().clone()
+
+    seqs = torch.randint(1, V, (B, T))
+    lengths = torch.IntTensor([v.size(0) for v in list(seqs)])
+    kjt = t.KeyedJaggedTensor.from_lengths_sync(keys=["item"], values=torch.cat(list(seqs), dim=0), lengths=lengths).to(dev)
+    model.train()
+    logits = model(kjt)
+    loss = nn.CrossEntropyLoss(ignore_index=0, label_smoothing=0.1)(logits.view(-1, V), seqs.to(dev).view(-1))
+    optimizer.zero_grad()
+    loss.backward()
+    optimizer.step()
+    assert np.isfinite(loss.item())
+    table1 = model.state_dict()["module.embed_collection.embeddings.item_embedding.weight"]
+    touched = torch.zeros(V, dtype=torch.bool)
+    touched[seqs.unique()] = True
+    changed = (table1 != table0).any(dim=1).cpu()
+    assert torch.equal(changed, touched)                       # exactly the looked-up rows moved (in backward)
+    assert not torch.equal(model.module.out.weight, dense0)    # the dense optimizer stepped too
