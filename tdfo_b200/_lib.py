@@ -9,7 +9,10 @@ import ctypes
 from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_ulonglong, c_void_p
 from pathlib import Path
 
-LIB_PATH = Path(__file__).resolve().parent / "libtdfo_b200.so"
+import os
+
+# TDFO_B200_LIB overrides the in-tree library (deployments that install it elsewhere, A/B builds)
+LIB_PATH = Path(os.environ.get("TDFO_B200_LIB") or Path(__file__).resolve().parent / "libtdfo_b200.so")
 
 # constants of include/tdfo_b200.h
 F32, BF16 = 0, 1

@@ -15,10 +15,17 @@ constexpr int kRadixLog = 9;                            // up to 9 bits per pass
 constexpr int kRadix = 1 << kRadixLog;                  // bins per pass (lookback / histogram row stride)
 constexpr int kBinsPerThread = kRadix / kSortThreads;   // 2
 constexpr int kMaxPasses = 4;
+#ifndef TDFO_SORT_BALLOT_MATCH
+#define TDFO_SORT_BALLOT_MATCH 1
+#endif
+#ifndef TDFO_SORT_MINB
+#define TDFO_SORT_MINB 4
+#endif
 
 constexpr uint32_t kLbAgg  = 1u << 30;
 constexpr uint32_t kLbIncl = 2u << 30;
 constexpr uint32_t kLbMask = (1u << 30) - 1;
+constexpr int kLbBatch = 8;                             // look-back words requested per round trip
 
 struct SortPlan {
     int passes;
@@ -71,7 +78,7 @@ radix_histogram_kernel(const uint32_t* __restrict__ keys, int64_t n, HistArgs h,
     }
 }
 
-__global__ void __launch_bounds__(kSortThreads)
+__global__ void __launch_bounds__(kSortThreads, TDFO_SORT_MINB)
 radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                       uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                       int64_t n, int shift, int bits,
@@ -120,7 +127,17 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __re
     for (int i = 0; i < kSortItems; ++i) {
         const int slot = warp * (kSortItems * 32) + i * 32 + lane;
         const uint32_t d = (slot < count) ? ((key[i] >> shift) & dmask) : (uint32_t)kRadix;
+#if TDFO_SORT_BALLOT_MATCH
+        // lanes holding the same digit, from one ballot per digit bit (10 bits: 9 + the "no key" bit)
+        uint32_t peers = kFullMask;
+#pragma unroll
+        for (int bit = 0; bit <= kRadixLog; ++bit) {
+            const uint32_t vote = __ballot_sync(kFullMask, (d >> bit) & 1u);
+            peers &= ((d >> bit) & 1u) ? vote : ~vote;
+        }
+#else
         const uint32_t peers = __match_any_sync(kFullMask, d);
+#endif
         const int leader = __ffs(peers) - 1;
         uint32_t pre = 0;
         if (lane == leader && d < (uint32_t)kRadix) {
@@ -163,20 +180,31 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __re
     for (int j = 0; j < kBinsPerThread; ++j) {
         const int d = tid * kBinsPerThread + j;
         if (d < nbins) {
+            // Walk back over earlier tiles until one holds an inclusive prefix.  kLbBatch words are
+            // requested per round trip: a walk of depth k costs k / kLbBatch L2 latencies, not k
+            // (with ~600 tiles in flight the serial walk was the longest chain in the pass).
             uint32_t excl = 0;
             int spins = 0;
-            for (int t = tile - 1; t >= 0; --t) {
-                uint32_t w = ld_relaxed_u32(lookback + (size_t)t * kRadix + d);
-                while ((w >> 30) == 0) {
-                    if (++spins > kScanWatchdog) {
-                        if (err_flag) atomicOr(err_flag, TDFO_FLAG_SCAN_TIMEOUT);
-                        w = kLbIncl;
-                        break;
+            bool done = false;
+            for (int t = tile - 1; t >= 0 && !done; t -= kLbBatch) {
+                uint32_t w[kLbBatch];
+#pragma unroll
+                for (int q = 0; q < kLbBatch; ++q)
+                    w[q] = (t - q >= 0) ? ld_relaxed_u32(lookback + (size_t)(t - q) * kRadix + d) : kLbIncl;
+#pragma unroll
+                for (int q = 0; q < kLbBatch; ++q) {
+                    if (done) break;
+                    while ((w[q] >> 30) == 0) {          // that tile has not published yet
+                        if (++spins > kScanWatchdog) {
+                            if (err_flag) atomicOr(err_flag, TDFO_FLAG_SCAN_TIMEOUT);
+                            w[q] = kLbIncl;
+                            break;
+                        }
+                        w[q] = ld_relaxed_u32(lookback + (size_t)(t - q) * kRadix + d);
                     }
-                    w = ld_relaxed_u32(lookback + (size_t)t * kRadix + d);
+                    excl += w[q] & kLbMask;
+                    if ((w[q] >> 30) == 2) done = true;
                 }
-                excl += w & kLbMask;
-                if ((w >> 30) == 2) break;
             }
             if (tile > 0)
                 st_relaxed_u32(lookback + (size_t)tile * kRadix + d, kLbIncl | ((excl + tile_count[j]) & kLbMask));
