@@ -314,6 +314,11 @@ typedef struct tdfo_optimizer_args {
  *   state0     ROWWISE_ADAGRAD: float[total_rows] sum of mean squared grads
  *              ADAM: float[total_rows, D] first moment;  SGD: NULL
  *   state1     ADAM: float[total_rows, D] second moment; else NULL
+ * worklist (optional, uint32[worklist_entries], entries >= L/256 + 2): rows with more than 256
+ *   occurrences ("hot" rows of a skewed id distribution) are queued here by the main kernel and
+ *   reduced by a second kernel that puts a whole thread block on each such row (fixed
+ *   assignment and combination order, so results are reproducible; the summation order differs
+ *   from the strictly sequential one).  Without a worklist every row is reduced by one lane group.
  * ROWWISE_ADAGRAD: h += mean_d(g_d^2); w -= lr / (sqrt(h) + eps) * g.
  * SGD: w -= lr * g.  bf16 tables: fp32 math, round-to-nearest-even on store.
  * Replaces: upstream split_embedding_backward_codegen_{sgd,rowwise_adagrad,adam}
@@ -329,6 +334,7 @@ int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t total_rows,
                        const int64_t* offsets, const int64_t* feat_out_col,
                        int32_t F, int64_t B, int64_t L, int32_t pooling_mode,
                        const tdfo_optimizer_args* opt /* HOST */,
+                       uint32_t* worklist, int64_t worklist_entries,
                        void* stream);
 
 /*
@@ -347,6 +353,7 @@ int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t total_rows,
 typedef struct tdfo_backward_layout {
     size_t input_keys, input_vals;   /* where linearised pairs go in (clobbered by the sort) */
     size_t sorted_keys, sorted_vals, unique_keys, seg_starts, first_vals, num_unique; /* byte offsets */
+    size_t worklist, worklist_entries;   /* hot-row worklist for tdfo_sparse_update: byte offset, uint32 entries */
     size_t total_bytes;
     int32_t key_bits;
 } tdfo_backward_layout;

@@ -30,7 +30,8 @@ class OptimizerArgs(Structure):
 
 class BackwardLayout(Structure):
     _fields_ = [("input_keys", c_size_t), ("input_vals", c_size_t), ("sorted_keys", c_size_t), ("sorted_vals", c_size_t), ("unique_keys", c_size_t),
-                ("seg_starts", c_size_t), ("first_vals", c_size_t), ("num_unique", c_size_t), ("total_bytes", c_size_t),
+                ("seg_starts", c_size_t), ("first_vals", c_size_t), ("num_unique", c_size_t),
+                ("worklist", c_size_t), ("worklist_entries", c_size_t), ("total_bytes", c_size_t),
                 ("key_bits", c_int32)]
 
 
@@ -56,7 +57,7 @@ _SIGNATURES = {
     "tdfo_radix_sort_pairs": (c_int, [P, P, P, P, c_int64, c_int32, P, P, c_size_t, P]),
     "tdfo_unique_segments": (c_int, [P, P, c_int64, P, P, P, P, P, P, c_size_t, P]),
     "tdfo_sparse_update": (c_int, [P, c_int32, c_int64, c_int32, P, P, P, c_int64, P, P, P, P, P, P, P, c_int32,
-                                   c_int64, c_int64, c_int32, POINTER(OptimizerArgs), P]),
+                                   c_int64, c_int64, c_int32, POINTER(OptimizerArgs), P, c_int64, P]),
     "tdfo_backward_scratch_bytes": (c_size_t, [c_int64, c_int64]),
     "tdfo_backward_scratch_layout": (c_int, [c_int64, c_int64, POINTER(BackwardLayout)]),
     "tdfo_embedding_backward_update": (c_int, [P, c_int32, c_int64, c_int32, P, P, P, c_int64, P, P, P, P, P, P,

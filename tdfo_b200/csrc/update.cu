@@ -54,6 +54,9 @@ struct UpdateArgs {
     const uint32_t* unique_keys;
     const uint32_t* seg_starts;
     const uint32_t* first_vals;
+    uint32_t* long_list;      // optional worklist of unique-row indices whose segments are long (hot rows)
+    uint32_t* long_count;
+    uint32_t long_cap;
     const uint32_t* num_unique;
     const int64_t* offsets;
     const int64_t* feat_out_col;
@@ -71,6 +74,8 @@ struct UpdateArgs {
 
 // Launch shape of the update kernel: 8 warps per CTA, persistent grid of 148 x MINB CTAs.
 constexpr int kUpdCtaThreads = 256;
+constexpr uint32_t kLongSegment = 256;   // occurrences above which a row goes to the block-per-row kernel
+constexpr int kLongMaxFloats = 8192;      // shared-memory floats for the partial sums of that kernel
 
 // Per unique row: key, first / one-past-last sorted position, payload of the first occurrence.
 struct RowMeta {
@@ -100,6 +105,80 @@ __device__ __forceinline__ const float* grad_row_of(const UpdateArgs& a, uint32_
     if (a.pooling_mode == TDFO_POOL_MEAN)
         scale = 1.f / (float)(__ldg(a.offsets + v + 1) - __ldg(a.offsets + v));
     return a.grad + (size_t)b * a.grad_stride + __ldg(a.feat_out_col + f);
+}
+
+// Optimizer step for one row held by an LPR-lane group: g = reduced gradient, w = current row
+// (both fp32, CPL chunks per lane); writes the row (and its state) back if `valid`.
+template <typename T, int LPR, int CPL, int OPT>
+__device__ __forceinline__ void apply_row_update(const UpdateArgs& a, uint32_t row, bool valid, float h_old,
+                                                 float (&g)[CPL][Chunk<T>::kElems], float (&w)[CPL][Chunk<T>::kElems],
+                                                 int sub, unsigned gmask) {
+    constexpr int E = Chunk<T>::kElems;
+    uint4* __restrict__ wbase = reinterpret_cast<uint4*>(a.weights);
+    if (OPT == TDFO_OPT_SGD) {
+#pragma unroll
+        for (int k = 0; k < CPL; ++k)
+#pragma unroll
+            for (int i = 0; i < E; ++i) {
+                const float gi = fmaf(a.wd, w[k][i], g[k][i]);
+                w[k][i] = fmaf(-a.lr, gi, w[k][i]);
+            }
+    } else if (OPT == TDFO_OPT_ROWWISE_ADAGRAD) {
+        float ss = 0.f;
+#pragma unroll
+        for (int k = 0; k < CPL; ++k)
+#pragma unroll
+            for (int i = 0; i < E; ++i) {
+                g[k][i] = fmaf(a.wd, w[k][i], g[k][i]);
+                if (sub + k * LPR >= a.nchunks) g[k][i] = 0.f;       // lanes past the row end
+                ss = fmaf(g[k][i], g[k][i], ss);
+            }
+#pragma unroll
+        for (int o = 1; o < LPR; o <<= 1) ss += __shfl_xor_sync(gmask, ss, o);
+        const float h = h_old + ss * a.inv_D;
+        // sqrt / divide through the SFU (2-3 ulp, far inside the 1e-5 parity bar)
+        const float sq = h > 0.f ? h * rsqrtf(h) : 0.f;
+        const float mult = __fdividef(a.lr, sq + a.eps);
+        if (valid && sub == 0) a.state0[row] = h;
+#pragma unroll
+        for (int k = 0; k < CPL; ++k)
+#pragma unroll
+            for (int i = 0; i < E; ++i) w[k][i] = fmaf(-mult, g[k][i], w[k][i]);
+    } else if (valid) {   // ADAM
+#pragma unroll
+        for (int k = 0; k < CPL; ++k) {
+            const int c = sub + k * LPR;
+            if (c < a.nchunks) {
+                float* m = a.state0 + (size_t)row * a.D + (size_t)c * E;
+                float* v = a.state1 + (size_t)row * a.D + (size_t)c * E;
+#pragma unroll
+                for (int t = 0; t < E; t += 4) {
+                    uint4 mr = ld_128(m + t), vr = ld_128(v + t);
+                    float mm[4] = {__uint_as_float(mr.x), __uint_as_float(mr.y), __uint_as_float(mr.z), __uint_as_float(mr.w)};
+                    float vv[4] = {__uint_as_float(vr.x), __uint_as_float(vr.y), __uint_as_float(vr.z), __uint_as_float(vr.w)};
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float gi = g[k][t + i];
+                        mm[i] = a.beta1 * mm[i] + (1.f - a.beta1) * gi;
+                        vv[i] = a.beta2 * vv[i] + (1.f - a.beta2) * gi * gi;
+                        const float mhat = mm[i] / a.bc1;
+                        const float vhat = vv[i] / a.bc2;
+                        w[k][t + i] -= a.lr * (mhat / (sqrtf(vhat) + a.eps) + a.wd * w[k][t + i]);
+                    }
+                    st_128(m + t, make_uint4(__float_as_uint(mm[0]), __float_as_uint(mm[1]), __float_as_uint(mm[2]), __float_as_uint(mm[3])));
+                    st_128(v + t, make_uint4(__float_as_uint(vv[0]), __float_as_uint(vv[1]), __float_as_uint(vv[2]), __float_as_uint(vv[3])));
+                }
+            }
+        }
+    }
+
+    if (valid) {
+#pragma unroll
+        for (int k = 0; k < CPL; ++k) {
+            const int c = sub + k * LPR;
+            if (c < a.nchunks) st_128(wbase + (size_t)row * a.nchunks + c, Chunk<T>::pack(w[k]));
+        }
+    }
 }
 
 // Persistent warps; a warp works on RPW*UR consecutive unique rows per step, one row per
@@ -153,6 +232,17 @@ sparse_update_kernel(const UpdateArgs a) {
 #pragma unroll
         for (int q = 0; q < UR; ++q) {
             valid[q] = cur[q].key < a.total_rows;      // padding rows and the out-of-range marker fail this
+            // A hot row (very long segment) would be reduced serially by this one group: hand it to
+            // the block-per-row kernel that runs right after this one instead.
+            if (a.long_list != nullptr && valid[q] && cur[q].e - cur[q].s > kLongSegment) {
+                uint32_t slot = 0;
+                if (sub == 0) slot = atomicAdd(a.long_count, 1u);
+                slot = __shfl_sync(gmask, slot, grp * LPR);
+                if (slot < a.long_cap) {
+                    if (sub == 0) a.long_list[slot] = u0 + q * RPW + grp;
+                    valid[q] = false;
+                }
+            }
             const float* grow = grad_row_of(a, valid[q] ? cur[q].v0 : 0u, scale[q]);
             const size_t wrow = (size_t)(valid[q] ? cur[q].key : 0u) * a.nchunks;
 #pragma unroll
@@ -203,74 +293,90 @@ sparse_update_kernel(const UpdateArgs a) {
                 }
             }
 
-            if (OPT == TDFO_OPT_SGD) {
-#pragma unroll
-                for (int k = 0; k < CPL; ++k)
-#pragma unroll
-                    for (int i = 0; i < E; ++i) {
-                        const float gi = fmaf(a.wd, w[k][i], g[k][i]);
-                        w[k][i] = fmaf(-a.lr, gi, w[k][i]);
-                    }
-            } else if (OPT == TDFO_OPT_ROWWISE_ADAGRAD) {
-                float ss = 0.f;
-#pragma unroll
-                for (int k = 0; k < CPL; ++k)
-#pragma unroll
-                    for (int i = 0; i < E; ++i) {
-                        g[k][i] = fmaf(a.wd, w[k][i], g[k][i]);
-                        if (sub + k * LPR >= a.nchunks) g[k][i] = 0.f;       // lanes past the row end
-                        ss = fmaf(g[k][i], g[k][i], ss);
-                    }
-#pragma unroll
-                for (int o = 1; o < LPR; o <<= 1) ss += __shfl_xor_sync(gmask, ss, o);
-                const float h = h_old[q] + ss * a.inv_D;
-                // sqrt / divide through the SFU (2-3 ulp, far inside the 1e-5 parity bar)
-                const float sq = h > 0.f ? h * rsqrtf(h) : 0.f;
-                const float mult = __fdividef(a.lr, sq + a.eps);
-                if (valid[q] && sub == 0) a.state0[row] = h;
-#pragma unroll
-                for (int k = 0; k < CPL; ++k)
-#pragma unroll
-                    for (int i = 0; i < E; ++i) w[k][i] = fmaf(-mult, g[k][i], w[k][i]);
-            } else if (valid[q]) {   // ADAM
-#pragma unroll
-                for (int k = 0; k < CPL; ++k) {
-                    const int c = sub + k * LPR;
-                    if (c < a.nchunks) {
-                        float* m = a.state0 + (size_t)row * a.D + (size_t)c * E;
-                        float* v = a.state1 + (size_t)row * a.D + (size_t)c * E;
-#pragma unroll
-                        for (int t = 0; t < E; t += 4) {
-                            uint4 mr = ld_128(m + t), vr = ld_128(v + t);
-                            float mm[4] = {__uint_as_float(mr.x), __uint_as_float(mr.y), __uint_as_float(mr.z), __uint_as_float(mr.w)};
-                            float vv[4] = {__uint_as_float(vr.x), __uint_as_float(vr.y), __uint_as_float(vr.z), __uint_as_float(vr.w)};
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                const float gi = g[k][t + i];
-                                mm[i] = a.beta1 * mm[i] + (1.f - a.beta1) * gi;
-                                vv[i] = a.beta2 * vv[i] + (1.f - a.beta2) * gi * gi;
-                                const float mhat = mm[i] / a.bc1;
-                                const float vhat = vv[i] / a.bc2;
-                                w[k][t + i] -= a.lr * (mhat / (sqrtf(vhat) + a.eps) + a.wd * w[k][t + i]);
-                            }
-                            st_128(m + t, make_uint4(__float_as_uint(mm[0]), __float_as_uint(mm[1]), __float_as_uint(mm[2]), __float_as_uint(mm[3])));
-                            st_128(v + t, make_uint4(__float_as_uint(vv[0]), __float_as_uint(vv[1]), __float_as_uint(vv[2]), __float_as_uint(vv[3])));
-                        }
-                    }
-                }
-            }
-
-            if (valid[q]) {
-#pragma unroll
-                for (int k = 0; k < CPL; ++k) {
-                    const int c = sub + k * LPR;
-                    if (c < a.nchunks) st_128(wbase + (size_t)row * a.nchunks + c, Chunk<T>::pack(w[k]));
-                }
-            }
+            apply_row_update<T, LPR, CPL, OPT>(a, row, valid[q], h_old[q], g, w, sub, gmask);
         }
         u0 += stride;
 #pragma unroll
         for (int q = 0; q < UR; ++q) cur[q] = PREFETCH ? nxt[q] : load_row_meta(a, u0 + q * RPW + grp, nu);
+    }
+}
+
+// Hot rows: one CTA per row.  Its G = 256 / LPR groups each reduce a strided share of the row's
+// occurrences (fixed assignment, each in increasing order), the partial sums meet in shared
+// memory and are added in group order, so the result does not depend on timing; then group 0
+// applies the optimizer as usual.
+template <typename T, int LPR, int CPL, int OPT>
+__global__ void __launch_bounds__(kUpdCtaThreads)
+sparse_update_long_kernel(const UpdateArgs a) {
+    constexpr int E = Chunk<T>::kElems;
+    constexpr int G = kUpdCtaThreads / LPR;
+    constexpr int GQ = E / 4;
+    __shared__ float s_part[kLongMaxFloats];
+    const int lane = lane_id();
+    const int sub = lane % LPR;
+    const int grp_in_warp = lane / LPR;
+    const int g_id = threadIdx.x / LPR;
+    const unsigned gmask = (LPR == 32) ? kFullMask : (((1u << (LPR & 31)) - 1u) << (grp_in_warp * LPR));
+    const uint32_t n_long = min(*a.long_count, a.long_cap);
+    uint4* __restrict__ wbase = reinterpret_cast<uint4*>(a.weights);
+    const int rowf = a.nchunks * E;                      // floats per row
+    // groups that fit the shared buffer take part in the reduction (all of them for rows <= 1 KB)
+    const int g_used = min(G, kLongMaxFloats / rowf);
+    for (uint32_t wi = blockIdx.x; wi < n_long; wi += gridDim.x) {
+        const uint32_t u = a.long_list[wi];
+        const uint32_t row = __ldg(a.unique_keys + u);
+        const uint32_t s0 = __ldg(a.seg_starts + u), e0 = __ldg(a.seg_starts + u + 1);
+        float g[CPL][E];
+#pragma unroll
+        for (int k = 0; k < CPL; ++k)
+#pragma unroll
+            for (int i = 0; i < E; ++i) g[k][i] = 0.f;
+        if (g_id < g_used) {
+            for (uint32_t i = s0 + g_id; i < e0; i += g_used) {
+                float sc;
+                const float* grow = grad_row_of(a, __ldg(a.sorted_vals + i), sc);
+#pragma unroll
+                for (int k = 0; k < CPL; ++k) {
+                    const int c = sub + k * LPR;
+                    if (c < a.nchunks) {
+#pragma unroll
+                        for (int t = 0; t < GQ; ++t) {
+                            const uint4 x = ldg_128(grow + (size_t)c * E + 4 * t);
+                            g[k][4 * t]     = fmaf(sc, __uint_as_float(x.x), g[k][4 * t]);
+                            g[k][4 * t + 1] = fmaf(sc, __uint_as_float(x.y), g[k][4 * t + 1]);
+                            g[k][4 * t + 2] = fmaf(sc, __uint_as_float(x.z), g[k][4 * t + 2]);
+                            g[k][4 * t + 3] = fmaf(sc, __uint_as_float(x.w), g[k][4 * t + 3]);
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < CPL; ++k) {
+                const int c = sub + k * LPR;
+                if (c < a.nchunks)
+#pragma unroll
+                    for (int i = 0; i < E; ++i) s_part[g_id * rowf + c * E + i] = g[k][i];
+            }
+        }
+        __syncthreads();
+        if (g_id == 0) {
+            float w[CPL][E];
+#pragma unroll
+            for (int k = 0; k < CPL; ++k) {
+                const int c = sub + k * LPR;
+#pragma unroll
+                for (int i = 0; i < E; ++i) {
+                    float acc = 0.f;
+                    if (c < a.nchunks)
+                        for (int gi = 0; gi < g_used; ++gi) acc += s_part[gi * rowf + c * E + i];
+                    g[k][i] = acc;
+                }
+                Chunk<T>::unpack(ld_row_128(wbase + (size_t)row * a.nchunks + min(c, a.nchunks - 1)), w[k]);
+            }
+            const float h_old = (OPT == TDFO_OPT_ROWWISE_ADAGRAD) ? __ldcg(a.state0 + row) : 0.f;
+            apply_row_update<T, LPR, CPL, OPT>(a, row, true, h_old, g, w, sub, gmask);
+        }
+        __syncthreads();
     }
 }
 
@@ -292,6 +398,19 @@ static int launch_update(const UpdateArgs& a, int opt, int64_t max_unique, cudaS
     }
     count_launch();
     TDFO_LAUNCH_CHECK("sparse_update");
+    if (a.long_list != nullptr) {
+        const unsigned lb = kNumSMs * 2;
+        switch (opt) {
+            case TDFO_OPT_SGD:
+                sparse_update_long_kernel<T, LPR, CPL, TDFO_OPT_SGD><<<lb, kUpdCtaThreads, 0, st>>>(a); break;
+            case TDFO_OPT_ROWWISE_ADAGRAD:
+                sparse_update_long_kernel<T, LPR, CPL, TDFO_OPT_ROWWISE_ADAGRAD><<<lb, kUpdCtaThreads, 0, st>>>(a); break;
+            default:
+                sparse_update_long_kernel<T, LPR, CPL, TDFO_OPT_ADAM><<<lb, kUpdCtaThreads, 0, st>>>(a); break;
+        }
+        count_launch();
+        TDFO_LAUNCH_CHECK("sparse_update_long");
+    }
     return TDFO_OK;
 }
 
@@ -373,10 +492,18 @@ int sparse_update_impl(void* weights, int32_t weights_dtype, int64_t total_rows,
                        const uint32_t* sorted_vals, const uint32_t* unique_keys,
                        const uint32_t* seg_starts, const uint32_t* first_vals, const uint32_t* num_unique,
                        const int64_t* offsets, const int64_t* feat_out_col, int32_t F, int64_t B,
-                       int64_t L, int32_t pooling_mode, const tdfo_optimizer_args* opt, cudaStream_t st) {
+                       int64_t L, int32_t pooling_mode, const tdfo_optimizer_args* opt,
+                       uint32_t* worklist, int64_t worklist_entries, cudaStream_t st) {
     if (L == 0) return TDFO_OK;
     const size_t esz = weights_dtype == TDFO_F32 ? 4 : 2;
     UpdateArgs a;
+    a.long_list = nullptr; a.long_count = nullptr; a.long_cap = 0;
+    if (worklist != nullptr && worklist_entries >= 2) {        // word 0 = counter, the rest = row indices
+        TDFO_CUDA(cudaMemsetAsync(worklist, 0, sizeof(uint32_t), st));
+        a.long_count = worklist;
+        a.long_list = worklist + 1;
+        a.long_cap = (uint32_t)(worklist_entries - 1);
+    }
     a.weights = weights; a.state0 = state0; a.state1 = state1; a.grad = grad_out;
     a.sorted_vals = sorted_vals; a.unique_keys = unique_keys; a.seg_starts = seg_starts; a.first_vals = first_vals;
     a.num_unique = num_unique; a.offsets = offsets; a.feat_out_col = feat_out_col;
@@ -429,7 +556,8 @@ extern "C" int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t 
                                   const uint32_t* seg_starts, const uint32_t* first_vals, const uint32_t* num_unique,
                                   const int64_t* offsets, const int64_t* feat_out_col, int32_t F,
                                   int64_t B, int64_t L, int32_t pooling_mode,
-                                  const tdfo_optimizer_args* opt, void* stream) {
+                                  const tdfo_optimizer_args* opt,
+                                  uint32_t* worklist, int64_t worklist_entries, void* stream) {
     int rc = check_common("sparse_update", weights_dtype, total_rows, D);
     if (rc) return rc;
     rc = check_opt("sparse_update", opt, state0, state1);
@@ -447,7 +575,8 @@ extern "C" int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t 
     TDFO_CHECK_ARG(pooling_mode != TDFO_POOL_MEAN || offsets, "sparse_update: MEAN pooling needs offsets");
     return sparse_update_impl(weights, weights_dtype, total_rows, D, state0, state1, grad_out, grad_stride,
                               sorted_vals, unique_keys, seg_starts, first_vals, num_unique, offsets, feat_out_col,
-                              F, B, L, pooling_mode, opt, static_cast<cudaStream_t>(stream));
+                              F, B, L, pooling_mode, opt, worklist, worklist_entries,
+                              static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int tdfo_backward_scratch_layout(int64_t L, int64_t total_rows, tdfo_backward_layout* layout) {
@@ -467,7 +596,9 @@ extern "C" int tdfo_backward_scratch_layout(int64_t L, int64_t total_rows, tdfo_
     layout->input_keys = 0;
     layout->input_vals = A;
     layout->num_unique = 5 * A;
-    const size_t sort_off = 5 * A + 256;
+    layout->worklist = 5 * A + 256;
+    layout->worklist_entries = (size_t)(L / kLongSegment) + 2;     // counter + at most L/257 hot rows
+    const size_t sort_off = layout->worklist + align_up(layout->worklist_entries * sizeof(uint32_t), 256);
     const size_t scan_off = sort_off + radix_sort_scratch_bytes_impl(L, bits);
     layout->total_bytes = scan_off + tdfo_scan_scratch_bytes(L);
     return TDFO_OK;
@@ -524,8 +655,9 @@ extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dty
     uint32_t* k1 = reinterpret_cast<uint32_t*>(base + 2 * A);
     uint32_t* v1 = reinterpret_cast<uint32_t*>(base + 3 * A);
     uint32_t* num_unique = reinterpret_cast<uint32_t*>(base + lay.num_unique);
-    void* sort_scratch = base + 5 * A + 256;
-    void* scan_scratch = base + 5 * A + 256 + radix_sort_scratch_bytes_impl(L, lay.key_bits);
+    const size_t sort_off = lay.worklist + align_up(lay.worklist_entries * sizeof(uint32_t), 256);
+    void* sort_scratch = base + sort_off;
+    void* scan_scratch = base + sort_off + radix_sort_scratch_bytes_impl(L, lay.key_bits);
 
     if (!keys_in_scratch) {
         rc = tdfo_linearize_indices(indices, offsets, feat_row_base, feat_rows, F, B, total_rows, pooling_mode,
@@ -547,5 +679,6 @@ extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dty
     rc = unique_segments_impl(sk, sv, L, uk, ss, fv, num_unique, err_flag, scan_scratch, st);
     if (rc) return rc;
     return sparse_update_impl(weights, weights_dtype, total_rows, D, state0, state1, grad_out, grad_stride,
-                              sv, uk, ss, fv, num_unique, offsets, feat_out_col, F, B, L, pooling_mode, opt, st);
+                              sv, uk, ss, fv, num_unique, offsets, feat_out_col, F, B, L, pooling_mode, opt,
+                              reinterpret_cast<uint32_t*>(base + lay.worklist), (int64_t)lay.worklist_entries, st);
 }

@@ -329,7 +329,8 @@ def unique_segments(sorted_keys: torch.Tensor, err_flag=None, sorted_vals: Optio
 
 
 def sparse_update(group: TableGroup, grad_out, sorted_vals, unique_keys, seg_starts, first_vals, num_unique, offsets,
-                  B, L, pooling_mode, opt: OptimizerArgs):
+                  B, L, pooling_mode, opt: OptimizerArgs, worklist: Optional[torch.Tensor] = None):
+    """``worklist``: optional int32 tensor of at least L/256 + 2 entries for the hot-row kernel."""
     grad_out = _cuda(grad_out, torch.float32, "grad_out")
     w = group.weights
     grad_stride = group.D if pooling_mode == POOL_NONE else grad_out.shape[-1]
@@ -337,7 +338,8 @@ def sparse_update(group: TableGroup, grad_out, sorted_vals, unique_keys, seg_sta
         _ptr(w), _wdtype(w), group.total_rows, group.D, _ptr(group.state0), _ptr(group.state1), _ptr(grad_out),
         grad_stride, _ptr(sorted_vals), _ptr(unique_keys), _ptr(seg_starts), _ptr(first_vals), _ptr(num_unique),
         _ptr(offsets),
-        _ptr(group.feat_out_col), group.F, B, L, pooling_mode, ctypes.byref(opt), _stream()))
+        _ptr(group.feat_out_col), group.F, B, L, pooling_mode, ctypes.byref(opt), _ptr(worklist),
+        0 if worklist is None else worklist.numel(), _stream()))
 
 
 def copy_feature_blocks(src: torch.Tensor, dst: torch.Tensor, B: int, D: int, meta: torch.Tensor) -> None:

@@ -412,3 +412,24 @@ def test_forward_emits_the_backward_pairs(ops):
         grp2 = group_for(ops, c, dev(c.weights), pooled=pooled)
         ops.embedding_backward_update(grp2, dev(grad), dev(idx), dev(c.offsets), c.B, mode, opt)
         assert torch.equal(grp.weights, grp2.weights)
+
+
+@pytest.mark.parametrize("D", [16, 128, 512])
+@pytest.mark.parametrize("optimizer", [orc.OPT_SGD, orc.OPT_ROWWISE_ADAGRAD, orc.OPT_ADAM])
+def test_backward_hot_rows_take_the_block_per_row_path(ops, D, optimizer):
+    """Skewed ids: rows with thousands of occurrences are queued on the worklist and reduced by a
+    whole thread block each.  Their summation order differs from the oracle's strictly sequential
+    one, so the bar for those rows is the fp32 reassociation error of a ~2000-term sum."""
+    c = make_case(seed=D + optimizer, F=3, B=3000, D=D, rows=[40, 3, 2], max_len=3, p_empty=0.0)
+    w_o, s0_o, s1_o, grp, routing, scratch = _run_backward_pair(ops, c, orc.POOL_SUM, optimizer, False, steps=1)
+    lay = ops.backward_layout(c.L, c.total_rows)
+    raw = scratch.cpu().numpy()
+    queued = int(raw[lay.worklist: lay.worklist + 4].view(np.uint32)[0])
+    seg = np.diff(routing["seg_starts"].astype(np.int64))
+    assert queued == int((seg > 256).sum()) and queued >= 5
+    np.testing.assert_allclose(table_to_f32(grp.weights), w_o, rtol=5e-5, atol=2e-5)
+    if s0_o is not None:
+        np.testing.assert_allclose(grp.state0.cpu().numpy(), s0_o, rtol=5e-5, atol=2e-5)
+    # and the result is reproducible bit for bit
+    w_o2, _, _, grp2, _, _ = _run_backward_pair(ops, c, orc.POOL_SUM, optimizer, False, steps=1)
+    assert torch.equal(grp.weights, grp2.weights)
