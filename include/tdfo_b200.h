@@ -314,7 +314,7 @@ typedef struct tdfo_optimizer_args {
  *   state0     ROWWISE_ADAGRAD: float[total_rows] sum of mean squared grads
  *              ADAM: float[total_rows, D] first moment;  SGD: NULL
  *   state1     ADAM: float[total_rows, D] second moment; else NULL
- * worklist (optional, uint32[worklist_entries], entries >= L/256 + 2): rows with more than 256
+ * worklist (optional, uint32[worklist_entries], entries >= L/64 + 2): rows with more than 64
  *   occurrences ("hot" rows of a skewed id distribution) are queued here by the main kernel and
  *   reduced by a second kernel that puts a whole thread block on each such row (fixed
  *   assignment and combination order, so results are reproducible; the summation order differs

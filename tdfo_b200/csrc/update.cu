@@ -74,7 +74,7 @@ struct UpdateArgs {
 
 // Launch shape of the update kernel: 8 warps per CTA, persistent grid of 148 x MINB CTAs.
 constexpr int kUpdCtaThreads = 256;
-constexpr uint32_t kLongSegment = 256;   // occurrences above which a row goes to the block-per-row kernel
+constexpr uint32_t kLongSegment = 64;    // occurrences above which a row goes to the block-per-row kernel
 constexpr int kLongMaxFloats = 8192;      // shared-memory floats for the partial sums of that kernel
 
 // Per unique row: key, first / one-past-last sorted position, payload of the first occurrence.
@@ -181,6 +181,53 @@ __device__ __forceinline__ void apply_row_update(const UpdateArgs& a, uint32_t r
     }
 }
 
+// g += sum over occurrences [lo, hi) of one row, in increasing order.  Payloads are fetched one per
+// lane of the group (coalesced), gradient rows four at a time, so a long segment is a stream of
+// independent loads rather than a chain of dependent ones.
+template <typename T, int LPR, int CPL, bool DEEP>
+__device__ __forceinline__ void accumulate_occurrences(const UpdateArgs& a, uint32_t lo, uint32_t hi,
+                                                       float (&g)[CPL][Chunk<T>::kElems], int sub, int grp,
+                                                       unsigned gmask) {
+    constexpr int E = Chunk<T>::kElems;
+    constexpr int GQ = E / 4;
+    // gradient rows in flight: one in the main kernel (register budget), several in the hot-row kernel
+    constexpr int UB = !DEEP ? 1 : ((CPL * GQ <= 2) ? 4 : ((CPL * GQ <= 4) ? 2 : 1));
+    for (uint32_t i = lo; i < hi; i += LPR) {
+        const uint32_t n = min((uint32_t)LPR, hi - i);
+        const uint32_t my_v = ((uint32_t)sub < n) ? __ldg(a.sorted_vals + i + sub) : 0u;
+        for (uint32_t j = 0; j < n; j += UB) {
+            uint4 x[UB][CPL][GQ];
+            float sc[UB];
+#pragma unroll
+            for (int u = 0; u < UB; ++u) {
+                const uint32_t v = __shfl_sync(gmask, my_v, grp * LPR + (int)((j + u) % LPR));
+                const float* grow = grad_row_of(a, (j + u < n) ? v : 0u, sc[u]);
+                if (j + u >= n) sc[u] = 0.f;
+#pragma unroll
+                for (int k = 0; k < CPL; ++k) {
+                    const int c = min(sub + k * LPR, a.nchunks - 1);
+#pragma unroll
+                    for (int t = 0; t < GQ; ++t) x[u][k][t] = ldg_128(grow + (size_t)c * E + 4 * t);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UB; ++u) {
+                if (j + u < n) {
+#pragma unroll
+                    for (int k = 0; k < CPL; ++k)
+#pragma unroll
+                        for (int t = 0; t < GQ; ++t) {
+                            g[k][4 * t]     = fmaf(sc[u], __uint_as_float(x[u][k][t].x), g[k][4 * t]);
+                            g[k][4 * t + 1] = fmaf(sc[u], __uint_as_float(x[u][k][t].y), g[k][4 * t + 1]);
+                            g[k][4 * t + 2] = fmaf(sc[u], __uint_as_float(x[u][k][t].z), g[k][4 * t + 2]);
+                            g[k][4 * t + 3] = fmaf(sc[u], __uint_as_float(x[u][k][t].w), g[k][4 * t + 3]);
+                        }
+                }
+            }
+        }
+    }
+}
+
 // Persistent warps; a warp works on RPW*UR consecutive unique rows per step, one row per
 // LPR-lane group and unroll slot.  Under load a B200 memory round trip takes ~3 us, so the
 // kernel is built to keep as many independent 128-bit row requests in flight per SM as the
@@ -272,26 +319,8 @@ sparse_update_kernel(const UpdateArgs a) {
                 Chunk<T>::unpack(wv[q][k], w[k]);
             }
             // further occurrences of the row, in sorted (= original) order
-            if (valid[q]) {
-                for (uint32_t i = cur[q].s + 1; i < cur[q].e; ++i) {
-                    float sc;
-                    const float* grow = grad_row_of(a, __ldg(a.sorted_vals + i), sc);
-#pragma unroll
-                    for (int k = 0; k < CPL; ++k) {
-                        const int c = sub + k * LPR;
-                        if (c < a.nchunks) {
-#pragma unroll
-                            for (int t = 0; t < GQ; ++t) {
-                                const uint4 x = ldg_128(grow + (size_t)c * E + 4 * t);
-                                g[k][4 * t]     = fmaf(sc, __uint_as_float(x.x), g[k][4 * t]);
-                                g[k][4 * t + 1] = fmaf(sc, __uint_as_float(x.y), g[k][4 * t + 1]);
-                                g[k][4 * t + 2] = fmaf(sc, __uint_as_float(x.z), g[k][4 * t + 2]);
-                                g[k][4 * t + 3] = fmaf(sc, __uint_as_float(x.w), g[k][4 * t + 3]);
-                            }
-                        }
-                    }
-                }
-            }
+            if (valid[q] && cur[q].e - cur[q].s > 1)
+                accumulate_occurrences<T, LPR, CPL, false>(a, cur[q].s + 1, cur[q].e, g, sub, grp, gmask);
 
             apply_row_update<T, LPR, CPL, OPT>(a, row, valid[q], h_old[q], g, w, sub, gmask);
         }
@@ -301,10 +330,9 @@ sparse_update_kernel(const UpdateArgs a) {
     }
 }
 
-// Hot rows: one CTA per row.  Its G = 256 / LPR groups each reduce a strided share of the row's
-// occurrences (fixed assignment, each in increasing order), the partial sums meet in shared
-// memory and are added in group order, so the result does not depend on timing; then group 0
-// applies the optimizer as usual.
+// Hot rows: one CTA per row.  Its G = 256 / LPR groups each reduce one contiguous share of the
+// row's occurrences in increasing order, the partial sums meet in shared memory and are added in
+// group order, so the result does not depend on timing; then group 0 applies the optimizer.
 template <typename T, int LPR, int CPL, int OPT>
 __global__ void __launch_bounds__(kUpdCtaThreads)
 sparse_update_long_kernel(const UpdateArgs a) {
@@ -332,24 +360,10 @@ sparse_update_long_kernel(const UpdateArgs a) {
 #pragma unroll
             for (int i = 0; i < E; ++i) g[k][i] = 0.f;
         if (g_id < g_used) {
-            for (uint32_t i = s0 + g_id; i < e0; i += g_used) {
-                float sc;
-                const float* grow = grad_row_of(a, __ldg(a.sorted_vals + i), sc);
-#pragma unroll
-                for (int k = 0; k < CPL; ++k) {
-                    const int c = sub + k * LPR;
-                    if (c < a.nchunks) {
-#pragma unroll
-                        for (int t = 0; t < GQ; ++t) {
-                            const uint4 x = ldg_128(grow + (size_t)c * E + 4 * t);
-                            g[k][4 * t]     = fmaf(sc, __uint_as_float(x.x), g[k][4 * t]);
-                            g[k][4 * t + 1] = fmaf(sc, __uint_as_float(x.y), g[k][4 * t + 1]);
-                            g[k][4 * t + 2] = fmaf(sc, __uint_as_float(x.z), g[k][4 * t + 2]);
-                            g[k][4 * t + 3] = fmaf(sc, __uint_as_float(x.w), g[k][4 * t + 3]);
-                        }
-                    }
-                }
-            }
+            // group g_id reduces the g_id-th contiguous share of the segment, in order
+            const uint32_t share = (e0 - s0 + g_used - 1) / g_used;
+            const uint32_t lo = min(e0, s0 + (uint32_t)g_id * share), hi = min(e0, lo + share);
+            accumulate_occurrences<T, LPR, CPL, true>(a, lo, hi, g, sub, grp_in_warp, gmask);
 #pragma unroll
             for (int k = 0; k < CPL; ++k) {
                 const int c = sub + k * LPR;

@@ -330,7 +330,7 @@ def unique_segments(sorted_keys: torch.Tensor, err_flag=None, sorted_vals: Optio
 
 def sparse_update(group: TableGroup, grad_out, sorted_vals, unique_keys, seg_starts, first_vals, num_unique, offsets,
                   B, L, pooling_mode, opt: OptimizerArgs, worklist: Optional[torch.Tensor] = None):
-    """``worklist``: optional int32 tensor of at least L/256 + 2 entries for the hot-row kernel."""
+    """``worklist``: optional int32 tensor of at least L/64 + 2 entries for the hot-row kernel."""
     grad_out = _cuda(grad_out, torch.float32, "grad_out")
     w = group.weights
     grad_stride = group.D if pooling_mode == POOL_NONE else grad_out.shape[-1]

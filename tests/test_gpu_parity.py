@@ -426,7 +426,7 @@ def test_backward_hot_rows_take_the_block_per_row_path(ops, D, optimizer):
     raw = scratch.cpu().numpy()
     queued = int(raw[lay.worklist: lay.worklist + 4].view(np.uint32)[0])
     seg = np.diff(routing["seg_starts"].astype(np.int64))
-    assert queued == int((seg > 256).sum()) and queued >= 5
+    assert queued == int((seg > 64).sum()) and queued >= 5
     np.testing.assert_allclose(table_to_f32(grp.weights), w_o, rtol=5e-5, atol=2e-5)
     if s0_o is not None:
         np.testing.assert_allclose(grp.state0.cpu().numpy(), s0_o, rtol=5e-5, atol=2e-5)

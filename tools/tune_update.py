@@ -20,6 +20,7 @@ grad = torch.randn((B, F * D), device=dev, generator=gen)
 opt = ops.make_optimizer_args(_lib.OPT_ROWWISE_ADAGRAD, 0.01, 1e-8)
 lay = ops.backward_layout(L, F * rows)
 out = torch.empty((B, F * D), device=dev)
+worklist = torch.empty(L // 64 + 2, dtype=torch.int32, device=dev)
 U = int(torch.unique(batches[0] + torch.arange(F, device=dev).repeat_interleave(B * P) * rows).numel())
 upd_bytes = F * B * D * 4 + U * (2 * D * 4 + 8)
 fwd_bytes = L * (D * 4 + 8) + (F * B + 1) * 8 + F * B * D * 4
@@ -33,7 +34,7 @@ def run(tag, n=10):
         e[1].record(); k, v = ops.linearize_indices(grp, idx, offsets, B, 0)
         e[2].record(); sk, sv = ops.radix_sort_pairs(k, v, lay.key_bits, grp.err_flag)
         e[3].record(); uk, ss, nu, fv = ops.unique_segments(sk, grp.err_flag, sv)
-        e[4].record(); ops.sparse_update(grp, grad, sv, uk, ss, fv, nu, offsets, B, L, 0, opt)
+        e[4].record(); ops.sparse_update(grp, grad, sv, uk, ss, fv, nu, offsets, B, L, 0, opt, worklist=worklist)
         e[5].record()
     torch.cuda.synchronize()
     ms = [statistics.mean(ev[i][j].elapsed_time(ev[i][j + 1]) for i in range(n)) for j in range(5)]
