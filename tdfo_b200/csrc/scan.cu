@@ -48,53 +48,68 @@ complete_cumsum_kernel(const int32_t* __restrict__ lengths, int64_t n, int64_t* 
 }
 
 // ---------------------------------------------------------------- unique / RLE
+// Tile = 8 warps x 16 steps x 32 keys.  A warp walks its 512 consecutive keys 32 at a time, so
+// every load is one coalesced 128-byte request; run heads are found with a ballot, positions
+// with popc, and the heads of a step are written to consecutive slots.
+constexpr int kUniqSteps = 16;
+constexpr int kUniqTile = kScanThreads * kUniqSteps;   // 4096
+
 __global__ void __launch_bounds__(kScanThreads)
 unique_segments_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t n,
                        uint32_t* __restrict__ unique_keys, uint32_t* __restrict__ seg_starts,
                        uint32_t* __restrict__ first_vals, uint32_t* __restrict__ num_unique, ScanScratch* hdr, uint64_t* status,
                        int32_t* err_flag) {
     __shared__ uint32_t warp_totals[8];
-    __shared__ uint32_t s_last[kScanThreads];
     __shared__ uint64_t s_prefix;
     __shared__ int s_tile;
     if (threadIdx.x == 0) s_tile = (int)atomicAdd(&hdr->ticket, 1u);
     __syncthreads();
     const int tile = s_tile;
-    const int64_t base = (int64_t)tile * kScanTile + (int64_t)threadIdx.x * kScanItems;
-    uint32_t k[kScanItems];
+    const int lane = lane_id();
+    const int warp = threadIdx.x >> 5;
+    const int64_t wbase = (int64_t)tile * kUniqTile + (int64_t)warp * (kUniqSteps * 32);
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t k[kUniqSteps], heads[kUniqSteps];
+    uint32_t count = 0;
+    uint32_t carry = (wbase > 0 && wbase <= n) ? keys[wbase - 1] : 0u;     // key just before this warp's span
 #pragma unroll
-    for (int i = 0; i < kScanItems; ++i) k[i] = (base + i < n) ? keys[base + i] : 0u;
-    s_last[threadIdx.x] = k[kScanItems - 1];
-    __syncthreads();
-    uint32_t prev;
-    if (threadIdx.x > 0) prev = s_last[threadIdx.x - 1];
-    else prev = (base > 0) ? keys[base - 1] : 0u;
-    uint32_t heads = 0, count = 0;
-#pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-        const bool valid = base + i < n;
-        const bool head = valid && ((base + i == 0) || k[i] != prev);
-        if (head) { heads |= 1u << i; ++count; }
-        prev = k[i];
+    for (int i = 0; i < kUniqSteps; ++i) {
+        const int64_t idx = wbase + i * 32 + lane;
+        k[i] = (idx < n) ? keys[idx] : 0u;
+        uint32_t prev = __shfl_up_sync(kFullMask, k[i], 1);
+        if (lane == 0) prev = carry;
+        const bool head = idx < n && (idx == 0 || k[i] != prev);
+        heads[i] = __ballot_sync(kFullMask, head);
+        count += __popc(heads[i]);
+        carry = __shfl_sync(kFullMask, k[i], 31);
     }
-    uint32_t total;
-    uint32_t excl = block_exclusive_scan_256<uint32_t>(count, warp_totals, total);
+    if (lane == 0) warp_totals[warp] = count;
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+        const uint32_t t = warp_totals[w];
+        if (w < warp) before += t;
+        total += t;
+    }
     if (threadIdx.x < 32) {
         const uint64_t p = scan_lookback(status, tile, (uint64_t)total, err_flag);
         if (threadIdx.x == 0) s_prefix = p;
     }
     __syncthreads();
-    uint32_t pos = (uint32_t)s_prefix + excl;
+    uint32_t pos = (uint32_t)s_prefix + before;
 #pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-        if (heads & (1u << i)) {
-            unique_keys[pos] = k[i];
-            seg_starts[pos] = (uint32_t)(base + i);
-            if (first_vals) first_vals[pos] = vals[base + i];
-            ++pos;
+    for (int i = 0; i < kUniqSteps; ++i) {
+        if (heads[i] & (1u << lane)) {
+            const int64_t idx = wbase + i * 32 + lane;
+            const uint32_t p = pos + __popc(heads[i] & lt);
+            unique_keys[p] = k[i];
+            seg_starts[p] = (uint32_t)idx;
+            if (first_vals) first_vals[p] = vals[idx];
         }
+        pos += __popc(heads[i]);
     }
-    const int64_t last_tile = (n - 1) / kScanTile;
+    const int64_t last_tile = (n - 1) / kUniqTile;
     if (tile == last_tile && threadIdx.x == 0) {
         const uint32_t u = (uint32_t)s_prefix + total;
         *num_unique = u;
@@ -143,7 +158,7 @@ int unique_segments_impl(const uint32_t* sorted_keys, const uint32_t* sorted_val
     TDFO_CUDA(cudaMemsetAsync(scratch, 0, bytes, st));
     auto* hdr = static_cast<ScanScratch*>(scratch);
     auto* status = reinterpret_cast<uint64_t*>(static_cast<char*>(scratch) + sizeof(ScanScratch));
-    unique_segments_kernel<<<(unsigned)scan_tiles(n), kScanThreads, 0, st>>>(
+    unique_segments_kernel<<<(unsigned)((n + kUniqTile - 1) / kUniqTile), kScanThreads, 0, st>>>(
         sorted_keys, sorted_vals, n, unique_keys, seg_starts, first_vals, num_unique, hdr, status, err_flag);
     count_launch();
     TDFO_LAUNCH_CHECK("unique_segments");
