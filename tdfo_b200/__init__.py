@@ -12,7 +12,7 @@ from .optim import (CombinedOptimizer, EmbOptimType, FusedOptimizer, KeyedOptimi
 from .ops import jagged_2d_to_dense
 from .sparse import JaggedTensor, KeyedJaggedTensor, KeyedTensor
 from .distributed import (DistributedModelParallel, EmbeddingBagCollectionSharder, EmbeddingCollectionSharder,
-                          ParameterSharding, ShardedEmbeddingBagCollection, ShardingType, balanced_table_wise_plan,
+                          ParameterSharding, ShardedEmbeddingBagCollection, ShardedEmbeddingCollection, ShardingType, balanced_table_wise_plan,
                           row_wise, table_wise)
 
 __all__ = [
@@ -20,5 +20,5 @@ __all__ = [
     "PoolingType", "CombinedOptimizer", "EmbOptimType", "FusedOptimizer", "KeyedOptimizerWrapper",
     "in_backward_optimizer_filter", "jagged_2d_to_dense", "JaggedTensor", "KeyedJaggedTensor", "KeyedTensor",
     "DistributedModelParallel", "EmbeddingBagCollectionSharder", "EmbeddingCollectionSharder", "ParameterSharding",
-    "ShardedEmbeddingBagCollection", "ShardingType", "balanced_table_wise_plan", "row_wise", "table_wise",
+    "ShardedEmbeddingBagCollection", "ShardedEmbeddingCollection", "ShardingType", "balanced_table_wise_plan", "row_wise", "table_wise",
 ]

@@ -90,6 +90,11 @@ class CudaKernelOps:
                                                         False, err_flag)
         return nl, no, ni
 
+    def bucketize_row_wise_with_permute(self, lengths, offsets, indices, block_sizes, F, B, world, err_flag):
+        nl, no, ni, _, perm = self._ops.bucketize_row_wise(lengths, offsets, indices, None, block_sizes, F, B, world,
+                                                           True, err_flag)
+        return nl, no, ni, perm
+
     def permute_2d(self, permute, B, lengths, offsets, indices, out_total):
         ol, oo, oi, _ = self._ops.permute_2d(permute, B, lengths, offsets, indices, None, out_total=out_total)
         return ol, oo, oi
@@ -210,11 +215,11 @@ class ShardedEmbeddingBagCollection(nn.Module):
         self._configs = list(tables)
         W, r = self._world, self._rank
         dims = {t.embedding_dim for t in tables}
-        kinds = {(t.data_type, t.pooling) for t in tables}
+        kinds = {(t.data_type, getattr(t, "pooling", PoolingType.SUM)) for t in tables}
         if len(dims) != 1 or len(kinds) != 1:
             raise ValueError("sharded tables must share embedding_dim, data_type and pooling in this version")
         self._D = tables[0].embedding_dim
-        self._pooling = _lib.POOL_MEAN if tables[0].pooling == PoolingType.MEAN else _lib.POOL_SUM
+        self._pooling = _lib.POOL_MEAN if getattr(tables[0], "pooling", PoolingType.SUM) == PoolingType.MEAN else _lib.POOL_SUM
         if self._pooling == _lib.POOL_MEAN and any(plan[t.name].sharding_type == ShardingType.ROW_WISE for t in tables):
             raise ValueError("row-wise sharding supports SUM pooling only (a bag's length is split across ranks)")
         dtype = torch.float32 if tables[0].data_type.value == "FP32" else torch.bfloat16
@@ -304,6 +309,8 @@ class ShardedEmbeddingBagCollection(nn.Module):
         self._scratch: Dict[str, torch.Tensor] = {}
         self._emit_keys = False                      # set per forward: training with the CUDA kernel table
         self._fwd_token = 0
+        self._track_positions = False                # sequence output: remember where every sent id came from
+        self._routing: Dict[str, object] = {}
         # Table-wise output dist / gradient return through NVLink peer memory instead of NCCL
         # all-to-alls (needs the CUDA kernels and symmetric memory; on by default when available).
         if peer_memory is None:
@@ -397,9 +404,16 @@ class ShardedEmbeddingBagCollection(nn.Module):
 
     # ------------------------------------------------------------------ forward
     def _forward_impl(self, values, lengths, B):
+        return self._pooled_lookup(self._input_dist(values, lengths, B), B)
+
+    def _input_dist(self, values, lengths, B):
+        """Route ids to the ranks that own their rows; returns the local KJT in
+        [feature][source rank][batch] layout (ids `lv`, offsets `lo`)."""
         W, r, D, ops = self._world, self._rank, self._D, self._ops
         dev = values.device
         offsets = ops.complete_cumsum(lengths)
+        track = self._track_positions
+        pos_parts: List[List[tuple]] = [[] for _ in range(W)]
         Fl, n_rw = self._F_local, self._n_rw
 
         n_tw_all = sum(self._n_tw)
@@ -447,9 +461,28 @@ class ShardedEmbeddingBagCollection(nn.Module):
                     len_parts[d].append(tl[f0 * B:f1 * B])
                     val_parts[d].append((tv, bounds, f0, f1))
                     f0 = f1
+                if track:       # where in the local KJT each sent id came from
+                    arange = torch.arange(values.numel(), dtype=torch.int64, device=dev)
+                    _, _, tpos = ops.permute_2d(self._tw_send_perm[:n_tw_all], B, lengths, offsets, arange,
+                                                values.numel())
+                    for d in range(W):
+                        pos_parts[d].append(tpos)
             if n_rw:
                 rl, ro, rv = ops.permute_2d(self._rw_select_perm[:n_rw], B, lengths, offsets, values, values.numel())
-                bl, bo, bv = ops.bucketize_row_wise(rl, ro, rv, self._rw_block_sizes[:n_rw], n_rw, B, W, self._err_flag)
+                if track:
+                    arange = torch.arange(values.numel(), dtype=torch.int64, device=dev)
+                    _, _, rpos = ops.permute_2d(self._rw_select_perm[:n_rw], B, lengths, offsets, arange,
+                                                values.numel())
+                    bl, bo, bv, unb = ops.bucketize_row_wise_with_permute(rl, ro, rv, self._rw_block_sizes[:n_rw],
+                                                                          n_rw, B, W, self._err_flag)
+                    n_rw_ids = int(ro[n_rw * B].item())        # buffers may be larger than the id count
+                    bpos = torch.empty(max(n_rw_ids, 1), dtype=torch.int64, device=dev)
+                    bpos[unb[:n_rw_ids]] = rpos[:n_rw_ids]     # slot in the bucketised order -> original position
+                    for d in range(W):
+                        pos_parts[d].append(bpos)
+                else:
+                    bl, bo, bv = ops.bucketize_row_wise(rl, ro, rv, self._rw_block_sizes[:n_rw], n_rw, B, W,
+                                                        self._err_flag)
                 bbounds = bo[:: max(n_rw * B, 1)]
                 for d in range(W):
                     len_parts[d].append(bl[d * n_rw * B:(d + 1) * n_rw * B])
@@ -461,12 +494,14 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 for (_, bnd, i0, i1) in val_parts[d]:
                     bound_list += [bnd[i0], bnd[i1]]
             b_host = torch.stack(bound_list).tolist() if bound_list else []
-            send_vals, send_splits, k = [], [0] * W, 0
+            send_vals, send_pos, send_splits, k = [], [], [0] * W, 0
             for d in range(W):
-                for (buf, _, _, _) in val_parts[d]:
+                for j, (buf, _, _, _) in enumerate(val_parts[d]):
                     lo, hi = b_host[k], b_host[k + 1]
                     k += 2
                     send_vals.append(buf[lo:hi])
+                    if track:
+                        send_pos.append(pos_parts[d][j][lo:hi])
                     send_splits[d] += hi - lo
             send_values = torch.cat(send_vals) if send_vals else values[:0]
 
@@ -488,10 +523,22 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 recv_offsets = ops.complete_cumsum(recv_lengths)
                 ll, lo_, lv = ops.permute_2d(self._recv_perm[:Fl * W], B, recv_lengths, recv_offsets, recv_values,
                                              int(sum(recv_splits)))
+                if track:
+                    n_recv = int(sum(recv_splits))
+                    _, _, lv_pos = ops.permute_2d(self._recv_perm[:Fl * W], B, recv_lengths, recv_offsets,
+                                                  torch.arange(n_recv, dtype=torch.int64, device=dev), n_recv)
+                    self._routing = dict(send_pos=torch.cat(send_pos) if send_pos else values[:0],
+                                         send_splits=send_splits, recv_splits=recv_splits, lv_pos=lv_pos[:n_recv])
             else:
                 ll = recv_lengths
                 lo_ = torch.zeros(1, dtype=torch.int64, device=dev)
                 lv = recv_values
+        return dict(lv=lv, lo=lo_, tw_total=tw_total, n_tw_r=n_tw_r, peer=peer, dev=dev)
+
+    def _pooled_lookup(self, c, B):
+        W, r, D, ops = self._world, self._rank, self._D, self._ops
+        lv, lo_, tw_total, n_tw_r, peer, dev = c["lv"], c["lo"], c["tw_total"], c["n_tw_r"], c["peer"], c["dev"]
+        Fl, n_rw, n_tw_all = self._F_local, self._n_rw, sum(self._n_tw)
         GB = W * B                                            # global batch seen by each local feature
 
         # ---- lookup on the local storage
@@ -670,6 +717,106 @@ class ShardedEmbeddingBagCollection(nn.Module):
             table.get_weight_init_min(), table.get_weight_init_max(), generator=g)
 
 
+# --------------------------------------------------------------------------- sequence (EmbeddingCollection)
+class _ShardedSequenceFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, anchor, module, values, lengths, B):
+        rows, saved = module._seq_forward(values, lengths, B)
+        ctx.module, ctx.saved, ctx.B = module, saved, B
+        return rows
+
+    @staticmethod
+    def backward(ctx, grad_rows):
+        ctx.module._seq_backward(grad_rows.contiguous(), ctx.saved, ctx.B)
+        return None, None, None, None, None
+
+
+class ShardedEmbeddingCollection(ShardedEmbeddingBagCollection):
+    """`EmbeddingCollection` (one embedding row per id, torchrec/models.py:158-164) whose tables are
+    spread over the ranks: the module DMP builds for the reference's Bert4Rec item table when it runs
+    on more than one device (torchrec/train.py:241-247).
+
+    Input dist as for the pooled module; the owners look the rows up (`TDFO_POOL_NONE`), put them
+    back into the order the ids arrived in and return them with one all-to-all of `[n, D]` rows
+    (split sizes = the id counts of the input dist, SURVEY.md §8 a13 "sequence"); the sender drops
+    each row at the position its id had in the local KeyedJaggedTensor (for row-wise tables this is
+    the un-bucketise permute).  Backward sends the gradient rows the same way round and runs the
+    fused sort / unique / update on the owner.
+    """
+
+    def __init__(self, tables, plan: Dict[str, ParameterSharding], device: torch.device,
+                 process_group: Optional[dist.ProcessGroup] = None, kernel_ops=None, init_seed: int = 0,
+                 init_on_device: bool = False):
+        super().__init__(tables, plan, device, process_group, kernel_ops, init_seed, init_on_device,
+                         peer_memory=False)
+        self._track_positions = True
+
+    def _seq_forward(self, values, lengths, B):
+        W, D, ops = self._world, self._D, self._ops
+        c = self._input_dist(values, lengths, B)
+        lv, lo_, tw_total, n_tw_r, dev = c["lv"], c["lo"], c["tw_total"], c["n_tw_r"], c["dev"]
+        GB, n_rw = W * B, self._n_rw
+        n_recv = lv.numel()
+        rows_local = torch.empty((n_recv, D), dtype=torch.float32, device=dev)
+        if n_tw_r and tw_total:
+            ops.embedding_forward(self._group("tw", False), lv[:tw_total], lo_[: n_tw_r * GB + 1], GB, _lib.POOL_NONE,
+                                  rows_local[:tw_total])
+        rw = None
+        if n_rw and n_recv > tw_total:
+            rw = (lv[tw_total:], lo_[n_tw_r * GB:] - tw_total if n_tw_r else lo_)
+            ops.embedding_forward(self._group("rw", False), rw[0], rw[1], GB, _lib.POOL_NONE, rows_local[tw_total:])
+        routing = dict(self._routing)
+        # back into arrival order, home with one all-to-all, then to the ids' original positions
+        back = torch.empty_like(rows_local)
+        back[routing["lv_pos"]] = rows_local
+        home = self._a2a(back, routing["recv_splits"], routing["send_splits"], (D,))
+        out = torch.zeros((values.numel(), D), dtype=torch.float32, device=dev)
+        out[routing["send_pos"]] = home
+        self._fwd_token += 1
+        saved = dict(lv=lv, lo=lo_, tw_total=tw_total, n_tw_r=n_tw_r, GB=GB, rw=rw, routing=routing)
+        return out, saved
+
+    def _seq_backward(self, grad_rows, saved, B):
+        W, D, ops = self._world, self._D, self._ops
+        self._fused.iteration += 1
+        opt = self._fused.args()
+        routing, tw_total, n_tw_r, GB = saved["routing"], saved["tw_total"], saved["n_tw_r"], saved["GB"]
+        g_send = grad_rows[routing["send_pos"]]
+        g_recv = self._a2a(g_send, routing["send_splits"], routing["recv_splits"], (D,))
+        g_local = g_recv[routing["lv_pos"]]                       # [feature][source rank][batch] order
+        if n_tw_r and tw_total:
+            ops.embedding_backward_update(self._group("tw", True), g_local[:tw_total].contiguous(),
+                                          saved["lv"][:tw_total], saved["lo"][: n_tw_r * GB + 1], GB, _lib.POOL_NONE, opt)
+        if saved["rw"] is not None:
+            rw_vals, rw_off = saved["rw"]
+            ops.embedding_backward_update(self._group("rw", True), g_local[tw_total:].contiguous(), rw_vals, rw_off, GB,
+                                          _lib.POOL_NONE, opt)
+
+    def forward(self, features: KeyedJaggedTensor):
+        from .sparse import JaggedTensor
+        if list(features.keys()) != self._feature_names:
+            keys = list(features.keys())
+            features = features.permute([keys.index(k) for k in self._feature_names])
+        values, lengths, B = features.values(), features.lengths(), features.stride()
+        if self.training and torch.is_grad_enabled():
+            if self._anchor is None or self._anchor.device != values.device:
+                self._anchor = torch.zeros(1, device=values.device, requires_grad=True)
+            rows = _ShardedSequenceFn.apply(self._anchor, self, values, lengths, B)
+        else:
+            rows, _ = self._seq_forward(values, lengths, B)
+        names = self._feature_names
+        offsets = features.offsets()
+        if len(names) == 1:
+            return {names[0]: JaggedTensor(rows, None, lengths, offsets)}
+        bounds = features.offset_per_key()
+        out = {}
+        for i, k in enumerate(names):
+            s0, e0 = bounds[i], bounds[i + 1]
+            off = offsets[i * B:(i + 1) * B + 1]
+            out[k] = JaggedTensor(rows[s0:e0], None, lengths[i * B:(i + 1) * B], off - s0 if s0 else off)
+        return out
+
+
 # --------------------------------------------------------------------------- DMP-style wrapper
 class _Sharder:
     """`EmbeddingCollectionSharder(fused_params)` / `EmbeddingBagCollectionSharder(fused_params)`:
@@ -710,8 +857,8 @@ class DistributedModelParallel(nn.Module):
       reference puts into `CombinedOptimizer`);
     * with more than one rank, EmbeddingBagCollections are replaced by
       `ShardedEmbeddingBagCollection` (plan: `plan[table_name]`, default size-balanced table-wise)
-      and the remaining (dense) parameters are wrapped in DistributedDataParallel.
-      Sharding an EmbeddingCollection (sequence output) across ranks is not built yet.
+      / EmbeddingCollections by `ShardedEmbeddingCollection`, and the remaining (dense)
+      parameters are wrapped in DistributedDataParallel.
     """
 
     def __init__(self, module: nn.Module, device: Optional[torch.device] = None,
@@ -739,11 +886,15 @@ class DistributedModelParallel(nn.Module):
                         child.to(device)
                     fused.append(child.set_fused_optimizer(**kw) if kw else child.fused_optimizer)
                 elif isinstance(child, EmbeddingCollection):
-                    if world > 1:
-                        raise NotImplementedError("sharding an EmbeddingCollection (sequence embeddings) over several "
-                                                  "ranks is not built yet; use EmbeddingBagCollection or one rank")
                     kw = by_kind["EmbeddingCollection"].optimizer_kwargs() if "EmbeddingCollection" in by_kind else {}
-                    child.to(device)
+                    if world > 1:
+                        tables = child.embedding_configs()
+                        p = plan or balanced_table_wise_plan(tables, world)
+                        new = ShardedEmbeddingCollection(tables, p, device, process_group)
+                        setattr(parent, name, new)
+                        child = new
+                    else:
+                        child.to(device)
                     fused.append(child.set_fused_optimizer(**kw) if kw else child.fused_optimizer)
                 else:
                     convert(child)

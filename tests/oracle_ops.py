@@ -30,6 +30,13 @@ class OracleKernelOps:
             err_flag |= 1
         return torch.from_numpy(nl), torch.from_numpy(no), torch.from_numpy(ni)
 
+    def bucketize_row_wise_with_permute(self, lengths, offsets, indices, block_sizes, F, B, world, err_flag):
+        nl, no, ni, _, perm, oob = orc.bucketize_row_wise(_np(offsets), _np(indices), None, _np(block_sizes), F, B,
+                                                          world, want_permute=True)
+        if oob:
+            err_flag |= 1
+        return torch.from_numpy(nl), torch.from_numpy(no), torch.from_numpy(ni), torch.from_numpy(perm)
+
     def permute_2d(self, permute, B, lengths, offsets, indices, out_total):
         ol, oo, oi, _ = orc.permute_2d(_np(permute), B, _np(lengths), _np(offsets), _np(indices))
         return torch.from_numpy(ol), torch.from_numpy(oo), torch.from_numpy(oi)

@@ -9,7 +9,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 import oracle as orc
-from test_sharded_gloo import B, D, W, free_port, global_batch, local_batch, make_tables
+from test_sharded_gloo import B, D, W, free_port, global_batch, local_batch, make_tables, run_rank_sequence
 
 pytestmark = pytest.mark.gpu
 
@@ -78,6 +78,27 @@ def test_sharded_equals_unsharded_on_2_gpus(plan_kind, peer):
     with ctx.Manager() as mgr:
         results = mgr.dict()
         procs = [ctx.Process(target=run_rank, args=(r, port, plan_kind, peer, results)) for r in range(W)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=300)
+        for p in procs:
+            if p.is_alive():
+                p.terminate()
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        assert dict(results) == {0: "ok", 1: "ok"}
+
+
+@pytest.mark.parametrize("plan_kind", ["tw", "rw", "mixed"])
+def test_sharded_sequence_on_2_gpus(plan_kind):
+    """ShardedEmbeddingCollection (one row per id) with the CUDA kernels over NCCL."""
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    port = free_port()
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        results = mgr.dict()
+        procs = [ctx.Process(target=run_rank_sequence, args=(r, port, plan_kind, results, True)) for r in range(W)]
         for p in procs:
             p.start()
         for p in procs:

@@ -134,3 +134,96 @@ def test_sharded_equals_unsharded_world2(plan_kind, optimizer_name):
                 p.terminate()
         assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
         assert dict(results) == {0: "ok", 1: "ok"}
+
+
+# ----------------------------------------------------------------------------- sequence (EmbeddingCollection)
+def seq_grad(rank, L):
+    return np.random.default_rng(500 + rank).normal(size=(L, D)).astype(np.float32)
+
+
+def run_rank_sequence(rank, port, plan_kind, results, cuda=False):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    if cuda:
+        torch.cuda.set_device(rank)
+        dev = torch.device("cuda", rank)
+        dist.init_process_group("nccl", rank=rank, world_size=W, device_id=dev)
+    else:
+        dev = torch.device("cpu")
+        dist.init_process_group("gloo", rank=rank, world_size=W)
+    try:
+        import tdfo_b200 as t
+        from tdfo_b200 import distributed as td
+        from oracle_ops import OracleKernelOps
+        specs = [("t0", 50, ["f0"]), ("t1", 41, ["f1"]), ("t2", 30, ["f2"]), ("t3", 17, ["f3"]), ("t4", 9, ["f4"])]
+        tables = [t.EmbeddingConfig(num_embeddings=r_, embedding_dim=D, name=n, feature_names=f) for n, r_, f in specs]
+        rows = [c.num_embeddings for c in tables]
+        F = len(rows)
+        plan = {"tw": {"t0": td.table_wise(0), "t1": td.table_wise(1), "t2": td.table_wise(0), "t3": td.table_wise(1),
+                       "t4": td.table_wise(1)},
+                "rw": {c.name: td.row_wise() for c in tables},
+                "mixed": {"t0": td.table_wise(1), "t1": td.row_wise(), "t2": td.table_wise(0), "t3": td.row_wise(),
+                          "t4": td.table_wise(1)}}[plan_kind]
+        m = td.ShardedEmbeddingCollection(tables, plan, dev, kernel_ops=None if cuda else OracleKernelOps(),
+                                          init_seed=5)
+        m.set_fused_optimizer(t.EmbOptimType.EXACT_SGD, learning_rate=0.05)
+        m.train()
+        lengths, idx, _ = local_batch(rank, rows)
+        kjt = t.KeyedJaggedTensor.from_lengths_sync([f"f{i}" for i in range(F)], torch.from_numpy(idx),
+                                                    torch.from_numpy(lengths)).to(dev)
+        jts = m(kjt)
+        got = torch.cat([jts[f"f{i}"].values() for i in range(F)])
+        grad = seq_grad(rank, idx.size)
+        (got * torch.from_numpy(grad).to(dev)).sum().backward()
+
+        full = np.concatenate([td.ShardedEmbeddingBagCollection.initial_table(c, 5).numpy() for c in tables])
+        base = np.concatenate([[0], np.cumsum(rows)[:-1]]).astype(np.int64)
+        off = orc.complete_cumsum(lengths)
+        want, _ = orc.embedding_forward(full, D, idx, off, None, base, rows, None, F, B, orc.POOL_NONE)
+        np.testing.assert_array_equal(got.detach().cpu().numpy(), want)      # pure gather + routing: bit-exact
+        for i in range(F):                                                  # per-key jagged views
+            np.testing.assert_array_equal(jts[f"f{i}"].lengths().cpu().numpy(), lengths[i * B:(i + 1) * B])
+            np.testing.assert_array_equal(jts[f"f{i}"].values().detach().cpu().numpy(), want[off[i * B]:off[(i + 1) * B]])
+
+        # unsharded update on the global batch: per feature, rank 0's ids then rank 1's
+        per = [local_batch(r_, rows) for r_ in range(W)]
+        g_len, g_idx, _ = global_batch(rows)
+        g_grad_parts = []
+        for f in range(F):
+            for r_ in range(W):
+                o = orc.complete_cumsum(per[r_][0])
+                g_grad_parts.append(seq_grad(r_, per[r_][1].size)[o[f * B]:o[(f + 1) * B]])
+        w_ref = full.copy()
+        orc.embedding_backward_update(w_ref, D, None, None, np.concatenate(g_grad_parts), g_idx,
+                                      orc.complete_cumsum(g_len), base, rows, None, F, W * B, orc.POOL_NONE,
+                                      orc.OptArgs(orc.OPT_SGD, 0.05))
+        mine = {c.name: m.local_table(c.name).detach().cpu().numpy().copy() for c in tables}
+        gathered = [None] * W
+        dist.all_gather_object(gathered, mine)
+        for i, c in enumerate(tables):
+            ps = plan[c.name]
+            got_t = gathered[ps.rank][c.name] if ps.sharding_type == td.ShardingType.TABLE_WISE else \
+                np.concatenate([gathered[r_][c.name] for r_ in range(W)])
+            np.testing.assert_allclose(got_t, w_ref[base[i]:base[i] + rows[i]], rtol=1e-5, atol=1e-6,
+                                       err_msg=f"table {c.name} ({plan_kind})")
+        results[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("plan_kind", ["tw", "rw", "mixed"])
+def test_sharded_sequence_equals_unsharded_world2(plan_kind):
+    port = free_port()
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        results = mgr.dict()
+        procs = [ctx.Process(target=run_rank_sequence, args=(r, port, plan_kind, results)) for r in range(W)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=180)
+        for p in procs:
+            if p.is_alive():
+                p.terminate()
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        assert dict(results) == {0: "ok", 1: "ok"}
