@@ -700,6 +700,78 @@ class ShardedEmbeddingBagCollection(nn.Module):
             out, _ = self._forward_impl(values, lengths, B)
         return KeyedTensor(self._feature_names, [self._D] * self._F_total, out)
 
+    # ------------------------------------------------------------------ checkpoints
+    # `torch.save(model.state_dict(), ...)` at torchrec/train.py:172-176 is called on every rank.
+    # state_dict() therefore carries, under the same per-table keys as the unsharded module
+    # (`embedding_bags.<table>.weight` / `embeddings.<table>.weight`), THIS rank's rows of every table
+    # (an empty [0, D] tensor for a table-wise table owned elsewhere) plus `_shard_metadata` saying
+    # which global rows they are.  load_state_dict() takes either such local shards or full tables
+    # (e.g. the state_dict of an unsharded module, or full_state_dict()), so a checkpoint can be
+    # resharded onto another plan / world size.
+    _state_prefix = "embedding_bags"
+
+    def _table_shards(self):
+        """(table, storage name, first local row, local rows, first global row) per local shard."""
+        W, r = self._world, self._rank
+        for shn, sh in (("tw", self._tw), ("rw", self._rw)):
+            for t, r0, rows in zip(sh.tables, sh.row0, sh.local_rows):
+                yield t, shn, r0, rows, (0 if shn == "tw" else r * ((t.num_embeddings + W - 1) // W))
+
+    def _save_to_state_dict(self, destination, prefix, keep_vars):
+        local = {t.name: (getattr(self, f"_{shn}_weight")[r0:r0 + rows], g0)
+                 for t, shn, r0, rows, g0 in self._table_shards()}
+        ref = self._tw_weight
+        meta = {"world": self._world, "rank": self._rank, "tables": {}}
+        for t in self._configs:
+            v, g0 = local.get(t.name, (ref.new_empty((0, self._D)), 0))
+            destination[f"{prefix}{self._state_prefix}.{t.name}.weight"] = v if keep_vars else v.detach()
+            meta["tables"][t.name] = {"row_offset": g0, "rows": int(v.shape[0]), "num_embeddings": t.num_embeddings}
+        destination[f"{prefix}_shard_metadata"] = meta
+
+    def _load_from_state_dict(self, state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys,
+                              error_msgs):
+        for t, shn, r0, rows, g0 in self._table_shards():
+            key = f"{prefix}{self._state_prefix}.{t.name}.weight"
+            if key not in state_dict:
+                if strict:
+                    missing_keys.append(key)
+                continue
+            src = state_dict[key]
+            if tuple(src.shape) == (t.num_embeddings, self._D) and rows != t.num_embeddings:
+                src = src[g0:g0 + rows]                       # a full table: take this rank's rows
+            if tuple(src.shape) != (rows, self._D):
+                error_msgs.append(f"size mismatch for {key}: {tuple(src.shape)} is neither this rank's shard "
+                                  f"{(rows, self._D)} nor the full table {(t.num_embeddings, self._D)}")
+                continue
+            with torch.no_grad():
+                getattr(self, f"_{shn}_weight")[r0:r0 + rows].copy_(src)
+
+    def full_state_dict(self, to_cpu: bool = True) -> Dict[str, torch.Tensor]:
+        """COLLECTIVE: every table whole, on every rank, under the unsharded module's keys."""
+        W = self._world
+        local = {t.name: getattr(self, f"_{shn}_weight")[r0:r0 + rows] for t, shn, r0, rows, _ in self._table_shards()}
+        owner = {f: d for d in range(W) for f in self._tw_feats[d]}
+        out: Dict[str, torch.Tensor] = {}
+        ref = self._tw_weight
+        k = 0
+        for t in self._configs:
+            f0 = k
+            k += len(t.feature_names)
+            if f0 in owner:                                   # table-wise: the owner broadcasts
+                src = owner[f0]
+                full = local[t.name].contiguous() if src == self._rank else ref.new_empty((t.num_embeddings, self._D))
+                dist.broadcast(full, src=dist.get_global_rank(self._pg, src) if self._pg is not None else src,
+                               group=self._pg)
+            else:                                             # row-wise: gather the (padded) blocks
+                bs = (t.num_embeddings + W - 1) // W
+                mine = ref.new_zeros((bs, self._D))
+                mine[:local[t.name].shape[0]].copy_(local[t.name])
+                parts = [torch.empty_like(mine) for _ in range(W)]
+                dist.all_gather(parts, mine, group=self._pg)
+                full = torch.cat(parts)[:t.num_embeddings]
+            out[f"{self._state_prefix}.{t.name}.weight"] = full.cpu() if to_cpu else full.clone()
+        return out
+
     # ------------------------------------------------------------------ inspection helpers
     def local_table(self, name: str) -> torch.Tensor:
         """This rank's rows of table `name` (whole table for TW on the owner, the row block for RW)."""
@@ -743,6 +815,8 @@ class ShardedEmbeddingCollection(ShardedEmbeddingBagCollection):
     the un-bucketise permute).  Backward sends the gradient rows the same way round and runs the
     fused sort / unique / update on the owner.
     """
+
+    _state_prefix = "embeddings"
 
     def __init__(self, tables, plan: Dict[str, ParameterSharding], device: torch.device,
                  process_group: Optional[dist.ProcessGroup] = None, kernel_ops=None, init_seed: int = 0,

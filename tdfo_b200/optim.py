@@ -70,9 +70,14 @@ class FusedOptimizer:
     def load_state_dict(self, sd: Dict[str, Any]) -> None:
         self.iteration = int(sd["iteration"])
         self.param_groups[0].update(sd["hyper"])
+        dev = next(iter(self.params.values())).device if self.params else None
         for k, v in sd.get("state", {}).items():
-            if k in self.state and isinstance(v, torch.Tensor):
+            if not isinstance(v, torch.Tensor):
+                continue
+            if k in self.state:
                 self.state[k].copy_(v)
+            else:                       # state is created lazily by the first backward: adopt the loaded one
+                self.state[k] = v.detach().clone().to(dev) if dev is not None else v.detach().clone()
 
 
 class EmptyFusedOptimizer(FusedOptimizer):
