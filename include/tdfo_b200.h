@@ -346,9 +346,13 @@ int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t total_rows,
  * keys_in_scratch != 0: the caller already had tdfo_embedding_forward write the
  * linearised pairs for these same indices / offsets into the input_keys /
  * input_vals slots of `scratch`; the linearise stage is skipped.
- * per_sample_weights must be NULL in this ABI version (weighted backward is
- * TDFO_ERR_UNSUPPORTED).
- * scratch: tdfo_backward_scratch_bytes(L, total_rows).
+ * per_sample_weights (float[L], pooled modes only, may be NULL): the gradient row
+ * of occurrence p is scaled by per_sample_weights[p] (and by 1/len for MEAN), the
+ * backward of the weighted pooled lookup.  The weights themselves
+ * receive no gradient.  With weights the sort payload is the id's position, the
+ * scratch must be tdfo_backward_scratch_bytes_weighted(L, total_rows) bytes, the
+ * sorted_vals read back are positions, and keys_in_scratch must be 0.
+ * scratch: tdfo_backward_scratch_bytes(L, total_rows) otherwise.
  */
 typedef struct tdfo_backward_layout {
     size_t input_keys, input_vals;   /* where linearised pairs go in (clobbered by the sort) */
@@ -359,6 +363,7 @@ typedef struct tdfo_backward_layout {
 } tdfo_backward_layout;
 
 size_t tdfo_backward_scratch_bytes(int64_t L, int64_t total_rows);
+size_t tdfo_backward_scratch_bytes_weighted(int64_t L, int64_t total_rows);
 int tdfo_backward_scratch_layout(int64_t L, int64_t total_rows, tdfo_backward_layout* layout /* HOST */);
 int tdfo_embedding_backward_update(void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
                                    float* state0, float* state1,

@@ -48,7 +48,7 @@ def lib() -> ctypes.CDLL:
         build()
         _lib = ctypes.CDLL(str(_LIB_PATH))
         _lib.orc_unique_segments.restype = c_int64
-        for name in ("orc_bucketize_row_wise", "orc_embedding_forward", "orc_linearize_indices",
+        for name in ("orc_bucketize_row_wise", "orc_embedding_forward", "orc_linearize_indices", "orc_embedding_backward_update_weighted",
                      "orc_embedding_backward_update"):
             getattr(_lib, name).restype = ctypes.c_int
     return _lib
@@ -210,6 +210,24 @@ def embedding_backward_update(weights, D, state0, state1, grad_out, indices, off
         res.update(sorted_keys=sk[:L], sorted_vals=sv[:L], unique_keys=uk[: nu.value],
                    seg_starts=ss[: nu.value + 1])
     return res
+
+
+def embedding_backward_update_weighted(weights, D, state0, state1, grad_out, indices, offsets, psw,
+                                       feat_row_base, feat_rows, feat_out_col, F, B, pooling_mode, opt: OptArgs):
+    """Weighted pooled backward, in place.  Returns dict(oob, sorted_vals = positions in sorted order)."""
+    assert weights.flags.c_contiguous and weights.flags.writeable and pooling_mode != POOL_NONE
+    indices, offsets = _c(indices, np.int64), _c(offsets, np.int64)
+    grad_out, psw = _c(grad_out, np.float32), _c(psw, np.float32)
+    frb, fr, foc = _c(feat_row_base, np.int64), _c(feat_rows, np.int64), _c(feat_out_col, np.int64)
+    L = indices.size
+    assert psw.size == L
+    sv = np.zeros(max(L, 1), np.uint32)
+    c_opt = opt.c()
+    oob = lib().orc_embedding_backward_update_weighted(
+        _p(weights), c_int32(_wdtype(weights)), c_int64(weights.shape[0]), c_int32(D), _p(state0), _p(state1),
+        _p(grad_out), c_int64(grad_out.shape[-1]), _p(indices), _p(offsets), _p(psw), _p(frb), _p(fr), _p(foc),
+        c_int32(F), c_int64(B), c_int64(L), c_int32(pooling_mode), ctypes.byref(c_opt), _p(sv))
+    return {"oob": bool(oob), "sorted_vals": sv[:L]}
 
 
 def jagged_2d_to_dense(values, offsets, max_len):

@@ -358,6 +358,50 @@ int orc_embedding_backward_update(void* weights, int32_t dtype, int64_t total_ro
     return oob;
 }
 
+/* Weighted pooled lookup backward (SURVEY 8 a14 "x per-sample weight"; KJT weights are the optional
+ * field of a9 -- the reference's own call sites never set them).  [UPSTREAM] nn.EmbeddingBag(mode=
+ * "sum", per_sample_weights=w): d out / d W[idx_p] = w_p * grad_out[bag(p)].  Restated on its own:
+ * the sort payload is the position p, bag(p) comes from a per-position table, the optimizer step
+ * reuses orc_sparse_update by materialising the scaled rows as a sequence-mode gradient [L, D].
+ * The weights receive no gradient.  Returns 1 if any id was out of range. */
+int orc_embedding_backward_update_weighted(void* weights, int32_t dtype, int64_t total_rows, int32_t D,
+                                           float* state0, float* state1, const float* grad_out,
+                                           int64_t grad_stride, const int64_t* indices,
+                                           const int64_t* offsets, const float* psw,
+                                           const int64_t* feat_row_base, const int64_t* feat_rows,
+                                           const int64_t* feat_out_col, int32_t F, int64_t B, int64_t L,
+                                           int32_t pooling_mode, const orc_optimizer_args* opt,
+                                           uint32_t* out_sorted_vals) {
+    const size_t n = (size_t)(L > 0 ? L : 1);
+    uint32_t* k = (uint32_t*)malloc(4 * n);
+    uint32_t* v = (uint32_t*)malloc(4 * n);
+    uint32_t* sk = (uint32_t*)malloc(4 * n);
+    uint32_t* sv = out_sorted_vals ? out_sorted_vals : (uint32_t*)malloc(4 * n);
+    uint32_t* uk = (uint32_t*)malloc(4 * n);
+    uint32_t* ss = (uint32_t*)malloc(4 * (n + 1));
+    float* rows = (float*)malloc(sizeof(float) * n * (size_t)D);
+    /* payload = position: linearise in sequence mode */
+    const int oob = orc_linearize_indices(indices, offsets, feat_row_base, feat_rows, F, B, total_rows,
+                                          ORC_POOL_NONE, k, v);
+    for (int64_t g = 0; g < (int64_t)F * B; ++g) {
+        const int64_t f = g / B, b = g % B;
+        const int64_t s = offsets[g], e = offsets[g + 1];
+        const float* gr = grad_out + b * grad_stride + feat_out_col[f];
+        for (int64_t p = s; p < e; ++p) {
+            float scale = psw[p];
+            if (pooling_mode == ORC_POOL_MEAN) scale = scale / (float)(e - s);
+            for (int d = 0; d < D; ++d) rows[p * D + d] = scale * gr[d];
+        }
+    }
+    orc_sort_pairs_stable(k, v, L, sk, sv);
+    const int64_t nu = orc_unique_segments(sk, L, uk, ss);
+    orc_sparse_update(weights, dtype, total_rows, D, state0, state1, rows, D, sv, uk, ss, nu,
+                      offsets, feat_out_col, B, ORC_POOL_NONE, opt);
+    free(k); free(v); free(sk); free(uk); free(ss); free(rows);
+    if (!out_sorted_vals) free(sv);
+    return oob;
+}
+
 /* torch.ops.fbgemm.jagged_2d_to_dense at torchrec/models.py:168-172.
  * [UPSTREAM] dense[b, t, :] = values[offsets[b] + t, :] for t < min(len_b, max_len), else 0. */
 void orc_jagged_2d_to_dense(const float* values, const int64_t* offsets, int64_t B, int32_t D,

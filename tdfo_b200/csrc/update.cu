@@ -24,7 +24,8 @@ __global__ void __launch_bounds__(kUpdThreads)
 linearize_kernel(const int64_t* __restrict__ indices, const int64_t* __restrict__ offsets,
                  const int64_t* __restrict__ feat_row_base, const int64_t* __restrict__ feat_rows,
                  int64_t B, int64_t num_bags, uint32_t oob_key, int vals_are_positions,
-                 uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, int32_t* err_flag) {
+                 uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ pos_bag,
+                 int32_t* err_flag) {
     const int64_t g = (int64_t)blockIdx.x * (kUpdThreads / 32) + (threadIdx.x >> 5);
     if (g >= num_bags) return;
     const int lane = lane_id();
@@ -40,6 +41,7 @@ linearize_kernel(const int64_t* __restrict__ indices, const int64_t* __restrict_
         else { k = oob_key; oob = true; }
         keys[p] = k;
         vals[p] = vals_are_positions ? (uint32_t)p : (uint32_t)g;
+        if (pos_bag) pos_bag[p] = (uint32_t)g;      // weighted pooled backward: payload = position, bag looked up
     }
     if (oob && err_flag) atomicOr(err_flag, TDFO_FLAG_INDEX_OOB);
 }
@@ -60,6 +62,8 @@ struct UpdateArgs {
     const uint32_t* num_unique;
     const int64_t* offsets;
     const int64_t* feat_out_col;
+    const float* psw;         // per-sample weights by position (pooled modes only) or null
+    const uint32_t* pos_bag;  // bag id of every position; set together with psw (payloads are positions then)
     int64_t grad_stride;
     int64_t B;
     uint64_t B_magic;    // ceil(2^64 / B): bag id / B == __umul64hi(id, B_magic) for every 32-bit id (B > 1)
@@ -100,10 +104,14 @@ __device__ __forceinline__ RowMeta load_row_meta(const UpdateArgs& a, uint32_t u
 __device__ __forceinline__ const float* grad_row_of(const UpdateArgs& a, uint32_t v, float& scale) {
     scale = 1.f;
     if (a.pooling_mode == TDFO_POOL_NONE) return a.grad + (size_t)v * a.D;
+    if (a.psw != nullptr) {
+        scale = __ldg(a.psw + v);
+        v = __ldg(a.pos_bag + v);
+    }
     const uint32_t f = a.B_magic ? (uint32_t)__umul64hi((uint64_t)v, a.B_magic) : v;
     const uint32_t b = v - f * (uint32_t)a.B;
     if (a.pooling_mode == TDFO_POOL_MEAN)
-        scale = 1.f / (float)(__ldg(a.offsets + v + 1) - __ldg(a.offsets + v));
+        scale = scale / (float)(__ldg(a.offsets + v + 1) - __ldg(a.offsets + v));
     return a.grad + (size_t)b * a.grad_stride + __ldg(a.feat_out_col + f);
 }
 
@@ -507,7 +515,8 @@ int sparse_update_impl(void* weights, int32_t weights_dtype, int64_t total_rows,
                        const uint32_t* seg_starts, const uint32_t* first_vals, const uint32_t* num_unique,
                        const int64_t* offsets, const int64_t* feat_out_col, int32_t F, int64_t B,
                        int64_t L, int32_t pooling_mode, const tdfo_optimizer_args* opt,
-                       uint32_t* worklist, int64_t worklist_entries, cudaStream_t st) {
+                       uint32_t* worklist, int64_t worklist_entries, const float* psw, const uint32_t* pos_bag,
+                       cudaStream_t st) {
     if (L == 0) return TDFO_OK;
     const size_t esz = weights_dtype == TDFO_F32 ? 4 : 2;
     UpdateArgs a;
@@ -521,6 +530,7 @@ int sparse_update_impl(void* weights, int32_t weights_dtype, int64_t total_rows,
     a.weights = weights; a.state0 = state0; a.state1 = state1; a.grad = grad_out;
     a.sorted_vals = sorted_vals; a.unique_keys = unique_keys; a.seg_starts = seg_starts; a.first_vals = first_vals;
     a.num_unique = num_unique; a.offsets = offsets; a.feat_out_col = feat_out_col;
+    a.psw = psw; a.pos_bag = pos_bag;
     a.grad_stride = grad_stride; a.B = B;
     a.B_magic = B > 1 ? (~0ull / (uint64_t)B + 1ull) : 0ull; a.total_rows = (uint32_t)total_rows; a.L = (uint32_t)L; a.D = D;
     a.nchunks = (int32_t)(D * esz / 16); a.pooling_mode = pooling_mode;
@@ -544,10 +554,10 @@ static size_t pair_array_bytes(int64_t L) { return align_up((size_t)(L + 1) * si
 
 using namespace tdfo;
 
-extern "C" int tdfo_linearize_indices(const int64_t* indices, const int64_t* offsets,
-                                      const int64_t* feat_row_base, const int64_t* feat_rows,
-                                      int32_t F, int64_t B, int64_t total_rows, int32_t pooling_mode,
-                                      uint32_t* keys, uint32_t* vals, int32_t* err_flag, void* stream) {
+static int linearize_impl(const int64_t* indices, const int64_t* offsets,
+                          const int64_t* feat_row_base, const int64_t* feat_rows,
+                          int32_t F, int64_t B, int64_t total_rows, int32_t pooling_mode,
+                          uint32_t* keys, uint32_t* vals, uint32_t* pos_bag, int32_t* err_flag, void* stream) {
     TDFO_CHECK_ARG(F >= 0 && B >= 0, "linearize_indices: negative size");
     TDFO_CHECK_ARG(total_rows >= 0 && total_rows < 0xffffffffll, "linearize_indices: total_rows must be < 2^32-1");
     TDFO_CHECK_ARG((int64_t)F * B < (1ll << 32), "linearize_indices: F*B must be < 2^32");
@@ -558,10 +568,18 @@ extern "C" int tdfo_linearize_indices(const int64_t* indices, const int64_t* off
     const int64_t blocks = (num_bags + kUpdThreads / 32 - 1) / (kUpdThreads / 32);
     linearize_kernel<<<(unsigned)blocks, kUpdThreads, 0, static_cast<cudaStream_t>(stream)>>>(
         indices, offsets, feat_row_base, feat_rows, B, num_bags, (uint32_t)total_rows,
-        pooling_mode == TDFO_POOL_NONE, keys, vals, err_flag);
+        pooling_mode == TDFO_POOL_NONE || pos_bag != nullptr, keys, vals, pos_bag, err_flag);
     count_launch();
     TDFO_LAUNCH_CHECK("linearize_indices");
     return TDFO_OK;
+}
+
+extern "C" int tdfo_linearize_indices(const int64_t* indices, const int64_t* offsets,
+                                      const int64_t* feat_row_base, const int64_t* feat_rows,
+                                      int32_t F, int64_t B, int64_t total_rows, int32_t pooling_mode,
+                                      uint32_t* keys, uint32_t* vals, int32_t* err_flag, void* stream) {
+    return linearize_impl(indices, offsets, feat_row_base, feat_rows, F, B, total_rows, pooling_mode, keys, vals,
+                          nullptr, err_flag, stream);
 }
 
 extern "C" int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
@@ -589,7 +607,7 @@ extern "C" int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t 
     TDFO_CHECK_ARG(pooling_mode != TDFO_POOL_MEAN || offsets, "sparse_update: MEAN pooling needs offsets");
     return sparse_update_impl(weights, weights_dtype, total_rows, D, state0, state1, grad_out, grad_stride,
                               sorted_vals, unique_keys, seg_starts, first_vals, num_unique, offsets, feat_out_col,
-                              F, B, L, pooling_mode, opt, worklist, worklist_entries,
+                              F, B, L, pooling_mode, opt, worklist, worklist_entries, nullptr, nullptr,
                               static_cast<cudaStream_t>(stream));
 }
 
@@ -624,6 +642,13 @@ extern "C" size_t tdfo_backward_scratch_bytes(int64_t L, int64_t total_rows) {
     return lay.total_bytes;
 }
 
+// With per-sample weights the sort payload is the id's position, and the bag of every position
+// is kept in one more uint32[L] array placed after the unweighted layout.
+extern "C" size_t tdfo_backward_scratch_bytes_weighted(int64_t L, int64_t total_rows) {
+    const size_t base = tdfo_backward_scratch_bytes(L, total_rows);
+    return base ? align_up(base, 256) + pair_array_bytes(L) : 0;
+}
+
 extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dtype, int64_t total_rows,
                                               int32_t D, float* state0, float* state1,
                                               const float* grad_out, int64_t grad_stride,
@@ -642,9 +667,15 @@ extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dty
     TDFO_CHECK_ARG(pooling_mode >= TDFO_POOL_SUM && pooling_mode <= TDFO_POOL_NONE,
                    "embedding_backward_update: unknown pooling_mode");
     TDFO_CHECK_ARG(F >= 0 && B >= 0 && L >= 0 && L < (1ll << 30), "embedding_backward_update: size out of range");
-    if (per_sample_weights) {
-        set_error("embedding_backward_update: per-sample weights are not supported in the backward yet");
-        return TDFO_ERR_UNSUPPORTED;
+    const bool weighted = per_sample_weights != nullptr;
+    if (weighted && pooling_mode == TDFO_POOL_NONE) {
+        set_error("embedding_backward_update: per-sample weights need a pooled mode (SUM / MEAN)");
+        return TDFO_ERR_INVALID_ARG;
+    }
+    if (weighted && keys_in_scratch) {
+        set_error("embedding_backward_update: keys_in_scratch (pairs written by the forward) cannot be combined "
+                  "with per-sample weights");
+        return TDFO_ERR_INVALID_ARG;
     }
     if (F == 0 || B == 0 || L == 0) return TDFO_OK;
     TDFO_CHECK_ARG(weights && grad_out && indices && offsets && feat_row_base && feat_rows,
@@ -657,8 +688,9 @@ extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dty
     tdfo_backward_layout lay;
     rc = tdfo_backward_scratch_layout(L, total_rows, &lay);
     if (rc) return rc;
-    if (!scratch || !aligned(scratch, 256) || scratch_bytes < lay.total_bytes) {
-        set_error("embedding_backward_update: scratch null, misaligned or smaller than %zu bytes", lay.total_bytes);
+    const size_t need = weighted ? tdfo_backward_scratch_bytes_weighted(L, total_rows) : lay.total_bytes;
+    if (!scratch || !aligned(scratch, 256) || scratch_bytes < need) {
+        set_error("embedding_backward_update: scratch null, misaligned or smaller than %zu bytes", need);
         return TDFO_ERR_SCRATCH;
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -673,9 +705,10 @@ extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dty
     void* sort_scratch = base + sort_off;
     void* scan_scratch = base + sort_off + radix_sort_scratch_bytes_impl(L, lay.key_bits);
 
+    uint32_t* pos_bag = weighted ? reinterpret_cast<uint32_t*>(base + align_up(lay.total_bytes, 256)) : nullptr;
     if (!keys_in_scratch) {
-        rc = tdfo_linearize_indices(indices, offsets, feat_row_base, feat_rows, F, B, total_rows, pooling_mode,
-                                    k0, v0, err_flag, stream);
+        rc = linearize_impl(indices, offsets, feat_row_base, feat_rows, F, B, total_rows, pooling_mode,
+                            k0, v0, pos_bag, err_flag, stream);
         if (rc) return rc;
     }
     int where = 0;
@@ -694,5 +727,6 @@ extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dty
     if (rc) return rc;
     return sparse_update_impl(weights, weights_dtype, total_rows, D, state0, state1, grad_out, grad_stride,
                               sv, uk, ss, fv, num_unique, offsets, feat_out_col, F, B, L, pooling_mode, opt,
-                              reinterpret_cast<uint32_t*>(base + lay.worklist), (int64_t)lay.worklist_entries, st);
+                              reinterpret_cast<uint32_t*>(base + lay.worklist), (int64_t)lay.worklist_entries,
+                              per_sample_weights, pos_bag, st);
 }

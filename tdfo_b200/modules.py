@@ -88,14 +88,15 @@ class _LookupFn(torch.autograd.Function):
     def forward(ctx, anchor, module, values, offsets, B, psw):
         ctx.module, ctx.B = module, B
         ctx.save_for_backward(values, offsets)
-        out = module._forward_impl(values, offsets, B, psw, emit_keys=True)
+        ctx.psw = psw                      # constants of the step: the weights get no gradient
+        out = module._forward_impl(values, offsets, B, psw, emit_keys=psw is None)
         ctx.keys_token = module._keys_token
         return out
 
     @staticmethod
     def backward(ctx, grad_out):
         values, offsets = ctx.saved_tensors
-        ctx.module._backward_impl(grad_out.contiguous(), values, offsets, ctx.B, ctx.keys_token)
+        ctx.module._backward_impl(grad_out.contiguous(), values, offsets, ctx.B, ctx.keys_token, ctx.psw)
         return None, None, None, None, None, None
 
 
@@ -240,7 +241,7 @@ class _FusedEmbeddingBase(nn.Module):
                                   backward_scratch=scratch)
         return out
 
-    def _backward_impl(self, grad_out, values, offsets, B, keys_token: int = -1):
+    def _backward_impl(self, grad_out, values, offsets, B, keys_token: int = -1, psw=None):
         self._fused.iteration += 1
         opt = self._fused.args()
         for g in self._groups:
@@ -251,14 +252,15 @@ class _FusedEmbeddingBase(nn.Module):
             if len(self._groups) == 1:
                 scratch = self._scratch_for(values.numel(), g.total_rows, values.device)
                 # the pairs in `scratch` are still this call's unless another forward ran in between
-                fused = keys_token == self._keys_token and values.numel() > 0
+                fused = keys_token == self._keys_token and values.numel() > 0 and psw is None
                 ops.embedding_backward_update(self._table_group(g, True), grad_out, values, off, B, g.pooling, opt,
-                                              scratch=scratch, keys_in_scratch=fused)
+                                              scratch=scratch, keys_in_scratch=fused, per_sample_weights=psw)
                 self._keys_token += 1          # the sort consumed them
             else:
                 lo, hi = self._group_bounds(offsets, g, B)
                 ops.embedding_backward_update(self._table_group(g, True), grad_out, values[lo:hi], off - lo, B,
-                                              g.pooling, opt)
+                                              g.pooling, opt,
+                                              per_sample_weights=None if psw is None else psw[lo:hi])
 
     @staticmethod
     def _group_bounds(offsets, g: _Group, B: int):
@@ -282,8 +284,6 @@ class _FusedEmbeddingBase(nn.Module):
                                "move the module and the KeyedJaggedTensor to a cuda device")
         psw = kjt.weights_or_none() if getattr(self, "_is_weighted", False) else None
         if self.training and torch.is_grad_enabled():
-            if psw is not None:
-                raise NotImplementedError("per-sample weights are forward-only in this version")
             if self._anchor is None or self._anchor.device != values.device:
                 self._anchor = torch.zeros(1, device=values.device, requires_grad=True)
             return _LookupFn.apply(self._anchor, self, values, offsets, B, psw)

@@ -265,22 +265,30 @@ def backward_layout(L: int, total_rows: int) -> BackwardLayout:
 
 def embedding_backward_update(group: TableGroup, grad_out: torch.Tensor, indices: torch.Tensor,
                               offsets: torch.Tensor, B: int, pooling_mode: int, opt: OptimizerArgs,
-                              scratch: Optional[torch.Tensor] = None, keys_in_scratch: bool = False) -> torch.Tensor:
+                              scratch: Optional[torch.Tensor] = None, keys_in_scratch: bool = False,
+                              per_sample_weights: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Fused backward + optimizer, in place on ``group.weights`` / state.  Returns the scratch buffer
-    (sorted keys / unique rows are readable at ``backward_layout`` offsets)."""
+    (sorted keys / unique rows are readable at ``backward_layout`` offsets).  With
+    ``per_sample_weights`` (pooled modes) each occurrence's gradient row is scaled by its weight."""
     indices = _cuda(indices, torch.int64, "indices")
     offsets = _cuda(offsets, torch.int64, "offsets")
     grad_out = _cuda(grad_out, torch.float32, "grad_out")
     w = group.weights
     L = indices.numel()
     lib = _lib.load()
-    nb = lib.tdfo_backward_scratch_bytes(L, group.total_rows)
-    if scratch is None:
+    if per_sample_weights is not None:
+        per_sample_weights = _cuda(per_sample_weights, torch.float32, "per_sample_weights")
+        if per_sample_weights.numel() != L:
+            raise ValueError(f"per_sample_weights has {per_sample_weights.numel()} entries for {L} ids")
+        nb = lib.tdfo_backward_scratch_bytes_weighted(L, group.total_rows)
+    else:
+        nb = lib.tdfo_backward_scratch_bytes(L, group.total_rows)
+    if scratch is None or (per_sample_weights is not None and scratch.numel() < nb):
         scratch = _get_scratch(w.device, nb)
     grad_stride = group.D if pooling_mode == POOL_NONE else grad_out.shape[-1]
     check(lib.tdfo_embedding_backward_update(
         _ptr(w), _wdtype(w), group.total_rows, group.D, _ptr(group.state0), _ptr(group.state1),
-        _ptr(grad_out), grad_stride, _ptr(indices), _ptr(offsets), None,
+        _ptr(grad_out), grad_stride, _ptr(indices), _ptr(offsets), _ptr(per_sample_weights),
         _ptr(group.feat_row_base), _ptr(group.feat_rows), _ptr(group.feat_out_col), group.F, B, L, pooling_mode,
         ctypes.byref(opt), 1 if keys_in_scratch else 0, _ptr(group.err_flag), _ptr(scratch), scratch.numel(),
         _stream()))

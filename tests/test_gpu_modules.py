@@ -52,6 +52,46 @@ def test_ebc_forward_backward_matches_oracle(t):
     ebc.check_errors()
 
 
+def test_weighted_ebc_trains_like_the_oracle(t):
+    """EmbeddingBagCollection(is_weighted=True): KJT weights scale the pooled sum and, in the fused
+    backward, each occurrence's gradient row (two tables of different D = two kernel groups)."""
+    rows, dims, B = [60, 25], [32, 64], 24
+    rng = np.random.default_rng(8)
+    tables = [t.EmbeddingBagConfig(num_embeddings=r, embedding_dim=d, name=f"t{i}", feature_names=[f"f{i}"],
+                                   pooling=t.PoolingType.SUM) for i, (r, d) in enumerate(zip(rows, dims))]
+    ebc = t.EmbeddingBagCollection(tables, is_weighted=True, device=torch.device("cuda"))
+    assert ebc.is_weighted()
+    w0 = [rng.uniform(-1, 1, size=(r, d)).astype(np.float32) for r, d in zip(rows, dims)]
+    ebc.load_state_dict({f"embedding_bags.t{i}.weight": torch.from_numpy(w0[i]) for i in range(2)})
+    fused = ebc.set_fused_optimizer(t.EmbOptimType.SGD, learning_rate=0.2)
+    ebc.train()
+    w_o = [w.copy() for w in w0]
+    for step in range(3):
+        lens = [rng.integers(0, 6, size=B).astype(np.int32) for _ in rows]
+        ids = [rng.integers(0, r, size=int(l.sum())) for r, l in zip(rows, lens)]
+        psw = [rng.uniform(0.2, 1.8, size=i.size).astype(np.float32) for i in ids]
+        kjt = t.KeyedJaggedTensor.from_lengths_sync(["f0", "f1"], torch.from_numpy(np.concatenate(ids)),
+                                                    torch.from_numpy(np.concatenate(lens)),
+                                                    weights=torch.from_numpy(np.concatenate(psw))).to("cuda")
+        out = ebc(kjt).values()
+        grad = rng.normal(size=(B, sum(dims))).astype(np.float32)
+        out.backward(torch.from_numpy(grad).cuda())
+        fused.step()
+        col = 0
+        for i, d in enumerate(dims):
+            off = orc.complete_cumsum(lens[i])
+            want, _ = orc.embedding_forward(w_o[i], d, ids[i], off, psw[i], [0], [rows[i]], [0], 1, B, orc.POOL_SUM)
+            np.testing.assert_allclose(out[:, col:col + d].detach().cpu().numpy(), want, rtol=1e-5, atol=1e-5)
+            orc.embedding_backward_update_weighted(w_o[i], d, None, None, np.ascontiguousarray(grad[:, col:col + d]),
+                                                   ids[i], off, psw[i], [0], [rows[i]], [0], 1, B, orc.POOL_SUM,
+                                                   orc.OptArgs(orc.OPT_SGD, 0.2))
+            col += d
+    sd = ebc.state_dict()
+    for i in range(2):
+        np.testing.assert_allclose(sd[f"embedding_bags.t{i}.weight"].cpu().numpy(), w_o[i], rtol=1e-5, atol=2e-6)
+    ebc.check_errors()
+
+
 def test_ebc_mixed_dims_and_key_order(t):
     rows, dims = [30, 20, 10], [16, 32, 16]
     tables = [t.EmbeddingBagConfig(num_embeddings=r, embedding_dim=d, name=f"t{i}", feature_names=[f"f{i}"],

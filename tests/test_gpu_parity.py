@@ -268,6 +268,42 @@ def test_backward_update_vs_oracle(ops, D, mode, optimizer, bf16):
     assert int(grp.err_flag.item()) == 0
 
 
+@pytest.mark.parametrize("bf16", [False, True])
+@pytest.mark.parametrize("optimizer", [orc.OPT_SGD, orc.OPT_ROWWISE_ADAGRAD, orc.OPT_ADAM])
+@pytest.mark.parametrize("mode", [orc.POOL_SUM, orc.POOL_MEAN])
+@pytest.mark.parametrize("D", [16, 128])
+def test_weighted_backward_update_vs_oracle(ops, D, mode, optimizer, bf16):
+    """Per-sample weights in the backward: payload = position, scale = weight."""
+    c = make_case(seed=7 * D + mode + optimizer, F=4, B=40, D=D, rows=[50, 7, 300, 19], max_len=10,
+                  long_bag=150, zipf=True)
+    rng = np.random.default_rng(17)
+    psw = rng.uniform(-1.0, 2.0, size=c.L).astype(np.float32)
+    w_o, w_t = oracle_weights(c, bf16), device_weights(c, bf16)
+    s0_o = s1_o = s0_t = s1_t = None
+    if optimizer == orc.OPT_ROWWISE_ADAGRAD:
+        s0_o = rng.uniform(0, 0.3, size=c.total_rows).astype(np.float32); s0_t = dev(s0_o)
+    elif optimizer == orc.OPT_ADAM:
+        s0_o = np.zeros_like(c.weights); s1_o = np.zeros_like(c.weights)
+        s0_t = dev(s0_o); s1_t = dev(s1_o)
+    grp = group_for(ops, c, w_t, state0=s0_t, state1=s1_t)
+    for step in (1, 2):
+        grad = rng.normal(size=(c.B, c.F * c.D)).astype(np.float32)
+        res = orc.embedding_backward_update_weighted(
+            w_o, c.D, s0_o, s1_o, grad, c.indices, c.offsets, psw, c.row_base, c.rows, c.out_col, c.F, c.B, mode,
+            orc.OptArgs(optimizer, learning_rate=0.05, eps=1e-8, weight_decay=0.01, step=step))
+        scratch = ops.embedding_backward_update(
+            grp, dev(grad), dev(c.indices), dev(c.offsets), c.B, mode,
+            ops.make_optimizer_args(optimizer, 0.05, 1e-8, 0.01, 0.9, 0.999, step), per_sample_weights=dev(psw))
+    rtol, atol = (BF16_RTOL, BF16_ATOL) if bf16 else (FP32_RTOL, 4e-6)
+    np.testing.assert_allclose(table_to_f32(grp.weights), oracle_table_to_f32(w_o), rtol=rtol, atol=atol)
+    if s0_o is not None:
+        np.testing.assert_allclose(grp.state0.cpu().numpy(), s0_o, rtol=max(rtol, 2e-5), atol=atol)
+    lay = ops.backward_layout(c.L, c.total_rows)
+    got_vals = scratch.cpu().numpy()[lay.sorted_vals: lay.sorted_vals + 4 * c.L].view(np.uint32)
+    np.testing.assert_array_equal(got_vals, res["sorted_vals"])          # positions, bit-exact
+    assert int(grp.err_flag.item()) == 0
+
+
 def test_backward_untouched_rows_unchanged_and_oob_skipped(ops):
     c = make_case(seed=5, F=2, B=10, D=32, rows=[1000, 1000], max_len=3)
     idx = c.indices.copy()

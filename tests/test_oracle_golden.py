@@ -131,3 +131,40 @@ def test_out_of_range_ids_are_skipped_and_reported(golden):
     idx2 = np.where(keep, idx, 0)
     want, _ = orc.embedding_forward(g.weights, g.D, idx2, g.offsets, psw, base, rows, col, g.F, g.B, orc.POOL_SUM)
     np.testing.assert_allclose(out, want, rtol=RTOL, atol=ATOL)
+
+
+def test_weighted_backward_matches_torch_embedding_bag():
+    """Pins the weighted-backward restatement on torch itself (live: torch is present wherever the
+    tests run): nn.EmbeddingBag(mode="sum", per_sample_weights) + autograd + dense SGD step."""
+    import torch
+    from helpers import make_case
+    c = make_case(seed=31, F=3, B=12, D=8, rows=[40, 9, 17], max_len=5, long_bag=30, zipf=True)
+    rng = np.random.default_rng(3)
+    psw = rng.uniform(-1.5, 2.0, size=c.L).astype(np.float32)
+    grad = rng.normal(size=(c.B, c.F * c.D)).astype(np.float32)
+    lr = 0.1
+    want = c.weights.copy()
+    for f in range(c.F):
+        lo, hi = int(c.row_base[f]), int(c.row_base[f] + c.rows[f])
+        bag = torch.nn.EmbeddingBag(int(c.rows[f]), c.D, mode="sum", include_last_offset=True)
+        with torch.no_grad():
+            bag.weight.copy_(torch.from_numpy(c.weights[lo:hi]))
+        s, e = int(c.offsets[f * c.B]), int(c.offsets[(f + 1) * c.B])
+        off = torch.from_numpy(c.offsets[f * c.B:(f + 1) * c.B + 1] - s)
+        out = bag(torch.from_numpy(c.indices[s:e]), off, per_sample_weights=torch.from_numpy(psw[s:e]))
+        out.backward(torch.from_numpy(grad[:, f * c.D:(f + 1) * c.D]))
+        want[lo:hi] = (bag.weight - lr * bag.weight.grad).detach().numpy()
+    w = c.weights.copy()
+    res = orc.embedding_backward_update_weighted(w, c.D, None, None, grad, c.indices, c.offsets, psw, c.row_base,
+                                                 c.rows, c.out_col, c.F, c.B, orc.POOL_SUM,
+                                                 orc.OptArgs(orc.OPT_SGD, learning_rate=lr))
+    assert not res["oob"]
+    np.testing.assert_allclose(w, want, rtol=RTOL, atol=2e-6)
+    # weights of 1 reproduce the unweighted path exactly
+    w1, w2 = c.weights.copy(), c.weights.copy()
+    orc.embedding_backward_update_weighted(w1, c.D, None, None, grad, c.indices, c.offsets, np.ones(c.L, np.float32),
+                                           c.row_base, c.rows, c.out_col, c.F, c.B, orc.POOL_MEAN,
+                                           orc.OptArgs(orc.OPT_SGD, learning_rate=lr))
+    orc.embedding_backward_update(w2, c.D, None, None, grad, c.indices, c.offsets, c.row_base, c.rows, c.out_col,
+                                  c.F, c.B, orc.POOL_MEAN, orc.OptArgs(orc.OPT_SGD, learning_rate=lr))
+    np.testing.assert_allclose(w1, w2, rtol=RTOL, atol=1e-6)
