@@ -5,20 +5,21 @@ Everything on the path runs in hand-written sm_100a kernels exported through the
 ``include/tdfo_b200.h`` (``libtdfo_b200.so``).  There is no CPU or PyTorch fallback.
 """
 from . import ops
-from .modules import (DataType, EmbeddingBagCollection, EmbeddingBagConfig, EmbeddingCollection,
+from .modules import (BoundsCheckMode, DataType, EmbeddingBagCollection, EmbeddingBagConfig, EmbeddingCollection,
                       EmbeddingConfig, PoolingType)
 from .optim import (CombinedOptimizer, EmbOptimType, FusedOptimizer, KeyedOptimizerWrapper,
                     in_backward_optimizer_filter)
 from .ops import jagged_2d_to_dense
 from .sparse import JaggedTensor, KeyedJaggedTensor, KeyedTensor
+from .adapters import DLPackEmbeddingTables
 from .distributed import (DistributedModelParallel, EmbeddingBagCollectionSharder, EmbeddingCollectionSharder,
                           ParameterSharding, ShardedEmbeddingBagCollection, ShardedEmbeddingCollection, ShardingType, balanced_table_wise_plan,
                           row_wise, table_wise)
 
 __all__ = [
-    "ops", "DataType", "EmbeddingBagCollection", "EmbeddingBagConfig", "EmbeddingCollection", "EmbeddingConfig",
+    "ops", "BoundsCheckMode", "DataType", "EmbeddingBagCollection", "EmbeddingBagConfig", "EmbeddingCollection", "EmbeddingConfig",
     "PoolingType", "CombinedOptimizer", "EmbOptimType", "FusedOptimizer", "KeyedOptimizerWrapper",
-    "in_backward_optimizer_filter", "jagged_2d_to_dense", "JaggedTensor", "KeyedJaggedTensor", "KeyedTensor",
+    "in_backward_optimizer_filter", "jagged_2d_to_dense", "DLPackEmbeddingTables", "JaggedTensor", "KeyedJaggedTensor", "KeyedTensor",
     "DistributedModelParallel", "EmbeddingBagCollectionSharder", "EmbeddingCollectionSharder", "ParameterSharding",
     "ShardedEmbeddingBagCollection", "ShardedEmbeddingCollection", "ShardingType", "balanced_table_wise_plan", "row_wise", "table_wise",
 ]

@@ -424,6 +424,11 @@ class ShardedEmbeddingBagCollection(nn.Module):
             # directly where the owner's lookup reads them; no all-to-all, no split sizes on the host
             if self._peer is None or self._peer.B != B:
                 cap = self._max_ids_per_rank or int(1.5 * W * max(values.numel(), 1)) + 1024
+                # symmetric buffers must have one size on every rank: agree on the largest proposal
+                # (creation is collective anyway; happens once per batch size)
+                cap_t = torch.tensor([cap], dtype=torch.int64, device=dev)
+                dist.all_reduce(cap_t, op=dist.ReduceOp.MAX, group=self._pg)
+                cap = int(cap_t.item())
                 self._peer = _PeerExchange(self._pg, dev, B, self._F_total, D, self._n_tw, n_rw, cap)
                 self._meta_cache.clear()
             peer = self._peer

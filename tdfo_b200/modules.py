@@ -28,6 +28,18 @@ class PoolingType(enum.Enum):
     NONE = "NONE"
 
 
+class BoundsCheckMode(enum.Enum):
+    """What happens to an id outside its table (SURVEY.md §8b "Errors"; [UPSTREAM] fbgemm's
+    BoundsCheckMode).  In every mode the kernels skip such an id (it contributes nothing to the
+    lookup and no row is updated) and raise the device error word; the modes differ in who reads it:
+    FATAL    the forward synchronises and raises IndexError at once (debugging; costs a sync per step)
+    WARNING  nothing is read until `check_errors()`, which raises IndexError (default)
+    IGNORE   `check_errors()` clears the word silently"""
+    FATAL = "FATAL"
+    WARNING = "WARNING"
+    IGNORE = "IGNORE"
+
+
 class DataType(enum.Enum):
     FP32 = "FP32"
     BF16 = "BF16"
@@ -286,12 +298,22 @@ class _FusedEmbeddingBase(nn.Module):
         if self.training and torch.is_grad_enabled():
             if self._anchor is None or self._anchor.device != values.device:
                 self._anchor = torch.zeros(1, device=values.device, requires_grad=True)
-            return _LookupFn.apply(self._anchor, self, values, offsets, B, psw)
-        return self._forward_impl(values, offsets, B, psw)
+            out = _LookupFn.apply(self._anchor, self, values, offsets, B, psw)
+        else:
+            out = self._forward_impl(values, offsets, B, psw)
+        if self.bounds_check_mode == BoundsCheckMode.FATAL:
+            ops.check_error_flag(self._err_flag)
+        return out
+
+    bounds_check_mode: BoundsCheckMode = BoundsCheckMode.WARNING
 
     def check_errors(self) -> None:
         """Synchronising check of the device error word (out-of-range ids)."""
-        ops.check_error_flag(self._err_flag)
+        try:
+            ops.check_error_flag(self._err_flag)
+        except IndexError:
+            if self.bounds_check_mode != BoundsCheckMode.IGNORE:
+                raise
 
     # ------------------------------------------------------------------ state_dict: one entry per table
     def _table_slices(self):

@@ -14,6 +14,13 @@ def _np(t):
     return None if t is None else t.detach().cpu().numpy()
 
 
+def _table(t):
+    """Weight storage as the oracle takes it, sharing memory: float32, or uint16 bit patterns for bf16."""
+    if t.dtype == torch.bfloat16:
+        return t.detach().view(torch.int16).numpy().view(np.uint16)
+    return t.detach().numpy()
+
+
 class OracleKernelOps:
     def make_group(self, weights, feat_row_base, feat_rows, feat_out_col, out_stride, state0, state1, err_flag):
         return SimpleNamespace(weights=weights, feat_row_base=feat_row_base, feat_rows=feat_rows,
@@ -43,7 +50,7 @@ class OracleKernelOps:
 
     def embedding_forward(self, group, indices, offsets, B, pooling_mode, out, backward_scratch=None):
         F = group.feat_row_base.numel()
-        w = np.ascontiguousarray(_np(group.weights))
+        w = np.ascontiguousarray(_table(group.weights))
         res, oob = orc.embedding_forward(w, w.shape[1], _np(indices), _np(offsets), None, _np(group.feat_row_base),
                                          _np(group.feat_rows), _np(group.feat_out_col), F, B, pooling_mode,
                                          out_stride=group.out_stride)
@@ -55,7 +62,7 @@ class OracleKernelOps:
     def embedding_backward_update(self, group, grad_out, indices, offsets, B, pooling_mode, opt, scratch=None,
                                   keys_in_scratch=False):
         F = group.feat_row_base.numel()
-        w = group.weights.numpy()                       # shares memory with the parameter
+        w = _table(group.weights)                       # shares memory with the parameter
         o = orc.OptArgs(opt.optimizer, opt.learning_rate, opt.eps, opt.weight_decay, opt.beta1, opt.beta2, opt.step)
         orc.embedding_backward_update(w, w.shape[1], _np(group.state0) if group.state0 is None else group.state0.numpy(),
                                       None if group.state1 is None else group.state1.numpy(), _np(grad_out),

@@ -247,3 +247,24 @@ def test_train_py_model_parallel_block(t):
     changed = (table1 != table0).any(dim=1).cpu()
     assert torch.equal(changed, touched)                       # exactly the looked-up rows moved (in backward)
     assert not torch.equal(model.module.out.weight, dense0)    # the dense optimizer stepped too
+
+
+def test_bounds_check_modes(t):
+    """Out-of-range ids never touch memory; who hears about them is selectable."""
+    tables = [t.EmbeddingBagConfig(num_embeddings=10, embedding_dim=16, name="a", feature_names=["a"])]
+    kjt = t.KeyedJaggedTensor.from_lengths_sync(["a"], torch.tensor([3, 10, 4]), torch.tensor([2, 1],
+                                                                                               dtype=torch.int32)).to("cuda")
+    ebc = t.EmbeddingBagCollection(tables, device=torch.device("cuda")).eval()
+    w = ebc.state_dict()["embedding_bags.a.weight"]
+    out = ebc(kjt).values()                                   # WARNING (default): deferred
+    torch.testing.assert_close(out[0], w[3])                  # id 10 skipped
+    torch.testing.assert_close(out[1], w[4])
+    with pytest.raises(IndexError):
+        ebc.check_errors()
+    ebc.check_errors()                                        # the word was cleared by the raise
+    ebc.bounds_check_mode = t.BoundsCheckMode.IGNORE
+    ebc(kjt)
+    ebc.check_errors()
+    ebc.bounds_check_mode = t.BoundsCheckMode.FATAL
+    with pytest.raises(IndexError):
+        ebc(kjt)

@@ -108,3 +108,83 @@ def test_sharded_sequence_on_2_gpus(plan_kind):
                 p.terminate()
         assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
         assert dict(results) == {0: "ok", 1: "ok"}
+
+
+@pytest.mark.parametrize("cfg", [3, 4, 5])
+def test_scaled_baseline_configs_on_2_gpus(cfg):
+    """BASELINE configs 3 (Criteo cardinalities, table-wise, P=1), 4 (row-wise bf16, P=20) and 5 (mixed plan,
+    Zipf lengths and ids) scaled down, two training steps on the CUDA kernels with D = 128
+    (tests/test_configs_gloo.py holds the checks)."""
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from test_configs_gloo import run_rank as run_config_rank
+    port = free_port()
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        results = mgr.dict()
+        procs = [ctx.Process(target=run_config_rank, args=(r, port, cfg, results, True, 128, 48)) for r in range(W)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=300)
+        for p in procs:
+            if p.is_alive():
+                p.terminate()
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        assert dict(results) == {0: "ok", 1: "ok"}
+
+
+def run_rank_replicated_adapter(rank, port, results):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=W, device_id=dev)
+    try:
+        import tdfo_b200 as t
+        from tdfo_b200.adapters import DLPackEmbeddingTables
+        tables = {"user_id": (90, 16), "item_id": (120, 16)}
+        Bn, lr = 32, 0.1
+        tabs = DLPackEmbeddingTables(tables, dev, optimizer=t.EmbOptimType.EXACT_SGD, learning_rate=lr)
+        w = {n: np.random.default_rng(3).uniform(-1, 1, size=s).astype(np.float32) for n, s in tables.items()}
+        tabs.load_state_dict({f"embedding_bags.{n}.weight": torch.from_numpy(a) for n, a in w.items()})   # same replica everywhere
+        per = []
+        for r in range(W):
+            rng = np.random.default_rng(50 + r)
+            per.append(({n: rng.integers(0, s[0], size=Bn) for n, s in tables.items()},
+                        {n: rng.normal(size=(Bn, s[1])).astype(np.float32) for n, s in tables.items()}))
+        ids, grads = per[rank]
+        tabs.apply_gradients({n: torch.from_numpy(a).to(dev) for n, a in ids.items()},
+                             {n: torch.from_numpy(g).to(dev) for n, g in grads.items()}, replicated=True, average=True)
+        for n, (rows, d) in tables.items():       # pmean + SGD restated: global batch in rank order, gradients / W
+            g_ids = np.concatenate([per[r][0][n] for r in range(W)]).astype(np.int64)
+            g_grad = np.concatenate([per[r][1][n] for r in range(W)]) / W
+            orc.embedding_backward_update(w[n], d, None, None, g_grad.astype(np.float32), g_ids,
+                                          np.arange(W * Bn + 1, dtype=np.int64), [0], [rows], [0], 1, W * Bn,
+                                          orc.POOL_SUM, orc.OptArgs(orc.OPT_SGD, lr))
+            got = tabs.state_dict()[f"embedding_bags.{n}.weight"].cpu().numpy()
+            np.testing.assert_allclose(got, w[n], rtol=1e-5, atol=2e-6)
+        results[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+def test_replicated_adapter_tables_stay_identical_on_2_gpus():
+    """jax pmap / tf MirroredStrategy shape: every rank holds a replica and feeds its own batch; the sparse
+    apply_gradients gathers (ids, rows) so all replicas take the same step (jax-flax/train_dp.py:63-65)."""
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    port = free_port()
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        results = mgr.dict()
+        procs = [ctx.Process(target=run_rank_replicated_adapter, args=(r, port, results)) for r in range(W)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=300)
+        for p in procs:
+            if p.is_alive():
+                p.terminate()
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        assert dict(results) == {0: "ok", 1: "ok"}
