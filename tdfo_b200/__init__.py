@@ -13,13 +13,13 @@ from .ops import jagged_2d_to_dense
 from .sparse import JaggedTensor, KeyedJaggedTensor, KeyedTensor
 from .adapters import DLPackEmbeddingTables
 from .distributed import (DistributedModelParallel, EmbeddingBagCollectionSharder, EmbeddingCollectionSharder,
-                          ParameterSharding, ShardedEmbeddingBagCollection, ShardedEmbeddingCollection, ShardingType, balanced_table_wise_plan,
-                          row_wise, table_wise)
+                          ParameterSharding, ShardedEmbeddingBagCollection, ShardedEmbeddingCollection, ShardingType, balanced_plan,
+                          balanced_table_wise_plan, column_wise, row_wise, table_wise)
 
 __all__ = [
     "ops", "BoundsCheckMode", "DataType", "EmbeddingBagCollection", "EmbeddingBagConfig", "EmbeddingCollection", "EmbeddingConfig",
     "PoolingType", "CombinedOptimizer", "EmbOptimType", "FusedOptimizer", "KeyedOptimizerWrapper",
     "in_backward_optimizer_filter", "jagged_2d_to_dense", "DLPackEmbeddingTables", "JaggedTensor", "KeyedJaggedTensor", "KeyedTensor",
     "DistributedModelParallel", "EmbeddingBagCollectionSharder", "EmbeddingCollectionSharder", "ParameterSharding",
-    "ShardedEmbeddingBagCollection", "ShardedEmbeddingCollection", "ShardingType", "balanced_table_wise_plan", "row_wise", "table_wise",
+    "ShardedEmbeddingBagCollection", "ShardedEmbeddingCollection", "ShardingType", "balanced_plan", "balanced_table_wise_plan", "column_wise", "row_wise", "table_wise",
 ]

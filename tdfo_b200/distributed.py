@@ -43,12 +43,14 @@ from .sparse import KeyedJaggedTensor, KeyedTensor
 class ShardingType(enum.Enum):
     TABLE_WISE = "table_wise"
     ROW_WISE = "row_wise"
+    COLUMN_WISE = "column_wise"
 
 
 @dataclass
 class ParameterSharding:
     sharding_type: ShardingType
     rank: Optional[int] = None          # owner for TABLE_WISE
+    ranks: Optional[List[int]] = None   # owners of the column shards for COLUMN_WISE (shard j -> ranks[j])
 
 
 def table_wise(rank: int) -> ParameterSharding:
@@ -57,6 +59,34 @@ def table_wise(rank: int) -> ParameterSharding:
 
 def row_wise() -> ParameterSharding:
     return ParameterSharding(ShardingType.ROW_WISE)
+
+
+def column_wise(ranks: Sequence[int]) -> ParameterSharding:
+    """Split the embedding dimension into len(ranks) equal column shards; shard j lives on ranks[j].
+    Every shard sees all ids of the table and returns its own columns of the pooled row, so unlike
+    row-wise there are no partial sums to reduce: it balances a table count that does not divide
+    the world size at table-wise cost."""
+    return ParameterSharding(ShardingType.COLUMN_WISE, None, [int(r) for r in ranks])
+
+
+def balanced_plan(tables: Sequence[EmbeddingBagConfig], world: int, min_shard_bytes: int = 64
+                  ) -> Dict[str, ParameterSharding]:
+    """Equal tables: floor(T / world) * world of them table-wise round-robin, the remainder R split
+    column-wise into world / gcd(R, world) shards each so every rank holds the same number of columns.
+    Falls back to table-wise for the remainder when a shard's row would drop below `min_shard_bytes`."""
+    import math
+    T = len(tables)
+    n_tw = (T // world) * world
+    plan = {t.name: table_wise(i % world) for i, t in enumerate(tables[:n_tw])}
+    rest = list(tables[n_tw:])
+    if rest:
+        k = world // math.gcd(len(rest), world)
+        esz = 4 if tables[0].data_type.value == "FP32" else 2
+        ok = all(t.embedding_dim % k == 0 and (t.embedding_dim // k) * esz >= min_shard_bytes
+                 and ((t.embedding_dim // k) * esz) % 16 == 0 for t in rest)
+        for i, t in enumerate(rest):
+            plan[t.name] = column_wise([(i * k + j) % world for j in range(k)]) if ok and k > 1 else table_wise(i % world)
+    return plan
 
 
 def balanced_table_wise_plan(tables: Sequence[EmbeddingBagConfig], world: int) -> Dict[str, ParameterSharding]:
@@ -153,13 +183,15 @@ class _PeerExchange:
     rows into, and one gradient landing buffer per rank that the sample owners push gradient rows
     into.  Barriers are the symmetric-memory signal-pad barriers, enqueued on the current stream."""
 
-    def __init__(self, pg, device, B: int, F_total: int, D: int, n_tw: List[int], n_rw: int, ids_capacity: int):
+    def __init__(self, pg, device, B: int, F_total: int, D: int, n_tw: List[int], n_rw: int, ids_capacity: int,
+                 n_cw: Optional[List[int]] = None, Dc: int = 0):
         import torch.distributed._symmetric_memory as symm
         W = len(n_tw)
         group = pg if pg is not None else dist.group.WORLD
         self.B = B
         # input dist landing zones, already in the [feature][source rank][batch] layout
-        fl_max = max(n_tw) + n_rw
+        n_cw = n_cw if n_cw is not None else [0] * W
+        fl_max = max(a + b for a, b in zip(n_tw, n_cw)) + n_rw
         self.capacity = int(ids_capacity)
         self.len_x = symm.empty(max(fl_max * W * B, 4), dtype=torch.int32, device=device)
         self.off_x = symm.empty(fl_max * W * B + 4, dtype=torch.int64, device=device)
@@ -167,7 +199,7 @@ class _PeerExchange:
         self.len_ptrs = list(symm.rendezvous(self.len_x, group).buffer_ptrs)
         self.off_ptrs = list(symm.rendezvous(self.off_x, group).buffer_ptrs)
         self.ids_ptrs = list(symm.rendezvous(self.ids_x, group).buffer_ptrs)
-        self.counts_host = torch.zeros(2, dtype=torch.int64).pin_memory()
+        self.counts_host = torch.zeros(3, dtype=torch.int64).pin_memory()     # ids: end of TW, end of CW, total
         self.counts_event = torch.cuda.Event()
         self.out = [symm.empty(B * F_total * D, dtype=torch.float32, device=device) for _ in range(2)]
         self.out_hdl = [symm.rendezvous(t_, group) for t_ in self.out]
@@ -175,6 +207,10 @@ class _PeerExchange:
         self.grad = symm.empty(max(W * B * max(n_tw) * D, 4), dtype=torch.float32, device=device)
         self.grad_hdl = symm.rendezvous(self.grad, group)
         self.grad_ptrs = list(self.grad_hdl.buffer_ptrs)
+        self.grad_cw, self.grad_cw_ptrs = None, []
+        if max(n_cw) > 0:                          # landing buffer for the gradient columns of column shards
+            self.grad_cw = symm.empty(max(W * B * max(n_cw) * Dc, 4), dtype=torch.float32, device=device)
+            self.grad_cw_ptrs = list(symm.rendezvous(self.grad_cw, group).buffer_ptrs)
         self.step = 0
 
     def barrier(self):
@@ -235,12 +271,32 @@ class ShardedEmbeddingBagCollection(nn.Module):
 
         # who serves which feature
         self._tw_feats: List[List[int]] = [[] for _ in range(W)]   # per owner rank, module order
+        self._cw_slots: List[List[tuple]] = [[] for _ in range(W)] # per owner rank: (feature, column shard)
         self._rw_feats: List[int] = []
         self._rw_block: List[int] = []                             # block size per RW feature
-        self._tw, self._rw = _Shard(), _Shard()
+        self._tw, self._cw, self._rw = _Shard(), _Shard(), _Shard()
+        self._cw_local_shard: List[int] = []                       # column shard index of each local CW table
+        self._Dc = 0                                               # columns per column-wise shard
         for t in tables:
             ps = plan[t.name]
-            if ps.sharding_type == ShardingType.TABLE_WISE:
+            if ps.sharding_type == ShardingType.COLUMN_WISE:
+                k = len(ps.ranks or [])
+                if k < 1 or len(set(ps.ranks)) != k or not all(0 <= x < W for x in ps.ranks):
+                    raise ValueError(f"table {t.name}: column-wise owners {ps.ranks} must be distinct ranks in [0, {W})")
+                if self._D % k:
+                    raise ValueError(f"table {t.name}: embedding_dim {self._D} does not split into {k} column shards")
+                dc = self._D // k
+                if self._Dc not in (0, dc):
+                    raise ValueError("all column-wise tables must use the same number of shards in this version")
+                if (dc * (4 if dtype == torch.float32 else 2)) % 16:
+                    raise ValueError(f"table {t.name}: a column shard of {dc} elements is not a multiple of 16 bytes")
+                self._Dc = dc
+                for j, owner in enumerate(ps.ranks):
+                    self._cw_slots[owner] += [(f, j) for f in feat_ids[t.name]]
+                    if owner == r:
+                        self._cw.add(t, t.num_embeddings, feat_ids[t.name])
+                        self._cw_local_shard.append(j)
+            elif ps.sharding_type == ShardingType.TABLE_WISE:
                 if ps.rank is None or not 0 <= ps.rank < W:
                     raise ValueError(f"table {t.name}: table-wise owner rank {ps.rank} outside [0, {W})")
                 self._tw_feats[ps.rank] += feat_ids[t.name]
@@ -253,18 +309,24 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 self._rw.add(t, max(0, min(bs, t.num_embeddings - r * bs)), feat_ids[t.name])
         self._F_total = F_total
         self._n_tw = [len(x) for x in self._tw_feats]
+        self._n_cw = [len(x) for x in self._cw_slots]
         self._n_rw = len(self._rw_feats)
-        self._F_local = self._n_tw[r] + self._n_rw
+        self._F_local = self._n_tw[r] + self._n_cw[r] + self._n_rw      # local order: TW, CW, RW features
 
         # storage: identical initial values to an unsharded module built with the same seed would
         # need a shared generator; each table is drawn from its own seeded stream instead.
-        for name, sh in (("tw", self._tw), ("rw", self._rw)):
-            w = torch.empty((max(sh.total_rows, 1), self._D), dtype=dtype, device=device)
-            for t, r0, rows in zip(sh.tables, sh.row0, sh.local_rows):
+        for name, sh in (("tw", self._tw), ("cw", self._cw), ("rw", self._rw)):
+            width = (self._Dc or 4) if name == "cw" else self._D
+            w = torch.empty((max(sh.total_rows, 1), width), dtype=dtype, device=device)
+            for ti, (t, r0, rows) in enumerate(zip(sh.tables, sh.row0, sh.local_rows)):
                 if init_on_device:          # large tables: draw the local rows in place (not rank-consistent)
                     w[r0:r0 + rows].uniform_(t.get_weight_init_min(), t.get_weight_init_max())
                     continue
                 full = self.initial_table(t, init_seed)
+                if name == "cw":
+                    c0 = self._cw_local_shard[ti] * self._Dc
+                    w[r0:r0 + rows].copy_(full[:, c0:c0 + self._Dc].to(dtype))
+                    continue
                 lo = 0 if sh is self._tw else r * ((t.num_embeddings + W - 1) // W)
                 w[r0:r0 + rows].copy_(full[lo:lo + rows].to(dtype))
             p = nn.Parameter(w, requires_grad=False)
@@ -276,14 +338,16 @@ class ShardedEmbeddingBagCollection(nn.Module):
             self.register_buffer(f"_{name}_rows", torch.tensor([sh.local_rows[ti] for ti in sh.feat_table] or [0],
                                                                 dtype=torch.int64, device=device)[:max(n_f, 0)],
                                  persistent=False)
-            self.register_buffer(f"_{name}_out_col", (torch.arange(max(n_f, 1), device=device) * self._D)[:n_f],
+            self.register_buffer(f"_{name}_out_col", (torch.arange(max(n_f, 1), device=device) * width)[:n_f],
                                  persistent=False)
         self.register_buffer("_rw_block_sizes", torch.tensor(self._rw_block or [1], dtype=torch.int64, device=device),
                              persistent=False)
         self.register_buffer("_err_flag", torch.zeros(1, dtype=torch.int32, device=device), persistent=False)
 
         # static permutes
-        tw_order = [f for d in range(W) for f in self._tw_feats[d]]
+        # features in destination order: for every owner its TW features, then the features of its column shards
+        tw_order = [f for d in range(W) for f in self._tw_feats[d] + [f_ for (f_, _) in self._cw_slots[d]]]
+        self._send_mult = max([tw_order.count(f) for f in set(tw_order)] or [1])
         self.register_buffer("_tw_send_perm", torch.tensor(tw_order or [0], dtype=torch.int32, device=device),
                              persistent=False)
         self.register_buffer("_rw_select_perm", torch.tensor(self._rw_feats or [0], dtype=torch.int32, device=device),
@@ -303,6 +367,13 @@ class ShardedEmbeddingBagCollection(nn.Module):
             acc += self._n_tw[d] * D_
         self._tw_cols_total = acc
         self._unpack_slots = [(d, j, f) for d in range(W) for j, f in enumerate(self._tw_feats[d])]
+        self._cw_block_off: List[int] = []
+        acc = 0
+        for d in range(W):
+            self._cw_block_off.append(acc)
+            acc += self._n_cw[d] * self._Dc
+        self._cw_cols_total = acc
+        self._cw_unpack_slots = [(d, jj, f, j) for d in range(W) for jj, (f, j) in enumerate(self._cw_slots[d])]
         self._anchor: Optional[torch.Tensor] = None
         self._fused: Optional[FusedOptimizer] = None
         self._meta_cache: Dict[tuple, torch.Tensor] = {}
@@ -315,45 +386,65 @@ class ShardedEmbeddingBagCollection(nn.Module):
         # all-to-alls (needs the CUDA kernels and symmetric memory; on by default when available).
         if peer_memory is None:
             peer_memory = (isinstance(self._ops, CudaKernelOps) and W > 1 and device.type == "cuda"
-                           and sum(self._n_tw) > 0)
+                           and sum(self._n_tw) + sum(self._n_cw) > 0)
         self._use_peer = bool(peer_memory)
         self._max_ids_per_rank = max_ids_per_rank
         self._peer: Optional[_PeerExchange] = None
         self.register_buffer("_tw_global_col", torch.tensor([f * self._D for f in self._tw.features] or [0],
                                                             dtype=torch.int64, device=device)[:len(self._tw.features)],
                              persistent=False)
+        cw_cols = [f * self._D + self._cw_local_shard[ti] * self._Dc
+                   for f, ti in zip(self._cw.features, self._cw.feat_table)]
+        self.register_buffer("_cw_global_col", torch.tensor(cw_cols or [0], dtype=torch.int64,
+                                                            device=device)[:len(cw_cols)], persistent=False)
         self.set_fused_optimizer(EmbOptimType.EXACT_SGD, learning_rate=0.01)
 
-    def _tw_meta(self, B: int, to_output: bool, device) -> torch.Tensor:
-        """Copy table for batch size B: exchange layout <-> KeyedTensor layout (cached per B)."""
-        key = (B, to_output, str(device))
+    def _tw_meta(self, B: int, to_output: bool, device, cls: str = "tw") -> torch.Tensor:
+        """Copy table for batch size B: exchange layout <-> KeyedTensor layout (cached per B).
+        cls "tw": whole-row slots of width D; "cw": column-shard slots of width Dc."""
+        key = (B, to_output, str(device), cls)
         m = self._meta_cache.get(key)
         if m is None:
-            D_, Ft = self._D, self._F_total
+            D_, Ft, Dc = self._D, self._F_total, self._Dc
             ex_off, ex_stride, kt_off, kt_stride = [], [], [], []
-            for (d, j, f) in self._unpack_slots:
-                ex_off.append(self._tw_block_off[d] * B + j * D_)
-                ex_stride.append(self._n_tw[d] * D_)
-                kt_off.append(f * D_)
-                kt_stride.append(Ft * D_)
+            if cls == "tw":
+                for (d, j, f) in self._unpack_slots:
+                    ex_off.append(self._tw_block_off[d] * B + j * D_)
+                    ex_stride.append(self._n_tw[d] * D_)
+                    kt_off.append(f * D_)
+                    kt_stride.append(Ft * D_)
+            else:
+                for (d, jj, f, j) in self._cw_unpack_slots:
+                    ex_off.append(self._cw_block_off[d] * B + jj * Dc)
+                    ex_stride.append(self._n_cw[d] * Dc)
+                    kt_off.append(f * D_ + j * Dc)
+                    kt_stride.append(Ft * D_)
             rows = [ex_off, ex_stride, kt_off, kt_stride] if to_output else [kt_off, kt_stride, ex_off, ex_stride]
             m = torch.tensor(rows, dtype=torch.int64, device=device).reshape(-1)
             self._meta_cache[key] = m
         return m
 
-    def _peer_grad_meta(self, B: int, device) -> torch.Tensor:
+    def _peer_grad_meta(self, B: int, device, cls: str = "tw") -> torch.Tensor:
         """Copy table: my gradient columns -> rows [rank*B, rank*B + B) of each owner's landing buffer."""
-        key = (B, "peer_grad", str(device))
+        key = (B, "peer_grad", str(device), cls)
         m = self._meta_cache.get(key)
         if m is None:
-            D_, Ft, r = self._D, self._F_total, self._rank
+            D_, Ft, r, Dc = self._D, self._F_total, self._rank, self._Dc
             so, ss, do, ds = [], [], [], []
-            for (d, j, f) in self._unpack_slots:
-                n = self._n_tw[d]
-                so.append(f * D_)
-                ss.append(Ft * D_)
-                do.append(self._peer.grad_ptrs[d] // 4 + r * B * n * D_ + j * D_)     # absolute address / 4
-                ds.append(n * D_)
+            if cls == "tw":
+                for (d, j, f) in self._unpack_slots:
+                    n = self._n_tw[d]
+                    so.append(f * D_)
+                    ss.append(Ft * D_)
+                    do.append(self._peer.grad_ptrs[d] // 4 + r * B * n * D_ + j * D_)     # absolute address / 4
+                    ds.append(n * D_)
+            else:
+                for (d, jj, f, j) in self._cw_unpack_slots:
+                    n = self._n_cw[d]
+                    so.append(f * D_ + j * Dc)
+                    ss.append(Ft * D_)
+                    do.append(self._peer.grad_cw_ptrs[d] // 4 + r * B * n * Dc + jj * Dc)
+                    ds.append(n * Dc)
             m = torch.tensor([so, ss, do, ds], dtype=torch.int64, device=device).reshape(-1)
             self._meta_cache[key] = m
         return m
@@ -361,7 +452,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
     # ------------------------------------------------------------------ optimizer
     def set_fused_optimizer(self, optimizer=EmbOptimType.EXACT_SGD, learning_rate=0.01, eps=1e-8, weight_decay=0.0,
                             beta1=0.9, beta2=0.999) -> FusedOptimizer:
-        params = {"_tw_weight": self._tw_weight, "_rw_weight": self._rw_weight}
+        params = {"_tw_weight": self._tw_weight, "_cw_weight": self._cw_weight, "_rw_weight": self._rw_weight}
         self._fused = FusedOptimizer(params, optimizer, learning_rate, eps, weight_decay, beta1, beta2)
         for p in params.values():
             p._in_backward_optimizers = [self._fused]
@@ -388,11 +479,12 @@ class ShardedEmbeddingBagCollection(nn.Module):
         return st[k0], st[k1]
 
     def _group(self, name: str, with_state: bool):
-        sh = self._tw if name == "tw" else self._rw
+        sh = {"tw": self._tw, "cw": self._cw, "rw": self._rw}[name]
         s0, s1 = self._state_for(name, sh.total_rows) if with_state else (None, None)
+        width = self._Dc if name == "cw" else self._D
         return self._ops.make_group(getattr(self, f"_{name}_weight").data, getattr(self, f"_{name}_row_base"),
                                     getattr(self, f"_{name}_rows"), getattr(self, f"_{name}_out_col"),
-                                    len(sh.features) * self._D, s0, s1, self._err_flag)
+                                    len(sh.features) * width, s0, s1, self._err_flag)
 
     # ------------------------------------------------------------------ collectives (plumbing)
     def _a2a(self, send: torch.Tensor, send_splits: Optional[List[int]], recv_splits: Optional[List[int]],
@@ -416,8 +508,9 @@ class ShardedEmbeddingBagCollection(nn.Module):
         pos_parts: List[List[tuple]] = [[] for _ in range(W)]
         Fl, n_rw = self._F_local, self._n_rw
 
-        n_tw_all = sum(self._n_tw)
-        n_tw_r = self._n_tw[r]
+        n_tw_all = sum(self._n_tw) + sum(self._n_cw)      # slots served whole-table or column-wise
+        n_tw_r, n_cw_r = self._n_tw[r], self._n_cw[r]
+        n_own = n_tw_r + n_cw_r                            # local features ahead of the row-wise ones
         peer = None
         if self._use_peer:
             # ---- input dist through NVLink peer memory: lengths, then ids, are stored by the senders
@@ -429,7 +522,8 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 cap_t = torch.tensor([cap], dtype=torch.int64, device=dev)
                 dist.all_reduce(cap_t, op=dist.ReduceOp.MAX, group=self._pg)
                 cap = int(cap_t.item())
-                self._peer = _PeerExchange(self._pg, dev, B, self._F_total, D, self._n_tw, n_rw, cap)
+                self._peer = _PeerExchange(self._pg, dev, B, self._F_total, D, self._n_tw, n_rw, cap,
+                                           n_cw=self._n_cw, Dc=self._Dc)
                 self._meta_cache.clear()
             peer = self._peer
             peer.barrier()                 # everyone is done reading last step's landing zones / outputs
@@ -442,7 +536,8 @@ class ShardedEmbeddingBagCollection(nn.Module):
             peer.barrier()                 # lengths have landed
             lo_ = peer.off_x[: Fl * W * B + 1]
             ops.complete_cumsum_into(peer.len_x[: Fl * W * B], lo_)
-            peer.counts_host.copy_(torch.stack([lo_[n_tw_r * W * B], lo_[Fl * W * B]]), non_blocking=True)
+            peer.counts_host.copy_(torch.stack([lo_[n_tw_r * W * B], lo_[n_own * W * B], lo_[Fl * W * B]]),
+                                   non_blocking=True)
             peer.counts_event.record()
             peer.barrier()                 # every owner's offsets are readable
             if n_tw_all:
@@ -451,18 +546,19 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 ops.push_ids(bv, bo, B, self._peer_meta("ids_rw", B, dev), peer.capacity, self._err_flag)
             peer.barrier()                 # ids have landed
             lv = peer.ids_x
-            tw_total = None                # known on the host only later (counts_event)
+            tw_total = cw_total = None     # known on the host only later (counts_event)
         else:
             # ---- input dist: per-destination blocks  [tw features of d | rw bucket d]
             len_parts: List[List[torch.Tensor]] = [[] for _ in range(W)]
             val_parts: List[List[torch.Tensor]] = [[] for _ in range(W)]
-            n_tw_all = sum(self._n_tw)
             if n_tw_all:
-                tl, to, tv = ops.permute_2d(self._tw_send_perm[:n_tw_all], B, lengths, offsets, values, values.numel())
+                # a column-wise feature is sent to each of its shard owners: size for the repeats
+                tl, to, tv = ops.permute_2d(self._tw_send_perm[:n_tw_all], B, lengths, offsets, values,
+                                            values.numel() * self._send_mult)
                 f0 = 0
                 bounds = to[:: max(B, 1)] if B else to
                 for d in range(W):
-                    f1 = f0 + self._n_tw[d]
+                    f1 = f0 + self._n_tw[d] + self._n_cw[d]
                     len_parts[d].append(tl[f0 * B:f1 * B])
                     val_parts[d].append((tv, bounds, f0, f1))
                     f0 = f1
@@ -510,17 +606,17 @@ class ShardedEmbeddingBagCollection(nn.Module):
                     send_splits[d] += hi - lo
             send_values = torch.cat(send_vals) if send_vals else values[:0]
 
-            len_send_splits = [(self._n_tw[d] + n_rw) * B for d in range(W)]
+            len_send_splits = [(self._n_tw[d] + self._n_cw[d] + n_rw) * B for d in range(W)]
             recv_lengths = self._a2a(send_lengths, len_send_splits, [Fl * B] * W)
-            n_tw_r = self._n_tw[r]
             if Fl * B:
                 rl3 = recv_lengths.view(W, Fl, B)
-                # per-source id counts and the id count of the TW part: one device->host read
+                # per-source id counts and the id counts of the TW / TW+CW parts: one device->host read
                 host = torch.cat([rl3.sum(dim=(1, 2), dtype=torch.int64),
-                                  rl3[:, :n_tw_r].sum(dtype=torch.int64).view(1)]).tolist()
-                recv_splits, tw_total = host[:W], host[W]
+                                  rl3[:, :n_tw_r].sum(dtype=torch.int64).view(1),
+                                  rl3[:, :n_own].sum(dtype=torch.int64).view(1)]).tolist()
+                recv_splits, tw_total, cw_total = host[:W], host[W], host[W + 1]
             else:
-                recv_splits, tw_total = [0] * W, 0
+                recv_splits, tw_total, cw_total = [0] * W, 0, 0
             recv_values = self._a2a(send_values, send_splits, recv_splits)
 
             # ---- [src][f][b] -> [f][src][b]
@@ -538,12 +634,15 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 ll = recv_lengths
                 lo_ = torch.zeros(1, dtype=torch.int64, device=dev)
                 lv = recv_values
-        return dict(lv=lv, lo=lo_, tw_total=tw_total, n_tw_r=n_tw_r, peer=peer, dev=dev)
+        return dict(lv=lv, lo=lo_, tw_total=tw_total, cw_total=cw_total, n_tw_r=n_tw_r, n_cw_r=n_cw_r, peer=peer,
+                    dev=dev)
 
     def _pooled_lookup(self, c, B):
         W, r, D, ops = self._world, self._rank, self._D, self._ops
         lv, lo_, tw_total, n_tw_r, peer, dev = c["lv"], c["lo"], c["tw_total"], c["n_tw_r"], c["peer"], c["dev"]
-        Fl, n_rw, n_tw_all = self._F_local, self._n_rw, sum(self._n_tw)
+        cw_total, n_cw_r = c["cw_total"], c["n_cw_r"]
+        n_own = n_tw_r + n_cw_r
+        Fl, n_rw, n_tw_all, n_cw_all = self._F_local, self._n_rw, sum(self._n_tw), sum(self._n_cw)
         GB = W * B                                            # global batch seen by each local feature
 
         # ---- lookup on the local storage
@@ -559,13 +658,21 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 grp.feat_out_col = self._tw_global_col        # columns of the final [B, F_total*D] layout
                 grp.out_stride = self._F_total * D
                 ops.embedding_forward_peer(grp, lv, lo_[: n_tw_r * GB + 1], GB, self._pooling, peer.out_ptrs[k], B)
+            if n_cw_r:
+                # column shards: the same, Dc columns per pooled row
+                grp = self._group("cw", False)
+                grp.feat_out_col = self._cw_global_col
+                grp.out_stride = self._F_total * D
+                ops.embedding_forward_peer(grp, lv, lo_[n_tw_r * GB: n_own * GB + 1], GB, self._pooling,
+                                           peer.out_ptrs[k], B)
             peer.barrier()                                    # all pooled rows have landed
             if n_rw:
                 rw_out = torch.empty((GB, n_rw * D), dtype=torch.float32, device=dev)
-                ops.embedding_forward(self._group("rw", False), lv, lo_[n_tw_r * GB: Fl * GB + 1], GB, _lib.POOL_SUM,
+                ops.embedding_forward(self._group("rw", False), lv, lo_[n_own * GB: Fl * GB + 1], GB, _lib.POOL_SUM,
                                       rw_out)
                 out3[:, self._rw_feats, :] = self._exchange_partial_sums(rw_out, B, n_rw)
-            return out, dict(peer=True, lo=lo_, n_tw_r=n_tw_r, GB=GB, token=self._fwd_token, fused=False)
+            return out, dict(peer=True, lo=lo_, n_tw_r=n_tw_r, n_cw_r=n_cw_r, GB=GB, token=self._fwd_token,
+                             fused=False)
 
         out = torch.empty((B, self._F_total * D), dtype=torch.float32, device=dev)
         out3 = out.view(B, self._F_total, D)
@@ -579,18 +686,32 @@ class ShardedEmbeddingBagCollection(nn.Module):
             # output dist TW: rank d returns B rows of n_tw[d]*D floats to every source rank
             recv_flat = self._a2a(tw_out.reshape(-1), [B * n_tw_r * D] * W, [B * self._n_tw[d] * D for d in range(W)])
             ops.copy_feature_blocks(recv_flat, out, B, D, self._tw_meta(B, True, dev))
+        saved_cw = None
+        if n_cw_all:
+            Dc = self._Dc
+            if n_cw_r:
+                cw_vals = lv[tw_total:cw_total]
+                cw_off = lo_[n_tw_r * GB: n_own * GB + 1] - tw_total if n_tw_r else lo_[: n_own * GB + 1]
+                cw_out = torch.empty((GB, n_cw_r * Dc), dtype=torch.float32, device=dev)
+                ops.embedding_forward(self._group("cw", False), cw_vals, cw_off, GB, self._pooling, cw_out,
+                                      self._bw_scratch("cw", cw_vals.numel(), dev))
+                saved_cw = (cw_vals, cw_off)
+            else:
+                cw_out = torch.empty((0,), dtype=torch.float32, device=dev)
+            recv_flat = self._a2a(cw_out.reshape(-1), [B * n_cw_r * Dc] * W, [B * self._n_cw[d] * Dc for d in range(W)])
+            ops.copy_feature_blocks(recv_flat, out, B, Dc, self._tw_meta(B, True, dev, "cw"))
         saved_rw = None
         if n_rw:
-            rw_off = lo_[n_tw_r * GB:] - tw_total if n_tw_r else lo_
-            rw_vals = lv[tw_total:]
+            rw_off = lo_[n_own * GB:] - cw_total if n_own else lo_
+            rw_vals = lv[cw_total:]
             rw_out = torch.empty((GB, n_rw * D), dtype=torch.float32, device=dev)
             ops.embedding_forward(self._group("rw", False), rw_vals, rw_off, GB, _lib.POOL_SUM, rw_out,
                                   self._bw_scratch("rw", rw_vals.numel(), dev))
             out3[:, self._rw_feats, :] = self._exchange_partial_sums(rw_out, B, n_rw)
             saved_rw = (rw_vals, rw_off)
         # the TW part of the local ids only: the backward sorts exactly the ids it is given
-        saved = dict(peer=False, lv=lv[:tw_total], lo=lo_, n_tw_r=n_tw_r, GB=GB, rw=saved_rw, fused=self._emit_keys,
-                     token=self._fwd_token)
+        saved = dict(peer=False, lv=lv[:tw_total], lo=lo_, n_tw_r=n_tw_r, n_cw_r=n_cw_r, GB=GB, cw=saved_cw, rw=saved_rw,
+                     fused=self._emit_keys, token=self._fwd_token)
         return out, saved
 
     def _exchange_partial_sums(self, rw_out: torch.Tensor, B: int, n_rw: int) -> torch.Tensor:
@@ -613,11 +734,14 @@ class ShardedEmbeddingBagCollection(nn.Module):
         W, r, n_rw, p = self._world, self._rank, self._n_rw, self._peer
         rows: List[List[int]] = []
         if kind in ("len_tw", "ids_tw"):
-            slots = [(d, j, f) for d in range(W) for j, f in enumerate(self._tw_feats[d])]
+            # whole-table slots, then the column-shard slots of each owner (a column-wise feature is
+            # pushed to every owner of one of its shards)
+            slots = [(d, j, f) for d in range(W)
+                     for j, f in enumerate(self._tw_feats[d] + [f_ for (f_, _) in self._cw_slots[d]])]
             seg = [f for (_, _, f) in slots]                               # segment = original feature
             word = [(j * W + r) * B for (_, j, _) in slots]                # (feature j, source r, batch 0) on owner d
         else:
-            slots = [(d, self._n_tw[d] + k_, None) for d in range(W) for k_ in range(n_rw)]
+            slots = [(d, self._n_tw[d] + self._n_cw[d] + k_, None) for d in range(W) for k_ in range(n_rw)]
             seg = [d * n_rw + k_ for d in range(W) for k_ in range(n_rw)]  # segment of the bucketised layout
             word = [(j * W + r) * B for (_, j, _) in slots]
         dsts = [d for (d, _, _) in slots]
@@ -634,7 +758,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
         if not self._emit_keys or L == 0:
             return None
         from . import ops as _o
-        sh = self._tw if name == "tw" else self._rw
+        sh = {"tw": self._tw, "cw": self._cw, "rw": self._rw}[name]
         need = _o.backward_layout(L, max(sh.total_rows, 1)).total_bytes
         buf = self._scratch.get(name)
         if buf is None or buf.numel() < need or buf.device != device:
@@ -644,42 +768,60 @@ class ShardedEmbeddingBagCollection(nn.Module):
 
     # ------------------------------------------------------------------ backward
     def _backward_impl(self, grad_out, saved, B):
-        W, D, ops = self._world, self._D, self._ops
+        W, D, Dc, ops = self._world, self._D, self._Dc, self._ops
         stale = saved["token"] != self._fwd_token          # another forward ran since
         self._fused.iteration += 1
         opt = self._fused.args()
-        GB, n_tw_r, n_rw = saved["GB"], saved["n_tw_r"], self._n_rw
-        Fl = self._F_local
+        GB, n_tw_r, n_cw_r, n_rw = saved["GB"], saved["n_tw_r"], saved["n_cw_r"], self._n_rw
+        n_own, Fl = n_tw_r + n_cw_r, self._F_local
+        n_tw_all, n_cw_all = sum(self._n_tw), sum(self._n_cw)
         if saved["peer"]:
             if stale:
                 raise RuntimeError("tdfo_b200: with peer-memory exchange, backward must run before the next forward "
                                    "(the received ids live in the shared landing buffers)")
             peer = self._peer
             peer.counts_event.synchronize()                 # counts were copied during the forward: no stall
-            tw_total, total = (int(x) for x in peer.counts_host.tolist())
+            tw_total, cw_total, total = (int(x) for x in peer.counts_host.tolist())
             lo_ = saved["lo"]
             lv_tw, lo_tw = peer.ids_x[:tw_total], lo_[: n_tw_r * GB + 1]
-            rw = (peer.ids_x[tw_total:total], lo_[n_tw_r * GB: Fl * GB + 1] - tw_total) if n_rw else None
+            cw = (peer.ids_x[tw_total:cw_total], lo_[n_tw_r * GB: n_own * GB + 1] - tw_total) if n_cw_r else None
+            rw = (peer.ids_x[cw_total:total], lo_[n_own * GB: Fl * GB + 1] - cw_total) if n_rw else None
             fused = False
         else:
-            lv_tw, lo_tw, rw = saved["lv"], saved["lo"][: n_tw_r * GB + 1], saved["rw"]
+            lv_tw, lo_tw, cw, rw = saved["lv"], saved["lo"][: n_tw_r * GB + 1], saved["cw"], saved["rw"]
             fused = saved["fused"] and not stale
-        if sum(self._n_tw):
-            # the owner of a TW feature needs the gradient rows of every rank's samples
-            if saved["peer"]:
-                # push every gradient row into the landing buffer of the feature's owner over NVLink
+        recv = recv_cw = None
+        if saved["peer"]:
+            # push every gradient row (column slice) into the landing buffer of its owner over NVLink
+            if n_tw_all:
                 ops.copy_feature_blocks(grad_out, None, B, D, self._peer_grad_meta(B, grad_out.device))
-                self._peer.barrier()
                 recv = self._peer.grad[: GB * n_tw_r * D]
-            else:
+            if n_cw_all:
+                ops.copy_feature_blocks(grad_out, None, B, Dc, self._peer_grad_meta(B, grad_out.device, "cw"))
+                recv_cw = self._peer.grad_cw[: GB * n_cw_r * Dc]
+            if n_tw_all or n_cw_all:
+                self._peer.barrier()
+        else:
+            # the owner of a TW feature / column shard needs the gradient of every rank's samples
+            if n_tw_all:
                 send = torch.empty(B * self._tw_cols_total, dtype=torch.float32, device=grad_out.device)
                 ops.copy_feature_blocks(grad_out, send, B, D, self._tw_meta(B, False, grad_out.device))
                 recv = self._a2a(send, [B * self._n_tw[d] * D for d in range(W)], [B * n_tw_r * D] * W)
-            if n_tw_r:
-                sc = self._scratch.get("tw") if fused else None
-                ops.embedding_backward_update(self._group("tw", True), recv.view(GB, n_tw_r * D), lv_tw, lo_tw, GB,
-                                              self._pooling, opt, scratch=sc,
-                                              keys_in_scratch=sc is not None and lv_tw.numel() > 0)
+            if n_cw_all:
+                send = torch.empty(B * self._cw_cols_total, dtype=torch.float32, device=grad_out.device)
+                ops.copy_feature_blocks(grad_out, send, B, Dc, self._tw_meta(B, False, grad_out.device, "cw"))
+                recv_cw = self._a2a(send, [B * self._n_cw[d] * Dc for d in range(W)], [B * n_cw_r * Dc] * W)
+        if n_tw_r:
+            sc = self._scratch.get("tw") if fused else None
+            ops.embedding_backward_update(self._group("tw", True), recv.view(GB, n_tw_r * D), lv_tw, lo_tw, GB,
+                                          self._pooling, opt, scratch=sc,
+                                          keys_in_scratch=sc is not None and lv_tw.numel() > 0)
+        if n_cw_r:
+            cw_vals, cw_off = cw
+            sc = self._scratch.get("cw") if fused else None
+            ops.embedding_backward_update(self._group("cw", True), recv_cw.view(GB, n_cw_r * Dc), cw_vals, cw_off, GB,
+                                          self._pooling, opt, scratch=sc,
+                                          keys_in_scratch=sc is not None and cw_vals.numel() > 0)
         if n_rw:
             g3 = grad_out.view(B, self._F_total, D)
             mine = g3[:, self._rw_feats, :].reshape(B, n_rw * D).contiguous()
@@ -716,37 +858,42 @@ class ShardedEmbeddingBagCollection(nn.Module):
     _state_prefix = "embedding_bags"
 
     def _table_shards(self):
-        """(table, storage name, first local row, local rows, first global row) per local shard."""
+        """(table, storage name, first local row, local rows, first global row, first global column,
+        columns) per local shard."""
         W, r = self._world, self._rank
-        for shn, sh in (("tw", self._tw), ("rw", self._rw)):
-            for t, r0, rows in zip(sh.tables, sh.row0, sh.local_rows):
-                yield t, shn, r0, rows, (0 if shn == "tw" else r * ((t.num_embeddings + W - 1) // W))
+        for shn, sh in (("tw", self._tw), ("cw", self._cw), ("rw", self._rw)):
+            for ti, (t, r0, rows) in enumerate(zip(sh.tables, sh.row0, sh.local_rows)):
+                g0 = r * ((t.num_embeddings + W - 1) // W) if shn == "rw" else 0
+                c0, cols = (self._cw_local_shard[ti] * self._Dc, self._Dc) if shn == "cw" else (0, self._D)
+                yield t, shn, r0, rows, g0, c0, cols
 
     def _save_to_state_dict(self, destination, prefix, keep_vars):
-        local = {t.name: (getattr(self, f"_{shn}_weight")[r0:r0 + rows], g0)
-                 for t, shn, r0, rows, g0 in self._table_shards()}
+        local = {t.name: (getattr(self, f"_{shn}_weight")[r0:r0 + rows], g0, c0)
+                 for t, shn, r0, rows, g0, c0, _ in self._table_shards()}
         ref = self._tw_weight
         meta = {"world": self._world, "rank": self._rank, "tables": {}}
         for t in self._configs:
-            v, g0 = local.get(t.name, (ref.new_empty((0, self._D)), 0))
+            v, g0, c0 = local.get(t.name, (ref.new_empty((0, self._D)), 0, 0))
             destination[f"{prefix}{self._state_prefix}.{t.name}.weight"] = v if keep_vars else v.detach()
             meta["tables"][t.name] = {"row_offset": g0, "rows": int(v.shape[0]), "num_embeddings": t.num_embeddings}
+            if v.shape[1] != self._D:
+                meta["tables"][t.name].update(col_offset=c0, cols=int(v.shape[1]))
         destination[f"{prefix}_shard_metadata"] = meta
 
     def _load_from_state_dict(self, state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys,
                               error_msgs):
-        for t, shn, r0, rows, g0 in self._table_shards():
+        for t, shn, r0, rows, g0, c0, cols in self._table_shards():
             key = f"{prefix}{self._state_prefix}.{t.name}.weight"
             if key not in state_dict:
                 if strict:
                     missing_keys.append(key)
                 continue
             src = state_dict[key]
-            if tuple(src.shape) == (t.num_embeddings, self._D) and rows != t.num_embeddings:
-                src = src[g0:g0 + rows]                       # a full table: take this rank's rows
-            if tuple(src.shape) != (rows, self._D):
+            if tuple(src.shape) == (t.num_embeddings, self._D) and (rows, cols) != (t.num_embeddings, self._D):
+                src = src[g0:g0 + rows, c0:c0 + cols]         # a full table: take this rank's rows / columns
+            if tuple(src.shape) != (rows, cols):
                 error_msgs.append(f"size mismatch for {key}: {tuple(src.shape)} is neither this rank's shard "
-                                  f"{(rows, self._D)} nor the full table {(t.num_embeddings, self._D)}")
+                                  f"{(rows, cols)} nor the full table {(t.num_embeddings, self._D)}")
                 continue
             with torch.no_grad():
                 getattr(self, f"_{shn}_weight")[r0:r0 + rows].copy_(src)
@@ -754,10 +901,13 @@ class ShardedEmbeddingBagCollection(nn.Module):
     def full_state_dict(self, to_cpu: bool = True) -> Dict[str, torch.Tensor]:
         """COLLECTIVE: every table whole, on every rank, under the unsharded module's keys."""
         W = self._world
-        local = {t.name: getattr(self, f"_{shn}_weight")[r0:r0 + rows] for t, shn, r0, rows, _ in self._table_shards()}
+        local = {t.name: getattr(self, f"_{shn}_weight")[r0:r0 + rows]
+                 for t, shn, r0, rows, _, _, _ in self._table_shards()}
         owner = {f: d for d in range(W) for f in self._tw_feats[d]}
+        cw_owner = {(f, j): d for d in range(W) for (f, j) in self._cw_slots[d]}
         out: Dict[str, torch.Tensor] = {}
         ref = self._tw_weight
+        grank = (lambda d: dist.get_global_rank(self._pg, d)) if self._pg is not None else (lambda d: d)
         k = 0
         for t in self._configs:
             f0 = k
@@ -765,8 +915,16 @@ class ShardedEmbeddingBagCollection(nn.Module):
             if f0 in owner:                                   # table-wise: the owner broadcasts
                 src = owner[f0]
                 full = local[t.name].contiguous() if src == self._rank else ref.new_empty((t.num_embeddings, self._D))
-                dist.broadcast(full, src=dist.get_global_rank(self._pg, src) if self._pg is not None else src,
-                               group=self._pg)
+                dist.broadcast(full, src=grank(src), group=self._pg)
+            elif (f0, 0) in cw_owner:                         # column-wise: every shard owner broadcasts its columns
+                parts = []
+                for j in range(self._D // self._Dc):
+                    src = cw_owner[(f0, j)]
+                    part = local[t.name].contiguous() if src == self._rank else \
+                        ref.new_empty((t.num_embeddings, self._Dc))
+                    dist.broadcast(part, src=grank(src), group=self._pg)
+                    parts.append(part)
+                full = torch.cat(parts, dim=1)
             else:                                             # row-wise: gather the (padded) blocks
                 bs = (t.num_embeddings + W - 1) // W
                 mine = ref.new_zeros((bs, self._D))
@@ -780,7 +938,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
     # ------------------------------------------------------------------ inspection helpers
     def local_table(self, name: str) -> torch.Tensor:
         """This rank's rows of table `name` (whole table for TW on the owner, the row block for RW)."""
-        for shn, sh in (("tw", self._tw), ("rw", self._rw)):
+        for shn, sh in (("tw", self._tw), ("cw", self._cw), ("rw", self._rw)):
             for t, r0, rows in zip(sh.tables, sh.row0, sh.local_rows):
                 if t.name == name:
                     return getattr(self, f"_{shn}_weight")[r0:r0 + rows]
@@ -826,6 +984,8 @@ class ShardedEmbeddingCollection(ShardedEmbeddingBagCollection):
     def __init__(self, tables, plan: Dict[str, ParameterSharding], device: torch.device,
                  process_group: Optional[dist.ProcessGroup] = None, kernel_ops=None, init_seed: int = 0,
                  init_on_device: bool = False):
+        if any(ps.sharding_type == ShardingType.COLUMN_WISE for ps in plan.values()):
+            raise ValueError("ShardedEmbeddingCollection supports table-wise and row-wise sharding (no column-wise)")
         super().__init__(tables, plan, device, process_group, kernel_ops, init_seed, init_on_device,
                          peer_memory=False)
         self._track_positions = True

@@ -40,7 +40,7 @@ def run_rank(rank, port, results):
         plan_a = {"t0": td.table_wise(1), "t1": td.row_wise(), "t2": td.table_wise(0), "t3": td.row_wise(),
                   "t4": td.table_wise(1)}
         plan_b = {"t0": td.row_wise(), "t1": td.table_wise(0), "t2": td.row_wise(), "t3": td.table_wise(1),
-                  "t4": td.table_wise(0)}
+                  "t4": td.column_wise([1, 0])}
         mk = lambda plan, seed: td.ShardedEmbeddingBagCollection(tables, plan, torch.device("cpu"),
                                                                  kernel_ops=OracleKernelOps(), init_seed=seed)
         a = mk(plan_a, 3)
@@ -97,6 +97,10 @@ def run_rank(rank, port, results):
         kjt = t.KeyedJaggedTensor.from_lengths_sync([f"f{i}" for i in range(5)], torch.from_numpy(idx),
                                                     torch.from_numpy(lengths))
         np.testing.assert_allclose(b(kjt).values().numpy(), a(kjt).values().numpy(), rtol=1e-6, atol=1e-6)
+        sd_b = b.state_dict()                                     # a column shard: half the columns of every row
+        assert sd_b["embedding_bags.t4.weight"].shape == (9, D // 2)
+        assert sd_b["_shard_metadata"]["tables"]["t4"]["col_offset"] == (D // 2) * (1 - rank)
+        b.load_state_dict(sd_b)                                   # own shards load back
         fb = b.full_state_dict()
         for k in fa:
             np.testing.assert_array_equal(fa[k].numpy(), fb[k].numpy())

@@ -9,7 +9,8 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 import oracle as orc
-from test_sharded_gloo import B, D, W, free_port, global_batch, local_batch, make_tables, run_rank_sequence
+from test_sharded_gloo import (B, D, W, free_port, global_batch, local_batch, make_tables, reference_update,
+                               run_rank_sequence)
 
 pytestmark = pytest.mark.gpu
 
@@ -29,7 +30,11 @@ def run_rank(rank, port, plan_kind, peer, results):
                        "t4": td.table_wise(1)},
                 "rw": {c.name: td.row_wise() for c in tables},
                 "mixed": {"t0": td.table_wise(1), "t1": td.row_wise(), "t2": td.table_wise(0), "t3": td.row_wise(),
-                          "t4": td.table_wise(1)}}[plan_kind]
+                          "t4": td.table_wise(1)},
+                "cw": {"t0": td.column_wise([0, 1]), "t1": td.column_wise([1, 0]), "t2": td.table_wise(0),
+                       "t3": td.table_wise(1), "t4": td.column_wise([0, 1])},
+                "all3": {"t0": td.column_wise([1, 0]), "t1": td.row_wise(), "t2": td.table_wise(0), "t3": td.row_wise(),
+                         "t4": td.column_wise([0, 1])}}[plan_kind]
         m = td.ShardedEmbeddingBagCollection(tables, plan, dev, init_seed=3, peer_memory=peer)
         m.set_fused_optimizer(t.EmbOptimType.EXACT_ROWWISE_ADAGRAD, learning_rate=0.05, eps=1e-8)
         m.train()
@@ -49,16 +54,10 @@ def run_rank(rank, port, plan_kind, peer, results):
                                         len(rows), B, orc.POOL_SUM)
         np.testing.assert_allclose(out_host, want, rtol=1e-5, atol=1e-6)
         g_len, g_idx, g_grad = global_batch(rows)
-        w_ref, h_ref = full.copy(), np.zeros(sum(rows), np.float32)
-        orc.embedding_backward_update(w_ref, D, h_ref, None, g_grad, g_idx, orc.complete_cumsum(g_len), base, rows, col,
-                                      len(rows), W * B, orc.POOL_SUM, orc.OptArgs(orc.OPT_ROWWISE_ADAGRAD, 0.05, 1e-8))
-        mine = {c.name: m.local_table(c.name).detach().cpu().numpy().copy() for c in tables}
-        gathered = [None] * W
-        dist.all_gather_object(gathered, mine)
+        w_ref = reference_update(full, rows, plan, td, g_len, g_idx, g_grad, orc.OPT_ROWWISE_ADAGRAD)
+        full_sd = m.full_state_dict()                       # shards reassembled (rows / columns / whole tables)
         for i, c in enumerate(tables):
-            ps = plan[c.name]
-            got = gathered[ps.rank][c.name] if ps.sharding_type == td.ShardingType.TABLE_WISE else \
-                np.concatenate([gathered[r][c.name] for r in range(W)])
+            got = full_sd[f"embedding_bags.{c.name}.weight"].numpy()
             np.testing.assert_allclose(got, w_ref[base[i]:base[i] + rows[i]], rtol=1e-5, atol=2e-6,
                                        err_msg=f"table {c.name} ({plan_kind})")
         results[rank] = "ok"
@@ -67,7 +66,7 @@ def run_rank(rank, port, plan_kind, peer, results):
 
 
 @pytest.mark.parametrize("plan_kind,peer", [("tw", False), ("tw", True), ("rw", False), ("mixed", False),
-                                            ("mixed", True)])
+                                            ("mixed", True), ("cw", False), ("cw", True), ("all3", True)])
 def test_sharded_equals_unsharded_on_2_gpus(plan_kind, peer):
     """peer=True: table-wise pooled rows and gradient rows travel through NVLink peer memory written
     by the kernels themselves; peer=False: NCCL all-to-alls."""

@@ -59,6 +59,31 @@ def global_batch(rows):
     return lengths, np.concatenate(idx_parts), grad
 
 
+def reference_update(full, rows, plan, td, g_len, g_idx, g_grad, code, lr=0.05):
+    """Unsharded oracle update on the global batch, table by table.  A column-wise table is updated
+    shard by shard: each column shard is an independent table of D/k columns ([UPSTREAM] torchrec
+    column-wise shards are separate TBE tables), which matters only for row-wise Adagrad, whose
+    per-row state then averages g^2 over the shard's own columns."""
+    w_ref = full.copy()
+    base = np.concatenate([[0], np.cumsum(rows)[:-1]]).astype(np.int64)
+    g_off = orc.complete_cumsum(g_len)
+    GB = W * B
+    for i, r_ in enumerate(rows):
+        ps = plan[f"t{i}"]
+        k = len(ps.ranks) if ps.sharding_type == td.ShardingType.COLUMN_WISE else 1
+        dc = D // k
+        idx = g_idx[g_off[i * GB]:g_off[(i + 1) * GB]]
+        off = g_off[i * GB:(i + 1) * GB + 1] - g_off[i * GB]
+        for j in range(k):
+            c0 = j * dc
+            w = np.ascontiguousarray(w_ref[base[i]:base[i] + r_, c0:c0 + dc])
+            g = np.ascontiguousarray(g_grad[:, i * D + c0:i * D + c0 + dc])
+            orc.embedding_backward_update(w, dc, np.zeros(r_, np.float32), None, g, idx, off, [0], [r_], [0], 1, GB,
+                                          orc.POOL_SUM, orc.OptArgs(code, lr, 1e-8))
+            w_ref[base[i]:base[i] + r_, c0:c0 + dc] = w
+    return w_ref
+
+
 def run_rank(rank, port, plan_kind, optimizer_name, results):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -74,6 +99,12 @@ def run_rank(rank, port, plan_kind, optimizer_name, results):
                     "t4": td.table_wise(1)}
         elif plan_kind == "rw":
             plan = {c.name: td.row_wise() for c in tables}
+        elif plan_kind == "cw":       # column shards (D/2 columns each) next to whole tables
+            plan = {"t0": td.column_wise([0, 1]), "t1": td.column_wise([1, 0]), "t2": td.table_wise(0),
+                    "t3": td.table_wise(1), "t4": td.column_wise([0, 1])}
+        elif plan_kind == "all3":     # table-wise + column-wise + row-wise in one module
+            plan = {"t0": td.column_wise([1, 0]), "t1": td.row_wise(), "t2": td.table_wise(0), "t3": td.row_wise(),
+                    "t4": td.column_wise([0, 1])}
         else:
             plan = {"t0": td.table_wise(1), "t1": td.row_wise(), "t2": td.table_wise(0), "t3": td.row_wise(),
                     "t4": td.table_wise(1)}
@@ -96,20 +127,11 @@ def run_rank(rank, port, plan_kind, optimizer_name, results):
         np.testing.assert_allclose(out.detach().numpy(), want, rtol=1e-5, atol=1e-6)
 
         g_len, g_idx, g_grad = global_batch(rows)
-        w_ref = full.copy()
         code = {"EXACT_SGD": orc.OPT_SGD, "EXACT_ROWWISE_ADAGRAD": orc.OPT_ROWWISE_ADAGRAD}[optimizer_name]
-        h_ref = np.zeros(sum(rows), np.float32)
-        orc.embedding_backward_update(w_ref, D, h_ref, None, g_grad, g_idx, orc.complete_cumsum(g_len), base, rows, col,
-                                      len(rows), W * B, orc.POOL_SUM, orc.OptArgs(code, 0.05, 1e-8))
-        mine = {c.name: m.local_table(c.name).detach().numpy().copy() for c in tables}
-        gathered = [None] * W
-        dist.all_gather_object(gathered, mine)
+        w_ref = reference_update(full, rows, plan, td, g_len, g_idx, g_grad, code)
+        full_sd = m.full_state_dict()                       # shards reassembled (rows / columns / whole tables)
         for i, c in enumerate(tables):
-            ps = plan[c.name]
-            if ps.sharding_type == td.ShardingType.TABLE_WISE:
-                got = gathered[ps.rank][c.name]
-            else:
-                got = np.concatenate([gathered[r][c.name] for r in range(W)])
+            got = full_sd[f"embedding_bags.{c.name}.weight"].numpy()
             np.testing.assert_allclose(got, w_ref[base[i]:base[i] + rows[i]], rtol=1e-5, atol=1e-6,
                                        err_msg=f"table {c.name} ({plan_kind})")
         results[rank] = "ok"
@@ -118,7 +140,8 @@ def run_rank(rank, port, plan_kind, optimizer_name, results):
 
 
 @pytest.mark.parametrize("plan_kind,optimizer_name", [("tw", "EXACT_SGD"), ("rw", "EXACT_ROWWISE_ADAGRAD"),
-                                                      ("mixed", "EXACT_ROWWISE_ADAGRAD")])
+                                                      ("mixed", "EXACT_ROWWISE_ADAGRAD"),
+                                                      ("cw", "EXACT_ROWWISE_ADAGRAD"), ("all3", "EXACT_SGD")])
 def test_sharded_equals_unsharded_world2(plan_kind, optimizer_name):
     port = free_port()
     ctx = mp.get_context("spawn")
