@@ -343,9 +343,11 @@ int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t total_rows,
  * at the offsets reported by tdfo_backward_scratch_layout, the sorted keys,
  * sorted vals, unique keys, segment starts and the unique count, so a caller
  * (or a parity test) can read them.
- * keys_in_scratch != 0: the caller already had tdfo_embedding_forward write the
+ * keys_in_scratch == 1: the caller already had tdfo_embedding_forward write the
  * linearised pairs for these same indices / offsets into the input_keys /
  * input_vals slots of `scratch`; the linearise stage is skipped.
+ * keys_in_scratch == TDFO_SCRATCH_PREPARED: tdfo_embedding_backward_prepare already ran on this
+ * scratch; only the update kernel runs (indices / feat_row_base / feat_rows may be NULL).
  * per_sample_weights (float[L], pooled modes only, may be NULL): the gradient row
  * of occurrence p is scaled by per_sample_weights[p] (and by 1/len for MEAN), the
  * backward of the weighted pooled lookup.  The weights themselves
@@ -364,6 +366,23 @@ typedef struct tdfo_backward_layout {
 
 size_t tdfo_backward_scratch_bytes(int64_t L, int64_t total_rows);
 size_t tdfo_backward_scratch_bytes_weighted(int64_t L, int64_t total_rows);
+
+/*
+ * The id-only half of the backward (linearise -> sort -> unique) on its own, so a caller can run
+ * it on `stream` while the gradient is still being produced or exchanged (the sharded path
+ * overlaps it with the NVLink gradient push): it needs the ids, not grad_out.  Follow with
+ * tdfo_embedding_backward_update(..., keys_in_scratch = TDFO_SCRATCH_PREPARED, same scratch, same
+ * indices / offsets / L / total_rows / pooling_mode), which then runs only the update kernel.
+ * weighted != 0 selects the weighted layout (scratch of tdfo_backward_scratch_bytes_weighted).
+ * keys_in_scratch: 0, or 1 if tdfo_embedding_forward already wrote the pairs (see above).
+ */
+#define TDFO_SCRATCH_PREPARED 2
+int tdfo_embedding_backward_prepare(const int64_t* indices, const int64_t* offsets,
+                                    const int64_t* feat_row_base, const int64_t* feat_rows,
+                                    int32_t F, int64_t B, int64_t L, int64_t total_rows,
+                                    int32_t pooling_mode, int32_t weighted, int32_t keys_in_scratch,
+                                    int32_t* err_flag,
+                                    void* scratch, size_t scratch_bytes, void* stream);
 int tdfo_backward_scratch_layout(int64_t L, int64_t total_rows, tdfo_backward_layout* layout /* HOST */);
 int tdfo_embedding_backward_update(void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
                                    float* state0, float* state1,

@@ -20,6 +20,7 @@ POOL_SUM, POOL_MEAN, POOL_NONE = 0, 1, 2
 OPT_SGD, OPT_ROWWISE_ADAGRAD, OPT_ADAM = 0, 1, 2
 FLAG_INDEX_OOB, FLAG_SCAN_TIMEOUT, FLAG_RECV_OVERFLOW = 1, 2, 4
 ABI_VERSION = 1
+SCRATCH_PREPARED = 2
 CUMSUM_STATIC_MAX_N = 1 << 22
 
 
@@ -64,6 +65,8 @@ _SIGNATURES = {
     "tdfo_embedding_backward_update": (c_int, [P, c_int32, c_int64, c_int32, P, P, P, c_int64, P, P, P, P, P, P,
                                                c_int32, c_int64, c_int64, c_int32, POINTER(OptimizerArgs), c_int32,
                                                P, P, c_size_t, P]),
+    "tdfo_embedding_backward_prepare": (c_int, [P, P, P, P, c_int32, c_int64, c_int64, c_int64, c_int32, c_int32,
+                                                c_int32, P, P, c_size_t, P]),
     "tdfo_copy_feature_blocks": (c_int, [P, P, c_int64, c_int32, c_int32, P, P]),
     "tdfo_jagged_2d_to_dense": (c_int, [P, P, c_int64, c_int32, c_int64, P, P]),
     "tdfo_dense_to_jagged": (c_int, [P, P, c_int64, c_int32, c_int64, c_int64, P, P]),

@@ -649,6 +649,86 @@ extern "C" size_t tdfo_backward_scratch_bytes_weighted(int64_t L, int64_t total_
     return base ? align_up(base, 256) + pair_array_bytes(L) : 0;
 }
 
+// stages: bit 0 = linearise (unless the pairs are already in scratch) + sort + unique, bit 1 = update
+static int backward_stages(int stages, const char* who, void* weights, int32_t weights_dtype, int64_t total_rows,
+                           int32_t D, float* state0, float* state1, const float* grad_out, int64_t grad_stride,
+                           const int64_t* indices, const int64_t* offsets, const float* per_sample_weights,
+                           bool weighted, const int64_t* feat_row_base, const int64_t* feat_rows,
+                           const int64_t* feat_out_col, int32_t F, int64_t B, int64_t L, int32_t pooling_mode,
+                           const tdfo_optimizer_args* opt, int32_t keys_in_scratch, int32_t* err_flag, void* scratch,
+                           size_t scratch_bytes, void* stream) {
+    tdfo_backward_layout lay;
+    int rc = tdfo_backward_scratch_layout(L, total_rows, &lay);
+    if (rc) return rc;
+    const size_t need = weighted ? tdfo_backward_scratch_bytes_weighted(L, total_rows) : lay.total_bytes;
+    if (!scratch || !aligned(scratch, 256) || scratch_bytes < need) {
+        set_error("%s: scratch null, misaligned or smaller than %zu bytes", who, need);
+        return TDFO_ERR_SCRATCH;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    char* base = static_cast<char*>(scratch);
+    const size_t A = pair_array_bytes(L);
+    uint32_t* k0 = reinterpret_cast<uint32_t*>(base);
+    uint32_t* v0 = reinterpret_cast<uint32_t*>(base + A);
+    uint32_t* k1 = reinterpret_cast<uint32_t*>(base + 2 * A);
+    uint32_t* v1 = reinterpret_cast<uint32_t*>(base + 3 * A);
+    uint32_t* num_unique = reinterpret_cast<uint32_t*>(base + lay.num_unique);
+    const size_t sort_off = lay.worklist + align_up(lay.worklist_entries * sizeof(uint32_t), 256);
+    void* sort_scratch = base + sort_off;
+    void* scan_scratch = base + sort_off + radix_sort_scratch_bytes_impl(L, lay.key_bits);
+    uint32_t* pos_bag = weighted ? reinterpret_cast<uint32_t*>(base + align_up(lay.total_bytes, 256)) : nullptr;
+    uint32_t* sk = reinterpret_cast<uint32_t*>(base + lay.sorted_keys);
+    uint32_t* sv = reinterpret_cast<uint32_t*>(base + lay.sorted_vals);
+    uint32_t* uk = reinterpret_cast<uint32_t*>(base + lay.unique_keys);
+    uint32_t* ss = reinterpret_cast<uint32_t*>(base + lay.seg_starts);
+    uint32_t* fv = reinterpret_cast<uint32_t*>(base + lay.first_vals);
+
+    if (stages & 1) {
+        if (!keys_in_scratch) {
+            rc = linearize_impl(indices, offsets, feat_row_base, feat_rows, F, B, total_rows, pooling_mode,
+                                k0, v0, pos_bag, err_flag, stream);
+            if (rc) return rc;
+        }
+        int where = 0;
+        rc = radix_sort_impl(k0, v0, k1, v1, L, lay.key_bits, err_flag, sort_scratch, st, &where);
+        if (rc) return rc;
+        if ((where ? k1 : k0) != sk) {
+            set_error("%s: internal layout mismatch", who);
+            return TDFO_ERR_INVALID_ARG;
+        }
+        rc = unique_segments_impl(sk, sv, L, uk, ss, fv, num_unique, err_flag, scan_scratch, st);
+        if (rc) return rc;
+    }
+    if (stages & 2) {
+        rc = sparse_update_impl(weights, weights_dtype, total_rows, D, state0, state1, grad_out, grad_stride,
+                                sv, uk, ss, fv, num_unique, offsets, feat_out_col, F, B, L, pooling_mode, opt,
+                                reinterpret_cast<uint32_t*>(base + lay.worklist), (int64_t)lay.worklist_entries,
+                                per_sample_weights, pos_bag, st);
+        if (rc) return rc;
+    }
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_embedding_backward_prepare(const int64_t* indices, const int64_t* offsets,
+                                               const int64_t* feat_row_base, const int64_t* feat_rows,
+                                               int32_t F, int64_t B, int64_t L, int64_t total_rows,
+                                               int32_t pooling_mode, int32_t weighted, int32_t keys_in_scratch,
+                                               int32_t* err_flag, void* scratch, size_t scratch_bytes,
+                                               void* stream) {
+    TDFO_CHECK_ARG(total_rows >= 0 && total_rows < 0xffffffffll, "embedding_backward_prepare: total_rows must be < 2^32-1");
+    TDFO_CHECK_ARG(pooling_mode >= TDFO_POOL_SUM && pooling_mode <= TDFO_POOL_NONE,
+                   "embedding_backward_prepare: unknown pooling_mode");
+    TDFO_CHECK_ARG(F >= 0 && B >= 0 && L >= 0 && L < (1ll << 30), "embedding_backward_prepare: size out of range");
+    TDFO_CHECK_ARG(keys_in_scratch == 0 || keys_in_scratch == 1, "embedding_backward_prepare: keys_in_scratch must be 0 or 1");
+    TDFO_CHECK_ARG(!(weighted && (pooling_mode == TDFO_POOL_NONE || keys_in_scratch)),
+                   "embedding_backward_prepare: weighted needs a pooled mode and keys_in_scratch = 0");
+    if (F == 0 || B == 0 || L == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(indices && offsets && feat_row_base && feat_rows, "embedding_backward_prepare: null pointer");
+    return backward_stages(1, "embedding_backward_prepare", nullptr, TDFO_F32, total_rows, 4, nullptr, nullptr, nullptr,
+                           0, indices, offsets, nullptr, weighted != 0, feat_row_base, feat_rows, nullptr, F, B, L,
+                           pooling_mode, nullptr, keys_in_scratch, err_flag, scratch, scratch_bytes, stream);
+}
+
 extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dtype, int64_t total_rows,
                                               int32_t D, float* state0, float* state1,
                                               const float* grad_out, int64_t grad_stride,
@@ -667,66 +747,29 @@ extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dty
     TDFO_CHECK_ARG(pooling_mode >= TDFO_POOL_SUM && pooling_mode <= TDFO_POOL_NONE,
                    "embedding_backward_update: unknown pooling_mode");
     TDFO_CHECK_ARG(F >= 0 && B >= 0 && L >= 0 && L < (1ll << 30), "embedding_backward_update: size out of range");
+    TDFO_CHECK_ARG(keys_in_scratch >= 0 && keys_in_scratch <= TDFO_SCRATCH_PREPARED,
+                   "embedding_backward_update: keys_in_scratch must be 0, 1 or TDFO_SCRATCH_PREPARED");
     const bool weighted = per_sample_weights != nullptr;
     if (weighted && pooling_mode == TDFO_POOL_NONE) {
         set_error("embedding_backward_update: per-sample weights need a pooled mode (SUM / MEAN)");
         return TDFO_ERR_INVALID_ARG;
     }
-    if (weighted && keys_in_scratch) {
+    if (weighted && keys_in_scratch == 1) {
         set_error("embedding_backward_update: keys_in_scratch (pairs written by the forward) cannot be combined "
                   "with per-sample weights");
         return TDFO_ERR_INVALID_ARG;
     }
     if (F == 0 || B == 0 || L == 0) return TDFO_OK;
-    TDFO_CHECK_ARG(weights && grad_out && indices && offsets && feat_row_base && feat_rows,
+    const bool prepared = keys_in_scratch == TDFO_SCRATCH_PREPARED;
+    TDFO_CHECK_ARG(weights && grad_out && offsets && (prepared || (indices && feat_row_base && feat_rows)),
                    "embedding_backward_update: null pointer");
     TDFO_CHECK_ARG(aligned(weights, 16) && aligned(grad_out, 16), "embedding_backward_update: weights/grad_out not 16-byte aligned");
     if (pooling_mode != TDFO_POOL_NONE) {
         TDFO_CHECK_ARG(feat_out_col != nullptr, "embedding_backward_update: feat_out_col is null");
         TDFO_CHECK_ARG(grad_stride % 4 == 0, "embedding_backward_update: grad_stride not a multiple of 4");
     }
-    tdfo_backward_layout lay;
-    rc = tdfo_backward_scratch_layout(L, total_rows, &lay);
-    if (rc) return rc;
-    const size_t need = weighted ? tdfo_backward_scratch_bytes_weighted(L, total_rows) : lay.total_bytes;
-    if (!scratch || !aligned(scratch, 256) || scratch_bytes < need) {
-        set_error("embedding_backward_update: scratch null, misaligned or smaller than %zu bytes", need);
-        return TDFO_ERR_SCRATCH;
-    }
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    char* base = static_cast<char*>(scratch);
-    const size_t A = pair_array_bytes(L);
-    uint32_t* k0 = reinterpret_cast<uint32_t*>(base);
-    uint32_t* v0 = reinterpret_cast<uint32_t*>(base + A);
-    uint32_t* k1 = reinterpret_cast<uint32_t*>(base + 2 * A);
-    uint32_t* v1 = reinterpret_cast<uint32_t*>(base + 3 * A);
-    uint32_t* num_unique = reinterpret_cast<uint32_t*>(base + lay.num_unique);
-    const size_t sort_off = lay.worklist + align_up(lay.worklist_entries * sizeof(uint32_t), 256);
-    void* sort_scratch = base + sort_off;
-    void* scan_scratch = base + sort_off + radix_sort_scratch_bytes_impl(L, lay.key_bits);
-
-    uint32_t* pos_bag = weighted ? reinterpret_cast<uint32_t*>(base + align_up(lay.total_bytes, 256)) : nullptr;
-    if (!keys_in_scratch) {
-        rc = linearize_impl(indices, offsets, feat_row_base, feat_rows, F, B, total_rows, pooling_mode,
-                            k0, v0, pos_bag, err_flag, stream);
-        if (rc) return rc;
-    }
-    int where = 0;
-    rc = radix_sort_impl(k0, v0, k1, v1, L, lay.key_bits, err_flag, sort_scratch, st, &where);
-    if (rc) return rc;
-    uint32_t* sk = reinterpret_cast<uint32_t*>(base + lay.sorted_keys);
-    uint32_t* sv = reinterpret_cast<uint32_t*>(base + lay.sorted_vals);
-    uint32_t* uk = reinterpret_cast<uint32_t*>(base + lay.unique_keys);
-    uint32_t* ss = reinterpret_cast<uint32_t*>(base + lay.seg_starts);
-    if ((where ? k1 : k0) != sk) {
-        set_error("embedding_backward_update: internal layout mismatch");
-        return TDFO_ERR_INVALID_ARG;
-    }
-    uint32_t* fv = reinterpret_cast<uint32_t*>(base + lay.first_vals);
-    rc = unique_segments_impl(sk, sv, L, uk, ss, fv, num_unique, err_flag, scan_scratch, st);
-    if (rc) return rc;
-    return sparse_update_impl(weights, weights_dtype, total_rows, D, state0, state1, grad_out, grad_stride,
-                              sv, uk, ss, fv, num_unique, offsets, feat_out_col, F, B, L, pooling_mode, opt,
-                              reinterpret_cast<uint32_t*>(base + lay.worklist), (int64_t)lay.worklist_entries,
-                              per_sample_weights, pos_bag, st);
+    return backward_stages(prepared ? 2 : 3, "embedding_backward_update", weights, weights_dtype, total_rows, D, state0,
+                           state1, grad_out, grad_stride, indices, offsets, per_sample_weights, weighted, feat_row_base,
+                           feat_rows, feat_out_col, F, B, L, pooling_mode, opt, prepared ? 0 : keys_in_scratch, err_flag,
+                           scratch, scratch_bytes, stream);
 }

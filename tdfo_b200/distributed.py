@@ -138,6 +138,12 @@ class CudaKernelOps:
         self._ops.embedding_backward_update(group, grad_out, indices, offsets, B, pooling_mode, opt, scratch=scratch,
                                             keys_in_scratch=keys_in_scratch)
 
+    def embedding_backward_prepare(self, group, indices, offsets, B, pooling_mode, scratch):
+        self._ops.embedding_backward_prepare(group, indices, offsets, B, pooling_mode, scratch)
+
+    def backward_scratch_bytes(self, L, total_rows):
+        return self._ops.backward_layout(L, total_rows).total_bytes
+
     def embedding_forward_peer(self, group, indices, offsets, B, pooling_mode, peer_out, peer_batch,
                                backward_scratch=None):
         self._ops.embedding_forward_peer(group, indices, offsets, B, pooling_mode, peer_out, peer_batch,
@@ -767,6 +773,22 @@ class ShardedEmbeddingBagCollection(nn.Module):
         return buf
 
     # ------------------------------------------------------------------ backward
+    def _side_stream(self, device):
+        st = getattr(self, "_side", None)
+        if st is None or st.device != device:
+            st = self._side = torch.cuda.Stream(device=device)
+        return st
+
+    def _prepared_scratch(self, name: str, L: int, device):
+        """Workspace the id-only half of the backward sorts into (one per shard kind: they are in flight together)."""
+        sh = {"tw": self._tw, "cw": self._cw}[name]
+        need = self._ops.backward_scratch_bytes(L, max(sh.total_rows, 1))
+        buf = self._scratch.get("prep_" + name)
+        if buf is None or buf.numel() < need or buf.device != device:
+            buf = torch.empty(int(need * 1.1) + 256, dtype=torch.uint8, device=device)
+            self._scratch["prep_" + name] = buf
+        return buf
+
     def _backward_impl(self, grad_out, saved, B):
         W, D, Dc, ops = self._world, self._D, self._Dc, self._ops
         stale = saved["token"] != self._fwd_token          # another forward ran since
@@ -791,16 +813,32 @@ class ShardedEmbeddingBagCollection(nn.Module):
             lv_tw, lo_tw, cw, rw = saved["lv"], saved["lo"][: n_tw_r * GB + 1], saved["cw"], saved["rw"]
             fused = saved["fused"] and not stale
         recv = recv_cw = None
+        prepared = {}
         if saved["peer"]:
-            # push every gradient row (column slice) into the landing buffer of its owner over NVLink
-            if n_tw_all:
-                ops.copy_feature_blocks(grad_out, None, B, D, self._peer_grad_meta(B, grad_out.device))
-                recv = self._peer.grad[: GB * n_tw_r * D]
-            if n_cw_all:
-                ops.copy_feature_blocks(grad_out, None, B, Dc, self._peer_grad_meta(B, grad_out.device, "cw"))
-                recv_cw = self._peer.grad_cw[: GB * n_cw_r * Dc]
-            if n_tw_all or n_cw_all:
-                self._peer.barrier()
+            # Push every gradient row (column slice) into the landing buffer of its owner over NVLink, on a
+            # side stream: the push is NVLink-bound and the id-only half of the backward (linearise, sort,
+            # unique: latency-bound, needs no gradient) runs on the main stream meanwhile.
+            main = torch.cuda.current_stream(grad_out.device)
+            side = self._side_stream(grad_out.device)
+            side.wait_stream(main)                          # grad_out has been produced
+            grad_out.record_stream(side)
+            with torch.cuda.stream(side):
+                if n_tw_all:
+                    ops.copy_feature_blocks(grad_out, None, B, D, self._peer_grad_meta(B, grad_out.device))
+                    recv = self._peer.grad[: GB * n_tw_r * D]
+                if n_cw_all:
+                    ops.copy_feature_blocks(grad_out, None, B, Dc, self._peer_grad_meta(B, grad_out.device, "cw"))
+                    recv_cw = self._peer.grad_cw[: GB * n_cw_r * Dc]
+                if n_tw_all or n_cw_all:
+                    self._peer.barrier()
+                landed = torch.cuda.Event()
+                landed.record(side)
+            for name, have, ids_, off_ in (("tw", n_tw_r, lv_tw, lo_tw), ("cw", n_cw_r) + (cw if cw else (None, None))):
+                if have and ids_.numel() > 0:
+                    sc = self._prepared_scratch(name, ids_.numel(), grad_out.device)
+                    ops.embedding_backward_prepare(self._group(name, False), ids_, off_, GB, self._pooling, sc)
+                    prepared[name] = sc
+            main.wait_event(landed)
         else:
             # the owner of a TW feature / column shard needs the gradient of every rank's samples
             if n_tw_all:
@@ -812,16 +850,18 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 ops.copy_feature_blocks(grad_out, send, B, Dc, self._tw_meta(B, False, grad_out.device, "cw"))
                 recv_cw = self._a2a(send, [B * self._n_cw[d] * Dc for d in range(W)], [B * n_cw_r * Dc] * W)
         if n_tw_r:
-            sc = self._scratch.get("tw") if fused else None
+            sc = prepared.get("tw", self._scratch.get("tw") if fused else None)
             ops.embedding_backward_update(self._group("tw", True), recv.view(GB, n_tw_r * D), lv_tw, lo_tw, GB,
                                           self._pooling, opt, scratch=sc,
-                                          keys_in_scratch=sc is not None and lv_tw.numel() > 0)
+                                          keys_in_scratch="prepared" if "tw" in prepared else
+                                          (sc is not None and lv_tw.numel() > 0))
         if n_cw_r:
             cw_vals, cw_off = cw
-            sc = self._scratch.get("cw") if fused else None
+            sc = prepared.get("cw", self._scratch.get("cw") if fused else None)
             ops.embedding_backward_update(self._group("cw", True), recv_cw.view(GB, n_cw_r * Dc), cw_vals, cw_off, GB,
                                           self._pooling, opt, scratch=sc,
-                                          keys_in_scratch=sc is not None and cw_vals.numel() > 0)
+                                          keys_in_scratch="prepared" if "cw" in prepared else
+                                          (sc is not None and cw_vals.numel() > 0))
         if n_rw:
             g3 = grad_out.view(B, self._F_total, D)
             mine = g3[:, self._rw_feats, :].reshape(B, n_rw * D).contiguous()

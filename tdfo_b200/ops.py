@@ -265,11 +265,13 @@ def backward_layout(L: int, total_rows: int) -> BackwardLayout:
 
 def embedding_backward_update(group: TableGroup, grad_out: torch.Tensor, indices: torch.Tensor,
                               offsets: torch.Tensor, B: int, pooling_mode: int, opt: OptimizerArgs,
-                              scratch: Optional[torch.Tensor] = None, keys_in_scratch: bool = False,
+                              scratch: Optional[torch.Tensor] = None, keys_in_scratch=False,
                               per_sample_weights: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Fused backward + optimizer, in place on ``group.weights`` / state.  Returns the scratch buffer
     (sorted keys / unique rows are readable at ``backward_layout`` offsets).  With
-    ``per_sample_weights`` (pooled modes) each occurrence's gradient row is scaled by its weight."""
+    ``per_sample_weights`` (pooled modes) each occurrence's gradient row is scaled by its weight.
+    ``keys_in_scratch``: False / True (pairs written by the forward) / ``"prepared"`` (``embedding_backward_prepare``
+    already sorted and run-length encoded into ``scratch``: only the update kernel runs)."""
     indices = _cuda(indices, torch.int64, "indices")
     offsets = _cuda(offsets, torch.int64, "offsets")
     grad_out = _cuda(grad_out, torch.float32, "grad_out")
@@ -290,9 +292,23 @@ def embedding_backward_update(group: TableGroup, grad_out: torch.Tensor, indices
         _ptr(w), _wdtype(w), group.total_rows, group.D, _ptr(group.state0), _ptr(group.state1),
         _ptr(grad_out), grad_stride, _ptr(indices), _ptr(offsets), _ptr(per_sample_weights),
         _ptr(group.feat_row_base), _ptr(group.feat_rows), _ptr(group.feat_out_col), group.F, B, L, pooling_mode,
-        ctypes.byref(opt), 1 if keys_in_scratch else 0, _ptr(group.err_flag), _ptr(scratch), scratch.numel(),
-        _stream()))
+        ctypes.byref(opt), _lib.SCRATCH_PREPARED if keys_in_scratch == "prepared" else (1 if keys_in_scratch else 0),
+        _ptr(group.err_flag), _ptr(scratch), scratch.numel(), _stream()))
     return scratch
+
+
+def embedding_backward_prepare(group: TableGroup, indices: torch.Tensor, offsets: torch.Tensor, B: int,
+                               pooling_mode: int, scratch: torch.Tensor, keys_in_scratch: bool = False,
+                               weighted: bool = False) -> None:
+    """The id-only half of the backward (linearise, sort, unique) into ``scratch``; enqueue it on any stream
+    while the gradient is still on its way, then call ``embedding_backward_update(..., scratch=scratch,
+    keys_in_scratch="prepared")``."""
+    indices = _cuda(indices, torch.int64, "indices")
+    offsets = _cuda(offsets, torch.int64, "offsets")
+    check(_lib.load().tdfo_embedding_backward_prepare(
+        _ptr(indices), _ptr(offsets), _ptr(group.feat_row_base), _ptr(group.feat_rows), group.F, B, indices.numel(),
+        group.total_rows, pooling_mode, 1 if weighted else 0, 1 if keys_in_scratch else 0, _ptr(group.err_flag),
+        _ptr(scratch), scratch.numel(), _stream()))
 
 
 def linearize_indices(group: TableGroup, indices, offsets, B, pooling_mode):

@@ -304,6 +304,36 @@ def test_weighted_backward_update_vs_oracle(ops, D, mode, optimizer, bf16):
     assert int(grp.err_flag.item()) == 0
 
 
+@pytest.mark.parametrize("mode,weighted", [(orc.POOL_SUM, False), (orc.POOL_NONE, False), (orc.POOL_MEAN, True)])
+def test_backward_prepare_then_update_equals_the_one_call_form(ops, mode, weighted):
+    """tdfo_embedding_backward_prepare (ids only: linearise, sort, unique; here on a side stream) followed by
+    the update with keys_in_scratch = PREPARED must give bit-identical tables to the single call."""
+    c = make_case(seed=21 + mode, F=3, B=50, D=64, rows=[80, 11, 400], max_len=9, long_bag=120, zipf=True)
+    rng = np.random.default_rng(4)
+    pooled = mode != orc.POOL_NONE
+    grad = dev(rng.normal(size=(c.B, c.F * c.D) if pooled else (c.L, c.D)).astype(np.float32))
+    psw = dev(rng.uniform(0.1, 2.0, size=c.L).astype(np.float32)) if weighted else None
+    h0 = rng.uniform(0, 0.3, size=c.total_rows).astype(np.float32)
+    opt = ops.make_optimizer_args(orc.OPT_ROWWISE_ADAGRAD, 0.05, 1e-8, 0.01)
+    idx, off = dev(c.indices), dev(c.offsets)
+    a = group_for(ops, c, dev(c.weights), pooled=pooled, state0=dev(h0))
+    ops.embedding_backward_update(a, grad, idx, off, c.B, mode, opt, per_sample_weights=psw)
+    b = group_for(ops, c, dev(c.weights), pooled=pooled, state0=dev(h0))
+    lib = __import__("tdfo_b200")._lib.load()
+    nb = (lib.tdfo_backward_scratch_bytes_weighted if weighted else lib.tdfo_backward_scratch_bytes)(c.L, c.total_rows)
+    scratch = torch.empty(nb, dtype=torch.uint8, device="cuda")
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        ops.embedding_backward_prepare(b, idx, off, c.B, mode, scratch, weighted=weighted)
+    torch.cuda.current_stream().wait_stream(side)
+    ops.embedding_backward_update(b, grad, idx, off, c.B, mode, opt, scratch=scratch, keys_in_scratch="prepared",
+                                  per_sample_weights=psw)
+    torch.testing.assert_close(b.weights, a.weights, rtol=0, atol=0)
+    torch.testing.assert_close(b.state0, a.state0, rtol=0, atol=0)
+    assert int(a.err_flag.item()) == 0 and int(b.err_flag.item()) == 0
+
+
 def test_backward_untouched_rows_unchanged_and_oob_skipped(ops):
     c = make_case(seed=5, F=2, B=10, D=32, rows=[1000, 1000], max_len=3)
     idx = c.indices.copy()

@@ -12,6 +12,8 @@ F, rows, D, P, B = 26, 1_000_000, 128, 20, 16384
 tables = [t.EmbeddingBagConfig(num_embeddings=rows, embedding_dim=D, name=f"t{i}", feature_names=[f"f{i}"]) for i in range(F)]
 n_tw = F if os.environ.get("PLAN", "mixed") == "tw" else (F // world) * world
 plan = {f"t{i}": (td.table_wise(i % world) if i < n_tw else td.row_wise()) for i in range(F)}
+if os.environ.get("PLAN") == "cw":
+    plan = td.balanced_plan(tables, world)
 m = td.ShardedEmbeddingBagCollection(tables, plan, dev, init_on_device=True)
 m.set_fused_optimizer(t.EmbOptimType.EXACT_ROWWISE_ADAGRAD, learning_rate=0.01)
 m.train()
@@ -31,4 +33,11 @@ with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
     torch.cuda.synchronize()
 if rank == 0:
     print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=32, max_name_column_width=70), flush=True)
+    # timeline of one step on rank 0: kernel name, start offset, duration (us)
+    evs = sorted((e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA),
+                 key=lambda e: e.time_range.start)
+    t0 = evs[0].time_range.start
+    n_per = len(evs) // 5
+    for e in evs[-n_per:]:
+        print(f"{(e.time_range.start - t0):9.0f} {e.time_range.elapsed_us():8.0f}  {e.name[:90]}", flush=True)
 os._exit(0)
