@@ -176,19 +176,47 @@ __global__ void jagged_1d_to_padded_dense_kernel(const int64_t* __restrict__ val
 
 // Strided block copy used around the pooled-output exchanges: slot j moves B rows of D floats
 // from src + src_off[j] (+ b * src_stride[j]) to dst + dst_off[j] (+ b * dst_stride[j]).
-__global__ void copy_feature_blocks_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t B,
-                                           int32_t D4, int32_t nslots, const int64_t* __restrict__ meta) {
+struct CopyItem {
+    const uint4* src;
+    uint4* dst;
+};
+
+__device__ __forceinline__ CopyItem copy_item(const float* src, float* dst, int64_t i, int32_t D4, int32_t nslots,
+                                              const int64_t* __restrict__ meta) {
+    const int c = (int)(i % D4);
+    const int64_t rb = i / D4;
+    const int j = (int)(rb % nslots);
+    const int64_t b = rb / nslots;
+    const int64_t so = __ldg(meta + j), ss = __ldg(meta + nslots + j);
+    const int64_t dof = __ldg(meta + 2 * nslots + j), ds = __ldg(meta + 3 * nslots + j);
+    CopyItem it;
+    it.src = reinterpret_cast<const uint4*>(src + so + b * ss) + c;
+    it.dst = reinterpret_cast<uint4*>(dst + dof + b * ds) + c;
+    return it;
+}
+
+// UNROLL independent 16-byte loads are issued before their stores.  The peer-push form (dst == NULL,
+// destinations are NVLink peer addresses) runs with few CTAs and UNROLL 4: it is NVLink-bound, and a
+// small grid leaves the SMs to the kernels that overlap it (the sort of the sharded backward).
+template <int UNROLL>
+__global__ void __launch_bounds__(256)
+copy_feature_blocks_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t B,
+                           int32_t D4, int32_t nslots, const int64_t* __restrict__ meta) {
     const int64_t total = (int64_t)nslots * B * D4;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-         i += (int64_t)gridDim.x * blockDim.x) {
-        const int c = (int)(i % D4);
-        const int64_t rb = i / D4;
-        const int j = (int)(rb % nslots);
-        const int64_t b = rb / nslots;
-        const int64_t so = __ldg(meta + j), ss = __ldg(meta + nslots + j);
-        const int64_t dof = __ldg(meta + 2 * nslots + j), ds = __ldg(meta + 3 * nslots + j);
-        const uint4 v = __ldcs(reinterpret_cast<const uint4*>(src + so + b * ss) + c);
-        __stcs(reinterpret_cast<uint4*>(dst + dof + b * ds) + c, v);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < total; i0 += stride * UNROLL) {
+        CopyItem it[UNROLL];
+        uint4 v[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            const int64_t i = i0 + u * stride;
+            it[u] = copy_item(src, dst, i < total ? i : i0, D4, nslots, meta);
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) v[u] = __ldcs(it[u].src);
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u)
+            if (i0 + u * stride < total) __stcs(it[u].dst, v[u]);
     }
 }
 
@@ -376,8 +404,15 @@ extern "C" int tdfo_copy_feature_blocks(const float* src, float* dst, int64_t B,
     if (B == 0 || nslots == 0) return TDFO_OK;
     TDFO_CHECK_ARG(src && meta, "copy_feature_blocks: null pointer");   // dst == NULL: absolute destinations
     TDFO_CHECK_ARG(aligned(src, 16) && aligned(dst, 16), "copy_feature_blocks: buffers not 16-byte aligned");
-    copy_feature_blocks_kernel<<<grid_for((int64_t)nslots * B * (D / 4), 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        src, dst, B, D / 4, nslots, meta);
+    const int64_t items = (int64_t)nslots * B * (D / 4);
+    if (dst == nullptr) {       // peer push: NVLink-bound, keep the grid small (see the kernel comment)
+        unsigned g = grid_for((items + 3) / 4, 256);
+        if (g > (unsigned)kNumSMs * 2) g = kNumSMs * 2;
+        copy_feature_blocks_kernel<4><<<g, 256, 0, static_cast<cudaStream_t>(stream)>>>(src, dst, B, D / 4, nslots, meta);
+    } else {
+        copy_feature_blocks_kernel<1><<<grid_for(items, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+            src, dst, B, D / 4, nslots, meta);
+    }
     count_launch();
     TDFO_LAUNCH_CHECK("copy_feature_blocks");
     return TDFO_OK;

@@ -138,8 +138,9 @@ class CudaKernelOps:
         self._ops.embedding_backward_update(group, grad_out, indices, offsets, B, pooling_mode, opt, scratch=scratch,
                                             keys_in_scratch=keys_in_scratch)
 
-    def embedding_backward_prepare(self, group, indices, offsets, B, pooling_mode, scratch):
-        self._ops.embedding_backward_prepare(group, indices, offsets, B, pooling_mode, scratch)
+    def embedding_backward_prepare(self, group, indices, offsets, B, pooling_mode, scratch, keys_in_scratch=False):
+        self._ops.embedding_backward_prepare(group, indices, offsets, B, pooling_mode, scratch,
+                                             keys_in_scratch=keys_in_scratch)
 
     def backward_scratch_bytes(self, L, total_rows):
         return self._ops.backward_layout(L, total_rows).total_bytes
@@ -776,7 +777,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
     def _side_stream(self, device):
         st = getattr(self, "_side", None)
         if st is None or st.device != device:
-            st = self._side = torch.cuda.Stream(device=device)
+            st = self._side = torch.cuda.Stream(device=device, priority=-1)
         return st
 
     def _prepared_scratch(self, name: str, L: int, device):
@@ -820,6 +821,13 @@ class ShardedEmbeddingBagCollection(nn.Module):
             # unique: latency-bound, needs no gradient) runs on the main stream meanwhile.
             main = torch.cuda.current_stream(grad_out.device)
             side = self._side_stream(grad_out.device)
+            todo = [(name, ids_, off_) for name, have, ids_, off_ in
+                    (("tw", n_tw_r, lv_tw, lo_tw), ("cw", n_cw_r) + (cw if cw else (None, None)))
+                    if have and ids_.numel() > 0]
+            # (Measured at N=8: linearising before the push starts does not help, 3.28 vs 3.24 ms/step: every
+            # kernel that runs next to the NVLink stores slows down, the streaming linearise pass most.)
+            for name, ids_, off_ in todo:
+                prepared[name] = self._prepared_scratch(name, ids_.numel(), grad_out.device)
             side.wait_stream(main)                          # grad_out has been produced
             grad_out.record_stream(side)
             with torch.cuda.stream(side):
@@ -833,11 +841,8 @@ class ShardedEmbeddingBagCollection(nn.Module):
                     self._peer.barrier()
                 landed = torch.cuda.Event()
                 landed.record(side)
-            for name, have, ids_, off_ in (("tw", n_tw_r, lv_tw, lo_tw), ("cw", n_cw_r) + (cw if cw else (None, None))):
-                if have and ids_.numel() > 0:
-                    sc = self._prepared_scratch(name, ids_.numel(), grad_out.device)
-                    ops.embedding_backward_prepare(self._group(name, False), ids_, off_, GB, self._pooling, sc)
-                    prepared[name] = sc
+            for name, ids_, off_ in todo:
+                ops.embedding_backward_prepare(self._group(name, False), ids_, off_, GB, self._pooling, prepared[name])
             main.wait_event(landed)
         else:
             # the owner of a TW feature / column shard needs the gradient of every rank's samples
