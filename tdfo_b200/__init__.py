@@ -12,6 +12,7 @@ from .optim import (CombinedOptimizer, EmbOptimType, FusedOptimizer, KeyedOptimi
 from .ops import jagged_2d_to_dense
 from .sparse import JaggedTensor, KeyedJaggedTensor, KeyedTensor
 from .adapters import DLPackEmbeddingTables
+from .pipeline import DevicePrefetcher
 from .distributed import (DistributedModelParallel, EmbeddingBagCollectionSharder, EmbeddingCollectionSharder,
                           ParameterSharding, ShardedEmbeddingBagCollection, ShardedEmbeddingCollection, ShardingType, balanced_plan,
                           balanced_table_wise_plan, column_wise, row_wise, table_wise)
@@ -19,7 +20,7 @@ from .distributed import (DistributedModelParallel, EmbeddingBagCollectionSharde
 __all__ = [
     "ops", "BoundsCheckMode", "DataType", "EmbeddingBagCollection", "EmbeddingBagConfig", "EmbeddingCollection", "EmbeddingConfig",
     "PoolingType", "CombinedOptimizer", "EmbOptimType", "FusedOptimizer", "KeyedOptimizerWrapper",
-    "in_backward_optimizer_filter", "jagged_2d_to_dense", "DLPackEmbeddingTables", "JaggedTensor", "KeyedJaggedTensor", "KeyedTensor",
+    "in_backward_optimizer_filter", "jagged_2d_to_dense", "DLPackEmbeddingTables", "DevicePrefetcher", "JaggedTensor", "KeyedJaggedTensor", "KeyedTensor",
     "DistributedModelParallel", "EmbeddingBagCollectionSharder", "EmbeddingCollectionSharder", "ParameterSharding",
     "ShardedEmbeddingBagCollection", "ShardedEmbeddingCollection", "ShardingType", "balanced_plan", "balanced_table_wise_plan", "column_wise", "row_wise", "table_wise",
 ]

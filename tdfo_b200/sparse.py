@@ -64,6 +64,11 @@ class JaggedTensor:
         mv = lambda t: None if t is None else t.to(device, non_blocking=non_blocking)
         return JaggedTensor(mv(self._values), mv(self._weights), mv(self._lengths), mv(self._offsets))
 
+    def record_stream(self, stream) -> None:
+        for t in (self._values, self._weights, self._lengths, self._offsets):
+            if t is not None and t.is_cuda:
+                t.record_stream(stream)
+
     def to_padded_dense(self, desired_length: Optional[int] = None, padding_value=0) -> torch.Tensor:
         """[B, desired_length] (1-D values) — torchrec/models.py:210-212."""
         if desired_length is None:
@@ -175,6 +180,12 @@ class KeyedJaggedTensor:
         pm = lambda t: None if t is None else t.pin_memory()
         return KeyedJaggedTensor(self._keys, pm(self._values), pm(self._weights), pm(self._lengths),
                                  pm(self._offsets), self._stride, self._length_per_key)
+
+    def record_stream(self, stream) -> None:
+        """Tell the caching allocator that `stream` uses this batch (it was filled on a copy stream)."""
+        for t in (self._values, self._weights, self._lengths, self._offsets):
+            if t is not None and t.is_cuda:
+                t.record_stream(stream)
 
     # ---- views
     def __getitem__(self, key: str) -> JaggedTensor:

@@ -78,3 +78,29 @@ def test_product_never_imports_the_oracle():
         assert "oracle" not in p.read_text(), f"{p} mentions the oracle"
     for p in (ROOT / "tdfo_b200" / "csrc").glob("*"):
         assert "oracle" not in p.read_text(), f"{p} mentions the oracle"
+
+
+def test_new_entry_points_validate_on_the_host(lib):
+    """Weighted scratch size, prepare / PREPARED flag: argument checks run before any CUDA call."""
+    from tdfo_b200 import _lib
+    base = lib.tdfo_backward_scratch_bytes(1000, 5000)
+    wtd = lib.tdfo_backward_scratch_bytes_weighted(1000, 5000)
+    assert wtd >= base + 1000 * 4 and wtd % 256 == 0
+    assert lib.tdfo_backward_scratch_bytes_weighted(1 << 31, 10) == 0                # L too large
+    # prepare: bad pooling mode, bad flag, weighted sequence mode
+    P = None
+    rc = lib.tdfo_embedding_backward_prepare(P, P, P, P, 1, 1, 10, 100, 9, 0, 0, P, P, 0, P)
+    assert rc == -1 and b"pooling_mode" in lib.tdfo_last_error()
+    rc = lib.tdfo_embedding_backward_prepare(P, P, P, P, 1, 1, 10, 100, _lib.POOL_SUM, 0, 2, P, P, 0, P)
+    assert rc == -1 and b"keys_in_scratch" in lib.tdfo_last_error()
+    rc = lib.tdfo_embedding_backward_prepare(P, P, P, P, 1, 1, 10, 100, _lib.POOL_NONE, 1, 0, P, P, 0, P)
+    assert rc == -1 and b"weighted" in lib.tdfo_last_error()
+    assert lib.tdfo_embedding_backward_prepare(P, P, P, P, 0, 0, 0, 100, _lib.POOL_SUM, 0, 0, P, P, 0, P) == 0   # nothing to do
+    rc = lib.tdfo_embedding_backward_prepare(P, P, P, P, 1, 1, 10, 100, _lib.POOL_SUM, 0, 0, P, P, 0, P)
+    assert rc == -1 and b"null pointer" in lib.tdfo_last_error()
+    # update: keys_in_scratch out of range
+    opt = _lib.OptimizerArgs(_lib.OPT_SGD, 0.1, 1e-8, 0.0, 0.9, 0.999, 1)
+    rc = lib.tdfo_embedding_backward_update(P, _lib.F32, 100, 16, P, P, P, 16, P, P, P, P, P, P, 1, 1, 10, _lib.POOL_SUM,
+                                            ctypes.byref(opt), 3, P, P, 0, P)
+    assert rc == -1 and b"keys_in_scratch" in lib.tdfo_last_error()
+    assert _lib.SCRATCH_PREPARED == 2
