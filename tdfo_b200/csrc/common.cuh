@@ -76,15 +76,6 @@ __device__ __forceinline__ void st_128(void* p, uint4 v) {
     *reinterpret_cast<uint4*>(p) = v;
 }
 
-// Ask L2 to fetch `bytes` (multiple of 16) starting at p; costs no registers and no shared
-// memory, so a warp can have a whole tile of rows on its way while it works on the current one.
-__device__ __forceinline__ void prefetch_l2_bulk(const void* p, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void prefetch_l2(const void* p) {
-    asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
-}
-
 __device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t* p) {
     uint64_t v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
