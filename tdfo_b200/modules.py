@@ -112,6 +112,25 @@ class _LookupFn(torch.autograd.Function):
         return None, None, None, None, None, None
 
 
+class _DenseLookupFn(torch.autograd.Function):
+    """Dense-gradient mode (`use_dense_gradients()`): the tables are ordinary trainable parameters and
+    backward returns a dense [rows, D] gradient per table group, as the unsharded torchrec modules do
+    in the reference's DDP branch (torchrec/train.py:255-260).  The gradient is built
+    by the same sort / unique / segmented-reduce kernels: "update" a zero buffer with SGD at lr = -1."""
+
+    @staticmethod
+    def forward(ctx, module, values, offsets, B, psw, *weights):
+        ctx.module, ctx.B, ctx.psw = module, B, psw
+        ctx.save_for_backward(values, offsets)
+        return module._forward_impl(values, offsets, B, psw)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        values, offsets = ctx.saved_tensors
+        grads = ctx.module._dense_backward(grad_out.contiguous(), values, offsets, ctx.B, ctx.psw)
+        return (None, None, None, None, None) + tuple(grads)
+
+
 class _FusedEmbeddingBase(nn.Module):
     _state_prefix = "embedding_bags"
 
@@ -200,6 +219,42 @@ class _FusedEmbeddingBase(nn.Module):
     @property
     def fused_optimizer(self) -> FusedOptimizer:
         return self._fused
+
+    def use_dense_gradients(self) -> "_FusedEmbeddingBase":
+        """Leave the fused mode: tables become trainable parameters with dense `.grad`, for callers that
+        wrap the model in DDP and hand `model.parameters()` to a dense optimizer (the reference's
+        non-model-parallel branch, torchrec/train.py:255-260).  O(rows x D) per step, like the reference."""
+        for g in self._groups:
+            if g.dtype != torch.float32:
+                raise ValueError("dense gradients need fp32 tables")
+            p = getattr(self, g.param_name)
+            p.requires_grad_(True)
+            if hasattr(p, "_in_backward_optimizers"):
+                del p._in_backward_optimizers
+        self._fused = None
+        self._dense = True
+        return self
+
+    def _dense_backward(self, grad_out, values, offsets, B, psw):
+        minus_one = ops.make_optimizer_args(_lib.OPT_SGD, -1.0)             # w <- 0 - (-1) * g
+        grads = []
+        for g in self._groups:
+            F = len(g.features)
+            dense = torch.zeros((g.total_rows, g.D), dtype=torch.float32, device=values.device)
+            grp = ops.TableGroup(weights=dense, feat_row_base=getattr(self, f"_group{g.index}_row_base"),
+                                 feat_rows=getattr(self, f"_group{g.index}_rows"),
+                                 feat_out_col=getattr(self, f"_group{g.index}_out_col"),
+                                 out_stride=g.D if self._sequence else self._total_D, err_flag=self._err_flag)
+            off = offsets[g.f0 * B:(g.f0 + F) * B + 1]
+            if len(self._groups) == 1:
+                ops.embedding_backward_update(grp, grad_out, values, off, B, g.pooling, minus_one,
+                                              per_sample_weights=psw)
+            else:
+                lo, hi = self._group_bounds(offsets, g, B)
+                ops.embedding_backward_update(grp, grad_out, values[lo:hi], off - lo, B, g.pooling, minus_one,
+                                              per_sample_weights=None if psw is None else psw[lo:hi])
+            grads.append(dense)
+        return grads
 
     def _state_for(self, g: _Group):
         """Optimizer state tensors of a group, allocated on first use next to the weights."""
@@ -295,7 +350,9 @@ class _FusedEmbeddingBase(nn.Module):
             raise RuntimeError("tdfo_b200 embedding modules run on CUDA only (no CPU path): "
                                "move the module and the KeyedJaggedTensor to a cuda device")
         psw = kjt.weights_or_none() if getattr(self, "_is_weighted", False) else None
-        if self.training and torch.is_grad_enabled():
+        if getattr(self, "_dense", False) and torch.is_grad_enabled():
+            out = _DenseLookupFn.apply(self, values, offsets, B, psw, *[getattr(self, g.param_name) for g in self._groups])
+        elif self.training and torch.is_grad_enabled():
             if self._anchor is None or self._anchor.device != values.device:
                 self._anchor = torch.zeros(1, device=values.device, requires_grad=True)
             out = _LookupFn.apply(self._anchor, self, values, offsets, B, psw)

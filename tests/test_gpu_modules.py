@@ -268,3 +268,48 @@ def test_bounds_check_modes(t):
     ebc.bounds_check_mode = t.BoundsCheckMode.FATAL
     with pytest.raises(IndexError):
         ebc(kjt)
+
+
+def test_dense_gradient_mode_matches_torch_modules_under_a_dense_optimizer(t):
+    """The reference's non-model-parallel branch (torchrec/train.py:255-260): the tables are
+    plain parameters, backward yields dense gradients, `optim.Adam(model.parameters())` updates them.
+    Checked against nn.Embedding / nn.EmbeddingBag + the same Adam: gradients to 1e-5, two steps."""
+    rng = np.random.default_rng(12)
+    B, T, V, D = 16, 7, 50, 16
+    # ---- EmbeddingCollection vs nn.Embedding (the Bert4Rec item table pattern)
+    ec = t.EmbeddingCollection([t.EmbeddingConfig(num_embeddings=V, embedding_dim=D, name="item",
+                                                  feature_names=["item"])], device=torch.device("cuda"))
+    ec.use_dense_gradients()
+    assert [n for n, _ in t.in_backward_optimizer_filter(ec.named_parameters())] == [n for n, _ in ec.named_parameters()]
+    ref = torch.nn.Embedding(V, D).cuda()
+    with torch.no_grad():
+        ref.weight.copy_(ec.state_dict()["embeddings.item.weight"])
+    opt_a = torch.optim.Adam(ec.parameters(), lr=0.05, weight_decay=1e-4)
+    opt_b = torch.optim.Adam(ref.parameters(), lr=0.05, weight_decay=1e-4)
+    for step in range(2):
+        seqs = torch.from_numpy(rng.integers(0, V, size=(B, T))).cuda()
+        kjt = t.KeyedJaggedTensor.from_lengths_sync(["item"], seqs.reshape(-1),
+                                                    torch.full((B,), T, dtype=torch.int32)).to("cuda")
+        proj = torch.from_numpy(rng.normal(size=(B * T, D)).astype(np.float32)).cuda()
+        opt_a.zero_grad(); opt_b.zero_grad()
+        (ec(kjt)["item"].values() * proj).sum().backward()
+        (ref(seqs.reshape(-1)) * proj).sum().backward()
+        ga = next(ec.parameters()).grad
+        torch.testing.assert_close(ga, ref.weight.grad, rtol=1e-5, atol=1e-6)
+        opt_a.step(); opt_b.step()
+        torch.testing.assert_close(ec.state_dict()["embeddings.item.weight"], ref.weight.detach(), rtol=1e-5, atol=1e-6)
+    # ---- EmbeddingBagCollection (MEAN pooling, ragged bags) vs nn.EmbeddingBag
+    ebc = t.EmbeddingBagCollection([t.EmbeddingBagConfig(num_embeddings=V, embedding_dim=D, name="g", feature_names=["g"],
+                                                         pooling=t.PoolingType.MEAN)], device=torch.device("cuda"))
+    ebc.use_dense_gradients()
+    bag = torch.nn.EmbeddingBag(V, D, mode="mean", include_last_offset=True).cuda()
+    with torch.no_grad():
+        bag.weight.copy_(ebc.state_dict()["embedding_bags.g.weight"])
+    lengths = torch.from_numpy(rng.integers(0, 6, size=B).astype(np.int32))
+    ids = torch.from_numpy(rng.integers(0, V, size=int(lengths.sum())))
+    kjt = t.KeyedJaggedTensor.from_lengths_sync(["g"], ids, lengths).to("cuda")
+    proj = torch.from_numpy(rng.normal(size=(B, D)).astype(np.float32)).cuda()
+    (ebc(kjt).values() * proj).sum().backward()
+    (bag(ids.cuda(), kjt.offsets()) * proj).sum().backward()
+    torch.testing.assert_close(next(ebc.parameters()).grad, bag.weight.grad, rtol=1e-5, atol=1e-6)
+    ebc.check_errors()
