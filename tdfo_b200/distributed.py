@@ -1147,7 +1147,8 @@ class DistributedModelParallel(nn.Module):
 
     def __init__(self, module: nn.Module, device: Optional[torch.device] = None,
                  sharders: Optional[List[_Sharder]] = None, plan: Optional[Dict[str, ParameterSharding]] = None,
-                 init_data_parallel: bool = True, process_group: Optional[dist.ProcessGroup] = None):
+                 init_data_parallel: bool = True, process_group: Optional[dist.ProcessGroup] = None,
+                 kernel_ops=None):
         super().__init__()
         from .modules import EmbeddingBagCollection, EmbeddingCollection
         from .optim import CombinedFusedOptimizer
@@ -1156,6 +1157,14 @@ class DistributedModelParallel(nn.Module):
         by_kind = {s.module_kind: s for s in (sharders or [])}
         fused: List[FusedOptimizer] = []
 
+        def adopt(old: nn.Module, new: nn.Module):
+            """The sharded module starts from the tables the unsharded one holds (every rank built the same
+            model, e.g. from one seed or one checkpoint), each rank keeping its rows / columns.  Modules
+            built on the meta device have nothing to hand over."""
+            sd = old.state_dict()
+            if sd and not any(v.is_meta for v in sd.values()):
+                new.load_state_dict(sd)
+
         def convert(parent: nn.Module):
             for name, child in list(parent.named_children()):
                 if isinstance(child, EmbeddingBagCollection):
@@ -1163,7 +1172,8 @@ class DistributedModelParallel(nn.Module):
                     if world > 1:
                         tables = child.embedding_bag_configs()
                         p = plan or balanced_table_wise_plan(tables, world)
-                        new = ShardedEmbeddingBagCollection(tables, p, device, process_group)
+                        new = ShardedEmbeddingBagCollection(tables, p, device, process_group, kernel_ops=kernel_ops)
+                        adopt(child, new)
                         setattr(parent, name, new)
                         child = new
                     else:
@@ -1174,7 +1184,8 @@ class DistributedModelParallel(nn.Module):
                     if world > 1:
                         tables = child.embedding_configs()
                         p = plan or balanced_table_wise_plan(tables, world)
-                        new = ShardedEmbeddingCollection(tables, p, device, process_group)
+                        new = ShardedEmbeddingCollection(tables, p, device, process_group, kernel_ops=kernel_ops)
+                        adopt(child, new)
                         setattr(parent, name, new)
                         child = new
                     else:
@@ -1191,6 +1202,16 @@ class DistributedModelParallel(nn.Module):
         dense = [p for p in module.parameters() if p.requires_grad]
         if world > 1 and init_data_parallel and dense:
             from torch.nn.parallel import DistributedDataParallel as DDP
+            # DDP broadcasts every parameter and buffer of the module from rank 0 when it is built and keeps
+            # buffers in sync afterwards: the shards (different on every rank, updated inside backward) and
+            # the routing buffers of the sharded modules must stay out of that
+            ignore = []
+            for mod_name, mod in module.named_modules():
+                if isinstance(mod, ShardedEmbeddingBagCollection):
+                    pre = mod_name + "." if mod_name else ""
+                    ignore += [pre + n for n, _ in mod.named_parameters(recurse=False)]
+                    ignore += [pre + n for n, _ in mod.named_buffers(recurse=False)]
+            DDP._set_params_and_buffers_to_ignore_for_model(module, ignore)
             module = DDP(module, device_ids=[device.index] if device.type == "cuda" else None,
                          process_group=process_group)
         self.module = module

@@ -1,0 +1,104 @@
+"""`DistributedModelParallel(module, device, sharders=[...])` (torchrec/train.py:241-247) on two gloo ranks:
+the EmbeddingBagCollection inside the model is replaced by its sharded form (table-wise + column-wise +
+row-wise plan), which ADOPTS the tables the unsharded module held; dense parameters go under DDP; the
+sharder's fused_params reach the fused optimizer; one training step equals the unsharded oracle."""
+import os
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+import torch.nn as nn
+
+import oracle as orc
+from test_sharded_gloo import B, D, W, free_port, global_batch, local_batch, make_tables, reference_update
+
+
+class Model(nn.Module):
+    def __init__(self, t, tables):
+        super().__init__()
+        self.sparse = t.EmbeddingBagCollection(tables, device=torch.device("cpu"))
+        self.over = nn.Linear(len(tables) * D, 1)
+
+    def forward(self, kjt):
+        return self.over(self.sparse(kjt).values())
+
+
+def run_rank(rank, port, results):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=W)
+    try:
+        import tdfo_b200 as t
+        from tdfo_b200 import distributed as td
+        from oracle_ops import OracleKernelOps
+        tables = make_tables(t)
+        rows = [c.num_embeddings for c in tables]
+        torch.manual_seed(1234)                               # every rank builds the same model
+        model = Model(t, tables)
+        held = {k: v.clone() for k, v in model.sparse.state_dict().items()}
+        plan = {"t0": td.column_wise([1, 0]), "t1": td.row_wise(), "t2": td.table_wise(0), "t3": td.table_wise(1),
+                "t4": td.column_wise([0, 1])}
+        fused_params = {"optimizer": t.EmbOptimType.EXACT_SGD, "learning_rate": 0.05}
+        dmp = t.DistributedModelParallel(model, device=torch.device("cpu"),
+                                         sharders=[t.EmbeddingBagCollectionSharder(fused_params)], plan=plan,
+                                         kernel_ops=OracleKernelOps())
+        inner = dmp.module.module if isinstance(dmp.module, nn.parallel.DistributedDataParallel) else dmp.module
+        assert isinstance(dmp.module, nn.parallel.DistributedDataParallel)          # dense part is data-parallel
+        assert isinstance(inner.sparse, td.ShardedEmbeddingBagCollection)
+        # the tables came along, split by the plan
+        full = inner.sparse.full_state_dict()
+        for k, v in held.items():
+            torch.testing.assert_close(full[k], v, rtol=0, atol=0)
+        # optimizer plumbing of torchrec/train.py:248-254
+        dense_named = dict(t.in_backward_optimizer_filter(dmp.named_parameters()))
+        assert sorted(n.split(".")[-2] + "." + n.split(".")[-1] for n in dense_named) == ["over.bias", "over.weight"]
+        dense_opt = t.KeyedOptimizerWrapper(dense_named, lambda params: torch.optim.SGD(params, lr=0.1))
+        optimizer = t.CombinedOptimizer([dmp.fused_optimizer, dense_opt])
+        assert dmp.fused_optimizer.param_groups[0]["lr"] == 0.05
+
+        dmp.train()
+        lengths, idx, _ = local_batch(rank, rows)
+        kjt = t.KeyedJaggedTensor.from_lengths_sync([f"f{i}" for i in range(len(rows))], torch.from_numpy(idx),
+                                                    torch.from_numpy(lengths))
+        w_over, b_over = inner.over.weight.detach().clone(), inner.over.bias.detach().clone()
+        out = dmp(kjt)
+        optimizer.zero_grad()
+        out.sum().backward()
+        optimizer.step()
+
+        # ---- unsharded restatement: pooled rows, then d(sum)/d(pooled) = over.weight for every sample
+        w_full = np.concatenate([held[f"embedding_bags.t{i}.weight"].numpy() for i in range(len(rows))])
+        base = np.concatenate([[0], np.cumsum(rows)[:-1]]).astype(np.int64)
+        col = (np.arange(len(rows)) * D).astype(np.int64)
+        pooled, _ = orc.embedding_forward(w_full, D, idx, orc.complete_cumsum(lengths), None, base, rows, col, len(rows), B,
+                                          orc.POOL_SUM)
+        np.testing.assert_allclose(out.detach().numpy(), pooled @ w_over.numpy().T + b_over.numpy(), rtol=1e-5, atol=1e-5)
+        g_len, g_idx, _ = global_batch(rows)
+        g_grad = np.tile(w_over.numpy(), (W * B, 1)).astype(np.float32)
+        w_ref = reference_update(w_full, rows, plan, td, g_len, g_idx, g_grad, orc.OPT_SGD, lr=0.05)
+        after = inner.sparse.full_state_dict()
+        for i, r_ in enumerate(rows):
+            np.testing.assert_allclose(after[f"embedding_bags.t{i}.weight"].numpy(), w_ref[base[i]:base[i] + r_],
+                                       rtol=1e-5, atol=1e-6, err_msg=f"t{i}")
+        assert not torch.equal(inner.over.weight.detach(), w_over)                   # the dense half stepped too
+        results[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+def test_dmp_shards_adopts_tables_and_trains_world2():
+    port = free_port()
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        results = mgr.dict()
+        procs = [ctx.Process(target=run_rank, args=(r, port, results)) for r in range(W)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=240)
+        for p in procs:
+            if p.is_alive():
+                p.terminate()
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        assert dict(results) == {0: "ok", 1: "ok"}
