@@ -102,3 +102,105 @@ def test_dmp_shards_adopts_tables_and_trains_world2():
                 p.terminate()
         assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
         assert dict(results) == {0: "ok", 1: "ok"}
+
+
+# --------------------------------------------------------------------------- the reference's own shape:
+# one item table in an EmbeddingCollection, sharded by DMP with fused ADAM (torchrec/train.py:235-254)
+V2, T2, B2 = 40, 5, 6
+
+
+class TinyBert(nn.Module):
+    def __init__(self, t):
+        super().__init__()
+        self.embed_collection = t.EmbeddingCollection(
+            tables=[t.EmbeddingConfig(name="item_embedding", embedding_dim=D, num_embeddings=V2, feature_names=["item"],
+                                      weight_init_max=1.0, weight_init_min=-1.0)], device=torch.device("cpu"))
+        self.out = nn.Linear(D, V2)
+
+    def forward(self, kjt):
+        jt = self.embed_collection(kjt)["item"]
+        return self.out(jt.values().view(-1, T2, D))          # every sequence has T2 ids here
+
+
+def run_rank_sequence(rank, port, results):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=W)
+    try:
+        import tdfo_b200 as t
+        from tdfo_b200 import distributed as td
+        from oracle_ops import OracleKernelOps
+        torch.manual_seed(77)
+        model = TinyBert(t)
+        table0 = model.embed_collection.state_dict()["embeddings.item_embedding.weight"].clone()
+        fused_params = {"optimizer": t.EmbOptimType.ADAM, "learning_rate": 3e-2, "weight_decay": 1e-4}
+        dmp = t.DistributedModelParallel(module=model, device=torch.device("cpu"),
+                                         sharders=[t.EmbeddingCollectionSharder(fused_params)],
+                                         plan={"item_embedding": td.row_wise()}, kernel_ops=OracleKernelOps())
+        inner = dmp.module.module
+        assert isinstance(inner.embed_collection, td.ShardedEmbeddingCollection)
+        dense_optimizer = t.KeyedOptimizerWrapper(dict(t.in_backward_optimizer_filter(dmp.named_parameters())),
+                                                  lambda params: torch.optim.Adam(params, lr=3e-2))
+        optimizer = t.CombinedOptimizer([dmp.fused_optimizer, dense_optimizer])
+        assert sorted(dense_optimizer.params) == ["module.module.out.bias", "module.module.out.weight"]
+        sd_key = "module.module.embed_collection.embeddings.item_embedding.weight"
+        assert dmp.state_dict()[sd_key].shape == (V2 // W, D)                   # this rank's row block
+        torch.testing.assert_close(inner.embed_collection.full_state_dict()["embeddings.item_embedding.weight"], table0,
+                                   rtol=0, atol=0)
+
+        per = [torch.from_numpy(np.random.default_rng(900 + r).integers(1, V2, size=(B2, T2))) for r in range(W)]
+        seqs = per[rank]
+        kjt = t.KeyedJaggedTensor.from_lengths_sync(keys=["item"], values=torch.cat(list(seqs), dim=0),
+                                                    lengths=torch.IntTensor([T2] * B2))
+        dmp.train()
+        w_out, b_out = inner.out.weight.detach().clone(), inner.out.bias.detach().clone()
+        logits = dmp(kjt)
+        loss = nn.CrossEntropyLoss()(logits.view(-1, V2), seqs.view(-1))
+        optimizer.zero_grad()
+        loss.backward()
+        optimizer.step()
+
+        # ---- restated without sharding: gather -> linear -> CE on every rank's batch, ADAM on the union
+        grads, ids_all = [], []
+        for r in range(W):
+            emb = table0[per[r].view(-1)].clone().requires_grad_(True)
+            l_r = nn.CrossEntropyLoss()((emb @ w_out.T + b_out).view(-1, V2), per[r].view(-1))
+            l_r.backward()
+            grads.append(emb.grad.numpy())
+            ids_all.append(per[r].view(-1).numpy())
+            if r == rank:
+                np.testing.assert_allclose(loss.item(), l_r.item(), rtol=1e-5)
+        w_ref = table0.numpy().copy()
+        m_ref, v_ref = np.zeros_like(w_ref), np.zeros_like(w_ref)
+        g_idx = np.concatenate(ids_all).astype(np.int64)
+        n = g_idx.size
+        orc.embedding_backward_update(w_ref, D, m_ref, v_ref, np.concatenate(grads).astype(np.float32), g_idx,
+                                      np.arange(0, n + 1, T2, dtype=np.int64), [0], [V2], None, 1, W * B2, orc.POOL_NONE,
+                                      orc.OptArgs(orc.OPT_ADAM, 3e-2, 1e-8, 1e-4, 0.9, 0.999, 1))
+        got = inner.embed_collection.full_state_dict()["embeddings.item_embedding.weight"].numpy()
+        np.testing.assert_allclose(got, w_ref, rtol=1e-5, atol=2e-6)
+        # DDP kept the dense half identical on both ranks
+        both = [None] * W
+        dist.all_gather_object(both, inner.out.weight.detach().numpy())
+        np.testing.assert_array_equal(both[0], both[1])
+        assert not np.array_equal(both[0], w_out.numpy())
+        results[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+def test_dmp_sequence_collection_fused_adam_world2():
+    port = free_port()
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        results = mgr.dict()
+        procs = [ctx.Process(target=run_rank_sequence, args=(r, port, results)) for r in range(W)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=240)
+        for p in procs:
+            if p.is_alive():
+                p.terminate()
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        assert dict(results) == {0: "ok", 1: "ok"}
