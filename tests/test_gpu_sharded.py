@@ -10,7 +10,7 @@ import torch.multiprocessing as mp
 
 import oracle as orc
 from test_sharded_gloo import (B, D, W, free_port, global_batch, local_batch, make_tables, reference_update,
-                               run_rank_sequence)
+                               run_rank_edges, run_rank_sequence)
 
 pytestmark = pytest.mark.gpu
 
@@ -182,6 +182,26 @@ def test_replicated_adapter_tables_stay_identical_on_2_gpus():
             p.start()
         for p in procs:
             p.join(timeout=300)
+        for p in procs:
+            if p.is_alive():
+                p.terminate()
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        assert dict(results) == {0: "ok", 1: "ok"}
+
+
+def test_empty_and_lopsided_batches_on_2_gpus():
+    """The peer-memory exchange with ranks that send nothing, steps without any id, one live feature."""
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    port = free_port()
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        results = mgr.dict()
+        procs = [ctx.Process(target=run_rank_edges, args=(r, port, results, True)) for r in range(W)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=200)
         for p in procs:
             if p.is_alive():
                 p.terminate()

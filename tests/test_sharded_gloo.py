@@ -250,3 +250,74 @@ def test_sharded_sequence_equals_unsharded_world2(plan_kind):
                 p.terminate()
         assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
         assert dict(results) == {0: "ok", 1: "ok"}
+
+
+# --------------------------------------------------------------------------- empty and lopsided batches
+def run_rank_edges(rank, port, results, cuda=False):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    if cuda:
+        torch.cuda.set_device(rank)
+        dev = torch.device("cuda", rank)
+        dist.init_process_group("nccl", rank=rank, world_size=W, device_id=dev)
+    else:
+        dev = torch.device("cpu")
+        dist.init_process_group("gloo", rank=rank, world_size=W)
+    try:
+        import tdfo_b200 as t
+        from tdfo_b200 import distributed as td
+        from oracle_ops import OracleKernelOps
+        tables = make_tables(t)
+        rows = [c.num_embeddings for c in tables]
+        F = len(rows)
+        plan = {"t0": td.column_wise([1, 0]), "t1": td.row_wise(), "t2": td.table_wise(0), "t3": td.row_wise(),
+                "t4": td.column_wise([0, 1])}
+        m = td.ShardedEmbeddingBagCollection(tables, plan, dev, kernel_ops=None if cuda else OracleKernelOps(),
+                                             init_seed=3)
+        m.set_fused_optimizer(t.EmbOptimType.EXACT_SGD, learning_rate=0.05)
+        m.train()
+        rng = np.random.default_rng(rank)
+        base = np.concatenate([[0], np.cumsum(rows)[:-1]]).astype(np.int64)
+        col = (np.arange(F) * D).astype(np.int64)
+        for case in ("one rank sends nothing", "nobody sends anything", "normal", "one feature only"):
+            lengths = rng.integers(0, 4, size=F * B).astype(np.int32)
+            if (case == "one rank sends nothing" and rank == 1) or case == "nobody sends anything":
+                lengths[:] = 0
+            if case == "one feature only":
+                lengths[B:] = 0
+            off = orc.complete_cumsum(lengths)
+            idx = np.concatenate([rng.integers(0, rows[f], size=int(off[(f + 1) * B] - off[f * B]))
+                                  for f in range(F)]).astype(np.int64)
+            kjt = t.KeyedJaggedTensor.from_lengths_sync([f"f{i}" for i in range(F)], torch.from_numpy(idx),
+                                                        torch.from_numpy(lengths)).to(dev)
+            full = m.full_state_dict()
+            w = np.concatenate([full[f"embedding_bags.t{i}.weight"].numpy() for i in range(F)])
+            out = m(kjt).values()
+            want, _ = orc.embedding_forward(w, D, idx, off, None, base, rows, col, F, B, orc.POOL_SUM)
+            np.testing.assert_allclose(out.detach().cpu().numpy(), want, rtol=1e-5, atol=1e-6, err_msg=case)
+            out.sum().backward()                                 # must not hang or fail on empty exchanges
+        if cuda:
+            torch.cuda.synchronize()
+            assert int(m._err_flag.item()) == 0
+        results[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_empty_and_lopsided_batches_world2():
+    """Ranks with no ids at all, a step where nobody has ids, a single live feature: the exchanges carry
+    zero-sized splits and the lookups zero bags (the reference's edge cases are torchrec's)."""
+    port = free_port()
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        results = mgr.dict()
+        procs = [ctx.Process(target=run_rank_edges, args=(r, port, results)) for r in range(W)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=240)
+        for p in procs:
+            if p.is_alive():
+                p.terminate()
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        assert dict(results) == {0: "ok", 1: "ok"}
