@@ -122,7 +122,10 @@ def cpu_arm(steps: int, warmup: int, sample_batch: int, rows: int | None = None)
     if need > 0.5 * avail:                               # keep tables <= half of free host RAM
         rows = max(1000, int(0.5 * avail / (F * D * 4)))
     B = sample_batch
-    cores = os.cpu_count() or 1
+    # all the host threads this process may use, whatever OMP_NUM_THREADS the launcher exported
+    # (torchrun sets it to 1); `cores` reports the OpenMP thread count actually in effect
+    avail_cpus = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    cores = orc.set_num_threads(avail_cpus)
     w = np.empty((F * rows, D), dtype=np.float32)
     w.fill(0.01)
     h = np.zeros(F * rows, dtype=np.float32)

@@ -54,6 +54,13 @@ def lib() -> ctypes.CDLL:
     return _lib
 
 
+def set_num_threads(n: int = 0) -> int:
+    """Use `n` OpenMP threads (0: leave as is) in the oracle; returns the thread count in effect."""
+    f = lib().orc_set_num_threads
+    f.restype = ctypes.c_int
+    return int(f(ctypes.c_int(n)))
+
+
 def _p(a):
     return None if a is None else a.ctypes.data_as(c_void_p)
 

@@ -29,6 +29,10 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
 
 #define ORC_F32 0
 #define ORC_BF16 1
@@ -433,4 +437,16 @@ void orc_jagged_1d_to_padded_dense(const int64_t* values, const int64_t* offsets
         for (int64_t t = 0; t < desired_length; ++t)
             dense[b * desired_length + t] = t < len ? values[offsets[b] + t] : padding_value;
     }
+}
+
+/* Thread control for the timed CPU baseline (bench.py): launchers such as torchrun export
+ * OMP_NUM_THREADS=1, which would silently turn the all-cores baseline into a one-core one. */
+int orc_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+    return omp_get_max_threads();
+#else
+    (void)n;
+    return 1;
+#endif
 }
