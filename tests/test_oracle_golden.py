@@ -168,3 +168,52 @@ def test_weighted_backward_matches_torch_embedding_bag():
     orc.embedding_backward_update(w2, c.D, None, None, grad, c.indices, c.offsets, c.row_base, c.rows, c.out_col,
                                   c.F, c.B, orc.POOL_MEAN, orc.OptArgs(orc.OPT_SGD, learning_rate=lr))
     np.testing.assert_allclose(w1, w2, rtol=RTOL, atol=1e-6)
+
+
+def test_forward_matches_fbgemm_reference_spmdm():
+    """FBGEMM's own CPU reference of the pooled lookup, `fbgemm::EmbeddingSpMDM_ref<float, int64, int64,
+    float>` as exported by libtorch_cpu.so (the kernel family fbgemm_gpu's CPU TBE and nn.EmbeddingBag
+    use): sum, mean (normalize_by_lengths) and per-sample-weighted sum, and the
+    sequence lookup (no_bag)."""
+    import ctypes
+    import os
+    import torch
+    from helpers import make_case
+    lib = ctypes.CDLL(os.path.join(os.path.dirname(torch.__file__), "lib", "libtorch_cpu.so"))
+    try:
+        fn = getattr(lib, "_ZN6fbgemm18EmbeddingSpMDM_refIfllfEEbllllPKT_PKT0_PKT1_PKfbPT2_bbllbbbb")
+    except AttributeError:
+        import pytest
+        pytest.skip("this libtorch does not export fbgemm::EmbeddingSpMDM_ref<float, long, long, float>")
+    i64, vp, cb = ctypes.c_int64, ctypes.c_void_p, ctypes.c_bool
+    fn.restype = cb
+    fn.argtypes = [i64, i64, i64, i64, vp, vp, vp, vp, cb, vp, cb, cb, i64, i64, cb, cb, cb, cb]
+    c = make_case(seed=77, F=3, B=20, D=24, rows=[30, 5, 64], max_len=7)
+    psw = np.random.default_rng(1).uniform(0.2, 2.0, size=c.L).astype(np.float32)
+    ptr = lambda a: None if a is None else a.ctypes.data_as(vp)
+    for mode, w in ((orc.POOL_SUM, None), (orc.POOL_MEAN, None), (orc.POOL_SUM, psw)):
+        got, oob = orc.embedding_forward(c.weights, c.D, c.indices, c.offsets, w, c.row_base, c.rows, c.out_col,
+                                         c.F, c.B, mode)
+        assert not oob
+        for f in range(c.F):
+            s, e = int(c.offsets[f * c.B]), int(c.offsets[(f + 1) * c.B])
+            table = np.ascontiguousarray(c.weights[c.row_base[f]:c.row_base[f] + c.rows[f]])
+            idx = np.ascontiguousarray(c.indices[s:e])
+            off = np.ascontiguousarray(c.offsets[f * c.B:(f + 1) * c.B + 1] - s)
+            wf = None if w is None else np.ascontiguousarray(w[s:e])
+            out = np.full((c.B, c.D), np.nan, dtype=np.float32)
+            ok = fn(c.D, c.B, e - s, int(c.rows[f]), ptr(table), ptr(idx), ptr(off), ptr(wf), mode == orc.POOL_MEAN,
+                    ptr(out), False, True, c.D, c.D, True, False, False, False)
+            assert ok
+            np.testing.assert_allclose(got[:, f * c.D:(f + 1) * c.D], out, rtol=RTOL, atol=ATOL, err_msg=f"mode {mode} f{f}")
+    seq, _ = orc.embedding_forward(c.weights, c.D, c.indices, c.offsets, None, c.row_base, c.rows, None, c.F, c.B,
+                                   orc.POOL_NONE)
+    for f in range(c.F):
+        s, e = int(c.offsets[f * c.B]), int(c.offsets[(f + 1) * c.B])
+        table = np.ascontiguousarray(c.weights[c.row_base[f]:c.row_base[f] + c.rows[f]])
+        idx = np.ascontiguousarray(c.indices[s:e])
+        out = np.full((e - s, c.D), np.nan, dtype=np.float32)
+        ok = fn(c.D, e - s, e - s, int(c.rows[f]), ptr(table), ptr(idx), None, None, False, ptr(out), False, True,
+                c.D, c.D, True, True, False, False)
+        assert ok
+        np.testing.assert_array_equal(seq[s:e], out)
