@@ -25,6 +25,7 @@ routing logic without a GPU.
 """
 from __future__ import annotations
 
+import contextlib
 import enum
 import zlib
 from dataclasses import dataclass
@@ -137,6 +138,9 @@ class CudaKernelOps:
                                   keys_in_scratch=False):
         self._ops.embedding_backward_update(group, grad_out, indices, offsets, B, pooling_mode, opt, scratch=scratch,
                                             keys_in_scratch=keys_in_scratch)
+
+    def make_peer_exchange(self, *args, **kwargs):
+        return _PeerExchange(*args, **kwargs)
 
     def embedding_backward_prepare(self, group, indices, offsets, B, pooling_mode, scratch, keys_in_scratch=False):
         self._ops.embedding_backward_prepare(group, indices, offsets, B, pooling_mode, scratch,
@@ -529,8 +533,8 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 cap_t = torch.tensor([cap], dtype=torch.int64, device=dev)
                 dist.all_reduce(cap_t, op=dist.ReduceOp.MAX, group=self._pg)
                 cap = int(cap_t.item())
-                self._peer = _PeerExchange(self._pg, dev, B, self._F_total, D, self._n_tw, n_rw, cap,
-                                           n_cw=self._n_cw, Dc=self._Dc)
+                self._peer = ops.make_peer_exchange(self._pg, dev, B, self._F_total, D, self._n_tw, n_rw, cap,
+                                                    n_cw=self._n_cw, Dc=self._Dc)
                 self._meta_cache.clear()
             peer = self._peer
             peer.barrier()                 # everyone is done reading last step's landing zones / outputs
@@ -819,8 +823,6 @@ class ShardedEmbeddingBagCollection(nn.Module):
             # Push every gradient row (column slice) into the landing buffer of its owner over NVLink, on a
             # side stream: the push is NVLink-bound and the id-only half of the backward (linearise, sort,
             # unique: latency-bound, needs no gradient) runs on the main stream meanwhile.
-            main = torch.cuda.current_stream(grad_out.device)
-            side = self._side_stream(grad_out.device)
             todo = [(name, ids_, off_) for name, have, ids_, off_ in
                     (("tw", n_tw_r, lv_tw, lo_tw), ("cw", n_cw_r) + (cw if cw else (None, None)))
                     if have and ids_.numel() > 0]
@@ -828,9 +830,13 @@ class ShardedEmbeddingBagCollection(nn.Module):
             # kernel that runs next to the NVLink stores slows down, the streaming linearise pass most.)
             for name, ids_, off_ in todo:
                 prepared[name] = self._prepared_scratch(name, ids_.numel(), grad_out.device)
-            side.wait_stream(main)                          # grad_out has been produced
-            grad_out.record_stream(side)
-            with torch.cuda.stream(side):
+            on_gpu = grad_out.is_cuda                       # (the CPU tests drive this branch with a fake exchange)
+            if on_gpu:
+                main = torch.cuda.current_stream(grad_out.device)
+                side = self._side_stream(grad_out.device)
+                side.wait_stream(main)                      # grad_out has been produced
+                grad_out.record_stream(side)
+            with (torch.cuda.stream(side) if on_gpu else contextlib.nullcontext()):
                 if n_tw_all:
                     ops.copy_feature_blocks(grad_out, None, B, D, self._peer_grad_meta(B, grad_out.device))
                     recv = self._peer.grad[: GB * n_tw_r * D]
@@ -839,11 +845,13 @@ class ShardedEmbeddingBagCollection(nn.Module):
                     recv_cw = self._peer.grad_cw[: GB * n_cw_r * Dc]
                 if n_tw_all or n_cw_all:
                     self._peer.barrier()
-                landed = torch.cuda.Event()
-                landed.record(side)
+                if on_gpu:
+                    landed = torch.cuda.Event()
+                    landed.record(side)
             for name, ids_, off_ in todo:
                 ops.embedding_backward_prepare(self._group(name, False), ids_, off_, GB, self._pooling, prepared[name])
-            main.wait_event(landed)
+            if on_gpu:
+                main.wait_event(landed)
         else:
             # the owner of a TW feature / column shard needs the gradient of every rank's samples
             if n_tw_all:
