@@ -29,6 +29,7 @@ import contextlib
 import enum
 import zlib
 from dataclasses import dataclass
+from types import SimpleNamespace
 from typing import Dict, List, Optional, Sequence
 
 import torch
@@ -212,6 +213,10 @@ class _PeerExchange:
         self.ids_ptrs = list(symm.rendezvous(self.ids_x, group).buffer_ptrs)
         self.counts_host = torch.zeros(3, dtype=torch.int64).pin_memory()     # ids: end of TW, end of CW, total
         self.counts_event = torch.cuda.Event()
+        # Landing zones of the input dist.  Zone 0 is this object's own buffers above; a second one is added
+        # only when input dists are prefetched (ensure_second_zone).
+        self._zone_args = (symm, group, device, fl_max * W * B)
+        self.zones = [self]
         self.out = [symm.empty(B * F_total * D, dtype=torch.float32, device=device) for _ in range(2)]
         self.out_hdl = [symm.rendezvous(t_, group) for t_ in self.out]
         self.out_ptrs = [torch.tensor(list(h.buffer_ptrs), dtype=torch.int64, device=device) for h in self.out_hdl]
@@ -224,21 +229,44 @@ class _PeerExchange:
             self.grad_cw_ptrs = list(symm.rendezvous(self.grad_cw, group).buffer_ptrs)
         self.step = 0
 
-    def barrier(self):
-        self.grad_hdl.barrier(channel=0)
+    def _make_zone(self):
+        """A further landing zone: lengths, offsets and ids in the owner's layout, plus the id counts the
+        backward needs on the host (same fields as zone 0 = this object)."""
+        symm, group, device, n_bags = self._zone_args
+        z = SimpleNamespace()
+        z.len_x = symm.empty(max(n_bags, 4), dtype=torch.int32, device=device)
+        z.off_x = symm.empty(n_bags + 4, dtype=torch.int64, device=device)
+        z.ids_x = symm.empty(max(self.capacity, 4), dtype=torch.int64, device=device)
+        z.len_ptrs = list(symm.rendezvous(z.len_x, group).buffer_ptrs)
+        z.off_ptrs = list(symm.rendezvous(z.off_x, group).buffer_ptrs)
+        z.ids_ptrs = list(symm.rendezvous(z.ids_x, group).buffer_ptrs)
+        z.counts_host = torch.zeros(3, dtype=torch.int64).pin_memory()     # ids: end of TW, end of CW, total
+        z.counts_event = torch.cuda.Event()
+        return z
+
+    def ensure_second_zone(self):
+        """COLLECTIVE, first call only: double-buffer the landing zones so that the input dist of the next
+        batch can run while this batch's lookup / backward still read theirs."""
+        if len(self.zones) < 2:
+            self.zones.append(self._make_zone())
+
+    def barrier(self, channel: int = 0):
+        """Channel 0: the training stream; channel 1: the stream prefetched input dists run on (two streams
+        must not share a signal pad)."""
+        self.grad_hdl.barrier(channel=channel)
 
 
 class _ShardedLookupFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, anchor, module, values, lengths, B):
-        out, saved = module._forward_impl(values, lengths, B)
+    def forward(ctx, anchor, module, values, lengths, B, dist_ctx=None):
+        out, saved = module._forward_impl(values, lengths, B, dist_ctx)
         ctx.module, ctx.saved, ctx.B = module, saved, B
         return out
 
     @staticmethod
     def backward(ctx, grad_out):
         ctx.module._backward_impl(grad_out.contiguous(), ctx.saved, ctx.B)
-        return None, None, None, None, None
+        return None, None, None, None, None, None
 
 
 class ShardedEmbeddingBagCollection(nn.Module):
@@ -391,6 +419,8 @@ class ShardedEmbeddingBagCollection(nn.Module):
         self._scratch: Dict[str, torch.Tensor] = {}
         self._emit_keys = False                      # set per forward: training with the CUDA kernel table
         self._fwd_token = 0
+        self._dist_count = 0                         # input dists issued (selects the landing zone)
+        self._prefetched = None                      # (features, ctx, event) of prefetch_input_dist
         self._track_positions = False                # sequence output: remember where every sent id came from
         self._routing: Dict[str, object] = {}
         # Table-wise output dist / gradient return through NVLink peer memory instead of NCCL
@@ -506,12 +536,13 @@ class ShardedEmbeddingBagCollection(nn.Module):
         return recv
 
     # ------------------------------------------------------------------ forward
-    def _forward_impl(self, values, lengths, B):
-        return self._pooled_lookup(self._input_dist(values, lengths, B), B)
+    def _forward_impl(self, values, lengths, B, ctx=None):
+        return self._pooled_lookup(ctx if ctx is not None else self._input_dist(values, lengths, B), B)
 
-    def _input_dist(self, values, lengths, B):
+    def _input_dist(self, values, lengths, B, channel: int = 0):
         """Route ids to the ranks that own their rows; returns the local KJT in
-        [feature][source rank][batch] layout (ids `lv`, offsets `lo`)."""
+        [feature][source rank][batch] layout (ids `lv`, offsets `lo`).  `channel` 1: called from
+        prefetch_input_dist on its own stream."""
         W, r, D, ops = self._world, self._rank, self._D, self._ops
         dev = values.device
         offsets = ops.complete_cumsum(lengths)
@@ -537,26 +568,30 @@ class ShardedEmbeddingBagCollection(nn.Module):
                                                     n_cw=self._n_cw, Dc=self._Dc)
                 self._meta_cache.clear()
             peer = self._peer
-            peer.barrier()                 # everyone is done reading last step's landing zones / outputs
+            # landing zone: always zone 0 unless input dists are being prefetched, then alternating
+            slot = self._dist_count % len(peer.zones)
+            self._dist_count += 1
+            z = peer.zones[slot]
+            peer.barrier(channel)          # everyone is done reading this zone (and last step's outputs)
             if n_tw_all:
-                ops.push_lengths(lengths, B, self._peer_meta("len_tw", B, dev))
+                ops.push_lengths(lengths, B, self._peer_meta("len_tw", B, dev, slot))
             if n_rw:
                 rl, ro, rv = ops.permute_2d(self._rw_select_perm[:n_rw], B, lengths, offsets, values, values.numel())
                 bl, bo, bv = ops.bucketize_row_wise(rl, ro, rv, self._rw_block_sizes[:n_rw], n_rw, B, W, self._err_flag)
-                ops.push_lengths(bl, B, self._peer_meta("len_rw", B, dev))
-            peer.barrier()                 # lengths have landed
-            lo_ = peer.off_x[: Fl * W * B + 1]
-            ops.complete_cumsum_into(peer.len_x[: Fl * W * B], lo_)
-            peer.counts_host.copy_(torch.stack([lo_[n_tw_r * W * B], lo_[n_own * W * B], lo_[Fl * W * B]]),
-                                   non_blocking=True)
-            peer.counts_event.record()
-            peer.barrier()                 # every owner's offsets are readable
+                ops.push_lengths(bl, B, self._peer_meta("len_rw", B, dev, slot))
+            peer.barrier(channel)          # lengths have landed
+            lo_ = z.off_x[: Fl * W * B + 1]
+            ops.complete_cumsum_into(z.len_x[: Fl * W * B], lo_)
+            z.counts_host.copy_(torch.stack([lo_[n_tw_r * W * B], lo_[n_own * W * B], lo_[Fl * W * B]]),
+                                non_blocking=True)
+            z.counts_event.record()
+            peer.barrier(channel)          # every owner's offsets are readable
             if n_tw_all:
-                ops.push_ids(values, offsets, B, self._peer_meta("ids_tw", B, dev), peer.capacity, self._err_flag)
+                ops.push_ids(values, offsets, B, self._peer_meta("ids_tw", B, dev, slot), peer.capacity, self._err_flag)
             if n_rw:
-                ops.push_ids(bv, bo, B, self._peer_meta("ids_rw", B, dev), peer.capacity, self._err_flag)
-            peer.barrier()                 # ids have landed
-            lv = peer.ids_x
+                ops.push_ids(bv, bo, B, self._peer_meta("ids_rw", B, dev, slot), peer.capacity, self._err_flag)
+            peer.barrier(channel)          # ids have landed
+            lv = z.ids_x
             tw_total = cw_total = None     # known on the host only later (counts_event)
         else:
             # ---- input dist: per-destination blocks  [tw features of d | rw bucket d]
@@ -646,7 +681,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 lo_ = torch.zeros(1, dtype=torch.int64, device=dev)
                 lv = recv_values
         return dict(lv=lv, lo=lo_, tw_total=tw_total, cw_total=cw_total, n_tw_r=n_tw_r, n_cw_r=n_cw_r, peer=peer,
-                    dev=dev)
+                    dev=dev, slot=slot if peer is not None else 0)
 
     def _pooled_lookup(self, c, B):
         W, r, D, ops = self._world, self._rank, self._D, self._ops
@@ -683,7 +718,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
                                       rw_out)
                 out3[:, self._rw_feats, :] = self._exchange_partial_sums(rw_out, B, n_rw)
             return out, dict(peer=True, lo=lo_, n_tw_r=n_tw_r, n_cw_r=n_cw_r, GB=GB, token=self._fwd_token,
-                             fused=False)
+                             fused=False, slot=c["slot"])
 
         out = torch.empty((B, self._F_total * D), dtype=torch.float32, device=dev)
         out3 = out.view(B, self._F_total, D)
@@ -736,13 +771,13 @@ class ShardedEmbeddingBagCollection(nn.Module):
             acc += parts[s_]
         return acc
 
-    def _peer_meta(self, kind: str, B: int, device) -> torch.Tensor:
-        """Push tables for the peer-memory input dist (cached per batch size)."""
-        key = (B, kind, str(device))
+    def _peer_meta(self, kind: str, B: int, device, slot: int = 0) -> torch.Tensor:
+        """Push tables for the peer-memory input dist (cached per batch size and landing zone)."""
+        key = (B, kind, str(device), slot)
         m = self._meta_cache.get(key)
         if m is not None:
             return m
-        W, r, n_rw, p = self._world, self._rank, self._n_rw, self._peer
+        W, r, n_rw, p = self._world, self._rank, self._n_rw, self._peer.zones[slot]
         rows: List[List[int]] = []
         if kind in ("len_tw", "ids_tw"):
             # whole-table slots, then the column-shard slots of each owner (a column-wise feature is
@@ -806,13 +841,13 @@ class ShardedEmbeddingBagCollection(nn.Module):
             if stale:
                 raise RuntimeError("tdfo_b200: with peer-memory exchange, backward must run before the next forward "
                                    "(the received ids live in the shared landing buffers)")
-            peer = self._peer
-            peer.counts_event.synchronize()                 # counts were copied during the forward: no stall
-            tw_total, cw_total, total = (int(x) for x in peer.counts_host.tolist())
+            z = self._peer.zones[saved["slot"]]
+            z.counts_event.synchronize()                    # counts were copied during the forward: no stall
+            tw_total, cw_total, total = (int(x) for x in z.counts_host.tolist())
             lo_ = saved["lo"]
-            lv_tw, lo_tw = peer.ids_x[:tw_total], lo_[: n_tw_r * GB + 1]
-            cw = (peer.ids_x[tw_total:cw_total], lo_[n_tw_r * GB: n_own * GB + 1] - tw_total) if n_cw_r else None
-            rw = (peer.ids_x[cw_total:total], lo_[n_own * GB: Fl * GB + 1] - cw_total) if n_rw else None
+            lv_tw, lo_tw = z.ids_x[:tw_total], lo_[: n_tw_r * GB + 1]
+            cw = (z.ids_x[tw_total:cw_total], lo_[n_tw_r * GB: n_own * GB + 1] - tw_total) if n_cw_r else None
+            rw = (z.ids_x[cw_total:total], lo_[n_own * GB: Fl * GB + 1] - cw_total) if n_rw else None
             fused = False
         else:
             lv_tw, lo_tw, cw, rw = saved["lv"], saved["lo"][: n_tw_r * GB + 1], saved["cw"], saved["rw"]
@@ -885,19 +920,75 @@ class ShardedEmbeddingBagCollection(nn.Module):
             ops.embedding_backward_update(self._group("rw", True), full, rw_vals, rw_off, GB, _lib.POOL_SUM, opt,
                                           scratch=sc, keys_in_scratch=sc is not None and rw_vals.numel() > 0)
 
-    def forward(self, features: KeyedJaggedTensor) -> KeyedTensor:
+    def _in_module_order(self, features: KeyedJaggedTensor) -> KeyedJaggedTensor:
         if list(features.keys()) != self._feature_names:
             keys = list(features.keys())
             features = features.permute([keys.index(k) for k in self._feature_names])
+        return features
+
+    def prefetch_input_dist(self, features: KeyedJaggedTensor) -> None:
+        """COLLECTIVE.  Start the input dist (lengths / ids exchange) of a batch that a later
+        `forward(features)` -- the same KeyedJaggedTensor object -- will consume, so that it runs next to
+        the backward of the batch in flight (the sparse-dist stage of torchrec's train
+        pipelines [UPSTREAM]):
+
+            out = module(kjt_i); module.prefetch_input_dist(kjt_next); loss(out).backward()
+
+        On CUDA it is enqueued on its own stream (ordered after everything already enqueued on the current
+        one); with the peer-memory exchange the landing zones are double-buffered from the first call on
+        and its barriers use their own signal-pad channel.  Every rank must call it for the same steps.
+        Status: checked on CPU ranks (gloo all-to-all path and the fake peer memory of tests/), not yet
+        timed on GPUs."""
+        if self._track_positions:
+            raise NotImplementedError("prefetch_input_dist is not available for ShardedEmbeddingCollection")
+        if self._prefetched is not None:
+            raise RuntimeError("tdfo_b200: one input dist is already prefetched; run its forward first")
+        feats = self._in_module_order(features)
+        values, lengths, B = feats.values(), feats.lengths(), feats.stride()
+        if self._use_peer and self._peer is not None and self._peer.B == B:
+            self._peer.ensure_second_zone()
+        ev = None
+        if values.is_cuda:
+            main = torch.cuda.current_stream(values.device)
+            side = getattr(self, "_dist_stream", None)
+            if side is None or side.device != values.device:
+                side = self._dist_stream = torch.cuda.Stream(device=values.device)
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                ctx = self._input_dist(values, lengths, B, channel=1)
+                ev = torch.cuda.Event()
+                ev.record(side)
+        else:
+            ctx = self._input_dist(values, lengths, B, channel=1)
+        self._prefetched = (features, ctx, ev)
+
+    def _take_prefetched(self, features: KeyedJaggedTensor):
+        if self._prefetched is None:
+            return None
+        src, ctx, ev = self._prefetched
+        if src is not features:
+            raise RuntimeError("tdfo_b200: forward() got another batch than the one whose input dist was prefetched")
+        self._prefetched = None
+        if ev is not None:
+            cur = torch.cuda.current_stream(ctx["dev"])
+            cur.wait_event(ev)
+            for v in ctx.values():                       # tensors produced on the prefetch stream
+                if isinstance(v, torch.Tensor) and v.is_cuda:
+                    v.record_stream(cur)
+        return ctx
+
+    def forward(self, features: KeyedJaggedTensor) -> KeyedTensor:
+        dist_ctx = self._take_prefetched(features)
+        features = self._in_module_order(features)
         values, lengths, B = features.values(), features.lengths(), features.stride()
         if self.training and torch.is_grad_enabled():
             if self._anchor is None or self._anchor.device != values.device:
                 self._anchor = torch.zeros(1, device=values.device, requires_grad=True)
             self._emit_keys = isinstance(self._ops, CudaKernelOps)
-            out = _ShardedLookupFn.apply(self._anchor, self, values, lengths, B)
+            out = _ShardedLookupFn.apply(self._anchor, self, values, lengths, B, dist_ctx)
         else:
             self._emit_keys = False
-            out, _ = self._forward_impl(values, lengths, B)
+            out, _ = self._forward_impl(values, lengths, B, dist_ctx)
         return KeyedTensor(self._feature_names, [self._D] * self._F_total, out)
 
     # ------------------------------------------------------------------ checkpoints (SURVEY 8f N4)

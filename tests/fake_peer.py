@@ -68,11 +68,6 @@ class _FakeEvent:
         pass
 
 
-class _Handle:
-    def __init__(self, ptrs):
-        self.buffer_ptrs = ptrs
-
-
 class FakePeerExchange:
     """Same buffers, in the same order, as tdfo_b200.distributed._PeerExchange."""
 
@@ -80,15 +75,13 @@ class FakePeerExchange:
         W = len(n_tw)
         n_cw = n_cw if n_cw is not None else [0] * W
         self.B, self.capacity, self.step, self._pg = B, int(ids_capacity), 0, pg
+        self._mem = mem
         fl_max = max(a + b for a, b in zip(n_tw, n_cw)) + n_rw
-        self.len_x, k = mem.empty(max(fl_max * W * B, 4), torch.int32)
-        self.len_ptrs = mem.ptrs(k)
-        self.off_x, k = mem.empty(fl_max * W * B + 4, torch.int64)
-        self.off_ptrs = mem.ptrs(k)
-        self.ids_x, k = mem.empty(max(self.capacity, 4), torch.int64)
-        self.ids_ptrs = mem.ptrs(k)
-        self.counts_host = torch.zeros(3, dtype=torch.int64)
-        self.counts_event = _FakeEvent()
+        self._n_bags = fl_max * W * B
+        z0 = self._make_zone()                              # zone 0 is the exchange object itself, as in the product
+        for k_, v_ in vars(z0).items():
+            setattr(self, k_, v_)
+        self.zones = [self]
         self.out, self.out_ptrs = [], []
         for _ in range(2):
             t_, k = mem.empty(B * F_total * D, torch.float32)
@@ -102,7 +95,25 @@ class FakePeerExchange:
             self.grad_cw_ptrs = mem.ptrs(k)
         dist.barrier(group=pg)                              # every rank's files exist
 
-    def barrier(self):
+    def _make_zone(self):
+        from types import SimpleNamespace
+        mem, z = self._mem, SimpleNamespace()
+        z.len_x, k = mem.empty(max(self._n_bags, 4), torch.int32)
+        z.len_ptrs = mem.ptrs(k)
+        z.off_x, k = mem.empty(self._n_bags + 4, torch.int64)
+        z.off_ptrs = mem.ptrs(k)
+        z.ids_x, k = mem.empty(max(self.capacity, 4), torch.int64)
+        z.ids_ptrs = mem.ptrs(k)
+        z.counts_host = torch.zeros(3, dtype=torch.int64)
+        z.counts_event = _FakeEvent()
+        return z
+
+    def ensure_second_zone(self):
+        if len(self.zones) < 2:
+            self.zones.append(self._make_zone())
+            dist.barrier(group=self._pg)                    # the new files exist everywhere
+
+    def barrier(self, channel: int = 0):
         dist.barrier(group=self._pg)
 
 

@@ -39,7 +39,7 @@ def batch(rank, step, ROWS):
     return lengths, idx.astype(np.int64), rng.normal(size=(B4, F * D4)).astype(np.float32)
 
 
-def run_rank(rank, port, tag, case, results):
+def run_rank(rank, port, tag, case, results, prefetch=False):
     W4, ROWS = CASES[case]["W"], CASES[case]["rows"]
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -72,10 +72,19 @@ def run_rank(rank, port, tag, case, results):
         base = np.concatenate([[0], np.cumsum(ROWS)[:-1]]).astype(np.int64)
         col = (np.arange(F) * D4).astype(np.int64)
         keys = [f"f{i}" for i in range(F)]
-        for step in range(2):
+        mk = lambda b_: t.KeyedJaggedTensor.from_lengths_sync(keys, torch.from_numpy(b_[1]), torch.from_numpy(b_[0]))
+        n_steps = 4 if prefetch else 2
+        nxt = None
+        for step in range(n_steps):
             lengths, idx, grad = batch(rank, step, ROWS)
-            kjt = t.KeyedJaggedTensor.from_lengths_sync(keys, torch.from_numpy(idx), torch.from_numpy(lengths))
+            kjt = nxt if nxt is not None else mk((lengths, idx))
             out = m(kjt).values()
+            nxt = None
+            if prefetch and step + 1 < n_steps:
+                # the next batch's exchange is issued before this batch's backward (double-buffered landing zones)
+                nxt = mk(batch(rank, step + 1, ROWS))
+                m.prefetch_input_dist(nxt)
+                assert len(m._peer.zones) == 2
             want, _ = orc.embedding_forward(w_ref, D4, idx, orc.complete_cumsum(lengths), None, base, ROWS, col, F, B4,
                                             orc.POOL_SUM)
             np.testing.assert_allclose(out.detach().numpy(), want, rtol=1e-5, atol=1e-6, err_msg=f"step {step}")
@@ -101,15 +110,17 @@ def run_rank(rank, port, tag, case, results):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("case", list(CASES))
-def test_peer_memory_layout_beyond_two_ranks(case):
+@pytest.mark.parametrize("case,prefetch", [("w4", False), ("w8_bench_plan", False), ("w4", True)])
+def test_peer_memory_layout_beyond_two_ranks(case, prefetch):
+    """prefetch=True: every step's input dist is issued through prefetch_input_dist before the previous
+    backward, alternating between two landing zones."""
     W4 = CASES[case]["W"]
     port = free_port()
     tag = "tdfo_fake_" + uuid.uuid4().hex[:8]
     ctx = mp.get_context("spawn")
     with ctx.Manager() as mgr:
         results = mgr.dict()
-        procs = [ctx.Process(target=run_rank, args=(r, port, tag, case, results)) for r in range(W4)]
+        procs = [ctx.Process(target=run_rank, args=(r, port, tag, case, results, prefetch)) for r in range(W4)]
         for p in procs:
             p.start()
         for p in procs:

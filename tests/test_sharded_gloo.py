@@ -253,7 +253,7 @@ def test_sharded_sequence_equals_unsharded_world2(plan_kind):
 
 
 # --------------------------------------------------------------------------- empty and lopsided batches
-def run_rank_edges(rank, port, results, cuda=False):
+def run_rank_edges(rank, port, results, cuda=False, prefetch=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     if cuda:
@@ -279,7 +279,9 @@ def run_rank_edges(rank, port, results, cuda=False):
         rng = np.random.default_rng(rank)
         base = np.concatenate([[0], np.cumsum(rows)[:-1]]).astype(np.int64)
         col = (np.arange(F) * D).astype(np.int64)
-        for case in ("one rank sends nothing", "nobody sends anything", "normal", "one feature only"):
+        cases = ("one rank sends nothing", "nobody sends anything", "normal", "one feature only")
+
+        def make(case):
             lengths = rng.integers(0, 4, size=F * B).astype(np.int32)
             if (case == "one rank sends nothing" and rank == 1) or case == "nobody sends anything":
                 lengths[:] = 0
@@ -290,9 +292,20 @@ def run_rank_edges(rank, port, results, cuda=False):
                                   for f in range(F)]).astype(np.int64)
             kjt = t.KeyedJaggedTensor.from_lengths_sync([f"f{i}" for i in range(F)], torch.from_numpy(idx),
                                                         torch.from_numpy(lengths)).to(dev)
+            return lengths, off, idx, kjt
+
+        nxt = make(cases[0])
+        if prefetch:
+            m.prefetch_input_dist(nxt[3])
+        for ci, case in enumerate(cases):
+            lengths, off, idx, kjt = nxt
             full = m.full_state_dict()
             w = np.concatenate([full[f"embedding_bags.t{i}.weight"].numpy() for i in range(F)])
             out = m(kjt).values()
+            if ci + 1 < len(cases):
+                nxt = make(cases[ci + 1])
+                if prefetch:                                     # next batch's exchange before this batch's backward
+                    m.prefetch_input_dist(nxt[3])
             want, _ = orc.embedding_forward(w, D, idx, off, None, base, rows, col, F, B, orc.POOL_SUM)
             np.testing.assert_allclose(out.detach().cpu().numpy(), want, rtol=1e-5, atol=1e-6, err_msg=case)
             out.sum().backward()                                 # must not hang or fail on empty exchanges
@@ -304,14 +317,16 @@ def run_rank_edges(rank, port, results, cuda=False):
         dist.destroy_process_group()
 
 
-def test_sharded_empty_and_lopsided_batches_world2():
+@pytest.mark.parametrize("prefetch", [False, True])
+def test_sharded_empty_and_lopsided_batches_world2(prefetch):
     """Ranks with no ids at all, a step where nobody has ids, a single live feature: the exchanges carry
-    zero-sized splits and the lookups zero bags (the reference's edge cases are torchrec's)."""
+    zero-sized splits and the lookups zero bags (the reference's edge cases are torchrec's).
+    prefetch=True issues every input dist through prefetch_input_dist, one step ahead."""
     port = free_port()
     ctx = mp.get_context("spawn")
     with ctx.Manager() as mgr:
         results = mgr.dict()
-        procs = [ctx.Process(target=run_rank_edges, args=(r, port, results)) for r in range(W)]
+        procs = [ctx.Process(target=run_rank_edges, args=(r, port, results, False, prefetch)) for r in range(W)]
         for p in procs:
             p.start()
         for p in procs:
