@@ -17,7 +17,11 @@
  *  - No entry point allocates or frees device memory.  Kernels that need
  *    workspace take a caller-owned `scratch` pointer; the matching
  *    `*_scratch_bytes` function (pure host arithmetic) says how large it must
- *    be.  Scratch must be 256-byte aligned.
+ *    be.  Scratch must be 256-byte aligned.  The one exception is
+ *    tdfo_kjt_complete_cumsum_static, which uses a fixed workspace inside the
+ *    library (its address is looked up on the first call per device); it is
+ *    limited to TDFO_CUMSUM_STATIC_MAX_N lengths and its calls on one device
+ *    must not overlap (see its declaration).
  *  - Return value: TDFO_OK (0) or a negative TDFO_ERR_* code; the message is
  *    available from tdfo_last_error() (thread-local).
  *  - ids (`indices`) are int64, `lengths` are int32, `offsets` are int64 and
@@ -25,6 +29,8 @@
  *  - Out-of-range ids never touch memory: the lookup is skipped (treated as a
  *    zero row) and bit TDFO_FLAG_INDEX_OOB is OR-ed into `*err_flag` (a device
  *    word the caller zeroes and reads back lazily).  `err_flag` may be NULL.
+ *    Likewise a bag whose offsets reach past the `L` ids passed in is cut at L
+ *    (bit TDFO_FLAG_OFFSETS_RANGE): the lookup never reads beyond `indices[L)`.
  *  - Row size `D * sizeof(element)` must be a multiple of 16 bytes (128-bit
  *    vector loads); tables must be 16-byte aligned.
  */
@@ -65,6 +71,7 @@ extern "C" {
 #define TDFO_FLAG_INDEX_OOB     1   /* an id was < 0 or >= rows of its table */
 #define TDFO_FLAG_SCAN_TIMEOUT  2   /* internal look-back watchdog fired (bug guard) */
 #define TDFO_FLAG_RECV_OVERFLOW 4   /* a peer's id receive buffer was too small for this batch */
+#define TDFO_FLAG_OFFSETS_RANGE 8   /* an offset pointed past the L ids given: the bag was cut at L */
 
 /* ------------------------------------------------------------------ misc */
 

@@ -18,7 +18,7 @@ LIB_PATH = Path(os.environ.get("TDFO_B200_LIB") or Path(__file__).resolve().pare
 F32, BF16 = 0, 1
 POOL_SUM, POOL_MEAN, POOL_NONE = 0, 1, 2
 OPT_SGD, OPT_ROWWISE_ADAGRAD, OPT_ADAM = 0, 1, 2
-FLAG_INDEX_OOB, FLAG_SCAN_TIMEOUT, FLAG_RECV_OVERFLOW = 1, 2, 4
+FLAG_INDEX_OOB, FLAG_SCAN_TIMEOUT, FLAG_RECV_OVERFLOW, FLAG_OFFSETS_RANGE = 1, 2, 4, 8
 ABI_VERSION = 1
 SCRATCH_PREPARED = 2
 CUMSUM_STATIC_MAX_N = 1 << 22

@@ -6,7 +6,7 @@
 namespace tdfo {
 
 static thread_local char g_error[512] = "";
-unsigned long long g_launch_count = 0;
+std::atomic<unsigned long long> g_launch_count{0};
 
 void set_error(const char* fmt, ...) {
     va_list ap;
@@ -30,6 +30,6 @@ const char* tdfo_last_error(void) { return tdfo::g_error; }
 
 // Number of kernels this library has launched since it was loaded (host counter;
 // bench.py reads it around the timed region for its "gpu_launches" claim).
-unsigned long long tdfo_launch_count(void) { return tdfo::g_launch_count; }
+unsigned long long tdfo_launch_count(void) { return tdfo::g_launch_count.load(std::memory_order_relaxed); }
 
 }  // extern "C"

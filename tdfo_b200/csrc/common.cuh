@@ -4,6 +4,7 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <atomic>
 #include "../../include/tdfo_b200.h"
 
 #if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
@@ -43,8 +44,9 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 inline bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 
 // Launch-count bookkeeping: bench.py reports how many of OUR kernels ran.
-extern unsigned long long g_launch_count;
-inline void count_launch(int n = 1) { g_launch_count += (unsigned long long)n; }
+// (atomic: the ABI allows several host threads to call into the library at once)
+extern std::atomic<unsigned long long> g_launch_count;
+inline void count_launch(int n = 1) { g_launch_count.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
 // ---------------------------------------------------------------- device side
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }

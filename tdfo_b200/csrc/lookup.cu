@@ -43,7 +43,7 @@ struct BagHead {
     int64_t s, e;
     uint32_t row;   // 0xffffffff = no id in this lane / id out of range
     float w;
-    bool oob;
+    uint32_t flags; // TDFO_FLAG_* bits raised while loading
 };
 
 __device__ __forceinline__ BagHead load_bag_head(const LookupArgs& a, int64_t g, int lane) {
@@ -52,15 +52,20 @@ __device__ __forceinline__ BagHead load_bag_head(const LookupArgs& a, int64_t g,
     h.e = __ldg(a.offsets + g + 1);
     h.row = 0xffffffffu;
     h.w = 1.f;
-    h.oob = false;
+    h.flags = 0;
+    if (h.e > a.L) {          // offsets reach past the ids we were given (e.g. a receive buffer that overflowed)
+        h.flags = TDFO_FLAG_OFFSETS_RANGE;
+        h.e = a.L;
+        h.s = min(h.s, a.L);
+    }
     if (h.s + lane < h.e) {
         const int f = (int)((uint64_t)g / (uint64_t)a.B);
         const int64_t idx = __ldg(a.indices + h.s + lane);
         if ((uint64_t)idx < (uint64_t)__ldg(a.feat_rows + f)) h.row = (uint32_t)(__ldg(a.feat_row_base + f) + idx);
-        else h.oob = true;
+        else h.flags |= TDFO_FLAG_INDEX_OOB;
         if (a.psw) h.w = __ldg(a.psw + h.s + lane);
         if (a.sort_keys) {
-            a.sort_keys[h.s + lane] = h.oob ? a.oob_key : h.row;
+            a.sort_keys[h.s + lane] = (h.row == 0xffffffffu) ? a.oob_key : h.row;
             a.sort_vals[h.s + lane] = (uint32_t)g;
         }
     }
@@ -126,13 +131,13 @@ pooled_forward_kernel(const LookupArgs a) {
     int64_t g = (int64_t)blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5);
     if (g >= a.num_bags) return;
     const uint4* __restrict__ wbase = reinterpret_cast<const uint4*>(a.weights);
-    bool oob = false;
+    uint32_t flags = 0;
 
     BagHead cur = load_bag_head(a, g, lane);
     while (g < a.num_bags) {
         const int64_t gn = g + nwarps;
         BagHead nxt;
-        nxt.s = nxt.e = 0; nxt.row = 0xffffffffu; nxt.w = 1.f; nxt.oob = false;
+        nxt.s = nxt.e = 0; nxt.row = 0xffffffffu; nxt.w = 1.f; nxt.flags = 0;
         if (gn < a.num_bags) nxt = load_bag_head(a, gn, lane);      // in flight during this bag's gather
 
         float acc[CPL][E];
@@ -140,7 +145,7 @@ pooled_forward_kernel(const LookupArgs a) {
         for (int k = 0; k < CPL; ++k)
 #pragma unroll
             for (int i = 0; i < E; ++i) acc[k][i] = 0.f;
-        oob |= cur.oob;
+        flags |= cur.flags;
         const int f = (int)((uint64_t)g / (uint64_t)a.B);
         const int64_t b = g - (int64_t)f * a.B;
 
@@ -155,7 +160,7 @@ pooled_forward_kernel(const LookupArgs a) {
                     const int64_t idx = __ldg(a.indices + base + lane);
                     if ((uint64_t)idx < (uint64_t)__ldg(a.feat_rows + f))
                         my_row = (uint32_t)(__ldg(a.feat_row_base + f) + idx);
-                    else oob = true;
+                    else flags |= TDFO_FLAG_INDEX_OOB;
                     if (WEIGHTED) my_w = __ldg(a.psw + base + lane);
                     if (a.sort_keys) {
                         a.sort_keys[base + lane] = (my_row == 0xffffffffu) ? a.oob_key : my_row;
@@ -218,7 +223,7 @@ pooled_forward_kernel(const LookupArgs a) {
         g = gn;
         cur = nxt;
     }
-    if (oob && a.err_flag) atomicOr(a.err_flag, TDFO_FLAG_INDEX_OOB);
+    if (flags && a.err_flag) atomicOr(a.err_flag, (int)flags);
 }
 
 // Sequence lookup (EmbeddingCollection): out[p,:] = W[row_base(f(p)) + indices[p], :].

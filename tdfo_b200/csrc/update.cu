@@ -23,14 +23,19 @@ constexpr int kUpdThreads = 256;    // linearise kernel
 __global__ void __launch_bounds__(kUpdThreads)
 linearize_kernel(const int64_t* __restrict__ indices, const int64_t* __restrict__ offsets,
                  const int64_t* __restrict__ feat_row_base, const int64_t* __restrict__ feat_rows,
-                 int64_t B, int64_t num_bags, uint32_t oob_key, int vals_are_positions,
+                 int64_t B, int64_t num_bags, int64_t L, uint32_t oob_key, int vals_are_positions,
                  uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ pos_bag,
                  int32_t* err_flag) {
     const int64_t g = (int64_t)blockIdx.x * (kUpdThreads / 32) + (threadIdx.x >> 5);
     if (g >= num_bags) return;
     const int lane = lane_id();
     const int f = (int)(g / B);
-    const int64_t s = __ldg(offsets + g), e = __ldg(offsets + g + 1);
+    int64_t s = __ldg(offsets + g), e = __ldg(offsets + g + 1);
+    if (e > L) {                  // offsets reach past the ids given: cut the bag, never read beyond indices[L)
+        if (lane == 0 && err_flag) atomicOr(err_flag, TDFO_FLAG_OFFSETS_RANGE);
+        e = L;
+        s = min(s, L);
+    }
     const int64_t row_base = __ldg(feat_row_base + f);
     const uint64_t rows = (uint64_t)__ldg(feat_rows + f);
     bool oob = false;
@@ -556,7 +561,7 @@ using namespace tdfo;
 
 static int linearize_impl(const int64_t* indices, const int64_t* offsets,
                           const int64_t* feat_row_base, const int64_t* feat_rows,
-                          int32_t F, int64_t B, int64_t total_rows, int32_t pooling_mode,
+                          int32_t F, int64_t B, int64_t L, int64_t total_rows, int32_t pooling_mode,
                           uint32_t* keys, uint32_t* vals, uint32_t* pos_bag, int32_t* err_flag, void* stream) {
     TDFO_CHECK_ARG(F >= 0 && B >= 0, "linearize_indices: negative size");
     TDFO_CHECK_ARG(total_rows >= 0 && total_rows < 0xffffffffll, "linearize_indices: total_rows must be < 2^32-1");
@@ -567,7 +572,7 @@ static int linearize_impl(const int64_t* indices, const int64_t* offsets,
     const int64_t num_bags = (int64_t)F * B;
     const int64_t blocks = (num_bags + kUpdThreads / 32 - 1) / (kUpdThreads / 32);
     linearize_kernel<<<(unsigned)blocks, kUpdThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-        indices, offsets, feat_row_base, feat_rows, B, num_bags, (uint32_t)total_rows,
+        indices, offsets, feat_row_base, feat_rows, B, num_bags, L, (uint32_t)total_rows,
         pooling_mode == TDFO_POOL_NONE || pos_bag != nullptr, keys, vals, pos_bag, err_flag);
     count_launch();
     TDFO_LAUNCH_CHECK("linearize_indices");
@@ -578,8 +583,9 @@ extern "C" int tdfo_linearize_indices(const int64_t* indices, const int64_t* off
                                       const int64_t* feat_row_base, const int64_t* feat_rows,
                                       int32_t F, int64_t B, int64_t total_rows, int32_t pooling_mode,
                                       uint32_t* keys, uint32_t* vals, int32_t* err_flag, void* stream) {
-    return linearize_impl(indices, offsets, feat_row_base, feat_rows, F, B, total_rows, pooling_mode, keys, vals,
-                          nullptr, err_flag, stream);
+    // this entry point is not told how many ids there are: offsets are taken at face value
+    return linearize_impl(indices, offsets, feat_row_base, feat_rows, F, B, INT64_MAX, total_rows, pooling_mode, keys,
+                          vals, nullptr, err_flag, stream);
 }
 
 extern "C" int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
@@ -629,7 +635,7 @@ extern "C" int tdfo_backward_scratch_layout(int64_t L, int64_t total_rows, tdfo_
     layout->input_vals = A;
     layout->num_unique = 5 * A;
     layout->worklist = 5 * A + 256;
-    layout->worklist_entries = (size_t)(L / kLongSegment) + 2;     // counter + at most L/257 hot rows
+    layout->worklist_entries = (size_t)(L / kLongSegment) + 2;     // counter + at most L/kLongSegment hot rows
     const size_t sort_off = layout->worklist + align_up(layout->worklist_entries * sizeof(uint32_t), 256);
     const size_t scan_off = sort_off + radix_sort_scratch_bytes_impl(L, bits);
     layout->total_bytes = scan_off + tdfo_scan_scratch_bytes(L);
@@ -685,7 +691,7 @@ static int backward_stages(int stages, const char* who, void* weights, int32_t w
 
     if (stages & 1) {
         if (!keys_in_scratch) {
-            rc = linearize_impl(indices, offsets, feat_row_base, feat_rows, F, B, total_rows, pooling_mode,
+            rc = linearize_impl(indices, offsets, feat_row_base, feat_rows, F, B, L, total_rows, pooling_mode,
                                 k0, v0, pos_bag, err_flag, stream);
             if (rc) return rc;
         }

@@ -419,7 +419,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
         self._scratch: Dict[str, torch.Tensor] = {}
         self._emit_keys = False                      # set per forward: training with the CUDA kernel table
         self._fwd_token = 0
-        self._dist_count = 0                         # input dists issued (selects the landing zone)
+        self._peer_by_B: Dict[int, "_PeerExchange"] = {}
         self._prefetched = None                      # (features, ctx, event) of prefetch_input_dist
         self._track_positions = False                # sequence output: remember where every sent id came from
         self._routing: Dict[str, object] = {}
@@ -477,14 +477,14 @@ class ShardedEmbeddingBagCollection(nn.Module):
                     n = self._n_tw[d]
                     so.append(f * D_)
                     ss.append(Ft * D_)
-                    do.append(self._peer.grad_ptrs[d] // 4 + r * B * n * D_ + j * D_)     # absolute address / 4
+                    do.append(self._peer_by_B[B].grad_ptrs[d] // 4 + r * B * n * D_ + j * D_)     # absolute address / 4
                     ds.append(n * D_)
             else:
                 for (d, jj, f, j) in self._cw_unpack_slots:
                     n = self._n_cw[d]
                     so.append(f * D_ + j * Dc)
                     ss.append(Ft * D_)
-                    do.append(self._peer.grad_cw_ptrs[d] // 4 + r * B * n * Dc + jj * Dc)
+                    do.append(self._peer_by_B[B].grad_cw_ptrs[d] // 4 + r * B * n * Dc + jj * Dc)
                     ds.append(n * Dc)
             m = torch.tensor([so, ss, do, ds], dtype=torch.int64, device=device).reshape(-1)
             self._meta_cache[key] = m
@@ -558,19 +558,22 @@ class ShardedEmbeddingBagCollection(nn.Module):
             # ---- input dist through NVLink peer memory: lengths, then ids, are stored by the senders
             # directly where the owner's lookup reads them; no all-to-all, no split sizes on the host
             if self._peer is None or self._peer.B != B:
+                # one exchange (symmetric buffers + rendezvous, collective to create) per batch size, kept: a
+                # train / eval alternation or a short last batch switches between them without reallocating
+                self._peer = self._peer_by_B.get(B)
+            if self._peer is None:
                 cap = self._max_ids_per_rank or int(1.5 * W * max(values.numel(), 1)) + 1024
                 # symmetric buffers must have one size on every rank: agree on the largest proposal
-                # (creation is collective anyway; happens once per batch size)
                 cap_t = torch.tensor([cap], dtype=torch.int64, device=dev)
                 dist.all_reduce(cap_t, op=dist.ReduceOp.MAX, group=self._pg)
                 cap = int(cap_t.item())
-                self._peer = ops.make_peer_exchange(self._pg, dev, B, self._F_total, D, self._n_tw, n_rw, cap,
-                                                    n_cw=self._n_cw, Dc=self._Dc)
-                self._meta_cache.clear()
+                self._peer = self._peer_by_B[B] = ops.make_peer_exchange(
+                    self._pg, dev, B, self._F_total, D, self._n_tw, n_rw, cap, n_cw=self._n_cw, Dc=self._Dc)
+                self._peer.dist_count = 0
             peer = self._peer
             # landing zone: always zone 0 unless input dists are being prefetched, then alternating
-            slot = self._dist_count % len(peer.zones)
-            self._dist_count += 1
+            slot = peer.dist_count % len(peer.zones)
+            peer.dist_count += 1
             z = peer.zones[slot]
             peer.barrier(channel)          # everyone is done reading this zone (and last step's outputs)
             if n_tw_all:
@@ -717,7 +720,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 ops.embedding_forward(self._group("rw", False), lv, lo_[n_own * GB: Fl * GB + 1], GB, _lib.POOL_SUM,
                                       rw_out)
                 out3[:, self._rw_feats, :] = self._exchange_partial_sums(rw_out, B, n_rw)
-            return out, dict(peer=True, lo=lo_, n_tw_r=n_tw_r, n_cw_r=n_cw_r, GB=GB, token=self._fwd_token,
+            return out, dict(peer=True, px=peer, lo=lo_, n_tw_r=n_tw_r, n_cw_r=n_cw_r, GB=GB, token=self._fwd_token,
                              fused=False, slot=c["slot"])
 
         out = torch.empty((B, self._F_total * D), dtype=torch.float32, device=dev)
@@ -777,7 +780,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
         m = self._meta_cache.get(key)
         if m is not None:
             return m
-        W, r, n_rw, p = self._world, self._rank, self._n_rw, self._peer.zones[slot]
+        W, r, n_rw, p = self._world, self._rank, self._n_rw, self._peer_by_B[B].zones[slot]
         rows: List[List[int]] = []
         if kind in ("len_tw", "ids_tw"):
             # whole-table slots, then the column-shard slots of each owner (a column-wise feature is
@@ -841,9 +844,15 @@ class ShardedEmbeddingBagCollection(nn.Module):
             if stale:
                 raise RuntimeError("tdfo_b200: with peer-memory exchange, backward must run before the next forward "
                                    "(the received ids live in the shared landing buffers)")
-            z = self._peer.zones[saved["slot"]]
+            px = saved["px"]
+            z = px.zones[saved["slot"]]
             z.counts_event.synchronize()                    # counts were copied during the forward: no stall
             tw_total, cw_total, total = (int(x) for x in z.counts_host.tolist())
+            if total > px.capacity:
+                # senders dropped what did not fit (TDFO_FLAG_RECV_OVERFLOW on their side) and the lookup cut the
+                # bags at the buffer's end: nothing was read out of bounds, but this step's results are incomplete
+                raise RuntimeError(f"tdfo_b200: rank {self._rank} received {total} ids this step, its exchange buffer "
+                                   f"holds {px.capacity}; construct the module with a larger max_ids_per_rank")
             lo_ = saved["lo"]
             lv_tw, lo_tw = z.ids_x[:tw_total], lo_[: n_tw_r * GB + 1]
             cw = (z.ids_x[tw_total:cw_total], lo_[n_tw_r * GB: n_own * GB + 1] - tw_total) if n_cw_r else None
@@ -874,12 +883,12 @@ class ShardedEmbeddingBagCollection(nn.Module):
             with (torch.cuda.stream(side) if on_gpu else contextlib.nullcontext()):
                 if n_tw_all:
                     ops.copy_feature_blocks(grad_out, None, B, D, self._peer_grad_meta(B, grad_out.device))
-                    recv = self._peer.grad[: GB * n_tw_r * D]
+                    recv = px.grad[: GB * n_tw_r * D]
                 if n_cw_all:
                     ops.copy_feature_blocks(grad_out, None, B, Dc, self._peer_grad_meta(B, grad_out.device, "cw"))
-                    recv_cw = self._peer.grad_cw[: GB * n_cw_r * Dc]
+                    recv_cw = px.grad_cw[: GB * n_cw_r * Dc]
                 if n_tw_all or n_cw_all:
-                    self._peer.barrier()
+                    px.barrier()
                 if on_gpu:
                     landed = torch.cuda.Event()
                     landed.record(side)
@@ -920,6 +929,21 @@ class ShardedEmbeddingBagCollection(nn.Module):
             ops.embedding_backward_update(self._group("rw", True), full, rw_vals, rw_off, GB, _lib.POOL_SUM, opt,
                                           scratch=sc, keys_in_scratch=sc is not None and rw_vals.numel() > 0)
 
+    bounds_check_mode = None      # set to a modules.BoundsCheckMode to change what check_errors() does with bad ids
+
+    def check_errors(self) -> None:
+        """Synchronising check of this rank's device error word: ids outside their table (IndexError, unless
+        bounds_check_mode is IGNORE), a receive buffer that was too small for a batch, or offsets past the
+        received ids (RuntimeError).  The sharded kernels never read out of bounds in any of these cases; the
+        word says the step's results are incomplete."""
+        from .modules import BoundsCheckMode
+        from . import ops as _o
+        try:
+            _o.check_error_flag(self._err_flag, "the sharded lookup")
+        except IndexError:
+            if self.bounds_check_mode != BoundsCheckMode.IGNORE:
+                raise
+
     def _in_module_order(self, features: KeyedJaggedTensor) -> KeyedJaggedTensor:
         if list(features.keys()) != self._feature_names:
             keys = list(features.keys())
@@ -945,8 +969,8 @@ class ShardedEmbeddingBagCollection(nn.Module):
             raise RuntimeError("tdfo_b200: one input dist is already prefetched; run its forward first")
         feats = self._in_module_order(features)
         values, lengths, B = feats.values(), feats.lengths(), feats.stride()
-        if self._use_peer and self._peer is not None and self._peer.B == B:
-            self._peer.ensure_second_zone()
+        if self._use_peer and B in self._peer_by_B:
+            self._peer_by_B[B].ensure_second_zone()
         ev = None
         if values.is_cuda:
             main = torch.cuda.current_stream(values.device)
@@ -1026,6 +1050,11 @@ class ShardedEmbeddingBagCollection(nn.Module):
 
     def _load_from_state_dict(self, state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys,
                               error_msgs):
+        # Shards are only interchangeable with the rank / world / plan they were cut for: a row block of
+        # rank 0 has the same shape as rank 1's, so shape alone cannot tell them apart.  When the checkpoint
+        # carries `_shard_metadata` (every state_dict() of a sharded module does), a local shard is accepted
+        # only if the metadata says it is THIS rank's slice; full tables need no metadata.
+        meta = state_dict.get(f"{prefix}_shard_metadata")
         for t, shn, r0, rows, g0, c0, cols in self._table_shards():
             key = f"{prefix}{self._state_prefix}.{t.name}.weight"
             if key not in state_dict:
@@ -1033,8 +1062,20 @@ class ShardedEmbeddingBagCollection(nn.Module):
                     missing_keys.append(key)
                 continue
             src = state_dict[key]
-            if tuple(src.shape) == (t.num_embeddings, self._D) and (rows, cols) != (t.num_embeddings, self._D):
+            is_full = tuple(src.shape) == (t.num_embeddings, self._D)
+            if is_full and (rows, cols) != (t.num_embeddings, self._D):
                 src = src[g0:g0 + rows, c0:c0 + cols]         # a full table: take this rank's rows / columns
+            elif not is_full and isinstance(meta, dict):
+                tm = meta.get("tables", {}).get(t.name)
+                want = {"world": self._world, "rank": self._rank, "row_offset": g0, "col_offset": c0,
+                        "num_embeddings": t.num_embeddings}
+                have = None if tm is None else {"world": meta.get("world"), "rank": meta.get("rank"),
+                                                "row_offset": tm.get("row_offset"), "col_offset": tm.get("col_offset", 0),
+                                                "num_embeddings": tm.get("num_embeddings")}
+                if have != want:
+                    error_msgs.append(f"shard mismatch for {key}: the checkpoint holds {have}, this rank needs {want} "
+                                      "(per-rank checkpoints need per-rank files; or save full_state_dict() once)")
+                    continue
             if tuple(src.shape) != (rows, cols):
                 error_msgs.append(f"size mismatch for {key}: {tuple(src.shape)} is neither this rank's shard "
                                   f"{(rows, cols)} nor the full table {(t.num_embeddings, self._D)}")

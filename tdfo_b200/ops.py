@@ -106,6 +106,9 @@ def check_error_flag(flag: torch.Tensor, what: str = "embedding lookup") -> None
         flag.zero_()
         raise RuntimeError(f"tdfo_b200: a rank received more ids than its exchange buffer holds during {what}; "
                            "raise max_ids_per_rank")
+    if v & _lib.FLAG_OFFSETS_RANGE:
+        flag.zero_()
+        raise RuntimeError(f"tdfo_b200: offsets pointed past the ids given during {what} (the bags were cut there)")
     if v & _lib.FLAG_INDEX_OOB:
         flag.zero_()
         raise IndexError(f"tdfo_b200: an id was out of range of its table during {what}")

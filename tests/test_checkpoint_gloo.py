@@ -104,6 +104,17 @@ def run_rank(rank, port, results):
         fb = b.full_state_dict()
         for k in fa:
             np.testing.assert_array_equal(fa[k].numpy(), fb[k].numpy())
+        # the reference saves model.state_dict() to ONE path from every rank (torchrec/train.py:172-176), so
+        # the last writer wins: the other rank's shard file must be refused, not silently loaded.  Row blocks
+        # of t0 / t2 have the same shape on both ranks, so only the metadata can tell.
+        theirs = [None] * W
+        dist.all_gather_object(theirs, {k: (v.numpy() if torch.is_tensor(v) else v) for k, v in sd_b.items()})
+        other = {k: (torch.from_numpy(v) if isinstance(v, np.ndarray) else v) for k, v in theirs[1 - rank].items()}
+        try:
+            b.load_state_dict(other)
+            raise AssertionError("another rank's shards accepted")
+        except RuntimeError as e:
+            assert "shard mismatch" in str(e)
         try:
             b.load_state_dict({k: v[:3] for k, v in fa.items()})
             raise AssertionError("wrong-shaped checkpoint accepted")

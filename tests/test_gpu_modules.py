@@ -152,6 +152,68 @@ def test_history_arch_pattern(t):
                                rtol=1e-5, atol=1e-6)
 
 
+def test_full_size_values_config2_against_the_oracle(t):
+    """BASELINE config 2 at its real size, values this time: random fp32 tables, Poisson-ish jagged
+    lengths, one fused row-wise Adagrad step through the product path (forward emits the sort pairs,
+    backward consumes them).  The oracle sees (a) 4096 sampled bags, fed with the very rows the GPU
+    table holds, and (b) two whole tables (first and last): every row of them after the step, updated
+    or not, must match the oracle's update of a host copy of that table."""
+    free, _ = torch.cuda.mem_get_info()
+    if free < 40 << 30:
+        pytest.skip("needs 40 GB of free HBM")
+    ops = t.ops
+    F, rows, D, B, P = 26, 1_000_000, 128, 16384, 20
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(7)
+    w = torch.empty((F * rows, D), device=dev).uniform_(-0.05, 0.05, generator=g)
+    h = torch.empty(F * rows, device=dev).uniform_(0.0, 0.01, generator=g)
+    grp = ops.TableGroup(weights=w, feat_row_base=torch.arange(F, device=dev) * rows,
+                         feat_rows=torch.full((F,), rows, device=dev, dtype=torch.int64),
+                         feat_out_col=torch.arange(F, device=dev) * D, out_stride=F * D, state0=h)
+    lengths = torch.poisson(torch.full((F * B,), float(P), device=dev), generator=g).to(torch.int32)
+    lengths[::101] = 0
+    offsets = ops.complete_cumsum(lengths)
+    L = int(offsets[-1].item())
+    idx = torch.randint(0, rows, (L,), device=dev, generator=g)
+    grad = torch.randn((B, F * D), device=dev, generator=g)
+    check_tables = (0, F - 1)
+    before = {f: (w[f * rows:(f + 1) * rows].cpu().numpy(), h[f * rows:(f + 1) * rows].cpu().numpy()) for f in check_tables}
+
+    lay = ops.backward_layout(L, F * rows)
+    scratch = torch.empty(lay.total_bytes, dtype=torch.uint8, device=dev)
+    out = ops.embedding_forward(grp, idx, offsets, B, orc.POOL_SUM, backward_scratch=scratch)
+
+    # (a) sampled bags: gather their rows from the GPU table, pool them on the host in bag order
+    rng = np.random.default_rng(3)
+    bags = np.sort(rng.choice(F * B, size=4096, replace=False))
+    off_h, idx_h = offsets.cpu().numpy(), idx.cpu().numpy()
+    lens = (off_h[bags + 1] - off_h[bags]).astype(np.int32)
+    pos = np.concatenate([np.arange(off_h[b_], off_h[b_ + 1]) for b_ in bags]).astype(np.int64)
+    keys = (bags.repeat(lens) // B) * rows + idx_h[pos]
+    mini = w[torch.from_numpy(keys).to(dev)].cpu().numpy()                       # one row per sampled occurrence
+    want, _ = orc.embedding_forward(mini, D, np.arange(keys.size, dtype=np.int64), orc.complete_cumsum(lens), None,
+                                    [0], [keys.size], [0], 1, bags.size, orc.POOL_SUM)
+    got = out.view(B, F, D)[torch.from_numpy(bags % B).to(dev), torch.from_numpy(bags // B).to(dev)].cpu().numpy()
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-6)
+
+    ops.embedding_backward_update(grp, grad, idx, offsets, B, orc.POOL_SUM,
+                                  ops.make_optimizer_args(orc.OPT_ROWWISE_ADAGRAD, 0.01, 1e-8), scratch=scratch,
+                                  keys_in_scratch=True)
+    torch.cuda.synchronize()
+    assert int(grp.err_flag.item()) == 0
+    # (b) whole tables against the oracle's update of their host copies
+    grad_h = grad.cpu().numpy()
+    for f in check_tables:
+        w_o, h_o = before[f][0].copy(), before[f][1].copy()
+        s, e = int(off_h[f * B]), int(off_h[(f + 1) * B])
+        orc.embedding_backward_update(w_o, D, h_o, None, np.ascontiguousarray(grad_h[:, f * D:(f + 1) * D]), idx_h[s:e],
+                                      off_h[f * B:(f + 1) * B + 1] - s, [0], [rows], [0], 1, B, orc.POOL_SUM,
+                                      orc.OptArgs(orc.OPT_ROWWISE_ADAGRAD, 0.01, 1e-8))
+        np.testing.assert_allclose(w[f * rows:(f + 1) * rows].cpu().numpy(), w_o, rtol=1e-5, atol=1e-7)
+        np.testing.assert_allclose(h[f * rows:(f + 1) * rows].cpu().numpy(), h_o, rtol=1e-5, atol=1e-9)
+        assert int((w_o != before[f][0]).any(axis=1).sum()) > 250_000           # the step did touch most ids' rows
+
+
 def test_full_size_properties_config2(t):
     """BASELINE config 2 (26 tables x 1M rows x D128 fp32, B=16384, pooling 20): properties that
     do not need the oracle at this size.  Tables of ones => every pooled value is exactly the bag

@@ -484,18 +484,62 @@ def test_forward_emits_the_backward_pairs(ops):
 @pytest.mark.parametrize("optimizer", [orc.OPT_SGD, orc.OPT_ROWWISE_ADAGRAD, orc.OPT_ADAM])
 def test_backward_hot_rows_take_the_block_per_row_path(ops, D, optimizer):
     """Skewed ids: rows with thousands of occurrences are queued on the worklist and reduced by a
-    whole thread block each.  Their summation order differs from the oracle's strictly sequential
-    one, so the bar for those rows is the fp32 reassociation error of a ~2000-term sum."""
+    whole thread block each (fixed tree over contiguous shares), while the oracle adds strictly in
+    order.  Neither order is "the" answer, so both are held to the 1e-5 bar against a float64
+    restatement (tests/helpers.py::fp64_backward_update): |result - fp64| <= 1e-5 * (|w| + step *
+    sum |gradient terms|), the forward-error form of a relative bound for a long sum."""
+    from helpers import fp64_backward_update, within_budget
     c = make_case(seed=D + optimizer, F=3, B=3000, D=D, rows=[40, 3, 2], max_len=3, p_empty=0.0)
+    # the same draws _run_backward_pair makes (seed 99: state first, then the gradient)
+    rng = np.random.default_rng(99)
+    s0_in = s1_in = None
+    if optimizer == orc.OPT_ROWWISE_ADAGRAD:
+        s0_in = rng.uniform(0, 0.3, size=c.total_rows).astype(np.float32)
+    elif optimizer == orc.OPT_ADAM:
+        s0_in = np.zeros_like(c.weights); s1_in = np.zeros_like(c.weights)
+    grad = rng.normal(size=(c.B, c.F * c.D)).astype(np.float32)
+    w64, s0_64, _, _, scale = fp64_backward_update(c.weights, c.D, s0_in, s1_in, grad, c.indices, c.offsets, c.row_base,
+                                                   c.rows, c.out_col, c.F, c.B, orc.POOL_SUM, optimizer, 0.05, 1e-8, 0.0)
     w_o, s0_o, s1_o, grp, routing, scratch = _run_backward_pair(ops, c, orc.POOL_SUM, optimizer, False, steps=1)
     lay = ops.backward_layout(c.L, c.total_rows)
     raw = scratch.cpu().numpy()
     queued = int(raw[lay.worklist: lay.worklist + 4].view(np.uint32)[0])
     seg = np.diff(routing["seg_starts"].astype(np.int64))
     assert queued == int((seg > 64).sum()) and queued >= 5
-    np.testing.assert_allclose(table_to_f32(grp.weights), w_o, rtol=5e-5, atol=2e-5)
-    if s0_o is not None:
-        np.testing.assert_allclose(grp.state0.cpu().numpy(), s0_o, rtol=5e-5, atol=2e-5)
+    assert within_budget(table_to_f32(grp.weights), w64, scale, FP32_RTOL) <= 1.0      # kernel vs float64
+    assert within_budget(w_o, w64, scale, FP32_RTOL) <= 1.0                            # oracle vs float64
+    if optimizer == orc.OPT_ROWWISE_ADAGRAD:
+        np.testing.assert_allclose(grp.state0.cpu().numpy(), s0_64, rtol=FP32_RTOL, atol=0)
+        np.testing.assert_allclose(s0_o, s0_64, rtol=FP32_RTOL, atol=0)
     # and the result is reproducible bit for bit
     w_o2, _, _, grp2, _, _ = _run_backward_pair(ops, c, orc.POOL_SUM, optimizer, False, steps=1)
     assert torch.equal(grp.weights, grp2.weights)
+
+
+def test_lazy_adam_three_steps_with_changing_touched_rows(ops):
+    """Fused ADAM is lazy (moments of a row move only when the row is touched, bias correction by the
+    global step, decoupled decay on touched rows only): three steps whose touched sets differ, kernel
+    against the oracle, whose lazy semantics are pinned on torch.optim.SparseAdam in
+    tests/test_oracle_golden.py."""
+    rng = np.random.default_rng(21)
+    rows, D, B = 300, 64, 40
+    w0 = rng.uniform(-1, 1, size=(rows, D)).astype(np.float32)
+    w_o, m_o, v_o = w0.copy(), np.zeros_like(w0), np.zeros_like(w0)
+    grp = ops.TableGroup(weights=dev(w0), feat_row_base=dev(np.array([0], np.int64)),
+                         feat_rows=dev(np.array([rows], np.int64)), feat_out_col=dev(np.array([0], np.int64)),
+                         out_stride=D, state0=dev(m_o), state1=dev(v_o))
+    pools = [np.arange(0, 120), np.arange(60, 200), np.concatenate([np.arange(0, 30), np.arange(180, 300)])]
+    for step, pool in enumerate(pools, start=1):
+        lengths = rng.integers(0, 4, size=B).astype(np.int32)
+        off = orc.complete_cumsum(lengths)
+        idx = rng.choice(pool, size=int(off[-1])).astype(np.int64)
+        grad = rng.normal(size=(B, D)).astype(np.float32)
+        orc.embedding_backward_update(w_o, D, m_o, v_o, grad, idx, off, [0], [rows], [0], 1, B, orc.POOL_SUM,
+                                      orc.OptArgs(orc.OPT_ADAM, 0.05, 1e-8, 0.01, step=step))
+        ops.embedding_backward_update(grp, dev(grad), dev(idx), dev(off), B, orc.POOL_SUM,
+                                      ops.make_optimizer_args(orc.OPT_ADAM, 0.05, 1e-8, 0.01, 0.9, 0.999, step))
+    np.testing.assert_allclose(grp.weights.cpu().numpy(), w_o, rtol=FP32_RTOL, atol=2e-6)
+    np.testing.assert_allclose(grp.state0.cpu().numpy(), m_o, rtol=FP32_RTOL, atol=1e-7)
+    np.testing.assert_allclose(grp.state1.cpu().numpy(), v_o, rtol=FP32_RTOL, atol=1e-9)
+    never = np.setdiff1d(np.arange(rows), np.concatenate(pools))
+    assert never.size == 0 or np.array_equal(grp.weights.cpu().numpy()[never], w0[never])

@@ -217,3 +217,72 @@ def test_forward_matches_fbgemm_reference_spmdm():
                 c.D, c.D, True, True, False, False)
         assert ok
         np.testing.assert_array_equal(seq[s:e], out)
+
+
+def _lazy_adam_case():
+    """Three steps on a 12-row table with a different set of touched rows each step (rows 2 and 7 sit
+    a step out and come back), some rows never touched, some touched twice in one step."""
+    rng = np.random.default_rng(21)
+    rows, D, B = 12, 8, 5
+    steps = [np.array([0, 2, 2, 5, 7]), np.array([0, 1, 5, 9, 9]), np.array([2, 7, 7, 9, 11])]
+    grads = [rng.normal(size=(B, D)).astype(np.float32) for _ in steps]
+    w0 = rng.uniform(-1, 1, size=(rows, D)).astype(np.float32)
+    return rows, D, B, steps, grads, w0
+
+
+def _oracle_adam_steps(wd):
+    rows, D, B, steps, grads, w0 = _lazy_adam_case()
+    w, m, v = w0.copy(), np.zeros_like(w0), np.zeros_like(w0)
+    off = np.arange(B + 1, dtype=np.int64)                     # one id per bag: grad row b belongs to ids[b]
+    for t, (ids, g) in enumerate(zip(steps, grads), start=1):
+        orc.embedding_backward_update(w, D, m, v, g, ids.astype(np.int64), off, [0], [rows], [0], 1, B, orc.POOL_SUM,
+                                      orc.OptArgs(orc.OPT_ADAM, learning_rate=0.05, eps=1e-8, weight_decay=wd, step=t))
+    return w, m, v
+
+
+def test_lazy_adam_matches_torch_sparse_adam():
+    """The fused ADAM is lazy: a row's moments move only in steps that touch the row, and the bias
+    correction uses the global step count.  torch.optim.SparseAdam over nn.Embedding(sparse=True) is
+    an implementation of exactly that contract that was not written here (it places eps after the
+    bias correction of v instead of before, a 1e-8-relative difference at these gradient sizes)."""
+    import torch
+    rows, D, B, steps, grads, w0 = _lazy_adam_case()
+    emb = torch.nn.Embedding(rows, D, sparse=True)
+    with torch.no_grad():
+        emb.weight.copy_(torch.from_numpy(w0))
+    opt = torch.optim.SparseAdam(emb.parameters(), lr=0.05, betas=(0.9, 0.999), eps=1e-8)
+    for ids, g in zip(steps, grads):
+        opt.zero_grad()
+        (emb(torch.from_numpy(ids)) * torch.from_numpy(g)).sum().backward()
+        opt.step()
+    w, m, v = _oracle_adam_steps(wd=0.0)
+    np.testing.assert_allclose(w, emb.weight.detach().numpy(), rtol=RTOL, atol=ATOL)
+    st = opt.state[emb.weight]
+    np.testing.assert_allclose(m, st["exp_avg"].numpy(), rtol=RTOL, atol=ATOL)
+    # beta2 crosses the ABI as a float (as it does in fbgemm's kernels [UPSTREAM]): 1 - 0.999f is 1.3e-5 below
+    # 0.001, so v itself carries that factor; the step sees sqrt(v), half of it, and stays inside 1e-5
+    np.testing.assert_allclose(v, st["exp_avg_sq"].numpy(), rtol=2e-5, atol=1e-9)
+    untouched = [3, 4, 6, 8, 10]
+    np.testing.assert_array_equal(w[untouched], w0[untouched])
+
+
+def test_lazy_adam_weight_decay_against_masked_dense_restatement():
+    """With weight decay: decoupled (AdamW-style) and applied to the touched rows only, next to stale
+    moments for the rows that sat a step out.  Restated densely in float64 with a touched-row mask."""
+    rows, D, B, steps, grads, w0 = _lazy_adam_case()
+    lr, wd, b1, b2, eps = 0.05, 0.1, 0.9, 0.999, 1e-8
+    w = w0.astype(np.float64)
+    m, v = np.zeros_like(w), np.zeros_like(w)
+    for t, (ids, g) in enumerate(zip(steps, grads), start=1):
+        dense = np.zeros_like(w)
+        np.add.at(dense, ids, g.astype(np.float64))
+        mask = np.zeros(rows, bool)
+        mask[ids] = True
+        m[mask] = b1 * m[mask] + (1 - b1) * dense[mask]
+        v[mask] = b2 * v[mask] + (1 - b2) * dense[mask] ** 2
+        mh, vh = m / (1 - b1 ** t), v / (1 - b2 ** t)
+        w[mask] -= lr * (mh[mask] / (np.sqrt(vh[mask]) + eps) + wd * w[mask])
+    got_w, got_m, got_v = _oracle_adam_steps(wd=wd)
+    np.testing.assert_allclose(got_w, w, rtol=RTOL, atol=ATOL)
+    np.testing.assert_allclose(got_m, m, rtol=RTOL, atol=ATOL)
+    np.testing.assert_allclose(got_v, v, rtol=2e-5, atol=1e-9)     # 1 - 0.999f, see the test above

@@ -68,6 +68,10 @@ def test_static_cumsum_matches_regular_entry_point_twice_in_a_row(lib):
     assert torch.equal(got_first, _reference_offsets(lib, first))        # integer scan: bit-exact
     assert torch.equal(got_second, _reference_offsets(lib, second))
     assert int(got_second[-1]) == int(second.sum(dtype=torch.int64))
+    # and against the CPU oracle's scan, so the static variant is checked by something other than its sibling
+    import oracle as orc
+    np.testing.assert_array_equal(got_first.cpu().numpy(), orc.complete_cumsum(first.cpu().numpy()))
+    np.testing.assert_array_equal(got_second.cpu().numpy(), orc.complete_cumsum(second.cpu().numpy()))
     # and once more with the first input, now after a smaller call
     assert torch.equal(_static_offsets(lib, first), got_first)
 
