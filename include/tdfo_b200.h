@@ -417,6 +417,20 @@ int tdfo_embedding_backward_update(void* weights, int32_t weights_dtype, int64_t
 int tdfo_copy_feature_blocks(const float* src, float* dst, int64_t B, int32_t D, int32_t nslots,
                              const int64_t* meta, void* stream);
 
+/*
+ * Row-wise output dist, second half: every rank s holds the partial pooled sums of its row block for
+ * all samples; the owners' lookups (tdfo_embedding_forward_peer) store them into slot s of the sample
+ * owner's buffer `parts` = float[W][B][nslots * D], and this kernel adds the W slots in rank order
+ * (s = 0, 1, ..., W-1: a reduce-scatter with a fixed, reproducible summation order) into the
+ * KeyedTensor layout: out[b * out_stride + out_col[k] + d] = sum_s parts[s][b][k * D + d].
+ * out_col = device int64[nslots] (multiples of 4); `part_stride` = floats between two source slots.
+ * Replaces: PooledEmbeddingsReduceScatter of the row-wise sharded module DMP builds
+ *   (torchrec/train.py:241-247; the reference's only explicit row partition is
+ *   tensorflow2/train_ps.py:55-61).
+ */
+int tdfo_reduce_partial_sums(const float* parts, int32_t W, int64_t part_stride, int64_t B, int32_t nslots,
+                             int32_t D, const int64_t* out_col, float* out, int64_t out_stride, void* stream);
+
 /* ------------------------------------------------------------------ jagged */
 
 /*

@@ -220,6 +220,46 @@ copy_feature_blocks_kernel(const float* __restrict__ src, float* __restrict__ ds
     }
 }
 
+// ---------------------------------------------------------------- row-wise partial sums
+// out[b][out_col[k] + 4c ..] = parts[0][b][k][c] + parts[1][b][k][c] + ... in source-rank order.
+// W independent 16-byte loads per output chunk; HBM-bound (W reads, 1 write).
+__global__ void __launch_bounds__(256)
+reduce_partial_sums_kernel(const float* __restrict__ parts, int W, int64_t part_stride, int64_t B, int32_t nslots,
+                           int32_t D4, const int64_t* __restrict__ out_col, float* __restrict__ out,
+                           int64_t out_stride) {
+    const int64_t row4 = (int64_t)nslots * D4;                 // 16-byte chunks per sample in one slot
+    const int64_t total = B * row4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t b = i / row4;
+        const int64_t kc = i - b * row4;
+        const int k = (int)(kc / D4);
+        const int c = (int)(kc - (int64_t)k * D4);
+        const uint4* src = reinterpret_cast<const uint4*>(parts) + i;
+        const int64_t stride4 = part_stride / 4;
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        int s = 0;
+        for (; s + 4 <= W; s += 4) {
+            uint4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = __ldcs(src + (int64_t)(s + u) * stride4);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                acc[0] += __uint_as_float(v[u].x); acc[1] += __uint_as_float(v[u].y);
+                acc[2] += __uint_as_float(v[u].z); acc[3] += __uint_as_float(v[u].w);
+            }
+        }
+        for (; s < W; ++s) {
+            const uint4 v = __ldcs(src + (int64_t)s * stride4);
+            acc[0] += __uint_as_float(v.x); acc[1] += __uint_as_float(v.y);
+            acc[2] += __uint_as_float(v.z); acc[3] += __uint_as_float(v.w);
+        }
+        float* o = out + b * out_stride + __ldg(out_col + k) + 4 * c;
+        st_128(o, make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]),
+                             __float_as_uint(acc[3])));
+    }
+}
+
 // ---------------------------------------------------------------- input dist over peer memory
 // Slot j copies B lengths from src + src_off[j] to the absolute address dst_addr[j]
 // (a peer rank's receive buffer, already in its final [feature][source rank][batch] layout).
@@ -441,5 +481,23 @@ extern "C" int tdfo_kjt_push_ids(const int64_t* values, const int64_t* offsets, 
                                                                         err_flag);
     count_launch();
     TDFO_LAUNCH_CHECK("kjt_push_ids");
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_reduce_partial_sums(const float* parts, int32_t W, int64_t part_stride, int64_t B, int32_t nslots,
+                                        int32_t D, const int64_t* out_col, float* out, int64_t out_stride,
+                                        void* stream) {
+    TDFO_CHECK_ARG(W >= 1 && B >= 0 && nslots >= 0 && D > 0 && D % 4 == 0,
+                   "reduce_partial_sums: bad size (D must be a multiple of 4)");
+    if (B == 0 || nslots == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(parts && out && out_col, "reduce_partial_sums: null pointer");
+    TDFO_CHECK_ARG(aligned(parts, 16) && aligned(out, 16) && part_stride % 4 == 0 && out_stride % 4 == 0,
+                   "reduce_partial_sums: buffers / strides not 16-byte aligned");
+    TDFO_CHECK_ARG(part_stride >= B * (int64_t)nslots * D, "reduce_partial_sums: part_stride smaller than one slot");
+    const int64_t items = B * (int64_t)nslots * (D / 4);
+    reduce_partial_sums_kernel<<<grid_for(items, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        parts, W, part_stride, B, nslots, D / 4, out_col, out, out_stride);
+    count_launch();
+    TDFO_LAUNCH_CHECK("reduce_partial_sums");
     return TDFO_OK;
 }

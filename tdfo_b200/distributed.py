@@ -167,6 +167,9 @@ class CudaKernelOps:
     def complete_cumsum_into(self, lengths, out):
         return self._ops.complete_cumsum(lengths, out=out)
 
+    def reduce_partial_sums(self, parts, W, B, nslots, D, out_col, out, out_stride):
+        self._ops.reduce_partial_sums(parts, W, B, nslots, D, out_col, out, out_stride)
+
 
 class _Shard:
     """Local storage of one sharding flavour (all TW tables this rank owns, or all RW row blocks)."""
@@ -227,6 +230,14 @@ class _PeerExchange:
         if max(n_cw) > 0:                          # landing buffer for the gradient columns of column shards
             self.grad_cw = symm.empty(max(W * B * max(n_cw) * Dc, 4), dtype=torch.float32, device=device)
             self.grad_cw_ptrs = list(symm.rendezvous(self.grad_cw, group).buffer_ptrs)
+        # row-wise tables: slot s of `rw_part` receives rank s's partial pooled sums for MY samples
+        # ([W][B][n_rw*D]); `grad_rw` receives every rank's gradient rows of the row-wise features ([W*B][n_rw*D])
+        self.rw_part, self.rw_part_ptrs, self.grad_rw, self.grad_rw_ptrs = None, [], None, []
+        if n_rw > 0:
+            self.rw_part = symm.empty(W * B * n_rw * D, dtype=torch.float32, device=device)
+            self.rw_part_ptrs = list(symm.rendezvous(self.rw_part, group).buffer_ptrs)
+            self.grad_rw = symm.empty(W * B * n_rw * D, dtype=torch.float32, device=device)
+            self.grad_rw_ptrs = list(symm.rendezvous(self.grad_rw, group).buffer_ptrs)
         self.step = 0
 
     def _make_zone(self):
@@ -426,8 +437,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
         # Table-wise output dist / gradient return through NVLink peer memory instead of NCCL
         # all-to-alls (needs the CUDA kernels and symmetric memory; on by default when available).
         if peer_memory is None:
-            peer_memory = (isinstance(self._ops, CudaKernelOps) and W > 1 and device.type == "cuda"
-                           and sum(self._n_tw) + sum(self._n_cw) > 0)
+            peer_memory = isinstance(self._ops, CudaKernelOps) and W > 1 and device.type == "cuda"
         self._use_peer = bool(peer_memory)
         self._max_ids_per_rank = max_ids_per_rank
         self._peer: Optional[_PeerExchange] = None
@@ -438,6 +448,9 @@ class ShardedEmbeddingBagCollection(nn.Module):
                    for f, ti in zip(self._cw.features, self._cw.feat_table)]
         self.register_buffer("_cw_global_col", torch.tensor(cw_cols or [0], dtype=torch.int64,
                                                             device=device)[:len(cw_cols)], persistent=False)
+        self.register_buffer("_rw_global_col", torch.tensor([f * self._D for f in self._rw_feats] or [0],
+                                                            dtype=torch.int64, device=device)[:self._n_rw],
+                             persistent=False)
         self.set_fused_optimizer(EmbOptimType.EXACT_SGD, learning_rate=0.01)
 
     def _tw_meta(self, B: int, to_output: bool, device, cls: str = "tw") -> torch.Tensor:
@@ -479,6 +492,16 @@ class ShardedEmbeddingBagCollection(nn.Module):
                     ss.append(Ft * D_)
                     do.append(self._peer_by_B[B].grad_ptrs[d] // 4 + r * B * n * D_ + j * D_)     # absolute address / 4
                     ds.append(n * D_)
+            elif cls == "rw":
+                # every rank needs the gradient of every sample for the row-wise features (an all-gather,
+                # written by the sample owners straight into the other ranks' landing buffers)
+                n = self._n_rw
+                for d in range(self._world):
+                    for k_, f in enumerate(self._rw_feats):
+                        so.append(f * D_)
+                        ss.append(Ft * D_)
+                        do.append(self._peer_by_B[B].grad_rw_ptrs[d] // 4 + r * B * n * D_ + k_ * D_)
+                        ds.append(n * D_)
             else:
                 for (d, jj, f, j) in self._cw_unpack_slots:
                     n = self._n_cw[d]
@@ -714,12 +737,19 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 grp.out_stride = self._F_total * D
                 ops.embedding_forward_peer(grp, lv, lo_[n_tw_r * GB: n_own * GB + 1], GB, self._pooling,
                                            peer.out_ptrs[k], B)
-            peer.barrier()                                    # all pooled rows have landed
             if n_rw:
-                rw_out = torch.empty((GB, n_rw * D), dtype=torch.float32, device=dev)
-                ops.embedding_forward(self._group("rw", False), lv, lo_[n_own * GB: Fl * GB + 1], GB, _lib.POOL_SUM,
-                                      rw_out)
-                out3[:, self._rw_feats, :] = self._exchange_partial_sums(rw_out, B, n_rw)
+                # row-wise: my block's partial sums of sample (src, b) go into slot `r` of rank src's buffer
+                key = (B, "rw_part_out", str(dev))
+                slot_ptrs = self._meta_cache.get(key)
+                if slot_ptrs is None:
+                    slot_ptrs = self._meta_cache[key] = torch.tensor(
+                        [p + 4 * r * B * n_rw * D for p in peer.rw_part_ptrs], dtype=torch.int64, device=dev)
+                ops.embedding_forward_peer(self._group("rw", False), lv, lo_[n_own * GB: Fl * GB + 1], GB, _lib.POOL_SUM,
+                                           slot_ptrs, B)
+            peer.barrier()                                    # all pooled rows / partial sums have landed
+            if n_rw:
+                # add the W slots in rank order into the row-wise columns of the output (fixed order: reproducible)
+                ops.reduce_partial_sums(peer.rw_part, W, B, n_rw, D, self._rw_global_col, out, self._F_total * D)
             return out, dict(peer=True, px=peer, lo=lo_, n_tw_r=n_tw_r, n_cw_r=n_cw_r, GB=GB, token=self._fwd_token,
                              fused=False, slot=c["slot"])
 
@@ -824,7 +854,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
 
     def _prepared_scratch(self, name: str, L: int, device):
         """Workspace the id-only half of the backward sorts into (one per shard kind: they are in flight together)."""
-        sh = {"tw": self._tw, "cw": self._cw}[name]
+        sh = {"tw": self._tw, "cw": self._cw, "rw": self._rw}[name]
         need = self._ops.backward_scratch_bytes(L, max(sh.total_rows, 1))
         buf = self._scratch.get("prep_" + name)
         if buf is None or buf.numel() < need or buf.device != device:
@@ -861,14 +891,15 @@ class ShardedEmbeddingBagCollection(nn.Module):
         else:
             lv_tw, lo_tw, cw, rw = saved["lv"], saved["lo"][: n_tw_r * GB + 1], saved["cw"], saved["rw"]
             fused = saved["fused"] and not stale
-        recv = recv_cw = None
+        recv = recv_cw = recv_rw = None
         prepared = {}
         if saved["peer"]:
             # Push every gradient row (column slice) into the landing buffer of its owner over NVLink, on a
             # side stream: the push is NVLink-bound and the id-only half of the backward (linearise, sort,
             # unique: latency-bound, needs no gradient) runs on the main stream meanwhile.
             todo = [(name, ids_, off_) for name, have, ids_, off_ in
-                    (("tw", n_tw_r, lv_tw, lo_tw), ("cw", n_cw_r) + (cw if cw else (None, None)))
+                    (("tw", n_tw_r, lv_tw, lo_tw), ("cw", n_cw_r) + (cw if cw else (None, None)),
+                     ("rw", n_rw) + (rw if rw else (None, None)))
                     if have and ids_.numel() > 0]
             # (Measured at N=8: linearising before the push starts does not help, 3.28 vs 3.24 ms/step: every
             # kernel that runs next to the NVLink stores slows down, the streaming linearise pass most.)
@@ -887,13 +918,17 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 if n_cw_all:
                     ops.copy_feature_blocks(grad_out, None, B, Dc, self._peer_grad_meta(B, grad_out.device, "cw"))
                     recv_cw = px.grad_cw[: GB * n_cw_r * Dc]
-                if n_tw_all or n_cw_all:
+                if n_rw:
+                    ops.copy_feature_blocks(grad_out, None, B, D, self._peer_grad_meta(B, grad_out.device, "rw"))
+                    recv_rw = px.grad_rw.view(GB, n_rw * D)
+                if n_tw_all or n_cw_all or n_rw:
                     px.barrier()
                 if on_gpu:
                     landed = torch.cuda.Event()
                     landed.record(side)
             for name, ids_, off_ in todo:
-                ops.embedding_backward_prepare(self._group(name, False), ids_, off_, GB, self._pooling, prepared[name])
+                ops.embedding_backward_prepare(self._group(name, False), ids_, off_, GB,
+                                               _lib.POOL_SUM if name == "rw" else self._pooling, prepared[name])
             if on_gpu:
                 main.wait_event(landed)
         else:
@@ -920,14 +955,20 @@ class ShardedEmbeddingBagCollection(nn.Module):
                                           keys_in_scratch="prepared" if "cw" in prepared else
                                           (sc is not None and cw_vals.numel() > 0))
         if n_rw:
-            g3 = grad_out.view(B, self._F_total, D)
-            mine = g3[:, self._rw_feats, :].reshape(B, n_rw * D).contiguous()
-            full = torch.empty((GB, n_rw * D), dtype=torch.float32, device=grad_out.device)
-            dist.all_gather_into_tensor(full, mine, group=self._pg)
             rw_vals, rw_off = rw
-            sc = self._scratch.get("rw") if fused else None
+            if saved["peer"]:
+                full = recv_rw
+                sc = prepared.get("rw")
+                kis = "prepared" if "rw" in prepared else False
+            else:
+                g3 = grad_out.view(B, self._F_total, D)
+                mine = g3[:, self._rw_feats, :].reshape(B, n_rw * D).contiguous()
+                full = torch.empty((GB, n_rw * D), dtype=torch.float32, device=grad_out.device)
+                dist.all_gather_into_tensor(full, mine, group=self._pg)
+                sc = self._scratch.get("rw") if fused else None
+                kis = sc is not None and rw_vals.numel() > 0
             ops.embedding_backward_update(self._group("rw", True), full, rw_vals, rw_off, GB, _lib.POOL_SUM, opt,
-                                          scratch=sc, keys_in_scratch=sc is not None and rw_vals.numel() > 0)
+                                          scratch=sc, keys_in_scratch=kis)
 
     bounds_check_mode = None      # set to a modules.BoundsCheckMode to change what check_errors() does with bad ids
 

@@ -377,6 +377,18 @@ def copy_feature_blocks(src: torch.Tensor, dst: torch.Tensor, B: int, D: int, me
     check(_lib.load().tdfo_copy_feature_blocks(_ptr(src), _ptr(dst), B, D, meta.numel() // 4, _ptr(meta), _stream()))
 
 
+def reduce_partial_sums(parts: torch.Tensor, W: int, B: int, nslots: int, D: int, out_col: torch.Tensor,
+                        out: torch.Tensor, out_stride: int) -> None:
+    """Row-wise output dist: ``out[b, out_col[k] + d] = sum_s parts[s, b, k*D + d]`` with s in rank order
+    (``parts``: float32 [W, B, nslots*D], the slots the owners' lookups stored their partial sums into)."""
+    parts = _cuda(parts, torch.float32, "parts")
+    out_col = _cuda(out_col, torch.int64, "out_col")
+    if not (out.is_cuda and out.dtype == torch.float32 and out.is_contiguous()):
+        raise TypeError("out must be a contiguous float32 CUDA tensor")
+    check(_lib.load().tdfo_reduce_partial_sums(_ptr(parts), W, B * nslots * D, B, nslots, D, _ptr(out_col), _ptr(out),
+                                               out_stride, _stream()))
+
+
 # --------------------------------------------------------------------------- jagged
 def _jagged_2d_to_dense_raw(values, offsets, max_len):
     values = _cuda(values, torch.float32, "values")

@@ -93,6 +93,12 @@ class FakePeerExchange:
         if max(n_cw) > 0:
             self.grad_cw, k = mem.empty(max(W * B * max(n_cw) * Dc, 4), torch.float32)
             self.grad_cw_ptrs = mem.ptrs(k)
+        self.rw_part, self.rw_part_ptrs, self.grad_rw, self.grad_rw_ptrs = None, [], None, []
+        if n_rw > 0:
+            self.rw_part, k = mem.empty(W * B * n_rw * D, torch.float32)
+            self.rw_part_ptrs = mem.ptrs(k)
+            self.grad_rw, k = mem.empty(W * B * n_rw * D, torch.float32)
+            self.grad_rw_ptrs = mem.ptrs(k)
         dist.barrier(group=pg)                              # every rank's files exist
 
     def _make_zone(self):
@@ -181,6 +187,16 @@ class FakePeerOps(OracleKernelOps):
             so, ss, do, ds = (int(x) for x in m[:, j])
             for b in range(B):
                 self.mem.view(4 * (do + b * ds), np.float32, D)[:] = s[so + b * ss: so + b * ss + D]
+
+    # ---- tdfo_reduce_partial_sums: out[b, out_col[k] + d] = sum over source slots, in rank order, fp32
+    def reduce_partial_sums(self, parts, W, B, nslots, D, out_col, out, out_stride):
+        p = _np(parts).reshape(W, B, nslots, D)
+        acc = p[0].copy()
+        for s in range(1, W):
+            acc += p[s]
+        o = out.view(B, out_stride)
+        for k, c in enumerate(_np(out_col)):
+            o[:, int(c): int(c) + D] = torch.from_numpy(acc[:, k])
 
     # ---- the id-only half of the backward has nothing to precompute for the oracle
     def backward_scratch_bytes(self, L, total_rows):

@@ -65,7 +65,7 @@ def run_rank(rank, port, plan_kind, peer, results):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("plan_kind,peer", [("tw", False), ("tw", True), ("rw", False), ("mixed", False),
+@pytest.mark.parametrize("plan_kind,peer", [("tw", False), ("tw", True), ("rw", False), ("rw", True), ("mixed", False),
                                             ("mixed", True), ("cw", False), ("cw", True), ("all3", True)])
 def test_sharded_equals_unsharded_on_2_gpus(plan_kind, peer):
     """peer=True: table-wise pooled rows and gradient rows travel through NVLink peer memory written
@@ -207,3 +207,31 @@ def test_empty_and_lopsided_batches_on_2_gpus():
                 p.terminate()
         assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
         assert dict(results) == {0: "ok", 1: "ok"}
+
+
+@pytest.mark.parametrize("case,prefetch", [("w4", False), ("w4", True), ("w4_all_rw", False), ("w8_bench_plan", False),
+                                           ("w8_mixed", False), ("w8_mixed", True)])
+def test_peer_memory_exchange_on_4_and_8_gpus(case, prefetch):
+    """The cases of tests/test_peer_layout_gloo.py (uneven table-wise ownership + column shards + a row-wise
+    table on 4 ranks; bench.py's balanced plan, BASELINE config 4's all-row-wise and config 5's mixed plan on
+    4 / 8 ranks) on real symmetric memory over NVLink: two training steps (four with the input dist
+    prefetched), every rank's pooled rows against the oracle on its batch, all tables afterwards against the
+    oracle's update on the global batch."""
+    from test_peer_layout_gloo import CASES, run_rank as run_layout_rank
+    world = CASES[case]["W"]
+    if not torch.cuda.is_available() or torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    port = free_port()
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        results = mgr.dict()
+        procs = [ctx.Process(target=run_layout_rank, args=(r, port, "", case, results, prefetch, True)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=300)
+        for p in procs:
+            if p.is_alive():
+                p.terminate()
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        assert dict(results) == {r: "ok" for r in range(world)}

@@ -26,6 +26,11 @@ CASES = {
     # the shape bench.py runs on 8 GPUs: 26 equal-sized tables under balanced_plan (24 table-wise round-robin +
     # 2 tables x 4 column shards, one shard per rank)
     "w8_bench_plan": dict(W=8, rows=[11 + (7 * i) % 13 for i in range(26)]),
+    # BASELINE config 4's plan: every table row-wise (partial sums land in per-source slots of the sample owner,
+    # gradient rows are written into every rank's landing buffer)
+    "w4_all_rw": dict(W=4, rows=[37, 50, 9, 64, 21]),
+    # BASELINE config 5's plan on 8 ranks: 8 tables table-wise (one per rank) + 8 row-wise
+    "w8_mixed": dict(W=8, rows=[20 + (5 * i) % 17 for i in range(8)] + [40 + (11 * i) % 23 for i in range(8)]),
 }
 
 
@@ -39,17 +44,27 @@ def batch(rank, step, ROWS):
     return lengths, idx.astype(np.int64), rng.normal(size=(B4, F * D4)).astype(np.float32)
 
 
-def run_rank(rank, port, tag, case, results, prefetch=False):
+def run_rank(rank, port, tag, case, results, prefetch=False, cuda=False):
+    """cuda=True (tests/test_gpu_sharded.py): the same steps on W real GPUs, CUDA kernels over symmetric memory."""
     W4, ROWS = CASES[case]["W"], CASES[case]["rows"]
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
-    dist.init_process_group("gloo", rank=rank, world_size=W4)
+    if cuda:
+        torch.cuda.set_device(rank)
+        dev = torch.device("cuda", rank)
+        dist.init_process_group("nccl", rank=rank, world_size=W4, device_id=dev)
+    else:
+        dev = torch.device("cpu")
+        dist.init_process_group("gloo", rank=rank, world_size=W4)
     mem = None
     try:
         import tdfo_b200 as t
         from tdfo_b200 import distributed as td
-        from fake_peer import FakeMem, FakePeerOps
-        mem = FakeMem(tag, rank, W4)
+        kernel_ops = None
+        if not cuda:
+            from fake_peer import FakeMem, FakePeerOps
+            mem = FakeMem(tag, rank, W4)
+            kernel_ops = FakePeerOps(mem)
         F = len(ROWS)
         tables = [t.EmbeddingBagConfig(num_embeddings=r, embedding_dim=D4, name=f"t{i}", feature_names=[f"f{i}"],
                                        pooling=t.PoolingType.SUM) for i, r in enumerate(ROWS)]
@@ -57,22 +72,30 @@ def run_rank(rank, port, tag, case, results, prefetch=False):
             plan = {"t0": td.table_wise(2), "t1": td.column_wise([3, 1, 0, 2]), "t2": td.table_wise(0),
                     "t3": td.row_wise(), "t4": td.table_wise(2), "t5": td.column_wise([1, 2, 3, 0]),
                     "t6": td.table_wise(3), "t7": td.table_wise(2)}
+        elif case == "w4_all_rw":
+            plan = {c.name: td.row_wise() for c in tables}
+        elif case == "w8_mixed":
+            plan = {c.name: (td.table_wise(i) if i < 8 else td.row_wise()) for i, c in enumerate(tables)}
         else:
             plan = td.balanced_plan(tables, W4, min_shard_bytes=16)
-        m = td.ShardedEmbeddingBagCollection(tables, plan, torch.device("cpu"), kernel_ops=FakePeerOps(mem), init_seed=21,
-                                             peer_memory=True)
-        assert m._use_peer and m._Dc == 4
+        m = td.ShardedEmbeddingBagCollection(tables, plan, dev, kernel_ops=kernel_ops, init_seed=21, peer_memory=True)
+        assert m._use_peer
         if case == "w4":
-            assert m._n_tw == [1, 0, 3, 1] and m._n_cw == [2, 2, 2, 2]
+            assert m._n_tw == [1, 0, 3, 1] and m._n_cw == [2, 2, 2, 2] and m._Dc == 4
+        elif case == "w4_all_rw":
+            assert m._n_tw == [0] * 4 and m._n_rw == 5
+        elif case == "w8_mixed":
+            assert m._n_tw == [1] * 8 and m._n_rw == 8
         else:
-            assert m._n_tw == [3] * 8 and m._n_cw == [1] * 8
+            assert m._n_tw == [3] * 8 and m._n_cw == [1] * 8 and m._Dc == 4
         m.set_fused_optimizer(t.EmbOptimType.EXACT_SGD, learning_rate=0.05)
         m.train()
         w_ref = np.concatenate([td.ShardedEmbeddingBagCollection.initial_table(c, 21).numpy() for c in tables])
         base = np.concatenate([[0], np.cumsum(ROWS)[:-1]]).astype(np.int64)
         col = (np.arange(F) * D4).astype(np.int64)
         keys = [f"f{i}" for i in range(F)]
-        mk = lambda b_: t.KeyedJaggedTensor.from_lengths_sync(keys, torch.from_numpy(b_[1]), torch.from_numpy(b_[0]))
+        mk = lambda b_: t.KeyedJaggedTensor.from_lengths_sync(keys, torch.from_numpy(b_[1]),
+                                                              torch.from_numpy(b_[0])).to(dev)
         n_steps = 4 if prefetch else 2
         nxt = None
         for step in range(n_steps):
@@ -87,9 +110,9 @@ def run_rank(rank, port, tag, case, results, prefetch=False):
                 assert len(m._peer.zones) == 2
             want, _ = orc.embedding_forward(w_ref, D4, idx, orc.complete_cumsum(lengths), None, base, ROWS, col, F, B4,
                                             orc.POOL_SUM)
-            np.testing.assert_allclose(out.detach().numpy(), want, rtol=1e-5, atol=1e-6, err_msg=f"step {step}")
-            out.backward(torch.from_numpy(grad))
-            assert int(m._err_flag.item()) == 0
+            np.testing.assert_allclose(out.detach().cpu().numpy(), want, rtol=1e-5, atol=1e-6, err_msg=f"step {step}")
+            out.backward(torch.from_numpy(grad).to(dev))
+            m.check_errors()
             # unsharded SGD on the global batch: per feature, rank 0's bags first
             per = [batch(r, step, ROWS) for r in range(W4)]
             offs = [orc.complete_cumsum(p[0]) for p in per]
@@ -110,7 +133,8 @@ def run_rank(rank, port, tag, case, results, prefetch=False):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("case,prefetch", [("w4", False), ("w8_bench_plan", False), ("w4", True)])
+@pytest.mark.parametrize("case,prefetch", [("w4", False), ("w8_bench_plan", False), ("w4", True),
+                                           ("w4_all_rw", False), ("w8_mixed", False), ("w4_all_rw", True)])
 def test_peer_memory_layout_beyond_two_ranks(case, prefetch):
     """prefetch=True: every step's input dist is issued through prefetch_input_dist before the previous
     backward, alternating between two landing zones."""
