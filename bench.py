@@ -348,15 +348,175 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def run_ours_sharded(args):
-    """N > 1: BASELINE config 2 with its 26 tables sharded over the N GPUs of the box, weak scaling
-    (every rank feeds its own batch of 16384, so per-GPU lookups stay fixed).  Tables are spread
-    table-wise, round-robin (--plan tw, default), or with the remainder that does not divide evenly
-    sharded row-wise (--plan mixed)."""
+def _measured_traffic(torch, dist, m, sp, world, rank, B, dev, lengths, ids):
+    """Exact per-rank counts for one batch (outside the timed region): ids received per local slot, unique
+    rows per slot (torch.unique on what landed), and the bytes this rank sends over NVLink.  Returns the
+    algorithmic HBM bytes of the rank (SURVEY.md §8d formula, per slot) and the NVLink send bytes."""
+    D, w = sp["D"], (2 if sp["bf16"] else 4)
+    W, r = world, rank
+    GB = W * B
+    with torch.no_grad():
+        c = m._input_dist(ids, lengths, B)                 # collective: the exchange alone, nothing consumes it
+    torch.cuda.synchronize()
+    z = m._peer.zones[c["slot"]]
+    Fl = m._F_local
+    off = z.off_x[: Fl * GB + 1]
+    bounds = off[::GB].tolist() if Fl else [0]
+    widths = [D] * m._n_tw[r] + [m._Dc] * m._n_cw[r] + [D] * m._n_rw
+    hbm, U_total = 0.0, 0
+    for j in range(Fl):
+        Lj = bounds[j + 1] - bounds[j]
+        Uj = int(torch.unique(z.ids_x[bounds[j]:bounds[j + 1]]).numel()) if Lj else 0
+        Dj = widths[j]
+        hbm += Lj * (Dj * w + 8) + (GB + 1) * 8 + GB * Dj * 4            # lookup
+        hbm += GB * Dj * 4 + Lj * 8 + Uj * (2 * Dj * w + 8)              # backward + row-wise Adagrad update
+        U_total += Uj
+    L_recv = bounds[-1]
+    # NVLink send bytes of this rank
+    off_local = torch.cat([torch.zeros(1, dtype=torch.int64, device=dev), torch.cumsum(lengths.long(), 0)])
+    per_f = (off_local[B::B] - off_local[:-1:B]).tolist()                # my ids per feature
+    send = 0
+    for d in range(W):
+        if d == r:
+            continue
+        for f in m._tw_feats[d] + [f_ for (f_, _) in m._cw_slots[d]]:
+            send += per_f[f] * 8 + B * 4                                 # ids + lengths to the owner
+        send += len(m._tw_feats[d]) * B * D * 4 + len(m._cw_slots[d]) * B * m._Dc * 4     # my gradient rows to the owner
+    send += (W - 1) * (m._n_tw[r] * B * D * 4 + m._n_cw[r] * B * m._Dc * 4)              # pooled rows I return
+    if m._n_rw:
+        for k_, f in enumerate(m._rw_feats):
+            seg = ids[off_local[f * B]:off_local[(f + 1) * B]]
+            send += int(((seg // m._rw_block[k_]) != r).sum().item()) * 8 + (W - 1) * B * 4
+        send += 2 * (W - 1) * B * m._n_rw * D * 4                        # partial sums out, gradient rows out
+    stats = torch.tensor([hbm, float(send), float(L_recv), float(U_total)], dtype=torch.float64, device=dev)
+    mx = stats.clone()
+    dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    sm = stats.clone()
+    dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+    return {"hbm_bytes_max_rank": float(mx[0]), "hbm_bytes_mean_rank": float(sm[0]) / W,
+            "nvlink_send_bytes_max_rank": float(mx[1]), "nvlink_send_bytes_mean_rank": float(sm[1]) / W,
+            "ids_received_max_rank": float(mx[2]), "ids_received_mean_rank": float(sm[2]) / W,
+            "unique_rows_max_rank": float(mx[3]), "unique_rows_mean_rank": float(sm[3]) / W}
+
+
+def sharded_workload(cfg, args, rank, world, dev, headline):
+    """Parity check + timed run of BASELINE config `cfg` sharded over the `world` GPUs (weak scaling in the
+    batch, except config 5 whose global batch is fixed at 65536)."""
+    import gc
     import torch
     import torch.distributed as dist
     import tdfo_b200 as t
+    import bench_workloads as bw
     from tdfo_b200 import distributed as td, ops
+
+    sp = bw.spec(cfg, world)
+    plan_override = args.plan if (cfg == 2 and args.plan != "cw") else None
+    parity = bw.parity_check(cfg, world, rank, dev, plan_override=plan_override)
+
+    rows, D, B = sp["rows"], sp["D"], sp["B"]
+    F = len(rows)
+    tables = bw.make_tables(t, sp)
+    plan = bw.make_plan(td, sp, tables, world, plan_override)
+    kinds = [plan[tb.name].sharding_type.value for tb in tables]
+    n_batches = N_BATCHES if cfg == 2 else 2
+    batches = [bw.device_batch(torch, sp, rows, B, dev, seed=42 + rank + 1000 * bi) for bi in range(n_batches)]
+    Ls = [int(b[1].numel()) for b in batches]
+    tot = torch.tensor([float(sum(Ls)) / n_batches, float(max(Ls))], dtype=torch.float64, device=dev)
+    dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    L_global, cap = float(tot[0]), int(tot[1]) + 1024      # no rank can receive more ids than exist
+    m = td.ShardedEmbeddingBagCollection(tables, plan, dev, init_on_device=True, max_ids_per_rank=cap)
+    m.set_fused_optimizer(t.EmbOptimType.EXACT_ROWWISE_ADAGRAD, learning_rate=CFG["lr"], eps=CFG["eps"])
+    m.train()
+    keys = [f"f{i}" for i in range(F)]
+    gen = torch.Generator(device=dev).manual_seed(42 + rank)
+    grad_out = torch.randn((B, F * D), device=dev, generator=gen)
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    prefetch = args.prefetch_input_dist
+
+    def make_kjt(i):
+        lengths, ids = batches[i % n_batches]
+        return t.KeyedJaggedTensor(keys, ids, lengths=lengths, stride=B)
+
+    state = {"next": None}
+
+    def step(i, last):
+        kjt = state["next"] if state["next"] is not None else make_kjt(i)
+        state["next"] = None
+        out = m(kjt).values()
+        if prefetch and not last:
+            state["next"] = make_kjt(i + 1)
+            m.prefetch_input_dist(state["next"])           # batch i+1's exchange runs next to this backward
+        out.backward(grad_out)
+
+    for i in range(args.warmup):
+        step(i, i + 1 == args.warmup)
+    barrier()
+    sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", "0"))) if headline else None
+    if sampler is not None and rank == 0:
+        sampler.start()
+    launches0 = ops.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        step(args.warmup + i, i + 1 == args.steps)
+    e1.record()
+    barrier()
+    launches = ops.launch_count() - launches0
+    tt = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms_step = float(tt.item()) / args.steps
+    value = L_global / (ms_step * 1e-3)
+    m.check_errors()
+
+    e2e = None
+    if headline:
+        lengths0 = batches[0][0]
+        same_len = all(torch.equal(b[0], lengths0) for b in batches)
+        if same_len:
+            e2e = run_e2e(args, t, m, keys, lengths0, [b[1] for b in batches], grad_out, F, B, D, Ls[0], world, dev,
+                          barrier)
+    clocks = sampler.stop() if (sampler is not None and rank == 0) else None
+    traffic = _measured_traffic(torch, dist, m, sp, world, rank, B, dev, *batches[0])
+    peak, peak_src = measured_peak_gbs()
+    hbm_gbs = traffic["hbm_bytes_max_rank"] / (ms_step * 1e-3) / 1e9
+    nv_gbs = traffic["nvlink_send_bytes_max_rank"] / (ms_step * 1e-3) / 1e9
+    n_cw = kinds.count("column_wise")
+    res = {
+        "workload": sp["name"], "value": value, "unit": UNIT, "ms_per_step": ms_step,
+        "lookups_per_step_global": L_global, "batch_per_gpu": B, "dtype": "bf16" if sp["bf16"] else "f32",
+        "plan": f"{kinds.count('table_wise')} table-wise + {n_cw} column-wise + {kinds.count('row_wise')} row-wise over "
+                f"{world} GPUs; every exchange (lengths, ids, pooled rows / partial sums, gradient rows) is written by "
+                "the kernels into NVLink peer memory, no collective library call on the step",
+        "prefetch_input_dist": bool(prefetch),
+        "hbm": {"algorithmic_bytes_per_step_max_rank": traffic["hbm_bytes_max_rank"],
+                "algorithmic_bytes_per_step_mean_rank": traffic["hbm_bytes_mean_rank"],
+                "achieved_GBps": hbm_gbs, "peak": peak, "frac": hbm_gbs / peak, "frac_of_8TBps_spec": hbm_gbs / 8000.0,
+                "unique_rows": "measured (torch.unique on the ids each rank received)",
+                "unique_rows_mean_rank": traffic["unique_rows_mean_rank"],
+                "ids_received_max_rank": traffic["ids_received_max_rank"],
+                "ids_received_mean_rank": traffic["ids_received_mean_rank"]},
+        "nvlink": {"send_bytes_per_gpu_per_step_max_rank": traffic["nvlink_send_bytes_max_rank"],
+                   "send_bytes_per_gpu_per_step_mean_rank": traffic["nvlink_send_bytes_mean_rank"],
+                   "GBps_if_serial": nv_gbs, "peak_GBps_per_direction": 900.0, "frac": nv_gbs / 900.0},
+        "parity_check": parity, "gpu_launches": int(launches),
+    }
+    extra = {"e2e": e2e, "clocks": clocks, "peak_src": peak_src, "kinds": kinds, "L_local": Ls[0]}
+    del m, batches, grad_out
+    gc.collect()
+    torch.cuda.empty_cache()
+    return res, extra
+
+
+def run_ours_sharded(args):
+    """N > 1.  Headline: BASELINE config 2 (or --config) with its tables sharded over the N GPUs of the box,
+    every rank feeding its own batch.  Each workload is preceded by a seeded value check against the oracle
+    (`parity_check`).  On 8 GPUs configs 3, 4 and 5 run after the headline and are reported under `configs`."""
+    import torch
+    import torch.distributed as dist
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -366,100 +526,53 @@ def run_ours_sharded(args):
     if not dist.is_initialized():
         dist.init_process_group("nccl", device_id=dev)
 
-    F, rows, D, P, B = CFG["tables"], CFG["rows"], CFG["dim"], CFG["pooling"], CFG["batch"]
-    gen = torch.Generator(device=dev).manual_seed(42 + rank)
-    tables = [t.EmbeddingBagConfig(num_embeddings=rows, embedding_dim=D, name=f"t{i}", feature_names=[f"f{i}"],
-                                   pooling=t.PoolingType.SUM) for i in range(F)]
-    n_tw = F if args.plan == "tw" else (F // world) * world
-    if args.plan == "cw":
-        plan = td.balanced_plan(tables, world)
-    else:
-        plan = {f"t{i}": (td.table_wise(i % world) if i < n_tw else td.row_wise()) for i in range(F)}
-    kinds = [plan[f"t{i}"].sharding_type.value for i in range(F)]
-    n_cw = kinds.count("column_wise")
-    cw_shards = len(plan[f"t{F - 1}"].ranks) if n_cw else 0
-    m = td.ShardedEmbeddingBagCollection(tables, plan, dev, init_on_device=True)
-    m.set_fused_optimizer(t.EmbOptimType.EXACT_ROWWISE_ADAGRAD, learning_rate=CFG["lr"], eps=CFG["eps"])
-    m.train()
-    keys = [f"f{i}" for i in range(F)]
-    lengths = torch.full((F * B,), P, dtype=torch.int32, device=dev)
-    L = F * B * P
-    batches = [torch.randint(0, rows, (L,), device=dev, generator=gen) for _ in range(N_BATCHES)]
-    grad_out = torch.randn((B, F * D), device=dev, generator=gen)
-
-    def barrier():
-        dist.barrier()
-        torch.cuda.synchronize()
-
-    def step(i):
-        kjt = t.KeyedJaggedTensor(keys, batches[i % N_BATCHES], lengths=lengths, stride=B)
-        out = m(kjt).values()
-        out.backward(grad_out)
-
-    for i in range(args.warmup):
-        step(i)
-    barrier()
-    sampler = ClockSampler(local_rank)
+    res, extra = sharded_workload(args.config, args, rank, world, dev, headline=True)
+    others = {}
+    want = [c for c in (args.configs.split(",") if args.configs not in ("auto", "none") else
+                        (["3", "4", "5"] if (args.configs == "auto" and world == 8 and args.config == 2) else []))]
+    for c in want:
+        try:
+            r_, _ = sharded_workload(int(c), args, rank, world, dev, headline=False)
+            others[c] = r_
+        except Exception as e:                              # keep the headline even if a side workload fails
+            others[c] = {"error": f"{type(e).__name__}: {e}"[:400]}
+    ok = res["parity_check"]["ok"] and all(o.get("parity_check", {}).get("ok", False) for o in others.values()
+                                            if "error" not in o)
     if rank == 0:
-        sampler.start()
-    launches0 = ops.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(args.steps):
-        step(args.warmup + i)
-    e1.record()
-    barrier()
-    launches = ops.launch_count() - launches0
-    tt = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
-    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    ms_total = float(tt.item())
-    ms_step = ms_total / args.steps
-    value = L * world * args.steps / (ms_total * 1e-3)
-    ops.check_error_flag(m._err_flag, "bench")
-
-    def barrier_fn():
-        barrier()
-    e2e = run_e2e(args, t, m, keys, lengths, batches, grad_out, F, B, D, L, world, dev, barrier_fn)
-    clocks = sampler.stop() if rank == 0 else None
-
-    # algorithmic bytes of this rank's share (same formula; unique rows from the expectation for uniform ids)
-    lookups_per_table = world * B * P
-    U = F / world * rows * (1.0 - np.exp(-lookups_per_table / rows)) if world > 1 else 0.0
-    bags_local = F / world * world * B
-    fwd_b, bwd_b, _ = algorithmic_bytes(L, bags_local, U, D)
-    peak, peak_src = measured_peak_gbs()
-    step_gbs = (fwd_b + bwd_b) / (ms_step * 1e-3) / 1e9
-    # bytes each rank sends per step: ids + lengths in, pooled rows out, gradient rows back
-    send = (world - 1) / world * (L * 8 + F * B * 4 + 2 * B * F * D * 4)
-    if rank == 0:
+        kinds = extra["kinds"]
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True,
+            "scaling": "strong" if args.config == 5 else "weak", "vs_baseline": None, "dtype": res["dtype"],
             "data": "synthetic",
-            "config": {"workload": WORKLOAD + f"; tables sharded over {world} GPUs, batch {B} per GPU",
-                       "lookups_per_step_per_gpu": L,
-                       "l2": f"inputs exceed L2: {13.3 / world:.1f} GB of tables per GPU, {N_BATCHES} rotating id batches",
-                       "parallelism": f"{kinds.count('table_wise')} tables table-wise (round-robin) + "
-                                      f"{n_cw} column-wise ({cw_shards} shards of {D // max(cw_shards, 1)} columns each; "
-                                      "a column shard keeps its own row-wise Adagrad state, as torchrec's does) + "
-                                      f"{kinds.count('row_wise')} row-wise over {world} ranks; "
-                                      "table-/column-wise lengths / ids / pooled rows / gradient rows are stored into "
-                                      "NVLink peer memory by the kernels themselves (no all-to-all); row-wise partial "
-                                      "sums and gradients use NCCL",
-                       "optimizer": "row-wise Adagrad lr 0.01 eps 1e-8, fused into backward"},
-            "roofline": {"bound": "hbm", "kernel": "whole sharded step per GPU (lookup + sort/unique + update + collectives)",
-                         "achieved": step_gbs, "peak": peak, "unit": "GB/s", "frac": step_gbs / peak, "traffic": None,
-                         "peak_source": peak_src, "algorithmic_bytes_per_launch": fwd_b + bwd_b, "launch_ms": ms_step,
-                         "note": "per-kernel rooflines are measured at N=1; unique rows per GPU from the uniform-id expectation"},
-            "nvlink": {"send_bytes_per_gpu_per_step": send, "achieved_GBps_if_serial": send / (ms_step * 1e-3) / 1e9,
-                       "peak_GBps": 770.0},
+            "config": {"workload": res["workload"], "lookups_per_step_per_gpu": extra["L_local"],
+                       "l2": "inputs exceed L2: GBs of tables per GPU, rotating id batches",
+                       "parallelism": res["plan"] + ("; a column shard keeps its own row-wise Adagrad state, as "
+                                                     "torchrec's does" if "column_wise" in kinds else ""),
+                       "optimizer": "row-wise Adagrad lr 0.01 eps 1e-8, fused into backward",
+                       "prefetch_input_dist": res["prefetch_input_dist"]},
+            "roofline": {"bound": "hbm", "kernel": "whole sharded step per GPU (lookup + sort/unique + update + exchanges), "
+                                                   "the rank with the most bytes",
+                         "achieved": res["hbm"]["achieved_GBps"], "peak": res["hbm"]["peak"], "unit": "GB/s",
+                         "frac": res["hbm"]["frac"], "traffic": None, "peak_source": extra["peak_src"],
+                         "algorithmic_bytes_per_launch": res["hbm"]["algorithmic_bytes_per_step_max_rank"],
+                         "launch_ms": res["ms_per_step"],
+                         "note": "per-kernel rooflines are measured at N=1; unique rows per GPU are measured, not estimated",
+                         "detail": res["hbm"]},
+            "nvlink": res["nvlink"],
+            "parity_check": res["parity_check"],
             "cpu_baseline": None,
-            "e2e": e2e,
-            "gpu_launches": int(launches),
-            "clocks": clocks,
+            "e2e": extra["e2e"],
+            "gpu_launches": res["gpu_launches"],
+            "clocks": extra["clocks"],
         }
+        if others:
+            line["configs"] = others
         print(json.dumps(line), flush=True)
+    dist.barrier()
     dist.destroy_process_group()
+    if not ok:
+        raise SystemExit("bench.py: parity_check failed (see the JSON line)")
 
 
 def run_e2e(args, t, ebc, keys, lengths_dev, batches, grad_out, F, B, D, L, world, dev, barrier):
@@ -564,6 +677,13 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ids", choices=["uniform", "zipf"], default="uniform",
                     help="N=1: id distribution; zipf = Zipf(1.05) hot-row variant of config 2 (reported separately)")
+    ap.add_argument("--config", type=int, choices=[2, 3, 4, 5], default=2,
+                    help="BASELINE config run as the headline (3-5 need N > 1; default 2)")
+    ap.add_argument("--configs", default="auto",
+                    help="N>1: further configs reported under `configs` after the headline: auto (3,4,5 on 8 GPUs), "
+                         "none, or a comma list such as 3,4")
+    ap.add_argument("--prefetch-input-dist", action="store_true",
+                    help="N>1: issue batch i+1's lengths / ids exchange before batch i's backward")
     ap.add_argument("--plan", choices=["tw", "mixed", "cw"], default="cw",
                     help="N>1: cw = table-wise round-robin with the tables that do not divide evenly split column-wise "
                          "(balanced; 21.1 G lookups/s at N=8), tw = all table-wise (19.5), mixed = remainder row-wise (16.7)")
@@ -575,6 +695,8 @@ def main():
             args.warmup = 3
         if int(os.environ.get("WORLD_SIZE", "1")) > 1:
             run_ours_sharded(args)
+        elif args.config != 2:
+            raise SystemExit("bench.py: configs 3-5 are sharded workloads, run them with --gpus >= 2 under torchrun")
         else:
             run_ours(args)
 
