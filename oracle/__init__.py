@@ -260,3 +260,64 @@ def jagged_1d_to_padded_dense(values, offsets, desired_length, padding_value):
     lib().orc_jagged_1d_to_padded_dense(_p(values), _p(offsets), c_int64(B), c_int64(desired_length),
                                         c_int64(padding_value), _p(dense))
     return dense
+
+
+# --------------------------------------------------------------------------- float64 yardstick
+def fp64_backward_update(w, D, state0, state1, grad, indices, offsets, row_base, rows, out_col, F, B, mode,
+                         optimizer, lr, eps=1e-8, wd=0.0, beta1=0.9, beta2=0.999, step=1, touched_only=True):
+    """float64 restatement of the fused backward + optimizer, independent of both the
+    C oracle and the kernels: np.add.at over occurrences, then the optimizer formulas.  It is the error
+    budget's yardstick: a summation order cannot matter at fp64 for the sizes the tests use.
+    `mode`: 0 sum, 1 mean, 2 none (grad is [L, D]).  Returns (w64, state0_64, state1_64, touched_mask, scale):
+    `scale[row, d]` = |w_old| + (step multiplier) * sum over occurrences of |gradient term|, the magnitude of
+    what enters each updated element.  An fp32 result is "within rtol" of this yardstick when
+    |got - w64| <= rtol * scale: the forward-error form for a sum (relative to the sum of magnitudes, not
+    to a result that cancellation can bring arbitrarily close to zero)."""
+    w64 = np.asarray(w, dtype=np.float64).copy()
+    total = w64.shape[0]
+    L = int(indices.size)
+    bag_of = np.repeat(np.arange(F * B, dtype=np.int64), np.diff(offsets).astype(np.int64))
+    f_of = bag_of // B
+    valid = (indices >= 0) & (indices < np.asarray(rows, dtype=np.int64)[f_of])
+    key = np.asarray(row_base, dtype=np.int64)[f_of] + indices
+    g = np.zeros((total, D), dtype=np.float64)
+    if mode == 2:
+        src = np.asarray(grad, dtype=np.float64)
+    else:
+        b_of = bag_of - f_of * B
+        cols = np.asarray(out_col, dtype=np.int64)[f_of][:, None] + np.arange(D)[None, :]
+        src = np.asarray(grad, dtype=np.float64)[b_of[:, None], cols]
+        if mode == 1:
+            src = src / np.diff(offsets).astype(np.float64)[bag_of][:, None]
+    np.add.at(g, key[valid], src[valid])
+    gabs = np.zeros((total, D), dtype=np.float64)
+    np.add.at(gabs, key[valid], np.abs(src[valid]))
+    scale = np.abs(w64).copy()
+    touched = np.zeros(total, dtype=bool)
+    touched[key[valid]] = True
+    s0 = None if state0 is None else np.asarray(state0, dtype=np.float64).copy()
+    s1 = None if state1 is None else np.asarray(state1, dtype=np.float64).copy()
+    t = touched
+    if optimizer == 0:                                   # SGD (L2 decay folded into the gradient)
+        gg = g[t] + wd * w64[t]
+        scale[t] += lr * gabs[t]
+        w64[t] -= lr * gg
+    elif optimizer == 1:                                 # row-wise Adagrad
+        gg = g[t] + wd * w64[t]
+        s0[t] += (gg * gg).sum(axis=1) / D
+        scale[t] += (lr / (np.sqrt(s0[t]) + eps))[:, None] * gabs[t]
+        w64[t] -= (lr / (np.sqrt(s0[t]) + eps))[:, None] * gg
+    else:                                                # ADAM, decoupled decay, touched rows only
+        gg = g[t]
+        s0[t] = beta1 * s0[t] + (1 - beta1) * gg
+        s1[t] = beta2 * s1[t] + (1 - beta2) * gg * gg
+        mhat = s0[t] / (1 - beta1 ** step)
+        vhat = s1[t] / (1 - beta2 ** step)
+        scale[t] += lr
+        w64[t] -= lr * (mhat / (np.sqrt(vhat) + eps) + wd * w64[t])
+    return w64, s0, s1, touched, scale
+
+
+def within_budget(got, want64, scale, rtol):
+    """max over elements of |got - want64| / (rtol * scale); <= 1 means inside the budget."""
+    return float((np.abs(np.asarray(got, dtype=np.float64) - want64) / (rtol * np.maximum(scale, 1e-30))).max())
