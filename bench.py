@@ -224,7 +224,7 @@ def run_ours(args):
     scratch = torch.empty(lay.total_bytes, dtype=torch.uint8, device=dev)
     out = torch.empty((B, F * D), dtype=torch.float32, device=dev)
     stages = ["forward", "linearize", "sort", "unique", "update"]
-    worklist = torch.empty(L // 64 + 2, dtype=torch.int32, device=dev)      # hot-row queue of the staged update
+    worklist = torch.empty(ops.hot_row_worklist_entries(L), dtype=torch.int32, device=dev)      # hot-row queue of the staged update
 
     def barrier():
         if world > 1:

@@ -321,11 +321,14 @@ typedef struct tdfo_optimizer_args {
  *   state0     ROWWISE_ADAGRAD: float[total_rows] sum of mean squared grads
  *              ADAM: float[total_rows, D] first moment;  SGD: NULL
  *   state1     ADAM: float[total_rows, D] second moment; else NULL
- * worklist (optional, uint32[worklist_entries], entries >= L/64 + 2): rows with more than 64
- *   occurrences ("hot" rows of a skewed id distribution) are queued here by the main kernel and
- *   reduced by a second kernel that puts a whole thread block on each such row (fixed
- *   assignment and combination order, so results are reproducible; the summation order differs
- *   from the strictly sequential one).  Without a worklist every row is reduced by one lane group.
+ * worklist (optional, uint32[worklist_entries], 16-byte aligned, entries >=
+ *   tdfo_hot_row_worklist_entries(L)): rows with more than 64 occurrences ("hot" rows of a skewed id
+ *   distribution) are skipped by the main kernel; a small kernel queues them here as (row, chunk) work
+ *   items and a third kernel puts a whole thread block on each chunk of at most max(2048, L/2048)
+ *   occurrences, so the hottest row is reduced by many blocks at once.  Shares of a chunk, chunks of a
+ *   row and their partial sums are combined in a fixed order: results are reproducible; the summation
+ *   order differs from the strictly sequential one.  Without a worklist every row is reduced by one
+ *   lane group.
  * ROWWISE_ADAGRAD: h += mean_d(g_d^2); w -= lr / (sqrt(h) + eps) * g.
  * SGD: w -= lr * g.  bf16 tables: fp32 math, round-to-nearest-even on store.
  * Replaces: upstream split_embedding_backward_codegen_{sgd,rowwise_adagrad,adam}
@@ -391,6 +394,8 @@ int tdfo_embedding_backward_prepare(const int64_t* indices, const int64_t* offse
                                     int32_t* err_flag,
                                     void* scratch, size_t scratch_bytes, void* stream);
 int tdfo_backward_scratch_layout(int64_t L, int64_t total_rows, tdfo_backward_layout* layout /* HOST */);
+/* uint32 entries the hot-row worklist of tdfo_sparse_update needs for L ids (pure host arithmetic). */
+size_t tdfo_hot_row_worklist_entries(int64_t L);
 int tdfo_embedding_backward_update(void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
                                    float* state0, float* state1,
                                    const float* grad_out, int64_t grad_stride,

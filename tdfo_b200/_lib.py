@@ -60,6 +60,7 @@ _SIGNATURES = {
     "tdfo_sparse_update": (c_int, [P, c_int32, c_int64, c_int32, P, P, P, c_int64, P, P, P, P, P, P, P, c_int32,
                                    c_int64, c_int64, c_int32, POINTER(OptimizerArgs), P, c_int64, P]),
     "tdfo_backward_scratch_bytes": (c_size_t, [c_int64, c_int64]),
+    "tdfo_hot_row_worklist_entries": (c_size_t, [c_int64]),
     "tdfo_backward_scratch_bytes_weighted": (c_size_t, [c_int64, c_int64]),
     "tdfo_backward_scratch_layout": (c_int, [c_int64, c_int64, POINTER(BackwardLayout)]),
     "tdfo_embedding_backward_update": (c_int, [P, c_int32, c_int64, c_int32, P, P, P, c_int64, P, P, P, P, P, P,

@@ -25,7 +25,10 @@ constexpr int kMaxPasses = 4;
 constexpr uint32_t kLbAgg  = 1u << 30;
 constexpr uint32_t kLbIncl = 2u << 30;
 constexpr uint32_t kLbMask = (1u << 30) - 1;
-constexpr int kLbBatch = 8;                             // look-back words requested per round trip
+#ifndef TDFO_SORT_LB_BATCH
+#define TDFO_SORT_LB_BATCH 8
+#endif
+constexpr int kLbBatch = TDFO_SORT_LB_BATCH;            // look-back words requested per round trip
 
 struct SortPlan {
     int passes;
@@ -127,7 +130,9 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __re
     for (int i = 0; i < kSortItems; ++i) {
         const int slot = warp * (kSortItems * 32) + i * 32 + lane;
         const uint32_t d = (slot < count) ? ((key[i] >> shift) & dmask) : (uint32_t)kRadix;
-#if TDFO_SORT_BALLOT_MATCH
+#if defined(TDFO_SORT_TIMING_NO_RANK)           // timing experiment only: results are wrong
+        const uint32_t peers = 1u << lane;
+#elif TDFO_SORT_BALLOT_MATCH
         // lanes holding the same digit, from one ballot per digit bit (10 bits: 9 + the "no key" bit)
         uint32_t peers = kFullMask;
 #pragma unroll
@@ -186,6 +191,9 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __re
             uint32_t excl = 0;
             int spins = 0;
             bool done = false;
+#if defined(TDFO_SORT_TIMING_NO_LOOKBACK)      // timing experiment only (tools/build_variant.py): results are wrong
+            done = true;
+#endif
             for (int t = tile - 1; t >= 0 && !done; t -= kLbBatch) {
                 uint32_t w[kLbBatch];
 #pragma unroll

@@ -61,9 +61,12 @@ struct UpdateArgs {
     const uint32_t* unique_keys;
     const uint32_t* seg_starts;
     const uint32_t* first_vals;
-    uint32_t* long_list;      // optional worklist of unique-row indices whose segments are long (hot rows)
-    uint32_t* long_count;
-    uint32_t long_cap;
+    // hot rows (segments longer than kLongSegment), see HotLayout; hot_hdr == nullptr: no hot-row path
+    uint32_t* hot_hdr;        // [0] records  [1] work items  [2] partial rows  [3] ticket of the block-per-chunk kernel
+    uint4* hot_recs;          // {unique-row index, first partial row, chunks, chunks done}
+    uint2* hot_items;         // {record, chunk}
+    float* hot_parts;         // partial sums of multi-chunk rows, `row floats` apart
+    uint32_t rec_cap, item_cap, part_cap, hot_chunk;
     const uint32_t* num_unique;
     const int64_t* offsets;
     const int64_t* feat_out_col;
@@ -83,8 +86,34 @@ struct UpdateArgs {
 
 // Launch shape of the update kernel: 8 warps per CTA, persistent grid of 148 x MINB CTAs.
 constexpr int kUpdCtaThreads = 256;
-constexpr uint32_t kLongSegment = 64;    // occurrences above which a row goes to the block-per-row kernel
+constexpr uint32_t kLongSegment = 64;    // occurrences above which a row goes to the block-per-chunk kernel
 constexpr int kLongMaxFloats = 8192;      // shared-memory floats for the partial sums of that kernel
+constexpr uint32_t kHotChunkMin = 2048;  // occurrences one CTA reduces at most (grows with L, see hot_layout)
+constexpr uint32_t kHotMaxRowFloats = 2048;   // widest row in fp32 accumulators (4096 B of bf16)
+
+// Hot-row work area inside the caller's worklist (uint32 words).  A row with more than kLongSegment
+// occurrences becomes one record and ceil(len / chunk) work items; rows longer than one chunk also get
+// that many partial-sum rows.  Counts: records <= L/65, items <= records + L/chunk, partial rows
+// <= 2 L/chunk, so nothing here can overflow for the L the layout was sized for.
+struct HotLayout {
+    uint32_t chunk, rec_cap, item_cap, part_cap;
+    size_t off_recs, off_items, off_parts, words;   // in uint32 words from the worklist start
+};
+
+static HotLayout hot_layout(int64_t L) {
+    HotLayout h;
+    const uint64_t l = (uint64_t)(L > 0 ? L : 0);
+    const uint64_t chunk = (l + 2047) / 2048 > kHotChunkMin ? (l + 2047) / 2048 : kHotChunkMin;
+    h.chunk = (uint32_t)chunk;
+    h.rec_cap = (uint32_t)(l / kLongSegment + 1);
+    h.item_cap = (uint32_t)(h.rec_cap + l / chunk + 1);
+    h.part_cap = (uint32_t)(2 * (l / chunk) + 2);
+    h.off_recs = 16;
+    h.off_items = h.off_recs + 4 * (size_t)h.rec_cap;
+    h.off_parts = (h.off_items + 2 * (size_t)h.item_cap + 3) / 4 * 4;
+    h.words = h.off_parts + (size_t)h.part_cap * kHotMaxRowFloats;
+    return h;
+}
 
 // Per unique row: key, first / one-past-last sorted position, payload of the first occurrence.
 struct RowMeta {
@@ -204,7 +233,7 @@ __device__ __forceinline__ void accumulate_occurrences(const UpdateArgs& a, uint
     constexpr int E = Chunk<T>::kElems;
     constexpr int GQ = E / 4;
     // gradient rows in flight: one in the main kernel (register budget), several in the hot-row kernel
-    constexpr int UB = !DEEP ? 1 : ((CPL * GQ <= 2) ? 4 : ((CPL * GQ <= 4) ? 2 : 1));
+    constexpr int UB = !DEEP ? 1 : ((CPL * GQ <= 2) ? 8 : ((CPL * GQ <= 4) ? 4 : ((CPL * GQ <= 8) ? 2 : 1)));
     for (uint32_t i = lo; i < hi; i += LPR) {
         const uint32_t n = min((uint32_t)LPR, hi - i);
         const uint32_t my_v = ((uint32_t)sub < n) ? __ldg(a.sorted_vals + i + sub) : 0u;
@@ -292,17 +321,9 @@ sparse_update_kernel(const UpdateArgs a) {
 #pragma unroll
         for (int q = 0; q < UR; ++q) {
             valid[q] = cur[q].key < a.total_rows;      // padding rows and the out-of-range marker fail this
-            // A hot row (very long segment) would be reduced serially by this one group: hand it to
-            // the block-per-row kernel that runs right after this one instead.
-            if (a.long_list != nullptr && valid[q] && cur[q].e - cur[q].s > kLongSegment) {
-                uint32_t slot = 0;
-                if (sub == 0) slot = atomicAdd(a.long_count, 1u);
-                slot = __shfl_sync(gmask, slot, grp * LPR);
-                if (slot < a.long_cap) {
-                    if (sub == 0) a.long_list[slot] = u0 + q * RPW + grp;
-                    valid[q] = false;
-                }
-            }
+            // A hot row (very long segment) would be reduced serially by this one group: skip it here.
+            // (hot_rows_enqueue_kernel has queued it for the block-per-chunk kernel that runs after this one)
+            if (a.hot_hdr != nullptr && cur[q].e - cur[q].s > kLongSegment) valid[q] = false;
             const float* grow = grad_row_of(a, valid[q] ? cur[q].v0 : 0u, scale[q]);
             const size_t wrow = (size_t)(valid[q] ? cur[q].key : 0u) * a.nchunks;
 #pragma unroll
@@ -343,62 +364,146 @@ sparse_update_kernel(const UpdateArgs a) {
     }
 }
 
-// Hot rows: one CTA per row.  Its G = 256 / LPR groups each reduce one contiguous share of the
-// row's occurrences in increasing order, the partial sums meet in shared memory and are added in
-// group order, so the result does not depend on timing; then group 0 applies the optimizer.
+// Hot rows, step 1: one thread per unique row; a row with more than kLongSegment occurrences becomes a
+// record plus one work item per chunk of `hot_chunk` occurrences.  (Slots are handed out by atomics, so
+// their order varies from run to run; the sums below do not depend on it.)
+__global__ void __launch_bounds__(256)
+hot_rows_enqueue_kernel(const uint32_t* __restrict__ seg_starts, const uint32_t* __restrict__ num_unique,
+                        const uint32_t* __restrict__ unique_keys, uint32_t total_rows, uint32_t* hdr, uint4* recs,
+                        uint2* items, uint32_t rec_cap, uint32_t item_cap, uint32_t part_cap, uint32_t chunk,
+                        int32_t* err_flag) {
+    const uint32_t nu = *num_unique;
+    const int lane = lane_id();
+    // whole warps walk the segment starts: one coalesced load per step, the neighbour's start by shuffle
+    for (uint32_t u0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; u0 < nu; u0 += gridDim.x * blockDim.x) {
+        const uint32_t u = u0 + lane;
+        const uint32_t s = (u <= nu) ? __ldg(seg_starts + u) : 0u;
+        uint32_t e = __shfl_down_sync(kFullMask, s, 1);
+        if (lane == 31) e = (u + 1 <= nu) ? __ldg(seg_starts + u + 1) : 0u;
+        if (u >= nu) continue;
+        const uint32_t len = e - s;
+        if (len <= kLongSegment || __ldg(unique_keys + u) >= total_rows) continue;
+        const uint32_t nch = (len + chunk - 1) / chunk;
+        const uint32_t slot = atomicAdd(hdr + 0, 1u);
+        const uint32_t ibase = atomicAdd(hdr + 1, nch);
+        const uint32_t pbase = nch > 1 ? atomicAdd(hdr + 2, nch) : 0u;
+        if (slot >= rec_cap || ibase + nch > item_cap || (nch > 1 && pbase + nch > part_cap)) {
+            if (err_flag) atomicOr(err_flag, TDFO_FLAG_SCAN_TIMEOUT);      // cannot happen for a correctly sized worklist
+            continue;
+        }
+        recs[slot] = make_uint4(u, pbase, nch, 0u);
+        for (uint32_t c = 0; c < nch; ++c) items[ibase + c] = make_uint2(slot, c);
+    }
+}
+
+// Hot rows, step 2: persistent CTAs take work items (row, chunk) from a ticket.  The G = 256 / LPR groups
+// of the CTA each reduce one contiguous share of the chunk's occurrences in increasing order, the partial
+// sums meet in shared memory and are added in group order.  A row of one chunk is updated right away; for a
+// longer row the chunk sum goes to its partial-sum row, and the CTA that finishes the row's last open chunk
+// adds the partial rows in chunk order and applies the optimizer.  Every sum has a fixed order, so the
+// result does not depend on timing or on which CTA did what.
 template <typename T, int LPR, int CPL, int OPT>
 __global__ void __launch_bounds__(kUpdCtaThreads)
 sparse_update_long_kernel(const UpdateArgs a) {
     constexpr int E = Chunk<T>::kElems;
     constexpr int G = kUpdCtaThreads / LPR;
-    constexpr int GQ = E / 4;
     __shared__ float s_part[kLongMaxFloats];
+    __shared__ uint32_t s_item;
+    __shared__ int s_last;
     const int lane = lane_id();
     const int sub = lane % LPR;
     const int grp_in_warp = lane / LPR;
     const int g_id = threadIdx.x / LPR;
     const unsigned gmask = (LPR == 32) ? kFullMask : (((1u << (LPR & 31)) - 1u) << (grp_in_warp * LPR));
-    const uint32_t n_long = min(*a.long_count, a.long_cap);
+    const uint32_t n_items = min(a.hot_hdr[1], a.item_cap);
     uint4* __restrict__ wbase = reinterpret_cast<uint4*>(a.weights);
     const int rowf = a.nchunks * E;                      // floats per row
     // groups that fit the shared buffer take part in the reduction (all of them for rows <= 1 KB)
     const int g_used = min(G, kLongMaxFloats / rowf);
-    for (uint32_t wi = blockIdx.x; wi < n_long; wi += gridDim.x) {
-        const uint32_t u = a.long_list[wi];
+    while (true) {
+        if (threadIdx.x == 0) s_item = atomicAdd(a.hot_hdr + 3, 1u);
+        __syncthreads();
+        const uint32_t item = s_item;
+        if (item >= n_items) break;
+        const uint2 it = a.hot_items[item];
+        const uint4 rec = a.hot_recs[it.x];
+        const uint32_t u = rec.x, pbase = rec.y, nch = rec.z, c = it.y;
         const uint32_t row = __ldg(a.unique_keys + u);
         const uint32_t s0 = __ldg(a.seg_starts + u), e0 = __ldg(a.seg_starts + u + 1);
+        const uint32_t lo_c = s0 + c * a.hot_chunk, hi_c = min(e0, lo_c + a.hot_chunk);
         float g[CPL][E];
 #pragma unroll
         for (int k = 0; k < CPL; ++k)
 #pragma unroll
             for (int i = 0; i < E; ++i) g[k][i] = 0.f;
         if (g_id < g_used) {
-            // group g_id reduces the g_id-th contiguous share of the segment, in order
-            const uint32_t share = (e0 - s0 + g_used - 1) / g_used;
-            const uint32_t lo = min(e0, s0 + (uint32_t)g_id * share), hi = min(e0, lo + share);
+            // group g_id reduces the g_id-th contiguous share of the chunk, in order
+            const uint32_t share = (hi_c - lo_c + g_used - 1) / g_used;
+            const uint32_t lo = min(hi_c, lo_c + (uint32_t)g_id * share), hi = min(hi_c, lo + share);
             accumulate_occurrences<T, LPR, CPL, true>(a, lo, hi, g, sub, grp_in_warp, gmask);
 #pragma unroll
             for (int k = 0; k < CPL; ++k) {
-                const int c = sub + k * LPR;
-                if (c < a.nchunks)
+                const int cc = sub + k * LPR;
+                if (cc < a.nchunks)
 #pragma unroll
-                    for (int i = 0; i < E; ++i) s_part[g_id * rowf + c * E + i] = g[k][i];
+                    for (int i = 0; i < E; ++i) s_part[g_id * rowf + cc * E + i] = g[k][i];
             }
         }
         __syncthreads();
         if (g_id == 0) {
-            float w[CPL][E];
 #pragma unroll
             for (int k = 0; k < CPL; ++k) {
-                const int c = sub + k * LPR;
+                const int cc = sub + k * LPR;
 #pragma unroll
                 for (int i = 0; i < E; ++i) {
                     float acc = 0.f;
-                    if (c < a.nchunks)
-                        for (int gi = 0; gi < g_used; ++gi) acc += s_part[gi * rowf + c * E + i];
+                    if (cc < a.nchunks)
+                        for (int gi = 0; gi < g_used; ++gi) acc += s_part[gi * rowf + cc * E + i];
                     g[k][i] = acc;
                 }
-                Chunk<T>::unpack(ld_row_128(wbase + (size_t)row * a.nchunks + min(c, a.nchunks - 1)), w[k]);
+            }
+        }
+        bool apply = g_id == 0;
+        if (nch > 1) {                                   // uniform over the CTA
+            float* prow = a.hot_parts + (size_t)pbase * rowf;
+            if (g_id == 0) {
+#pragma unroll
+                for (int k = 0; k < CPL; ++k) {
+                    const int cc = sub + k * LPR;
+                    if (cc < a.nchunks)
+#pragma unroll
+                        for (int i = 0; i < E; ++i) __stcg(prow + (size_t)c * rowf + cc * E + i, g[k][i]);
+                }
+                __threadfence();
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                const uint32_t done = atomicAdd(reinterpret_cast<uint32_t*>(a.hot_recs + it.x) + 3, 1u);
+                s_last = done + 1 == nch;
+            }
+            __syncthreads();
+            apply = apply && s_last;
+            if (apply) {                                 // last chunk of the row to finish: add the partial rows in chunk order
+                __threadfence();
+#pragma unroll
+                for (int k = 0; k < CPL; ++k) {
+                    const int cc = sub + k * LPR;
+#pragma unroll
+                    for (int i = 0; i < E; ++i) {
+                        float acc = 0.f;
+                        if (cc < a.nchunks)
+                            for (uint32_t pc = 0; pc < nch; ++pc) acc += __ldcg(prow + (size_t)pc * rowf + cc * E + i);
+                        g[k][i] = acc;
+                    }
+                }
+            }
+        }
+        if (apply) {
+            float w[CPL][E];
+#pragma unroll
+            for (int k = 0; k < CPL; ++k) {
+                const int cc = sub + k * LPR;
+                Chunk<T>::unpack(ld_row_128(wbase + (size_t)row * a.nchunks + min(cc, a.nchunks - 1)), w[k]);
             }
             const float h_old = (OPT == TDFO_OPT_ROWWISE_ADAGRAD) ? __ldcg(a.state0 + row) : 0.f;
             apply_row_update<T, LPR, CPL, OPT>(a, row, true, h_old, g, w, sub, gmask);
@@ -425,7 +530,7 @@ static int launch_update(const UpdateArgs& a, int opt, int64_t max_unique, cudaS
     }
     count_launch();
     TDFO_LAUNCH_CHECK("sparse_update");
-    if (a.long_list != nullptr) {
+    if (a.hot_hdr != nullptr) {
         const unsigned lb = kNumSMs * 2;
         switch (opt) {
             case TDFO_OPT_SGD:
@@ -521,16 +626,35 @@ int sparse_update_impl(void* weights, int32_t weights_dtype, int64_t total_rows,
                        const int64_t* offsets, const int64_t* feat_out_col, int32_t F, int64_t B,
                        int64_t L, int32_t pooling_mode, const tdfo_optimizer_args* opt,
                        uint32_t* worklist, int64_t worklist_entries, const float* psw, const uint32_t* pos_bag,
-                       cudaStream_t st) {
+                       int32_t* err_flag, cudaStream_t st) {
     if (L == 0) return TDFO_OK;
     const size_t esz = weights_dtype == TDFO_F32 ? 4 : 2;
     UpdateArgs a;
-    a.long_list = nullptr; a.long_count = nullptr; a.long_cap = 0;
-    if (worklist != nullptr && worklist_entries >= 2) {        // word 0 = counter, the rest = row indices
-        TDFO_CUDA(cudaMemsetAsync(worklist, 0, sizeof(uint32_t), st));
-        a.long_count = worklist;
-        a.long_list = worklist + 1;
-        a.long_cap = (uint32_t)(worklist_entries - 1);
+    a.hot_hdr = nullptr; a.hot_recs = nullptr; a.hot_items = nullptr; a.hot_parts = nullptr;
+    a.rec_cap = a.item_cap = a.part_cap = 0; a.hot_chunk = kHotChunkMin;
+    if (worklist != nullptr) {
+        const HotLayout h = hot_layout(L);
+        if ((size_t)worklist_entries < h.words || !aligned(worklist, 16)) {
+            set_error("sparse_update: the hot-row worklist needs %zu 16-byte-aligned uint32 entries for L = %lld "
+                      "(tdfo_hot_row_worklist_entries), got %lld", h.words, (long long)L, (long long)worklist_entries);
+            return TDFO_ERR_SCRATCH;
+        }
+        TDFO_CUDA(cudaMemsetAsync(worklist, 0, 16 * sizeof(uint32_t), st));
+        a.hot_hdr = worklist;
+        a.hot_recs = reinterpret_cast<uint4*>(worklist + h.off_recs);
+        a.hot_items = reinterpret_cast<uint2*>(worklist + h.off_items);
+        a.hot_parts = reinterpret_cast<float*>(worklist + h.off_parts);
+        a.rec_cap = h.rec_cap; a.item_cap = h.item_cap; a.hot_chunk = h.chunk;
+        // partial rows are `row floats` apart: a narrower row leaves room for more of them than the layout assumed
+        a.part_cap = (uint32_t)((size_t)h.part_cap * kHotMaxRowFloats / (size_t)D);
+        const int64_t mu = L < total_rows + 1 ? L : total_rows + 1;
+        int64_t eb = (mu + 255) / 256;
+        if (eb > kNumSMs * 8) eb = kNumSMs * 8;
+        hot_rows_enqueue_kernel<<<(unsigned)eb, 256, 0, st>>>(seg_starts, num_unique, unique_keys, (uint32_t)total_rows,
+                                                             a.hot_hdr, a.hot_recs, a.hot_items, a.rec_cap, a.item_cap,
+                                                             a.part_cap, a.hot_chunk, err_flag);
+        count_launch();
+        TDFO_LAUNCH_CHECK("hot_rows_enqueue");
     }
     a.weights = weights; a.state0 = state0; a.state1 = state1; a.grad = grad_out;
     a.sorted_vals = sorted_vals; a.unique_keys = unique_keys; a.seg_starts = seg_starts; a.first_vals = first_vals;
@@ -613,7 +737,7 @@ extern "C" int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t 
     TDFO_CHECK_ARG(pooling_mode != TDFO_POOL_MEAN || offsets, "sparse_update: MEAN pooling needs offsets");
     return sparse_update_impl(weights, weights_dtype, total_rows, D, state0, state1, grad_out, grad_stride,
                               sorted_vals, unique_keys, seg_starts, first_vals, num_unique, offsets, feat_out_col,
-                              F, B, L, pooling_mode, opt, worklist, worklist_entries, nullptr, nullptr,
+                              F, B, L, pooling_mode, opt, worklist, worklist_entries, nullptr, nullptr, nullptr,
                               static_cast<cudaStream_t>(stream));
 }
 
@@ -635,12 +759,14 @@ extern "C" int tdfo_backward_scratch_layout(int64_t L, int64_t total_rows, tdfo_
     layout->input_vals = A;
     layout->num_unique = 5 * A;
     layout->worklist = 5 * A + 256;
-    layout->worklist_entries = (size_t)(L / kLongSegment) + 2;     // counter + at most L/kLongSegment hot rows
+    layout->worklist_entries = hot_layout(L).words;                // records, work items, partial-sum rows
     const size_t sort_off = layout->worklist + align_up(layout->worklist_entries * sizeof(uint32_t), 256);
     const size_t scan_off = sort_off + radix_sort_scratch_bytes_impl(L, bits);
     layout->total_bytes = scan_off + tdfo_scan_scratch_bytes(L);
     return TDFO_OK;
 }
+
+extern "C" size_t tdfo_hot_row_worklist_entries(int64_t L) { return hot_layout(L).words; }
 
 extern "C" size_t tdfo_backward_scratch_bytes(int64_t L, int64_t total_rows) {
     tdfo_backward_layout lay;
@@ -709,7 +835,7 @@ static int backward_stages(int stages, const char* who, void* weights, int32_t w
         rc = sparse_update_impl(weights, weights_dtype, total_rows, D, state0, state1, grad_out, grad_stride,
                                 sv, uk, ss, fv, num_unique, offsets, feat_out_col, F, B, L, pooling_mode, opt,
                                 reinterpret_cast<uint32_t*>(base + lay.worklist), (int64_t)lay.worklist_entries,
-                                per_sample_weights, pos_bag, st);
+                                per_sample_weights, pos_bag, err_flag, st);
         if (rc) return rc;
     }
     return TDFO_OK;

@@ -357,7 +357,7 @@ def unique_segments(sorted_keys: torch.Tensor, err_flag=None, sorted_vals: Optio
 
 def sparse_update(group: TableGroup, grad_out, sorted_vals, unique_keys, seg_starts, first_vals, num_unique, offsets,
                   B, L, pooling_mode, opt: OptimizerArgs, worklist: Optional[torch.Tensor] = None):
-    """``worklist``: optional int32 tensor of at least L/64 + 2 entries for the hot-row kernel."""
+    """``worklist``: optional int32 tensor of ``hot_row_worklist_entries(L)`` entries for the hot-row kernels."""
     grad_out = _cuda(grad_out, torch.float32, "grad_out")
     w = group.weights
     grad_stride = group.D if pooling_mode == POOL_NONE else grad_out.shape[-1]
@@ -367,6 +367,10 @@ def sparse_update(group: TableGroup, grad_out, sorted_vals, unique_keys, seg_sta
         _ptr(offsets),
         _ptr(group.feat_out_col), group.F, B, L, pooling_mode, ctypes.byref(opt), _ptr(worklist),
         0 if worklist is None else worklist.numel(), _stream()))
+
+
+def hot_row_worklist_entries(L: int) -> int:
+    return int(_lib.load().tdfo_hot_row_worklist_entries(L))
 
 
 def copy_feature_blocks(src: torch.Tensor, dst: torch.Tensor, B: int, D: int, meta: torch.Tensor) -> None:

@@ -2,7 +2,10 @@
 import os, sys, statistics
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
+from pathlib import Path
 from tdfo_b200 import ops, _lib
+if os.environ.get("TDFO_TUNE_LIB"):          # a variant built by tools/build_variant.py
+    _lib.LIB_PATH = Path(os.environ["TDFO_TUNE_LIB"]).resolve()
 
 F, rows, D, P, B = 26, 1_000_000, 128, 20, 16384
 dev = torch.device("cuda")
@@ -20,7 +23,7 @@ grad = torch.randn((B, F * D), device=dev, generator=gen)
 opt = ops.make_optimizer_args(_lib.OPT_ROWWISE_ADAGRAD, 0.01, 1e-8)
 lay = ops.backward_layout(L, F * rows)
 out = torch.empty((B, F * D), device=dev)
-worklist = torch.empty(L // 64 + 2, dtype=torch.int32, device=dev)
+worklist = torch.empty(ops.hot_row_worklist_entries(L), dtype=torch.int32, device=dev)
 U = int(torch.unique(batches[0] + torch.arange(F, device=dev).repeat_interleave(B * P) * rows).numel())
 upd_bytes = F * B * D * 4 + U * (2 * D * 4 + 8)
 fwd_bytes = L * (D * 4 + 8) + (F * B + 1) * 8 + F * B * D * 4
