@@ -226,6 +226,149 @@ pooled_forward_kernel(const LookupArgs a) {
     if (flags && a.err_flag) atomicOr(a.err_flag, (int)flags);
 }
 
+// Short bags (about one id per bag: the Criteo-style one-hot features of BASELINE config 3).  The bag-at-a-time
+// kernel above has a single row in flight per warp there.  Here a warp takes a block of 32 consecutive bags,
+// reads their ids as one coalesced stream and gathers the rows kStreamUnroll at a time ACROSS bag boundaries;
+// a bag's pooled row is written when the stream moves on to the next bag.  Rows are added in bag order by
+// the whole warp (no sub-group tree), so the result equals the sequential sum.
+constexpr int kStreamUnroll = 8;
+constexpr int kStreamBlocksPerSM = 2;    // 128 registers: the eight rows in flight must not spill
+
+template <typename T, int CPL, bool WEIGHTED>
+__global__ void __launch_bounds__(kFwdThreads, kStreamBlocksPerSM)
+pooled_forward_stream_kernel(const LookupArgs a) {
+    constexpr int E = Chunk<T>::kElems;
+    constexpr int U = (CPL > 1) ? (kStreamUnroll / CPL > 1 ? kStreamUnroll / CPL : 1) : kStreamUnroll;
+    const int lane = lane_id();
+    const int64_t nwarps = (int64_t)gridDim.x * (kFwdThreads / 32);
+    const uint4* __restrict__ wbase = reinterpret_cast<const uint4*>(a.weights);
+    uint32_t flags = 0;
+
+    auto store_row = [&](int64_t g, float scale, const float (&acc)[CPL][E]) {
+        const int f = (int)((uint64_t)g / (uint64_t)a.B);
+        const int64_t b = g - (int64_t)f * a.B;
+        float* obase = a.out;
+        int64_t brow = b;
+        if (a.peer_out) {                               // sharded output dist fused in (see pooled_forward_kernel)
+            const int64_t src = b / a.peer_batch;
+            brow = b - src * a.peer_batch;
+            obase = reinterpret_cast<float*>(__ldg(a.peer_out + src));
+        }
+        float* orow = obase + brow * a.out_stride + __ldg(a.feat_out_col + f);
+#pragma unroll
+        for (int k = 0; k < CPL; ++k) {
+            const int c = lane + k * 32;
+            if (c < a.nchunks) {
+#pragma unroll
+                for (int i = 0; i < E; i += 4)
+                    st_stream_128(orow + (size_t)c * E + i,
+                                  make_uint4(__float_as_uint(acc[k][i] * scale), __float_as_uint(acc[k][i + 1] * scale),
+                                             __float_as_uint(acc[k][i + 2] * scale), __float_as_uint(acc[k][i + 3] * scale)));
+            }
+        }
+    };
+
+    for (int64_t g0 = ((int64_t)blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5)) * 32; g0 < a.num_bags;
+         g0 += nwarps * 32) {
+        const int nb = (int)min((int64_t)32, a.num_bags - g0);           // bags in this block
+        int64_t my_s = __ldg(a.offsets + g0 + min(lane, nb - 1));
+        int64_t my_e = __ldg(a.offsets + g0 + min(lane, nb - 1) + 1);
+        if (my_e > a.L) {                                                 // offsets past the ids given: cut there
+            flags |= TDFO_FLAG_OFFSETS_RANGE;
+            my_e = a.L;
+            my_s = min(my_s, a.L);
+        }
+        if (lane >= nb) my_s = my_e;                                      // lanes past the block: an empty bag at the end
+        const int64_t s0 = __shfl_sync(kFullMask, my_s, 0), e0 = __shfl_sync(kFullMask, my_e, nb - 1);
+        float acc[CPL][E];
+#pragma unroll
+        for (int k = 0; k < CPL; ++k)
+#pragma unroll
+            for (int i = 0; i < E; ++i) acc[k][i] = 0.f;
+        // empty bags never show up in the id stream: their rows are zero
+        unsigned empty = __ballot_sync(kFullMask, lane < nb && my_e == my_s);
+        while (empty) {
+            const int eb = __ffs(empty) - 1;
+            empty &= empty - 1;
+            store_row(g0 + eb, 1.f, acc);
+        }
+        int cur_bag = -1;
+        for (int64_t base = s0; base < e0; base += 32) {
+            const int n = (int)min((int64_t)32, e0 - base);
+            const int64_t p = base + lane;
+            uint32_t my_row = 0xffffffffu;
+            int my_bag = 0;
+            float my_w = 1.f;
+            {   // bag of position p: number of bags of the block that end at or before p (offsets are non-decreasing)
+                int lo = 0;
+#pragma unroll
+                for (int step = 16; step > 0; step >>= 1) {
+                    const int64_t e = __shfl_sync(kFullMask, my_e, min(lo + step - 1, 31));
+                    if (lo + step <= 32 && e <= p) lo += step;
+                }
+                my_bag = min(lo, nb - 1);
+            }
+            if (lane < n) {
+                const int64_t g = g0 + my_bag;
+                const int f = (int)((uint64_t)g / (uint64_t)a.B);
+                const int64_t idx = __ldg(a.indices + p);
+                if ((uint64_t)idx < (uint64_t)__ldg(a.feat_rows + f)) my_row = (uint32_t)(__ldg(a.feat_row_base + f) + idx);
+                else flags |= TDFO_FLAG_INDEX_OOB;
+                if (WEIGHTED) my_w = __ldg(a.psw + p);
+                if (a.sort_keys) {
+                    a.sort_keys[p] = (my_row == 0xffffffffu) ? a.oob_key : my_row;
+                    a.sort_vals[p] = (uint32_t)g;
+                }
+            }
+            for (int j0 = 0; j0 < n; j0 += U) {
+                uint4 v[U][CPL];
+                int bag[U];
+                float w[U];
+                bool ok[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {                             // unconditional loads, masked when consumed
+                    const int j = min(j0 + u, 31);
+                    const uint32_t row = __shfl_sync(kFullMask, my_row, j);
+                    bag[u] = __shfl_sync(kFullMask, my_bag, j);
+                    w[u] = WEIGHTED ? __shfl_sync(kFullMask, my_w, j) : 1.f;
+                    ok[u] = (j0 + u < n) && (row != 0xffffffffu);
+                    const size_t rbase = (size_t)(ok[u] ? row : 0u) * a.nchunks;
+#pragma unroll
+                    for (int k = 0; k < CPL; ++k) v[u][k] = ldg_stream_128(wbase + rbase + min(lane + k * 32, a.nchunks - 1));
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    if (j0 + u < n) {                                     // uniform over the warp
+                        if (bag[u] != cur_bag) {
+                            if (cur_bag >= 0) {
+                                const int64_t len = __shfl_sync(kFullMask, my_e - my_s, cur_bag);
+                                store_row(g0 + cur_bag, a.mean ? 1.f / (float)len : 1.f, acc);
+                            }
+#pragma unroll
+                            for (int k = 0; k < CPL; ++k)
+#pragma unroll
+                                for (int i = 0; i < E; ++i) acc[k][i] = 0.f;
+                            cur_bag = bag[u];
+                        }
+#pragma unroll
+                        for (int k = 0; k < CPL; ++k) {
+                            float x[E];
+                            Chunk<T>::unpack(v[u][k], x);
+#pragma unroll
+                            for (int i = 0; i < E; ++i) acc[k][i] = fmaf(w[u], ok[u] ? x[i] : 0.f, acc[k][i]);
+                        }
+                    }
+                }
+            }
+        }
+        if (cur_bag >= 0) {
+            const int64_t len = __shfl_sync(kFullMask, my_e - my_s, cur_bag);
+            store_row(g0 + cur_bag, a.mean ? 1.f / (float)len : 1.f, acc);
+        }
+    }
+    if (flags && a.err_flag) atomicOr(a.err_flag, (int)flags);
+}
+
 // Sequence lookup (EmbeddingCollection): out[p,:] = W[row_base(f(p)) + indices[p], :].
 // One LPR-lane group per id; feature of p by binary search over the F+1 feature
 // boundaries offsets[f*B] staged in shared memory.
@@ -290,6 +433,18 @@ static int launch_forward(const LookupArgs& a, int pooling_mode, cudaStream_t st
         sequence_forward_kernel<T, LPR, CPL><<<(unsigned)blocks, kFwdThreads, 0, st>>>(a);
     } else {
         if (a.num_bags == 0) return TDFO_OK;
+        if (a.L < 4 * a.num_bags) {
+            // short bags (fewer than 4 ids on average): stream the ids of 32-bag blocks, rows in flight across bags
+            constexpr int SCPL = (LPR == 32) ? CPL : 1;
+            const int64_t warps = (a.num_bags + 31) / 32;
+            int64_t blocks = (warps + kFwdThreads / 32 - 1) / (kFwdThreads / 32);
+            if (blocks > (int64_t)kNumSMs * kStreamBlocksPerSM) blocks = (int64_t)kNumSMs * kStreamBlocksPerSM;
+            if (a.psw) pooled_forward_stream_kernel<T, SCPL, true><<<(unsigned)blocks, kFwdThreads, 0, st>>>(a);
+            else       pooled_forward_stream_kernel<T, SCPL, false><<<(unsigned)blocks, kFwdThreads, 0, st>>>(a);
+            count_launch();
+            TDFO_LAUNCH_CHECK("embedding_forward");
+            return TDFO_OK;
+        }
         int64_t blocks = (a.num_bags + kFwdThreads / 32 - 1) / (kFwdThreads / 32);
         if (blocks > (int64_t)kNumSMs * kFwdBlocksPerSM) blocks = (int64_t)kNumSMs * kFwdBlocksPerSM;
         if (a.psw) pooled_forward_kernel<T, LPR, CPL, true><<<(unsigned)blocks, kFwdThreads, 0, st>>>(a);

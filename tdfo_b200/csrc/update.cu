@@ -550,9 +550,17 @@ static int launch_update(const UpdateArgs& a, int opt, int64_t max_unique, cudaS
 // 512 B row, one row per group per step, 3 CTAs / SM (80 registers, no spills) = 1.46 ms;
 // anything that spills, or 32 lanes per row, is 15-60 % slower.  Few lanes per row matter:
 // per-row bookkeeping is replicated in every lane of the group.
+#ifndef TDFO_UPD_PREFETCH
+#define TDFO_UPD_PREFETCH 0
+#endif
+#ifndef TDFO_UPD_MINB
+#define TDFO_UPD_MINB 3
+#endif
 template <typename T>
 static int dispatch_update(const UpdateArgs& a, int opt, int64_t max_unique, cudaStream_t st) {
     const int n = a.nchunks;
+    constexpr bool kPf = TDFO_UPD_PREFETCH != 0;
+    constexpr int kMb = TDFO_UPD_MINB;
     constexpr bool kWide = sizeof(T) == 4;          // fp32: 4 chunks per lane; bf16 (8 elems / chunk): 2
     if (kWide) {
         if (n <= 1)   return launch_update<T, 1, 1, 1, 3, false>(a, opt, max_unique, st);
@@ -560,7 +568,7 @@ static int dispatch_update(const UpdateArgs& a, int opt, int64_t max_unique, cud
         if (n <= 4)   return launch_update<T, 1, 4, 1, 3, false>(a, opt, max_unique, st);
         if (n <= 8)   return launch_update<T, 2, 4, 1, 3, false>(a, opt, max_unique, st);
         if (n <= 16)  return launch_update<T, 4, 4, 1, 3, false>(a, opt, max_unique, st);
-        if (n <= 32)  return launch_update<T, 8, 4, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 32)  return launch_update<T, 8, 4, 1, kMb, kPf>(a, opt, max_unique, st);
         if (n <= 64)  return launch_update<T, 16, 4, 1, 2, false>(a, opt, max_unique, st);
         if (n <= 128) return launch_update<T, 32, 4, 1, 2, false>(a, opt, max_unique, st);
         if (n <= 256) return launch_update<T, 32, 8, 1, 2, false>(a, opt, max_unique, st);
@@ -569,7 +577,7 @@ static int dispatch_update(const UpdateArgs& a, int opt, int64_t max_unique, cud
         if (n <= 2)   return launch_update<T, 1, 2, 1, 3, false>(a, opt, max_unique, st);
         if (n <= 4)   return launch_update<T, 2, 2, 1, 3, false>(a, opt, max_unique, st);
         if (n <= 8)   return launch_update<T, 4, 2, 1, 3, false>(a, opt, max_unique, st);
-        if (n <= 16)  return launch_update<T, 8, 2, 1, 3, false>(a, opt, max_unique, st);
+        if (n <= 16)  return launch_update<T, 8, 2, 1, kMb, kPf>(a, opt, max_unique, st);
         if (n <= 32)  return launch_update<T, 16, 2, 1, 3, false>(a, opt, max_unique, st);
         if (n <= 64)  return launch_update<T, 32, 2, 1, 3, false>(a, opt, max_unique, st);
         if (n <= 128) return launch_update<T, 32, 4, 1, 2, false>(a, opt, max_unique, st);
