@@ -148,24 +148,120 @@ def cpu_arm(steps: int, warmup: int, sample_batch: int, rows: int | None = None)
         if i >= warmup:
             times.append(dt)
     t = sum(times)
+    frac = "the whole workload batch" if B == CFG["batch"] else f"1/{CFG['batch'] // B} of the workload batch"
     info = {"cores": cores, "kind": "port",
-            "sample": f"{steps} steps of batch {B} (1/{CFG['batch'] // B} of the workload batch, L={L} lookups/step), "
-                      f"{F} tables x {rows} rows x dim {D} fp32, oracle/tdfo_oracle.c with OpenMP"}
+            "sample": f"{steps} steps of batch {B} ({frac}, L={L} lookups/step), "
+                      f"{F} tables x {rows} rows x dim {D} fp32, oracle/tdfo_oracle.c; every stage (lookup, linearise, "
+                      f"counting sort, run-length, update) runs on all {cores} OpenMP threads"}
     return L * steps / t, t / steps * 1e3, info
+
+
+# ----------------------------------------------------------------------------- the reference's literal CPU mode
+DDP_CFG1 = dict(tables=[("user", 6040, ["user"], 1), ("movie", 3952, ["movie", "history"], 20), ("gender", 2, ["gender"], 1),
+                        ("age", 7, ["age"], 1), ("occupation", 21, ["occupation"], 1), ("zip", 3439, ["zip"], 1),
+                        ("genre", 18, ["genres"], 6)], D=16, B=16, W=2)
+
+
+def _ddp_rank(rank, port, steps, warmup, q):
+    """One rank of BASELINE config 1 the way the reference runs on CPU (torchrec/train.py:192-195,255-260):
+    plain torch modules under DistributedDataParallel over gloo, dense [V, D] embedding gradients all-reduced
+    every step, a dense optimizer over every row.  None of this repository's code is on this path."""
+    import torch
+    import torch.distributed as dist
+    import torch.nn as nn
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=DDP_CFG1["W"])
+    torch.set_num_threads(max(1, (os.cpu_count() or 2) // DDP_CFG1["W"]))
+    torch.manual_seed(7)
+    D, B = DDP_CFG1["D"], DDP_CFG1["B"]
+    feats = [(f, rows, mx if f not in ("movie",) else 1) for _, rows, fs, mx in DDP_CFG1["tables"] for f in fs]
+
+    class Model(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.bags = nn.ModuleDict({name: nn.EmbeddingBag(rows, D, mode="sum") for name, rows, _, _ in DDP_CFG1["tables"]})
+            self.mlp = nn.Sequential(nn.Linear(len(feats) * D, 64), nn.ReLU(), nn.Linear(64, 32), nn.ReLU(), nn.Linear(32, 1))
+            self.table_of = {f: name for name, _, fs, _ in DDP_CFG1["tables"] for f in fs}
+
+        def forward(self, batch):
+            return self.mlp(torch.cat([self.bags[self.table_of[f]](ids, off) for f, (ids, off) in batch.items()], dim=1))
+
+    model = nn.parallel.DistributedDataParallel(Model())
+    opt = torch.optim.Adam(model.parameters(), lr=3e-4, weight_decay=1e-4)       # torchrec/train.py:258-260
+    bce = nn.BCEWithLogitsLoss()
+    rng = np.random.default_rng(100 + rank)
+    lookups = 0
+    t0 = None
+    for i in range(warmup + steps):
+        if i == warmup:
+            dist.barrier()
+            t0 = time.perf_counter()
+        batch = {}
+        for f, rows, mx in feats:
+            ln = np.ones(B, np.int64) if mx == 1 else rng.integers(1, mx + 1, size=B)
+            off = np.concatenate([[0], np.cumsum(ln)[:-1]])
+            batch[f] = (torch.from_numpy(rng.integers(0, rows, size=int(ln.sum()))), torch.from_numpy(off))
+            if i >= warmup:
+                lookups += int(ln.sum())
+        loss = bce(model(batch), torch.from_numpy(rng.integers(0, 2, size=(B, 1)).astype(np.float32)))
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+    dist.barrier()
+    dt = time.perf_counter() - t0
+    tot = torch.tensor([float(lookups)])
+    dist.all_reduce(tot)
+    if rank == 0:
+        q.put((float(tot.item()) / dt, dt / steps * 1e3))
+    dist.destroy_process_group()
+
+
+def cpu_ddp_baseline(steps=200, warmup=20):
+    """BASELINE config 1 timed in the reference's own CPU mode; returns the `cpu_baseline_ddp` block."""
+    import socket
+    import torch.multiprocessing as mp
+    with socket.socket() as s_:
+        s_.bind(("127.0.0.1", 0))
+        port = s_.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_ddp_rank, args=(r, port, steps, warmup, q)) for r in range(DDP_CFG1["W"])]
+    for p_ in procs:
+        p_.start()
+    value = ms = None
+    deadline = time.time() + 300
+    while time.time() < deadline:
+        try:
+            value, ms = q.get(timeout=1.0)
+            break
+        except Exception:
+            if not any(p_.is_alive() for p_ in procs):       # a rank died: report the block as unmeasured
+                break
+    for p_ in procs:
+        p_.join(timeout=60)
+        if p_.is_alive():
+            p_.terminate()
+    return {"value": value, "unit": UNIT, "ms_per_step": ms, "world_size": DDP_CFG1["W"], "steps": steps,
+            "kind": "reference mode restated with torch modules (torchrec itself is not installable here)",
+            "workload": "config 1: MovieLens-1M-shaped EmbeddingBag tables (user 6040, movie 3952 + history bag, gender, age, "
+                        "occupation, zip, genres) dim 16 + MLP(64,32,1), batch 16 per rank, DistributedDataParallel over gloo, "
+                        "dense embedding gradients all-reduced, dense Adam over every row (torchrec/train.py:255-260)"}
 
 
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    value, ms, info = cpu_arm(args.steps, min(args.warmup, 1), sample_batch=CFG["batch"] // 8)
+    # same workload, same batch, same step / warm-up counts as the GPU arm (about one second per step on 16 cores)
+    value, ms, info = cpu_arm(args.steps, args.warmup, sample_batch=CFG["batch"])
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": min(args.warmup, 1), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "note": "CPU arm: oracle port of the path on the host cores; the reference's own "
                    "CPU kernels (torchrec/fbgemm_gpu) are not installable on this image"},
         "cpu_baseline": {"value": value, "unit": UNIT, **info},
+        "cpu_baseline_ddp": cpu_ddp_baseline(),
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -317,12 +413,13 @@ def run_ours(args):
     e2e = run_e2e(args, t, ebc, keys, lengths, batches, grad_out, F, B, D, L, world, dev, barrier)
 
     # ---------------- CPU baseline on rank 0 at N=1
-    cpu = None
+    cpu = cpu_ddp = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         del ebc, grp, scratch, out, batches
         torch.cuda.empty_cache()
-        v, _, info = cpu_arm(steps=3, warmup=1, sample_batch=B // 8)
+        v, _, info = cpu_arm(steps=3, warmup=1, sample_batch=B)
         cpu = {"value": v, "unit": UNIT, **info}
+        cpu_ddp = cpu_ddp_baseline()
 
     if rank == 0:
         line = {
@@ -339,6 +436,7 @@ def run_ours(args):
                               "frac_of_measured_peak": step_gbs / peak, "frac_of_8TBps_spec": step_gbs / 8000.0},
             "kernels": kernels,
             "cpu_baseline": cpu,
+            "cpu_baseline_ddp": cpu_ddp,
             "e2e": e2e,
             "gpu_launches": int(launches),
             "clocks": clocks,

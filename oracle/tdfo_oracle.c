@@ -191,11 +191,12 @@ int orc_linearize_indices(const int64_t* indices, const int64_t* offsets, const 
                           const int64_t* feat_rows, int32_t F, int64_t B, int64_t total_rows,
                           int32_t pooling_mode, uint32_t* keys, uint32_t* vals) {
     int oob = 0;
+#pragma omp parallel for schedule(static) reduction(| : oob)
     for (int64_t g = 0; g < (int64_t)F * B; ++g) {
         const int f = (int)(g / B);
         for (int64_t p = offsets[g]; p < offsets[g + 1]; ++p) {
             const int64_t idx = indices[p];
-            if (idx < 0 || idx >= feat_rows[f]) { keys[p] = (uint32_t)total_rows; oob = 1; }
+            if (idx < 0 || idx >= feat_rows[f]) { keys[p] = (uint32_t)total_rows; oob |= 1; }
             else keys[p] = (uint32_t)(feat_row_base[f] + idx);
             vals[p] = pooling_mode == ORC_POOL_NONE ? (uint32_t)p : (uint32_t)g;
         }
@@ -208,22 +209,47 @@ int orc_linearize_indices(const int64_t* indices, const int64_t* offsets, const 
  * 16-bit digits; any stable sort gives the same permutation. */
 void orc_sort_pairs_stable(const uint32_t* keys_in, const uint32_t* vals_in, int64_t n,
                            uint32_t* keys_out, uint32_t* vals_out) {
+    /* Each pass: the input is cut into T contiguous chunks (one per thread); chunk c counts its digits,
+     * the exclusive prefix over (digit, chunk) gives every chunk its own output cursor per digit, and the
+     * chunks scatter independently.  Chunks are taken in input order inside a digit, so the pass is stable
+     * and the result is the same for any T. */
     uint32_t* tk = (uint32_t*)malloc(sizeof(uint32_t) * (size_t)(n > 0 ? n : 1));
     uint32_t* tv = (uint32_t*)malloc(sizeof(uint32_t) * (size_t)(n > 0 ? n : 1));
-    int64_t* count = (int64_t*)malloc(sizeof(int64_t) * 65537);
+    int T = 1;
+#ifdef _OPENMP
+    T = omp_get_max_threads();
+#endif
+    if (n < 65536 || T < 1) T = 1;
+    int64_t* count = (int64_t*)malloc(sizeof(int64_t) * 65536 * (size_t)T);
     for (int pass = 0; pass < 2; ++pass) {
         const uint32_t* sk = pass == 0 ? keys_in : tk;
         const uint32_t* sv = pass == 0 ? vals_in : tv;
         uint32_t* dk = pass == 0 ? tk : keys_out;
         uint32_t* dv = pass == 0 ? tv : vals_out;
         const int shift = 16 * pass;
-        memset(count, 0, sizeof(int64_t) * 65537);
-        for (int64_t i = 0; i < n; ++i) count[((sk[i] >> shift) & 0xffffu) + 1]++;
-        for (int d = 0; d < 65536; ++d) count[d + 1] += count[d];
-        for (int64_t i = 0; i < n; ++i) {
-            const int64_t slot = count[(sk[i] >> shift) & 0xffffu]++;
-            dk[slot] = sk[i];
-            dv[slot] = sv[i];
+        memset(count, 0, sizeof(int64_t) * 65536 * (size_t)T);
+#pragma omp parallel for schedule(static, 1) num_threads(T)
+        for (int c = 0; c < T; ++c) {
+            int64_t* cnt = count + (size_t)c * 65536;
+            const int64_t lo = n * c / T, hi = n * (c + 1) / T;
+            for (int64_t i = lo; i < hi; ++i) cnt[(sk[i] >> shift) & 0xffffu]++;
+        }
+        int64_t run = 0;
+        for (int d = 0; d < 65536; ++d)
+            for (int c = 0; c < T; ++c) {
+                const int64_t x = count[(size_t)c * 65536 + d];
+                count[(size_t)c * 65536 + d] = run;
+                run += x;
+            }
+#pragma omp parallel for schedule(static, 1) num_threads(T)
+        for (int c = 0; c < T; ++c) {
+            int64_t* cnt = count + (size_t)c * 65536;
+            const int64_t lo = n * c / T, hi = n * (c + 1) / T;
+            for (int64_t i = lo; i < hi; ++i) {
+                const int64_t slot = cnt[(sk[i] >> shift) & 0xffffu]++;
+                dk[slot] = sk[i];
+                dv[slot] = sv[i];
+            }
         }
     }
     free(tk); free(tv); free(count);
@@ -233,14 +259,35 @@ void orc_sort_pairs_stable(const uint32_t* keys_in, const uint32_t* vals_in, int
  * run starts; seg_starts[num_unique] = n.  Returns num_unique. */
 int64_t orc_unique_segments(const uint32_t* sorted_keys, int64_t n, uint32_t* unique_keys,
                             uint32_t* seg_starts) {
-    int64_t u = 0;
-    for (int64_t i = 0; i < n; ++i) {
-        if (i == 0 || sorted_keys[i] != sorted_keys[i - 1]) {
-            unique_keys[u] = sorted_keys[i];
-            seg_starts[u] = (uint32_t)i;
-            ++u;
+    /* chunks count their run heads, an exclusive prefix places them, chunks write independently */
+    int T = 1;
+#ifdef _OPENMP
+    T = omp_get_max_threads();
+#endif
+    if (n < 65536 || T < 1) T = 1;
+    int64_t* heads = (int64_t*)calloc((size_t)T + 1, sizeof(int64_t));
+#pragma omp parallel for schedule(static, 1) num_threads(T)
+    for (int c = 0; c < T; ++c) {
+        const int64_t lo = n * c / T, hi = n * (c + 1) / T;
+        int64_t h = 0;
+        for (int64_t i = lo; i < hi; ++i) h += (i == 0 || sorted_keys[i] != sorted_keys[i - 1]);
+        heads[c + 1] = h;
+    }
+    for (int c = 0; c < T; ++c) heads[c + 1] += heads[c];
+#pragma omp parallel for schedule(static, 1) num_threads(T)
+    for (int c = 0; c < T; ++c) {
+        const int64_t lo = n * c / T, hi = n * (c + 1) / T;
+        int64_t u = heads[c];
+        for (int64_t i = lo; i < hi; ++i) {
+            if (i == 0 || sorted_keys[i] != sorted_keys[i - 1]) {
+                unique_keys[u] = sorted_keys[i];
+                seg_starts[u] = (uint32_t)i;
+                ++u;
+            }
         }
     }
+    const int64_t u = heads[T];
+    free(heads);
     seg_starts[u] = (uint32_t)n;
     return u;
 }

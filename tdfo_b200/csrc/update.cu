@@ -561,6 +561,10 @@ static int dispatch_update(const UpdateArgs& a, int opt, int64_t max_unique, cud
     const int n = a.nchunks;
     constexpr bool kPf = TDFO_UPD_PREFETCH != 0;
     constexpr int kMb = TDFO_UPD_MINB;
+#ifndef TDFO_UPD_LPR512
+#define TDFO_UPD_LPR512 8
+#endif
+    constexpr int kL = TDFO_UPD_LPR512, kC = 32 / TDFO_UPD_LPR512;     // lanes x chunks for a 512-byte row
     constexpr bool kWide = sizeof(T) == 4;          // fp32: 4 chunks per lane; bf16 (8 elems / chunk): 2
     if (kWide) {
         if (n <= 1)   return launch_update<T, 1, 1, 1, 3, false>(a, opt, max_unique, st);
@@ -568,7 +572,7 @@ static int dispatch_update(const UpdateArgs& a, int opt, int64_t max_unique, cud
         if (n <= 4)   return launch_update<T, 1, 4, 1, 3, false>(a, opt, max_unique, st);
         if (n <= 8)   return launch_update<T, 2, 4, 1, 3, false>(a, opt, max_unique, st);
         if (n <= 16)  return launch_update<T, 4, 4, 1, 3, false>(a, opt, max_unique, st);
-        if (n <= 32)  return launch_update<T, 8, 4, 1, kMb, kPf>(a, opt, max_unique, st);
+        if (n <= 32)  return launch_update<T, kL, kC, 1, kMb, kPf>(a, opt, max_unique, st);
         if (n <= 64)  return launch_update<T, 16, 4, 1, 2, false>(a, opt, max_unique, st);
         if (n <= 128) return launch_update<T, 32, 4, 1, 2, false>(a, opt, max_unique, st);
         if (n <= 256) return launch_update<T, 32, 8, 1, 2, false>(a, opt, max_unique, st);

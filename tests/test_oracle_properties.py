@@ -122,3 +122,28 @@ def test_linearize_sort_unique_pipeline(case):
         uniq = sorted(set(want_keys))
         assert nu == len(uniq) and uk[:nu].tolist() == uniq
         assert ss[:nu + 1].tolist() == [sk.tolist().index(k) for k in uniq] + [len(want_keys)]
+
+
+def test_parallel_sort_and_unique_equal_numpy_for_any_thread_count():
+    """Above 65536 pairs the oracle's sort / run-length stages run on all OpenMP threads (chunked counting
+    sort, chunked head count): same permutation as numpy's stable argsort whatever the thread count."""
+    rng = np.random.default_rng(5)
+    n = 300_007
+    keys = rng.integers(0, 70_000, size=n).astype(np.uint32)          # many duplicates, both 16-bit digits in use
+    keys[rng.integers(0, n, size=50)] = np.uint32(0xfffffff0)
+    vals = np.arange(n, dtype=np.uint32)
+    order = np.argsort(keys, kind="stable")
+    heads = np.flatnonzero(np.concatenate([[True], keys[order][1:] != keys[order][:-1]]))
+    before = orc.set_num_threads(0)
+    try:
+        for threads in (1, 3, 8):
+            orc.set_num_threads(threads)
+            ko, vo = orc.sort_pairs_stable(keys, vals)
+            np.testing.assert_array_equal(ko, keys[order])
+            np.testing.assert_array_equal(vo, vals[order])
+            uk, ss, nu = orc.unique_segments(ko)
+            assert nu == heads.size
+            np.testing.assert_array_equal(uk, keys[order][heads])
+            np.testing.assert_array_equal(ss, np.concatenate([heads, [n]]).astype(np.uint32))
+    finally:
+        orc.set_num_threads(before)
