@@ -125,6 +125,15 @@ int tdfo_kjt_complete_cumsum(const int32_t* lengths, int64_t n, int64_t* offsets
 int tdfo_kjt_complete_cumsum_static(const int32_t* lengths, int64_t n, int64_t* offsets, void* stream);
 
 /*
+ * ids that fit 32 bits can cross PCIe as int32 (half the bytes of the per-step host->device copy, the
+ * end-to-end bound on 8 GPUs): this widens them to the int64 the lookups take, the first time the
+ * device touches them.  out[i] = in[i] (sign-extended), i < n.
+ * Replaces: nothing in the reference, whose DataLoader hands int64 ids to `_to_kjt`
+ *   (torchrec/train.py:33-41, 95-97); it is the device half of a narrower host format.
+ */
+int tdfo_kjt_widen_ids(const int32_t* in, int64_t n, int64_t* out, void* stream);
+
+/*
  * Row-wise input dist, step 1: bucketise ids by destination rank.
  * For feature f with `block_sizes[f]` rows per rank, id x goes to bucket
  * x / block_sizes[f] and becomes x - bucket*block_sizes[f].  Output is laid

@@ -298,6 +298,20 @@ push_ids_kernel(const int64_t* __restrict__ values, const int64_t* __restrict__ 
         dst[i] = __ldg(src + i);
 }
 
+// int32 -> int64 ids, four per thread (16-byte load, two 16-byte stores)
+__global__ void __launch_bounds__(256)
+widen_ids_kernel(const int32_t* __restrict__ in, int64_t n, int64_t* __restrict__ out) {
+    const int64_t n4 = n / 4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        const int4 v = __ldcs(reinterpret_cast<const int4*>(in) + i);
+        longlong2* o = reinterpret_cast<longlong2*>(out) + 2 * i;
+        o[0] = make_longlong2((long long)v.x, (long long)v.y);
+        o[1] = make_longlong2((long long)v.z, (long long)v.w);
+    }
+    const int64_t t = n4 * 4 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;      // tail (n % 4 ids)
+    if (t < n) out[t] = (int64_t)in[t];
+}
+
 static unsigned grid_for(int64_t items, int threads) {
     int64_t blocks = (items + threads - 1) / threads;
     const int64_t cap = (int64_t)kNumSMs * 32;
@@ -499,5 +513,16 @@ extern "C" int tdfo_reduce_partial_sums(const float* parts, int32_t W, int64_t p
         parts, W, part_stride, B, nslots, D / 4, out_col, out, out_stride);
     count_launch();
     TDFO_LAUNCH_CHECK("reduce_partial_sums");
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_kjt_widen_ids(const int32_t* in, int64_t n, int64_t* out, void* stream) {
+    TDFO_CHECK_ARG(n >= 0, "kjt_widen_ids: n < 0");
+    if (n == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(in && out, "kjt_widen_ids: null pointer");
+    TDFO_CHECK_ARG(aligned(in, 16) && aligned(out, 16), "kjt_widen_ids: buffers not 16-byte aligned");
+    widen_ids_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(in, n, out);
+    count_launch();
+    TDFO_LAUNCH_CHECK("kjt_widen_ids");
     return TDFO_OK;
 }

@@ -233,7 +233,10 @@ __device__ __forceinline__ void accumulate_occurrences(const UpdateArgs& a, uint
     constexpr int E = Chunk<T>::kElems;
     constexpr int GQ = E / 4;
     // gradient rows in flight: one in the main kernel (register budget), several in the hot-row kernel
-    constexpr int UB = !DEEP ? 1 : ((CPL * GQ <= 2) ? 8 : ((CPL * GQ <= 4) ? 4 : ((CPL * GQ <= 8) ? 2 : 1)));
+#ifndef TDFO_UPD_UB_MAIN
+#define TDFO_UPD_UB_MAIN 1
+#endif
+    constexpr int UB = !DEEP ? TDFO_UPD_UB_MAIN : ((CPL * GQ <= 2) ? 8 : ((CPL * GQ <= 4) ? 4 : ((CPL * GQ <= 8) ? 2 : 1)));
     for (uint32_t i = lo; i < hi; i += LPR) {
         const uint32_t n = min((uint32_t)LPR, hi - i);
         const uint32_t my_v = ((uint32_t)sub < n) ? __ldg(a.sorted_vals + i + sub) : 0u;

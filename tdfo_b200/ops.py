@@ -128,6 +128,14 @@ def complete_cumsum(lengths: torch.Tensor, out: Optional[torch.Tensor] = None) -
     return offsets
 
 
+def widen_ids(ids32: torch.Tensor) -> torch.Tensor:
+    """int32 ids (the narrow host->device format) -> the int64 ids the lookups take."""
+    ids32 = _cuda(ids32, torch.int32, "ids")
+    out = torch.empty(ids32.numel(), dtype=torch.int64, device=ids32.device)
+    check(_lib.load().tdfo_kjt_widen_ids(_ptr(ids32), ids32.numel(), _ptr(out), _stream()))
+    return out
+
+
 def bucketize_row_wise(lengths, offsets, indices, weights, block_sizes, F, B, world, want_permute=False,
                        err_flag=None):
     indices = _cuda(indices, torch.int64, "indices")

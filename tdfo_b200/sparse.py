@@ -37,6 +37,10 @@ class JaggedTensor:
         self._values, self._weights, self._lengths, self._offsets = values, weights, lengths, offsets
 
     def values(self) -> torch.Tensor:
+        """int64 ids.  A batch built from int32 ids (half the host->device bytes; fine whenever every table
+        has fewer than 2^31 rows) is widened here, once, by `tdfo_kjt_widen_ids` on the device."""
+        if self._values.dtype == torch.int32:
+            self._values = ops.widen_ids(self._values) if self._values.is_cuda else self._values.to(torch.int64)
         return self._values
 
     def weights(self) -> torch.Tensor:
@@ -197,7 +201,7 @@ class KeyedJaggedTensor:
         if s:
             offsets = offsets - s
         w = None if self._weights is None else self._weights[s:e]
-        return JaggedTensor(self._values[s:e], w, self.lengths()[f * B:(f + 1) * B], offsets)
+        return JaggedTensor(self.values()[s:e], w, self.lengths()[f * B:(f + 1) * B], offsets)
 
     def to_dict(self) -> Dict[str, JaggedTensor]:
         return {k: self[k] for k in self._keys}
@@ -209,7 +213,7 @@ class KeyedJaggedTensor:
         perm = torch.tensor(indices, dtype=torch.int32, device=self._values.device)
         lpk = self.length_per_key() if self._length_per_key is not None else None
         total = sum(lpk[i] for i in indices) if lpk is not None else None
-        ol, oo, oi, ow = ops.permute_2d(perm, self._stride, self.lengths(), self.offsets(), self._values,
+        ol, oo, oi, ow = ops.permute_2d(perm, self._stride, self.lengths(), self.offsets(), self.values(),
                                         self._weights, out_total=total)
         return KeyedJaggedTensor([self._keys[i] for i in indices], oi, ow, ol, oo, self._stride,
                                  None if lpk is None else [lpk[i] for i in indices])
@@ -222,7 +226,7 @@ class KeyedJaggedTensor:
             f1 = f0 + seg
             s, e = o[f0], o[f1]
             w = None if self._weights is None else self._weights[s:e]
-            out.append(KeyedJaggedTensor(self._keys[f0:f1], self._values[s:e], w,
+            out.append(KeyedJaggedTensor(self._keys[f0:f1], self.values()[s:e], w,
                                          lengths=self.lengths()[f0 * B:f1 * B], stride=B))
             f0 = f1
         return out

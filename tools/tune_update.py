@@ -7,7 +7,7 @@ from tdfo_b200 import ops, _lib
 if os.environ.get("TDFO_TUNE_LIB"):          # a variant built by tools/build_variant.py
     _lib.LIB_PATH = Path(os.environ["TDFO_TUNE_LIB"]).resolve()
 
-F, rows, D, P, B = 26, 1_000_000, 128, 20, 16384
+F, rows, D, P, B = (int(os.environ.get(k, d)) for k, d in (('F', 26), ('ROWS', 1_000_000), ('D', 128), ('P', 20), ('B', 16384)))
 dev = torch.device("cuda")
 gen = torch.Generator(device=dev).manual_seed(42)
 w = torch.empty((F * rows, D), device=dev).uniform_(-0.001, 0.001)
