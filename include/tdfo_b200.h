@@ -396,6 +396,14 @@ size_t tdfo_backward_scratch_bytes_weighted(int64_t L, int64_t total_rows);
  * keys_in_scratch: 0, or 1 if tdfo_embedding_forward already wrote the pairs (see above).
  */
 #define TDFO_SCRATCH_PREPARED 2
+/*
+ * The same from pairs that already exist: `keys` / `vals` (uint32[L], read only, anywhere in device memory)
+ * are the (row key, payload) pairs tdfo_embedding_forward / _peer wrote through its sort_keys / sort_vals
+ * arguments.  Used by the sharded path, where the forward runs before the host knows how many ids the rank
+ * received: it writes the pairs into a capacity-sized buffer, and the backward sorts the first L of them.
+ */
+int tdfo_embedding_backward_prepare_pairs(const uint32_t* keys, const uint32_t* vals, int64_t L, int64_t total_rows,
+                                          int32_t* err_flag, void* scratch, size_t scratch_bytes, void* stream);
 int tdfo_embedding_backward_prepare(const int64_t* indices, const int64_t* offsets,
                                     const int64_t* feat_row_base, const int64_t* feat_rows,
                                     int32_t F, int64_t B, int64_t L, int64_t total_rows,

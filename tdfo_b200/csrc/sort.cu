@@ -251,8 +251,11 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __re
 
 // Sorts in place over the two buffer pairs; returns 0 if the result is in (k0,v0),
 // 1 if it is in (k1,v1).  Input is in (k0,v0).
+// `kin` / `vin` (optional): the unsorted pairs live somewhere else and are only read; the first pass then
+// goes from there into (k1, v1) and (k0, v0) is scratch, with the result in the same place as without them.
 int radix_sort_impl(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int64_t n, int key_bits,
-                    int32_t* err_flag, void* scratch, cudaStream_t st, int* result_buf) {
+                    int32_t* err_flag, void* scratch, cudaStream_t st, int* result_buf,
+                    const uint32_t* kin, const uint32_t* vin) {
     *result_buf = 0;
     if (n == 0) return TDFO_OK;
     const SortPlan p = make_sort_plan(n, key_bits);
@@ -266,13 +269,13 @@ int radix_sort_impl(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int6
     for (int i = 0; i < p.passes; ++i) { h.bits[i] = p.bits[i]; h.shift[i] = p.shift[i]; }
     int64_t hb = (n + kSortThreads * 16 - 1) / (kSortThreads * 16);
     if (hb > kNumSMs * 8) hb = kNumSMs * 8;
-    radix_histogram_kernel<<<(unsigned)hb, kSortThreads, 0, st>>>(k0, n, h, ghist);
+    radix_histogram_kernel<<<(unsigned)hb, kSortThreads, 0, st>>>(kin ? kin : k0, n, h, ghist);
     count_launch();
     TDFO_LAUNCH_CHECK("radix_histogram");
     uint32_t *ki = k0, *vi = v0, *ko = k1, *vo = v1;
     for (int i = 0; i < p.passes; ++i) {
         radix_onesweep_kernel<<<(unsigned)p.tiles, kSortThreads, 0, st>>>(
-            ki, vi, ko, vo, n, p.shift[i], p.bits[i], ghist + i * kRadix,
+            (i == 0 && kin) ? kin : ki, (i == 0 && vin) ? vin : vi, ko, vo, n, p.shift[i], p.bits[i], ghist + i * kRadix,
             lookback + (size_t)i * p.tiles * kRadix, tickets + i, err_flag);
         count_launch();
         TDFO_LAUNCH_CHECK("radix_onesweep");
@@ -316,7 +319,7 @@ extern "C" int tdfo_radix_sort_pairs(uint32_t* keys_in, uint32_t* vals_in, uint3
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int where = 0;
-    const int rc = radix_sort_impl(keys_in, vals_in, keys_out, vals_out, n, key_bits, err_flag, scratch, st, &where);
+    const int rc = radix_sort_impl(keys_in, vals_in, keys_out, vals_out, n, key_bits, err_flag, scratch, st, &where, nullptr, nullptr);
     if (rc) return rc;
     if (where == 0) {   // even number of passes: result sits in the input pair
         TDFO_CUDA(cudaMemcpyAsync(keys_out, keys_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));

@@ -10,7 +10,8 @@
 namespace tdfo {
 
 int radix_sort_impl(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int64_t n, int key_bits,
-                    int32_t* err_flag, void* scratch, cudaStream_t st, int* result_buf);
+                    int32_t* err_flag, void* scratch, cudaStream_t st, int* result_buf,
+                    const uint32_t* kin, const uint32_t* vin);
 size_t radix_sort_scratch_bytes_impl(int64_t n, int key_bits);
 int radix_sort_passes_impl(int key_bits);
 int unique_segments_impl(const uint32_t* sorted_keys, const uint32_t* sorted_vals, int64_t n,
@@ -803,7 +804,8 @@ static int backward_stages(int stages, const char* who, void* weights, int32_t w
                            bool weighted, const int64_t* feat_row_base, const int64_t* feat_rows,
                            const int64_t* feat_out_col, int32_t F, int64_t B, int64_t L, int32_t pooling_mode,
                            const tdfo_optimizer_args* opt, int32_t keys_in_scratch, int32_t* err_flag, void* scratch,
-                           size_t scratch_bytes, void* stream) {
+                           size_t scratch_bytes, void* stream, const uint32_t* ext_keys = nullptr,
+                           const uint32_t* ext_vals = nullptr) {
     tdfo_backward_layout lay;
     int rc = tdfo_backward_scratch_layout(L, total_rows, &lay);
     if (rc) return rc;
@@ -831,13 +833,13 @@ static int backward_stages(int stages, const char* who, void* weights, int32_t w
     uint32_t* fv = reinterpret_cast<uint32_t*>(base + lay.first_vals);
 
     if (stages & 1) {
-        if (!keys_in_scratch) {
+        if (!keys_in_scratch && !ext_keys) {
             rc = linearize_impl(indices, offsets, feat_row_base, feat_rows, F, B, L, total_rows, pooling_mode,
                                 k0, v0, pos_bag, err_flag, stream);
             if (rc) return rc;
         }
         int where = 0;
-        rc = radix_sort_impl(k0, v0, k1, v1, L, lay.key_bits, err_flag, sort_scratch, st, &where);
+        rc = radix_sort_impl(k0, v0, k1, v1, L, lay.key_bits, err_flag, sort_scratch, st, &where, ext_keys, ext_vals);
         if (rc) return rc;
         if ((where ? k1 : k0) != sk) {
             set_error("%s: internal layout mismatch", who);
@@ -919,4 +921,16 @@ extern "C" int tdfo_embedding_backward_update(void* weights, int32_t weights_dty
                            state1, grad_out, grad_stride, indices, offsets, per_sample_weights, weighted, feat_row_base,
                            feat_rows, feat_out_col, F, B, L, pooling_mode, opt, prepared ? 0 : keys_in_scratch, err_flag,
                            scratch, scratch_bytes, stream);
+}
+
+extern "C" int tdfo_embedding_backward_prepare_pairs(const uint32_t* keys, const uint32_t* vals, int64_t L,
+                                                     int64_t total_rows, int32_t* err_flag, void* scratch,
+                                                     size_t scratch_bytes, void* stream) {
+    TDFO_CHECK_ARG(total_rows >= 0 && total_rows < 0xffffffffll, "embedding_backward_prepare_pairs: total_rows must be < 2^32-1");
+    TDFO_CHECK_ARG(L >= 0 && L < (1ll << 30), "embedding_backward_prepare_pairs: L must be in [0, 2^30)");
+    if (L == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(keys && vals, "embedding_backward_prepare_pairs: null pointer");
+    return backward_stages(1, "embedding_backward_prepare_pairs", nullptr, TDFO_F32, total_rows, 4, nullptr, nullptr,
+                           nullptr, 0, nullptr, nullptr, nullptr, false, nullptr, nullptr, nullptr, 0, 0, L, TDFO_POOL_SUM,
+                           nullptr, 0, err_flag, scratch, scratch_bytes, stream, keys, vals);
 }

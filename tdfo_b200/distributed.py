@@ -151,9 +151,12 @@ class CudaKernelOps:
         return self._ops.backward_layout(L, total_rows).total_bytes
 
     def embedding_forward_peer(self, group, indices, offsets, B, pooling_mode, peer_out, peer_batch,
-                               backward_scratch=None):
+                               backward_scratch=None, sort_pairs=None):
         self._ops.embedding_forward_peer(group, indices, offsets, B, pooling_mode, peer_out, peer_batch,
-                                         backward_scratch=backward_scratch)
+                                         backward_scratch=backward_scratch, sort_pairs=sort_pairs)
+
+    def embedding_backward_prepare_pairs(self, group, keys, vals, L, scratch):
+        self._ops.embedding_backward_prepare_pairs(group, keys, vals, L, scratch)
 
     def copy_feature_blocks(self, src, dst, B, D, meta):
         self._ops.copy_feature_blocks(src, dst, B, D, meta)
@@ -723,20 +726,29 @@ class ShardedEmbeddingBagCollection(nn.Module):
             k = peer.step % 2
             peer.step += 1
             out = peer.out[k].view(B, self._F_total * D)     # valid until the forward after next
-            out3 = out.view(B, self._F_total, D)
+            # Training: the lookups also write the backward's (row key, bag) pairs, at the ids' own positions in
+            # a capacity-sized buffer (how many ids arrived is not known on the host yet), so the backward can
+            # go straight to the sort.
+            pairs = None
+            if self._emit_keys and hasattr(ops, "embedding_backward_prepare_pairs"):
+                pairs = getattr(peer, "sort_pairs", None)
+                if pairs is None:
+                    pairs = peer.sort_pairs = (torch.empty(max(peer.capacity, 4), dtype=torch.int32, device=dev),
+                                               torch.empty(max(peer.capacity, 4), dtype=torch.int32, device=dev))
             if n_tw_r:
                 # pooled rows go straight into the output buffer of the rank that owns the sample
                 grp = self._group("tw", False)
                 grp.feat_out_col = self._tw_global_col        # columns of the final [B, F_total*D] layout
                 grp.out_stride = self._F_total * D
-                ops.embedding_forward_peer(grp, lv, lo_[: n_tw_r * GB + 1], GB, self._pooling, peer.out_ptrs[k], B)
+                ops.embedding_forward_peer(grp, lv, lo_[: n_tw_r * GB + 1], GB, self._pooling, peer.out_ptrs[k], B,
+                                           sort_pairs=pairs)
             if n_cw_r:
                 # column shards: the same, Dc columns per pooled row
                 grp = self._group("cw", False)
                 grp.feat_out_col = self._cw_global_col
                 grp.out_stride = self._F_total * D
                 ops.embedding_forward_peer(grp, lv, lo_[n_tw_r * GB: n_own * GB + 1], GB, self._pooling,
-                                           peer.out_ptrs[k], B)
+                                           peer.out_ptrs[k], B, sort_pairs=pairs)
             if n_rw:
                 # row-wise: my block's partial sums of sample (src, b) go into slot `r` of rank src's buffer
                 key = (B, "rw_part_out", str(dev))
@@ -745,13 +757,13 @@ class ShardedEmbeddingBagCollection(nn.Module):
                     slot_ptrs = self._meta_cache[key] = torch.tensor(
                         [p + 4 * r * B * n_rw * D for p in peer.rw_part_ptrs], dtype=torch.int64, device=dev)
                 ops.embedding_forward_peer(self._group("rw", False), lv, lo_[n_own * GB: Fl * GB + 1], GB, _lib.POOL_SUM,
-                                           slot_ptrs, B)
+                                           slot_ptrs, B, sort_pairs=pairs)
             peer.barrier()                                    # all pooled rows / partial sums have landed
             if n_rw:
                 # add the W slots in rank order into the row-wise columns of the output (fixed order: reproducible)
                 ops.reduce_partial_sums(peer.rw_part, W, B, n_rw, D, self._rw_global_col, out, self._F_total * D)
             return out, dict(peer=True, px=peer, lo=lo_, n_tw_r=n_tw_r, n_cw_r=n_cw_r, GB=GB, token=self._fwd_token,
-                             fused=False, slot=c["slot"])
+                             fused=False, slot=c["slot"], pairs=pairs)
 
         out = torch.empty((B, self._F_total * D), dtype=torch.float32, device=dev)
         out3 = out.view(B, self._F_total, D)
@@ -926,9 +938,16 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 if on_gpu:
                     landed = torch.cuda.Event()
                     landed.record(side)
+            starts = {"tw": 0, "cw": tw_total, "rw": cw_total}      # where each shard's ids start in the landing zone
             for name, ids_, off_ in todo:
-                ops.embedding_backward_prepare(self._group(name, False), ids_, off_, GB,
-                                               _lib.POOL_SUM if name == "rw" else self._pooling, prepared[name])
+                if saved.get("pairs") is not None:
+                    s0 = starts[name]
+                    ops.embedding_backward_prepare_pairs(self._group(name, False), saved["pairs"][0][s0:s0 + ids_.numel()],
+                                                         saved["pairs"][1][s0:s0 + ids_.numel()], ids_.numel(),
+                                                         prepared[name])
+                else:
+                    ops.embedding_backward_prepare(self._group(name, False), ids_, off_, GB,
+                                                   _lib.POOL_SUM if name == "rw" else self._pooling, prepared[name])
             if on_gpu:
                 main.wait_event(landed)
         else:

@@ -241,7 +241,8 @@ def embedding_forward(group: TableGroup, indices: torch.Tensor, offsets: torch.T
 
 def embedding_forward_peer(group: TableGroup, indices: torch.Tensor, offsets: torch.Tensor, B: int, pooling_mode: int,
                            peer_out: torch.Tensor, peer_batch: int,
-                           backward_scratch: Optional[torch.Tensor] = None) -> None:
+                           backward_scratch: Optional[torch.Tensor] = None,
+                           sort_pairs: Optional[tuple] = None) -> None:
     """Pooled lookup whose rows are stored into the output buffers of the samples' source ranks
     (``peer_out``: int64 device tensor of base addresses, one per source rank)."""
     indices = _cuda(indices, torch.int64, "indices")
@@ -256,6 +257,8 @@ def embedding_forward_peer(group: TableGroup, indices: torch.Tensor, offsets: to
             raise ValueError(f"backward_scratch has {backward_scratch.numel()} bytes, needs {lay.total_bytes}")
         sk = ctypes.c_void_p(backward_scratch.data_ptr() + lay.input_keys)
         sv = ctypes.c_void_p(backward_scratch.data_ptr() + lay.input_vals)
+    if sort_pairs is not None:          # (keys, vals) int32 buffers of at least `indices.numel()` entries
+        sk, sv = _ptr(sort_pairs[0]), _ptr(sort_pairs[1])
     check(_lib.load().tdfo_embedding_forward_peer(
         _ptr(w), _wdtype(w), group.total_rows, group.D, _ptr(indices), _ptr(offsets), None,
         _ptr(group.feat_row_base), _ptr(group.feat_rows), _ptr(group.feat_out_col), group.F, B, L, pooling_mode,
@@ -320,6 +323,18 @@ def embedding_backward_prepare(group: TableGroup, indices: torch.Tensor, offsets
         _ptr(indices), _ptr(offsets), _ptr(group.feat_row_base), _ptr(group.feat_rows), group.F, B, indices.numel(),
         group.total_rows, pooling_mode, 1 if weighted else 0, 1 if keys_in_scratch else 0, _ptr(group.err_flag),
         _ptr(scratch), scratch.numel(), _stream()))
+
+
+def embedding_backward_prepare_pairs(group: TableGroup, keys: torch.Tensor, vals: torch.Tensor, L: int,
+                                     scratch: torch.Tensor) -> None:
+    """`embedding_backward_prepare` from (row key, payload) pairs the forward already wrote (int32 tensors holding
+    uint32 bit patterns; only the first ``L`` entries are sorted)."""
+    keys = _cuda(keys, torch.int32, "keys")
+    vals = _cuda(vals, torch.int32, "vals")
+    if keys.numel() < L or vals.numel() < L:
+        raise ValueError(f"pair buffers hold {keys.numel()} / {vals.numel()} entries, fewer than L = {L}")
+    check(_lib.load().tdfo_embedding_backward_prepare_pairs(_ptr(keys), _ptr(vals), L, group.total_rows,
+                                                            _ptr(group.err_flag), _ptr(scratch), scratch.numel(), _stream()))
 
 
 def linearize_indices(group: TableGroup, indices, offsets, B, pooling_mode):
