@@ -15,9 +15,12 @@ kernels:
   process group the (ids, gradient rows) of every replica are all-gathered first, so replicated
   tables stay identical on every rank, and `average=True` reproduces pmean's 1 / world scaling.
 
-Arrays cross the framework boundary through DLPack: inputs may be torch tensors or any object with
-`__dlpack__` (jax.Array, tf.experimental.dlpack capsules wrapped by the caller); outputs are torch
-CUDA tensors, which jax / tf import zero-copy with `from_dlpack`.  Neither jax nor tensorflow is
+Arrays cross the framework boundary through DLPack: inputs may be torch tensors, any object with
+`__dlpack__` (jax.Array) or a raw DLPack capsule (`tf.experimental.dlpack.to_dlpack(t)`); outputs are
+torch CUDA tensors, which jax / tf import zero-copy with `from_dlpack`.  TensorFlow's embedding
+gradients arrive as `IndexedSlices`: `apply_indexed_slices` takes their (indices, values) as they are.
+The row partition of tensorflow2/train_ps.py:55-61 (`MinSizePartitioner` over axis 0) is the `row_wise()`
+plan of `ShardedEmbeddingBagCollection`.  Neither jax nor tensorflow is
 installed on this box, so only the torch side of the protocol is exercised by the tests.
 
 Semantics note: the fused ADAM is "lazy" (rows and moments of ids that do not occur in a step are
@@ -38,9 +41,14 @@ from . import ops
 
 def _as_tensor(x: Any, device: torch.device) -> torch.Tensor:
     if not isinstance(x, torch.Tensor):
-        if not hasattr(x, "__dlpack__"):
-            raise TypeError(f"expected a torch tensor or a DLPack producer, got {type(x).__name__}")
-        x = torch.from_dlpack(x)
+        if type(x).__name__ == "PyCapsule":
+            # a raw DLPack capsule: what `tf.experimental.dlpack.to_dlpack(tensor)` returns (TF 2.12 tensors
+            # have no __dlpack__ method; tensorflow2/README.md:22 pins that version)
+            x = torch.utils.dlpack.from_dlpack(x)
+        elif hasattr(x, "__dlpack__"):
+            x = torch.from_dlpack(x)
+        else:
+            raise TypeError(f"expected a torch tensor, a DLPack producer or a DLPack capsule, got {type(x).__name__}")
     if x.device != device:
         raise RuntimeError(f"array lives on {x.device}, the tables on {device}: hand over device arrays "
                            "(there is no host path)")
@@ -133,6 +141,39 @@ class DLPackEmbeddingTables:
             values = all_v.permute(1, 0, 2).reshape(-1)          # [f][rank][b]: sample index = rank * B + b
             g, B = all_g, W * B
         self._ebc._backward_impl(g, values, self._unit_offsets(F * B), B)
+
+    @torch.no_grad()
+    def apply_indexed_slices(self, slices: Mapping[str, Any]) -> None:
+        """One fused optimizer step from (indices, values) pairs, the shape TensorFlow hands an optimizer for an
+        embedding variable: `tape.gradient` of `Embedding(...)(ids)` is a `tf.IndexedSlices(values [n, D],
+        indices [n])` with duplicate indices left in and a different n per table (tensorflow2/models.py:48-58,
+        train_dp.py:71-72).  `slices[name]` is such an object (anything with `.indices` and `.values`) or an
+        `(indices, values)` tuple; the arrays are torch tensors, DLPack producers or DLPack capsules.  Tables not
+        named are left alone.  Duplicates are summed in order of appearance, as the dense scatter-add would."""
+        ebc = self._ebc
+        ebc._fused.iteration += 1
+        opt = ebc._fused.args()
+        for g in ebc._groups:
+            ids_parts, val_parts, counts = [], [], []
+            for n in g.features:
+                item = slices.get(n)
+                if item is None:
+                    counts.append(0)
+                    continue
+                idx, val = (item.indices, item.values) if hasattr(item, "indices") else item
+                idx = _as_tensor(idx, self.device).reshape(-1)
+                val = _as_tensor(val, self.device).reshape(-1, g.D).to(torch.float32)
+                if idx.dtype not in (torch.int32, torch.int64) or idx.numel() != val.shape[0]:
+                    raise ValueError(f"slices for {n!r}: need integer indices [n] and values [n, {g.D}]")
+                ids_parts.append(idx.to(torch.int64))
+                val_parts.append(val)
+                counts.append(idx.numel())
+            if not ids_parts:
+                continue
+            # one bag per table holding all of its slices; sequence-mode backward: gradient row p belongs to id p
+            offsets = torch.tensor([0] + counts, dtype=torch.int64).cumsum(0).to(self.device)
+            ops.embedding_backward_update(ebc._table_group(g, True), torch.cat(val_parts).contiguous(),
+                                          torch.cat(ids_parts), offsets, 1, ops.POOL_NONE, opt)
 
     def check_errors(self) -> None:
         self._ebc.check_errors()

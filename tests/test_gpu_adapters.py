@@ -113,3 +113,40 @@ def test_rejects_host_arrays_and_missing_tables(t):
     with pytest.raises(ValueError, match="same number"):
         tabs.lookup({"a": torch.zeros(4, dtype=torch.int64, device="cuda"),
                      "b": torch.zeros(5, dtype=torch.int64, device="cuda")})
+
+
+def test_tf_side_capsules_and_indexed_slices(t):
+    """The tensorflow2 face (tensorflow2/models.py:48-58, train_dp.py:71-72): ids arrive as raw DLPack capsules
+    (what `tf.experimental.dlpack.to_dlpack` returns), gradients as IndexedSlices-shaped (indices, values) with
+    duplicate indices and a different count per table, some tables absent.  One SGD step equals the dense
+    scatter-add + SGD that keras applies, restated with torch index_add_."""
+    from types import SimpleNamespace
+    from tdfo_b200.adapters import DLPackEmbeddingTables
+    dev = torch.device("cuda")
+    rng = np.random.default_rng(4)
+    lr = 0.1
+    tabs = DLPackEmbeddingTables(TABLES, dev, optimizer=t.EmbOptimType.EXACT_SGD, learning_rate=lr)
+    w0 = {n: tabs.state_dict()[f"embedding_bags.{n}.weight"].clone() for n in TABLES}
+    # lookup through capsules
+    ids = _ids(rng, 24)
+    caps = {n: torch.utils.dlpack.to_dlpack(torch.from_numpy(v).to(dev)) for n, v in ids.items()}
+    rows = tabs.lookup(caps)
+    for n, v in ids.items():
+        assert torch.equal(rows[n], w0[n][torch.from_numpy(v).long().to(dev)])
+    # IndexedSlices: ragged counts, duplicates, two tables without a gradient this step
+    slices, want = {}, {n: w.clone() for n, w in w0.items()}
+    for k, (n, (r, d)) in enumerate(TABLES.items()):
+        if n in ("is_ebook", "format"):
+            continue
+        cnt = 5 + 7 * k
+        idx = torch.from_numpy(rng.integers(0, min(r, 6), size=cnt)).to(dev)            # few distinct rows: many duplicates
+        val = torch.from_numpy(rng.normal(size=(cnt, d)).astype(np.float32)).to(dev)
+        dense = torch.zeros_like(w0[n]).index_add_(0, idx, val)
+        want[n] -= lr * dense
+        payload = (torch.utils.dlpack.to_dlpack(idx.to(torch.int32)), torch.utils.dlpack.to_dlpack(val))
+        slices[n] = SimpleNamespace(indices=payload[0], values=payload[1]) if k % 2 else payload
+    tabs.apply_indexed_slices(slices)
+    tabs.check_errors()
+    for n in TABLES:
+        np.testing.assert_allclose(tabs.state_dict()[f"embedding_bags.{n}.weight"].cpu().numpy(), want[n].cpu().numpy(),
+                                   rtol=1e-5, atol=1e-6, err_msg=n)
