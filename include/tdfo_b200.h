@@ -197,6 +197,23 @@ int tdfo_kjt_permute_2d(const int32_t* permute /* [S_out] */, int32_t S_in, int3
  *   sharded module DMP builds (torchrec/train.py:241-247, 98).
  */
 int tdfo_kjt_push_lengths(const int32_t* lengths, int64_t B, int32_t nslots, const int64_t* meta, void* stream);
+/*
+ * The same transport for rows of D floats, used by the sharded EmbeddingCollection's backward: element i of
+ * segment seg[j] is rows[positions ? positions[s0 + i] : s0 + i] (s0 = offsets[seg*B]) and lands at row
+ * *(int64*)off_addr[j] + i of the float buffer at rows_base[j].  meta = seg | off_addr | rows_base.
+ * Replaces: the gradient half of SequenceEmbeddingsAllToAll in the sharded module DMP builds for the
+ *   reference's item table (torchrec/models.py:158-164, torchrec/train.py:241-247, 104).
+ */
+int tdfo_kjt_push_rows(const float* rows, const int64_t* positions, const int64_t* offsets, int64_t B, int32_t D,
+                       int32_t nslots, const int64_t* meta, int64_t capacity, int32_t* err_flag, void* stream);
+/*
+ * out[permute[i]] = positions_in ? positions_in[i] : i, i < min(n, *n_dev) (n_dev: optional device word, for
+ * buffers sized to an upper bound of an id count only the device knows): turns tdfo_kjt_bucketize_row_wise's
+ * unbucketize_permute (original position -> bucketised position) into "original position of every
+ * bucketised id", which travels with the ids so the owner knows where each looked-up row belongs.
+ */
+int tdfo_kjt_scatter_positions(const int64_t* permute, const int64_t* positions_in, int64_t n, const int64_t* n_dev,
+                               int64_t* out, void* stream);
 int tdfo_kjt_push_ids(const int64_t* values, const int64_t* offsets, int64_t B, int32_t nslots,
                       const int64_t* meta, int64_t capacity, int32_t* err_flag, void* stream);
 
@@ -256,6 +273,26 @@ int tdfo_embedding_forward_peer(const void* weights, int32_t weights_dtype, int6
                                 const uint64_t* peer_out, int64_t peer_batch, int64_t out_stride,
                                 uint32_t* sort_keys, uint32_t* sort_vals,
                                 int32_t* err_flag, void* stream);
+
+/*
+ * Sequence lookup (EmbeddingCollection, one row per id) with the output dist fused in, on the owner of the
+ * rows.  `offsets` describes S = (local features x world) segments of B bags each, in the landing-zone order
+ * [feature][source rank][batch]; `indices` is the landing zone, read at positions [offsets[0], offsets[S*B])
+ * (never past L); seg_row_base / seg_rows give the table slice per SEGMENT (a feature's values repeated world
+ * times).  The row of landed id p is stored at row positions[p] of the output buffer of source rank
+ * (segment of p) % world: peer_out[src] + positions[p] * D floats, i.e. at the place the id had in the
+ * sender's own KeyedJaggedTensor (positions travel with the ids: tdfo_kjt_push_ids of a position array).
+ * sort_keys / sort_vals (optional): the backward's pairs, payload = p - offsets[0].
+ * Replaces: TBE "nobag" forward + SequenceEmbeddingsAllToAll (+ the un-bucketise permute for row-wise
+ *   tables) of the sharded EmbeddingCollection DMP builds for the reference's item table
+ *   (torchrec/models.py:158-164, torchrec/train.py:241-247, 98).
+ */
+int tdfo_embedding_forward_seq_peer(const void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
+                                    const int64_t* indices, const int64_t* offsets,
+                                    const int64_t* seg_row_base, const int64_t* seg_rows, int32_t S,
+                                    int64_t B, int64_t L, const int64_t* positions,
+                                    const uint64_t* peer_out, int32_t world,
+                                    uint32_t* sort_keys, uint32_t* sort_vals, int32_t* err_flag, void* stream);
 
 /* ------------------------------------------------------------------ backward */
 

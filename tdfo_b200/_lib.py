@@ -69,6 +69,10 @@ _SIGNATURES = {
     "tdfo_embedding_backward_prepare": (c_int, [P, P, P, P, c_int32, c_int64, c_int64, c_int64, c_int32, c_int32,
                                                 c_int32, P, P, c_size_t, P]),
     "tdfo_kjt_widen_ids": (c_int, [P, c_int64, P, P]),
+    "tdfo_kjt_push_rows": (c_int, [P, P, P, c_int64, c_int32, c_int32, P, c_int64, P, P]),
+    "tdfo_kjt_scatter_positions": (c_int, [P, P, c_int64, P, P, P]),
+    "tdfo_embedding_forward_seq_peer": (c_int, [P, c_int32, c_int64, c_int32, P, P, P, P, c_int32, c_int64, c_int64, P,
+                                                P, c_int32, P, P, P, P]),
     "tdfo_embedding_backward_prepare_pairs": (c_int, [P, P, c_int64, c_int64, P, P, c_size_t, P]),
     "tdfo_copy_feature_blocks": (c_int, [P, P, c_int64, c_int32, c_int32, P, P]),
     "tdfo_reduce_partial_sums": (c_int, [P, c_int32, c_int64, c_int64, c_int32, c_int32, P, P, c_int64, P]),

@@ -312,6 +312,42 @@ widen_ids_kernel(const int32_t* __restrict__ in, int64_t n, int64_t* __restrict_
     if (t < n) out[t] = (int64_t)in[t];
 }
 
+// Slot j moves the rows of one whole segment (B consecutive bags of the sender's offsets) to the owner:
+// element i of the segment is row rows[positions ? positions[s0 + i] : s0 + i] and lands at row
+// (remote offset word + i) of the owner's buffer.  blockIdx.y = slot.
+__global__ void __launch_bounds__(256)
+push_rows_kernel(const float* __restrict__ rows, const int64_t* __restrict__ positions,
+                 const int64_t* __restrict__ offsets, int64_t B, int32_t D4, const int64_t* __restrict__ meta,
+                 int32_t nslots, int64_t capacity, int32_t* err_flag) {
+    const int j = blockIdx.y;
+    const int64_t seg = __ldg(meta + j);
+    const int64_t s0 = __ldg(offsets + seg * B), s1 = __ldg(offsets + (seg + 1) * B);
+    const int64_t n = s1 - s0;
+    if (n <= 0) return;
+    const int64_t dst_off = *reinterpret_cast<const volatile int64_t*>(__ldg(meta + nslots + j));
+    if (dst_off < 0 || dst_off + n > capacity) {
+        if (err_flag && threadIdx.x == 0 && blockIdx.x == 0) atomicOr(err_flag, TDFO_FLAG_RECV_OVERFLOW);
+        return;
+    }
+    uint4* dst = reinterpret_cast<uint4*>(__ldg(meta + 2 * nslots + j)) + dst_off * D4;
+    const uint4* src = reinterpret_cast<const uint4*>(rows);
+    const int64_t total = n * D4;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = t / D4;
+        const int c = (int)(t - i * D4);
+        const int64_t r = positions ? __ldg(positions + s0 + i) : s0 + i;
+        __stcs(dst + t, __ldcs(src + r * D4 + c));
+    }
+}
+
+// out[permute[i]] = positions_in ? positions_in[i] : i   (the inverse of a permutation, composed with a map)
+__global__ void scatter_positions_kernel(const int64_t* __restrict__ permute, const int64_t* __restrict__ positions_in,
+                                         int64_t n, const int64_t* __restrict__ n_dev, int64_t* __restrict__ out) {
+    if (n_dev) n = min(n, __ldg(n_dev));          // the caller's buffers may be longer than the id count the device knows
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        out[__ldg(permute + i)] = positions_in ? __ldg(positions_in + i) : i;
+}
+
 static unsigned grid_for(int64_t items, int threads) {
     int64_t blocks = (items + threads - 1) / threads;
     const int64_t cap = (int64_t)kNumSMs * 32;
@@ -524,5 +560,32 @@ extern "C" int tdfo_kjt_widen_ids(const int32_t* in, int64_t n, int64_t* out, vo
     widen_ids_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(in, n, out);
     count_launch();
     TDFO_LAUNCH_CHECK("kjt_widen_ids");
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_kjt_push_rows(const float* rows, const int64_t* positions, const int64_t* offsets, int64_t B,
+                                  int32_t D, int32_t nslots, const int64_t* meta, int64_t capacity, int32_t* err_flag,
+                                  void* stream) {
+    TDFO_CHECK_ARG(B >= 0 && nslots >= 0 && capacity >= 0 && D > 0 && D % 4 == 0, "kjt_push_rows: bad size (D must be a multiple of 4)");
+    TDFO_CHECK_ARG(nslots <= 65535, "kjt_push_rows: at most 65535 segments per call");
+    if (B == 0 || nslots == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(offsets && meta, "kjt_push_rows: null pointer");
+    TDFO_CHECK_ARG(aligned(rows, 16), "kjt_push_rows: rows not 16-byte aligned");
+    dim3 grid(64, (unsigned)nslots);
+    push_rows_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(rows, positions, offsets, B, D / 4, meta, nslots,
+                                                                         capacity, err_flag);
+    count_launch();
+    TDFO_LAUNCH_CHECK("kjt_push_rows");
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_kjt_scatter_positions(const int64_t* permute, const int64_t* positions_in, int64_t n,
+                                          const int64_t* n_dev, int64_t* out, void* stream) {
+    TDFO_CHECK_ARG(n >= 0, "kjt_scatter_positions: n < 0");
+    if (n == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(permute && out, "kjt_scatter_positions: null pointer");
+    scatter_positions_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(permute, positions_in, n, n_dev, out);
+    count_launch();
+    TDFO_LAUNCH_CHECK("kjt_scatter_positions");
     return TDFO_OK;
 }

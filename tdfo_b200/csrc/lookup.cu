@@ -21,6 +21,8 @@ struct LookupArgs {
     float* out;
     const uint64_t* peer_out;   // optional: out base pointer of every source rank (NVLink peer memory)
     int64_t peer_batch;         // samples per source rank when peer_out is set
+    const int64_t* peer_pos;    // sequence mode over peer memory: output row of every id at its source rank
+    int32_t peer_world;         //   ... and the number of ranks (segment s belongs to source rank s % world)
     uint32_t* sort_keys;   // optional: backward's (row key, payload) pairs, emitted while the ids are in registers
     uint32_t* sort_vals;
     int32_t* err_flag;
@@ -385,7 +387,10 @@ sequence_forward_kernel(const LookupArgs a) {
     const int64_t groups_per_block = kFwdThreads / LPR;
     const uint4* __restrict__ wbase = reinterpret_cast<const uint4*>(a.weights);
     bool oob = false;
-    for (int64_t p = (int64_t)blockIdx.x * groups_per_block + threadIdx.x / LPR; p < a.L;
+    // ids of this call: positions [first, last) of `indices` (the whole array unless the offsets are a slice of a
+    // larger batch, as in the sharded landing zone); never past the L ids given
+    const int64_t first = fbound[0], last = min(a.L, fbound[a.F]);
+    for (int64_t p = first + (int64_t)blockIdx.x * groups_per_block + threadIdx.x / LPR; p < last;
          p += (int64_t)gridDim.x * groups_per_block) {
         int lo = 0, hi = a.F;                 // largest f with fbound[f] <= p
         while (hi - lo > 1) {
@@ -398,9 +403,12 @@ sequence_forward_kernel(const LookupArgs a) {
         const size_t row = (size_t)(__ldg(a.feat_row_base + lo) + idx);
         if (a.sort_keys && sub == 0) {
             a.sort_keys[p] = valid ? (uint32_t)row : a.oob_key;
-            a.sort_vals[p] = (uint32_t)p;
+            a.sort_vals[p] = (uint32_t)(p - first);         // payload: the id's gradient row, counted from this call's first id
         }
-        float* orow = a.out + (size_t)p * a.nchunks * E;
+        float* orow = a.out + (size_t)(p - first) * a.nchunks * E;
+        if (a.peer_out)     // sharded output dist fused in: the row goes to its id's place at the rank that sent the id
+            orow = reinterpret_cast<float*>(__ldg(a.peer_out + lo % a.peer_world)) +
+                   (size_t)__ldg(a.peer_pos + p) * a.nchunks * E;
 #pragma unroll
         for (int k = 0; k < CPL; ++k) {
             const int c = sub + k * LPR;
@@ -483,7 +491,8 @@ static int embedding_forward_impl(const void* weights, int32_t weights_dtype, in
                                   int32_t pooling_mode, float* out, int64_t out_stride,
                                   const uint64_t* peer_out, int64_t peer_batch,
                                   uint32_t* sort_keys, uint32_t* sort_vals,
-                                  int32_t* err_flag, void* stream) {
+                                  int32_t* err_flag, void* stream,
+                                  const int64_t* peer_pos = nullptr, int32_t peer_world = 0) {
     TDFO_CHECK_ARG(weights_dtype == TDFO_F32 || weights_dtype == TDFO_BF16,
                    "embedding_forward: unknown weights_dtype %d", weights_dtype);
     TDFO_CHECK_ARG(pooling_mode >= TDFO_POOL_SUM && pooling_mode <= TDFO_POOL_NONE,
@@ -499,8 +508,10 @@ static int embedding_forward_impl(const void* weights, int32_t weights_dtype, in
     TDFO_CHECK_ARG(weights && (indices || L == 0) && offsets && feat_row_base && feat_rows && (out || peer_out),
                    "embedding_forward: null pointer");
     TDFO_CHECK_ARG(aligned(weights, 16) && aligned(out, 16), "embedding_forward: weights/out not 16-byte aligned");
-    if (peer_out) {
-        TDFO_CHECK_ARG(pooling_mode != TDFO_POOL_NONE, "embedding_forward_peer: pooled modes only");
+    if (peer_out && pooling_mode == TDFO_POOL_NONE) {
+        TDFO_CHECK_ARG(peer_pos != nullptr && peer_world >= 1 && F % peer_world == 0,
+                       "embedding_forward_seq_peer: needs positions and a segment count that is a multiple of the world size");
+    } else if (peer_out) {
         TDFO_CHECK_ARG(peer_batch > 0 && B % peer_batch == 0,
                        "embedding_forward_peer: batch %lld is not a multiple of the per-rank batch %lld",
                        (long long)B, (long long)peer_batch);
@@ -519,6 +530,7 @@ static int embedding_forward_impl(const void* weights, int32_t weights_dtype, in
                    "embedding_forward: sort_keys and sort_vals must both be given or both be null");
     TDFO_CHECK_ARG(sort_keys == nullptr || ((int64_t)F * B < (1ll << 32) && L < (1ll << 32)),
                    "embedding_forward: sort keys need F*B and L below 2^32");
+    a.peer_pos = peer_pos; a.peer_world = peer_world;
     a.out = out; a.peer_out = peer_out; a.peer_batch = peer_batch; a.sort_keys = sort_keys; a.sort_vals = sort_vals; a.oob_key = (uint32_t)total_rows; a.err_flag = err_flag; a.B = B; a.num_bags = (int64_t)F * B; a.L = L;
     a.out_stride = out_stride; a.F = F; a.nchunks = (int32_t)(D * esz / 16);
     a.mean = pooling_mode == TDFO_POOL_MEAN;
@@ -555,4 +567,20 @@ extern "C" int tdfo_embedding_forward_peer(const void* weights, int32_t weights_
     return embedding_forward_impl(weights, weights_dtype, total_rows, D, indices, offsets, per_sample_weights,
                                   feat_row_base, feat_rows, feat_out_col, F, B, L, pooling_mode, nullptr, out_stride,
                                   peer_out, peer_batch, sort_keys, sort_vals, err_flag, stream);
+}
+
+extern "C" int tdfo_embedding_forward_seq_peer(const void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
+                                               const int64_t* indices, const int64_t* offsets,
+                                               const int64_t* seg_row_base, const int64_t* seg_rows, int32_t S,
+                                               int64_t B, int64_t L, const int64_t* positions,
+                                               const uint64_t* peer_out, int32_t world,
+                                               uint32_t* sort_keys, uint32_t* sort_vals, int32_t* err_flag,
+                                               void* stream) {
+    if (!peer_out || !positions) {
+        set_error("embedding_forward_seq_peer: peer_out / positions is null");
+        return TDFO_ERR_INVALID_ARG;
+    }
+    return embedding_forward_impl(weights, weights_dtype, total_rows, D, indices, offsets, nullptr, seg_row_base, seg_rows,
+                                  nullptr, S, B, L, TDFO_POOL_NONE, nullptr, D, peer_out, 0, sort_keys, sort_vals,
+                                  err_flag, stream, positions, world);
 }

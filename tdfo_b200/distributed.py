@@ -158,6 +158,15 @@ class CudaKernelOps:
     def embedding_backward_prepare_pairs(self, group, keys, vals, L, scratch):
         self._ops.embedding_backward_prepare_pairs(group, keys, vals, L, scratch)
 
+    def embedding_forward_seq_peer(self, group, indices, offsets, B, positions, peer_out, world, sort_pairs=None):
+        self._ops.embedding_forward_seq_peer(group, indices, offsets, B, positions, peer_out, world, sort_pairs=sort_pairs)
+
+    def push_rows(self, rows, positions, offsets, B, meta, capacity, err_flag):
+        self._ops.push_rows(rows, positions, offsets, B, meta, capacity, err_flag)
+
+    def scatter_positions(self, permute, positions_in, n, n_dev=None):
+        return self._ops.scatter_positions(permute, positions_in, n, n_dev)
+
     def copy_feature_blocks(self, src, dst, B, D, meta):
         self._ops.copy_feature_blocks(src, dst, B, D, meta)
 
@@ -202,8 +211,9 @@ class _PeerExchange:
     into.  Barriers are the symmetric-memory signal-pad barriers, enqueued on the current stream."""
 
     def __init__(self, pg, device, B: int, F_total: int, D: int, n_tw: List[int], n_rw: int, ids_capacity: int,
-                 n_cw: Optional[List[int]] = None, Dc: int = 0):
+                 n_cw: Optional[List[int]] = None, Dc: int = 0, seq_cap: int = 0):
         import torch.distributed._symmetric_memory as symm
+        self.seq_cap = int(seq_cap)
         W = len(n_tw)
         group = pg if pg is not None else dist.group.WORLD
         self.B = B
@@ -219,6 +229,10 @@ class _PeerExchange:
         self.ids_ptrs = list(symm.rendezvous(self.ids_x, group).buffer_ptrs)
         self.counts_host = torch.zeros(3, dtype=torch.int64).pin_memory()     # ids: end of TW, end of CW, total
         self.counts_event = torch.cuda.Event()
+        self.pos_x, self.pos_ptrs = None, []
+        if self.seq_cap:                           # sequence module: every landed id comes with its place at the sender
+            self.pos_x = symm.empty(max(self.capacity, 4), dtype=torch.int64, device=device)
+            self.pos_ptrs = list(symm.rendezvous(self.pos_x, group).buffer_ptrs)
         # Landing zones of the input dist.  Zone 0 is this object's own buffers above; a second one is added
         # only when input dists are prefetched (ensure_second_zone).
         self._zone_args = (symm, group, device, fl_max * W * B)
@@ -241,6 +255,15 @@ class _PeerExchange:
             self.rw_part_ptrs = list(symm.rendezvous(self.rw_part, group).buffer_ptrs)
             self.grad_rw = symm.empty(W * B * n_rw * D, dtype=torch.float32, device=device)
             self.grad_rw_ptrs = list(symm.rendezvous(self.grad_rw, group).buffer_ptrs)
+        # sequence module: rotating row buffers [seq_cap, D] the owners store looked-up rows into (at the ids' own
+        # positions), and the landing buffer for the gradient rows of the ids this rank owns
+        self.seq_out, self.seq_out_ptrs, self.grad_seq, self.grad_seq_ptrs = [], [], None, []
+        if self.seq_cap:
+            self.seq_out = [symm.empty(max(self.seq_cap * D, 4), dtype=torch.float32, device=device) for _ in range(2)]
+            self.seq_out_ptrs = [torch.tensor(list(symm.rendezvous(t_, group).buffer_ptrs), dtype=torch.int64, device=device)
+                                 for t_ in self.seq_out]
+            self.grad_seq = symm.empty(max(self.capacity * D, 4), dtype=torch.float32, device=device)
+            self.grad_seq_ptrs = list(symm.rendezvous(self.grad_seq, group).buffer_ptrs)
         self.step = 0
 
     def _make_zone(self):
@@ -256,6 +279,10 @@ class _PeerExchange:
         z.ids_ptrs = list(symm.rendezvous(z.ids_x, group).buffer_ptrs)
         z.counts_host = torch.zeros(3, dtype=torch.int64).pin_memory()     # ids: end of TW, end of CW, total
         z.counts_event = torch.cuda.Event()
+        z.pos_x, z.pos_ptrs = None, []
+        if self.seq_cap:
+            z.pos_x = symm.empty(max(self.capacity, 4), dtype=torch.int64, device=device)
+            z.pos_ptrs = list(symm.rendezvous(z.pos_x, group).buffer_ptrs)
         return z
 
     def ensure_second_zone(self):
@@ -593,8 +620,13 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 cap_t = torch.tensor([cap], dtype=torch.int64, device=dev)
                 dist.all_reduce(cap_t, op=dist.ReduceOp.MAX, group=self._pg)
                 cap = int(cap_t.item())
+                kw = {}
+                if track:      # sequence module: also agree on the largest local id count (rows of the output buffers)
+                    sc = torch.tensor([int(1.25 * values.numel()) + 256], dtype=torch.int64, device=dev)
+                    dist.all_reduce(sc, op=dist.ReduceOp.MAX, group=self._pg)
+                    kw["seq_cap"] = max(int(sc.item()), self._max_local_ids or 0)
                 self._peer = self._peer_by_B[B] = ops.make_peer_exchange(
-                    self._pg, dev, B, self._F_total, D, self._n_tw, n_rw, cap, n_cw=self._n_cw, Dc=self._Dc)
+                    self._pg, dev, B, self._F_total, D, self._n_tw, n_rw, cap, n_cw=self._n_cw, Dc=self._Dc, **kw)
                 self._peer.dist_count = 0
             peer = self._peer
             # landing zone: always zone 0 unless input dists are being prefetched, then alternating
@@ -604,9 +636,22 @@ class ShardedEmbeddingBagCollection(nn.Module):
             peer.barrier(channel)          # everyone is done reading this zone (and last step's outputs)
             if n_tw_all:
                 ops.push_lengths(lengths, B, self._peer_meta("len_tw", B, dev, slot))
+            seq = None
+            if track:
+                seq = dict(offsets=offsets, bo=None, bpos=None, arange=self._arange(values.numel(), dev))
             if n_rw:
                 rl, ro, rv = ops.permute_2d(self._rw_select_perm[:n_rw], B, lengths, offsets, values, values.numel())
-                bl, bo, bv = ops.bucketize_row_wise(rl, ro, rv, self._rw_block_sizes[:n_rw], n_rw, B, W, self._err_flag)
+                if track:
+                    # where in MY KeyedJaggedTensor every bucketised id came from (travels with the ids)
+                    _, _, rpos = ops.permute_2d(self._rw_select_perm[:n_rw], B, lengths, offsets, seq["arange"],
+                                                values.numel())
+                    bl, bo, bv, unb = ops.bucketize_row_wise_with_permute(rl, ro, rv, self._rw_block_sizes[:n_rw], n_rw,
+                                                                          B, W, self._err_flag)
+                    seq["bo"] = bo
+                    seq["bpos"] = ops.scatter_positions(unb, rpos, values.numel(), ro[n_rw * B:])
+                else:
+                    bl, bo, bv = ops.bucketize_row_wise(rl, ro, rv, self._rw_block_sizes[:n_rw], n_rw, B, W,
+                                                        self._err_flag)
                 ops.push_lengths(bl, B, self._peer_meta("len_rw", B, dev, slot))
             peer.barrier(channel)          # lengths have landed
             lo_ = z.off_x[: Fl * W * B + 1]
@@ -619,6 +664,12 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 ops.push_ids(values, offsets, B, self._peer_meta("ids_tw", B, dev, slot), peer.capacity, self._err_flag)
             if n_rw:
                 ops.push_ids(bv, bo, B, self._peer_meta("ids_rw", B, dev, slot), peer.capacity, self._err_flag)
+            if track:                      # the ids' positions, through the same transport into the zone's pos_x
+                if n_tw_all:
+                    ops.push_ids(seq["arange"], offsets, B, self._peer_meta("pos_tw", B, dev, slot), peer.capacity,
+                                 self._err_flag)
+                if n_rw:
+                    ops.push_ids(seq["bpos"], bo, B, self._peer_meta("pos_rw", B, dev, slot), peer.capacity, self._err_flag)
             peer.barrier(channel)          # ids have landed
             lv = z.ids_x
             tw_total = cw_total = None     # known on the host only later (counts_event)
@@ -710,7 +761,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 lo_ = torch.zeros(1, dtype=torch.int64, device=dev)
                 lv = recv_values
         return dict(lv=lv, lo=lo_, tw_total=tw_total, cw_total=cw_total, n_tw_r=n_tw_r, n_cw_r=n_cw_r, peer=peer,
-                    dev=dev, slot=slot if peer is not None else 0)
+                    dev=dev, slot=slot if peer is not None else 0, seq=seq if peer is not None else None)
 
     def _pooled_lookup(self, c, B):
         W, r, D, ops = self._world, self._rank, self._D, self._ops
@@ -824,7 +875,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
             return m
         W, r, n_rw, p = self._world, self._rank, self._n_rw, self._peer_by_B[B].zones[slot]
         rows: List[List[int]] = []
-        if kind in ("len_tw", "ids_tw"):
+        if kind in ("len_tw", "ids_tw", "pos_tw", "gseq_tw"):
             # whole-table slots, then the column-shard slots of each owner (a column-wise feature is
             # pushed to every owner of one of its shards)
             slots = [(d, j, f) for d in range(W)
@@ -839,10 +890,21 @@ class ShardedEmbeddingBagCollection(nn.Module):
         if kind.startswith("len"):
             rows = [[sg * B for sg in seg], [p.len_ptrs[d] + 4 * w_ for d, w_ in zip(dsts, word)]]
         else:
-            rows = [seg, [p.off_ptrs[d] + 8 * w_ for d, w_ in zip(dsts, word)], [p.ids_ptrs[d] for d in dsts]]
+            base = (p.ids_ptrs if kind.startswith("ids") else p.pos_ptrs if kind.startswith("pos")
+                    else self._peer_by_B[B].grad_seq_ptrs)
+            rows = [seg, [p.off_ptrs[d] + 8 * w_ for d, w_ in zip(dsts, word)], [base[d] for d in dsts]]
         m = torch.tensor(rows, dtype=torch.int64, device=device).reshape(-1)
         self._meta_cache[key] = m
         return m
+
+    _max_local_ids: Optional[int] = None
+
+    def _arange(self, n: int, device) -> torch.Tensor:
+        """0..n-1 on the device, grown geometrically and kept (positions of the local ids)."""
+        buf = getattr(self, "_arange_buf", None)
+        if buf is None or buf.numel() < n or buf.device != device:
+            buf = self._arange_buf = torch.arange(max(int(1.5 * n), 1024), dtype=torch.int64, device=device)
+        return buf[:n]
 
     def _bw_scratch(self, name: str, L: int, device):
         """Backward workspace of a shard; the forward writes the sort pairs into it when training."""
@@ -1228,14 +1290,104 @@ class ShardedEmbeddingCollection(ShardedEmbeddingBagCollection):
 
     def __init__(self, tables, plan: Dict[str, ParameterSharding], device: torch.device,
                  process_group: Optional[dist.ProcessGroup] = None, kernel_ops=None, init_seed: int = 0,
-                 init_on_device: bool = False):
+                 init_on_device: bool = False, peer_memory: Optional[bool] = None,
+                 max_ids_per_rank: Optional[int] = None, max_local_ids: Optional[int] = None):
         if any(ps.sharding_type == ShardingType.COLUMN_WISE for ps in plan.values()):
             raise ValueError("ShardedEmbeddingCollection supports table-wise and row-wise sharding (no column-wise)")
         super().__init__(tables, plan, device, process_group, kernel_ops, init_seed, init_on_device,
-                         peer_memory=False)
+                         peer_memory=peer_memory, max_ids_per_rank=max_ids_per_rank)
         self._track_positions = True
+        self._max_local_ids = max_local_ids        # rows of the output buffers (default: 1.25 x the first batch)
+        W = self._world
+        for name in ("tw", "rw"):                   # table slice per landing-zone SEGMENT (feature x source rank)
+            self.register_buffer(f"_{name}_seg_row_base", getattr(self, f"_{name}_row_base").repeat_interleave(W),
+                                 persistent=False)
+            self.register_buffer(f"_{name}_seg_rows", getattr(self, f"_{name}_rows").repeat_interleave(W),
+                                 persistent=False)
+
+    def _seg_group(self, name: str):
+        grp = self._group(name, False)
+        grp.feat_row_base, grp.feat_rows = getattr(self, f"_{name}_seg_row_base"), getattr(self, f"_{name}_seg_rows")
+        return grp
+
+    # ---- over NVLink peer memory: the owners' lookups store every row at its id's own position in the sender's
+    # output buffer; the gradient rows travel back the same way (tdfo_kjt_push_rows); no collective library call,
+    # no index ops on the step
+    def _seq_forward_peer(self, values, lengths, B):
+        W, D, ops, r = self._world, self._D, self._ops, self._rank
+        c = self._input_dist(values, lengths, B)
+        peer, lo_, dev = c["peer"], c["lo"], c["dev"]
+        z = peer.zones[c["slot"]]
+        n_tw_r, n_rw, GB = c["n_tw_r"], self._n_rw, W * B
+        L_local = values.numel()
+        if L_local > peer.seq_cap:
+            raise RuntimeError(f"tdfo_b200: this batch has {L_local} ids, the output buffers hold {peer.seq_cap}; "
+                               "construct the module with a larger max_local_ids")
+        k = peer.step % 2
+        peer.step += 1
+        self._fwd_token += 1
+        pairs = None
+        if self._emit_keys and hasattr(ops, "embedding_backward_prepare_pairs"):
+            pairs = getattr(peer, "sort_pairs", None)
+            if pairs is None:
+                pairs = peer.sort_pairs = (torch.empty(max(peer.capacity, 4), dtype=torch.int32, device=dev),
+                                           torch.empty(max(peer.capacity, 4), dtype=torch.int32, device=dev))
+        if n_tw_r:
+            ops.embedding_forward_seq_peer(self._seg_group("tw"), z.ids_x, lo_[: n_tw_r * GB + 1], B, z.pos_x,
+                                           peer.seq_out_ptrs[k], W, sort_pairs=pairs)
+        if n_rw:
+            ops.embedding_forward_seq_peer(self._seg_group("rw"), z.ids_x, lo_[n_tw_r * GB: (n_tw_r + n_rw) * GB + 1], B,
+                                           z.pos_x, peer.seq_out_ptrs[k], W, sort_pairs=pairs)
+        peer.barrier()                                   # every row of my ids has landed
+        out = peer.seq_out[k][: L_local * D].view(L_local, D)     # valid until the forward after next
+        saved = dict(px=peer, slot=c["slot"], lo=lo_, n_tw_r=n_tw_r, GB=GB, pairs=pairs, seq=c["seq"],
+                     token=self._fwd_token)
+        return out, saved
+
+    def _seq_backward_peer(self, grad_rows, saved, B):
+        W, D, ops = self._world, self._D, self._ops
+        if saved["token"] != self._fwd_token:
+            raise RuntimeError("tdfo_b200: with peer-memory exchange, backward must run before the next forward")
+        self._fused.iteration += 1
+        opt = self._fused.args()
+        px, lo_, n_tw_r, GB, seq = saved["px"], saved["lo"], saved["n_tw_r"], saved["GB"], saved["seq"]
+        n_rw, dev = self._n_rw, grad_rows.device
+        z = px.zones[saved["slot"]]
+        z.counts_event.synchronize()
+        tw_total, _, total = (int(x) for x in z.counts_host.tolist())
+        if total > px.capacity:
+            raise RuntimeError(f"tdfo_b200: rank {self._rank} received {total} ids this step, its exchange buffer "
+                               f"holds {px.capacity}; construct the module with a larger max_ids_per_rank")
+        # gradient rows to the owners of their ids, landing in the order the ids landed
+        if sum(self._n_tw):
+            ops.push_rows(grad_rows, None, seq["offsets"], B, self._peer_meta("gseq_tw", B, dev, saved["slot"]),
+                          px.capacity, self._err_flag)
+        if n_rw:
+            ops.push_rows(grad_rows, seq["bpos"], seq["bo"], B, self._peer_meta("gseq_rw", B, dev, saved["slot"]),
+                          px.capacity, self._err_flag)
+        shards = [(name, s0, n, off) for name, have, s0, n, off in
+                  (("tw", n_tw_r, 0, tw_total, lo_[: n_tw_r * GB + 1]),
+                   ("rw", n_rw, tw_total, total - tw_total, lo_[n_tw_r * GB: (n_tw_r + n_rw) * GB + 1]))
+                  if have and n > 0]
+        prepared = {}
+        for name, s0, n, off in shards:                  # the id-only half of the backward runs while the rows travel
+            if saved["pairs"] is not None:
+                prepared[name] = self._prepared_scratch(name, n, dev)
+                ops.embedding_backward_prepare_pairs(self._group(name, False), saved["pairs"][0][s0:s0 + n],
+                                                     saved["pairs"][1][s0:s0 + n], n, prepared[name])
+        px.barrier()                                     # gradient rows have landed
+        for name, s0, n, off in shards:
+            grad = px.grad_seq[s0 * D:(s0 + n) * D].view(n, D)
+            if name in prepared:
+                ops.embedding_backward_update(self._group(name, True), grad, z.ids_x[s0:s0 + n], off, GB, _lib.POOL_NONE,
+                                              opt, scratch=prepared[name], keys_in_scratch="prepared")
+            else:
+                ops.embedding_backward_update(self._group(name, True), grad, z.ids_x[s0:s0 + n], off - s0 if s0 else off,
+                                              GB, _lib.POOL_NONE, opt)
 
     def _seq_forward(self, values, lengths, B):
+        if self._use_peer:
+            return self._seq_forward_peer(values, lengths, B)
         W, D, ops = self._world, self._D, self._ops
         c = self._input_dist(values, lengths, B)
         lv, lo_, tw_total, n_tw_r, dev = c["lv"], c["lo"], c["tw_total"], c["n_tw_r"], c["dev"]
@@ -1261,6 +1413,8 @@ class ShardedEmbeddingCollection(ShardedEmbeddingBagCollection):
         return out, saved
 
     def _seq_backward(self, grad_rows, saved, B):
+        if "px" in saved:
+            return self._seq_backward_peer(grad_rows, saved, B)
         W, D, ops = self._world, self._D, self._ops
         self._fused.iteration += 1
         opt = self._fused.args()
@@ -1285,8 +1439,10 @@ class ShardedEmbeddingCollection(ShardedEmbeddingBagCollection):
         if self.training and torch.is_grad_enabled():
             if self._anchor is None or self._anchor.device != values.device:
                 self._anchor = torch.zeros(1, device=values.device, requires_grad=True)
+            self._emit_keys = isinstance(self._ops, CudaKernelOps)
             rows = _ShardedSequenceFn.apply(self._anchor, self, values, lengths, B)
         else:
+            self._emit_keys = False
             rows, _ = self._seq_forward(values, lengths, B)
         names = self._feature_names
         offsets = features.offsets()

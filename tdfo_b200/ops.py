@@ -171,6 +171,48 @@ def push_ids(values: torch.Tensor, offsets: torch.Tensor, B: int, meta: torch.Te
                                         _ptr(err_flag), _stream()))
 
 
+def push_rows(rows: torch.Tensor, positions: Optional[torch.Tensor], offsets: torch.Tensor, B: int, meta: torch.Tensor,
+              capacity: int, err_flag) -> None:
+    """Rows of ``rows`` ([n, D] float32), picked through ``positions`` (or in place order), to the owners' row buffers."""
+    rows = _cuda(rows, torch.float32, "rows")
+    offsets = _cuda(offsets, torch.int64, "offsets")
+    if positions is not None:
+        positions = _cuda(positions, torch.int64, "positions")
+    check(_lib.load().tdfo_kjt_push_rows(_ptr(rows), _ptr(positions), _ptr(offsets), B, rows.shape[1], meta.numel() // 3,
+                                         _ptr(meta), capacity, _ptr(err_flag), _stream()))
+
+
+def scatter_positions(permute: torch.Tensor, positions_in: Optional[torch.Tensor], n: int,
+                      n_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``out[permute[i]] = positions_in[i]`` (or ``i``) for i < min(n, n_dev[0])."""
+    permute = _cuda(permute, torch.int64, "permute")
+    if positions_in is not None:
+        positions_in = _cuda(positions_in, torch.int64, "positions_in")
+    out = torch.empty(max(n, 1), dtype=torch.int64, device=permute.device)
+    check(_lib.load().tdfo_kjt_scatter_positions(_ptr(permute), _ptr(positions_in), n, _ptr(n_dev), _ptr(out), _stream()))
+    return out
+
+
+def embedding_forward_seq_peer(group: TableGroup, indices: torch.Tensor, offsets: torch.Tensor, B: int,
+                               positions: torch.Tensor, peer_out: torch.Tensor, world: int,
+                               sort_pairs: Optional[tuple] = None) -> None:
+    """Sequence lookup on the owner with the rows stored at the ids' own positions in their source ranks' buffers.
+    ``group.feat_row_base`` / ``feat_rows`` are per SEGMENT (local feature x source rank)."""
+    indices = _cuda(indices, torch.int64, "indices")
+    offsets = _cuda(offsets, torch.int64, "offsets")
+    positions = _cuda(positions, torch.int64, "positions")
+    peer_out = _cuda(peer_out, torch.int64, "peer_out")
+    w = group.weights
+    S = group.feat_row_base.numel()
+    if offsets.numel() != S * B + 1:
+        raise ValueError(f"offsets has {offsets.numel()} entries, expected S*B+1 = {S * B + 1}")
+    sk, sv = (None, None) if sort_pairs is None else (_ptr(sort_pairs[0]), _ptr(sort_pairs[1]))
+    check(_lib.load().tdfo_embedding_forward_seq_peer(
+        _ptr(w), _wdtype(w), group.total_rows, group.D, _ptr(indices), _ptr(offsets), _ptr(group.feat_row_base),
+        _ptr(group.feat_rows), S, B, indices.numel(), _ptr(positions), _ptr(peer_out), world, sk, sv,
+        _ptr(group.err_flag), _stream()))
+
+
 def permute_2d(permute, B, in_lengths, in_offsets, in_indices, in_weights=None, out_total: Optional[int] = None):
     """``out_total``: number of ids the output holds, if the caller knows it (saves a sync);
     otherwise it is read back from the computed offsets (one D2H sync)."""

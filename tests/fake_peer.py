@@ -71,10 +71,11 @@ class _FakeEvent:
 class FakePeerExchange:
     """Same buffers, in the same order, as tdfo_b200.distributed._PeerExchange."""
 
-    def __init__(self, mem: FakeMem, pg, device, B, F_total, D, n_tw, n_rw, ids_capacity, n_cw=None, Dc=0):
+    def __init__(self, mem: FakeMem, pg, device, B, F_total, D, n_tw, n_rw, ids_capacity, n_cw=None, Dc=0, seq_cap=0):
         W = len(n_tw)
         n_cw = n_cw if n_cw is not None else [0] * W
         self.B, self.capacity, self.step, self._pg = B, int(ids_capacity), 0, pg
+        self.seq_cap = int(seq_cap)
         self._mem = mem
         fl_max = max(a + b for a, b in zip(n_tw, n_cw)) + n_rw
         self._n_bags = fl_max * W * B
@@ -99,6 +100,14 @@ class FakePeerExchange:
             self.rw_part_ptrs = mem.ptrs(k)
             self.grad_rw, k = mem.empty(W * B * n_rw * D, torch.float32)
             self.grad_rw_ptrs = mem.ptrs(k)
+        self.seq_out, self.seq_out_ptrs, self.grad_seq, self.grad_seq_ptrs = [], [], None, []
+        if self.seq_cap:
+            for _ in range(2):
+                t_, k = mem.empty(self.seq_cap * D, torch.float32)
+                self.seq_out.append(t_)
+                self.seq_out_ptrs.append(torch.tensor(mem.ptrs(k), dtype=torch.int64))
+            self.grad_seq, k = mem.empty(self.capacity * D, torch.float32)
+            self.grad_seq_ptrs = mem.ptrs(k)
         dist.barrier(group=pg)                              # every rank's files exist
 
     def _make_zone(self):
@@ -112,6 +121,10 @@ class FakePeerExchange:
         z.ids_ptrs = mem.ptrs(k)
         z.counts_host = torch.zeros(3, dtype=torch.int64)
         z.counts_event = _FakeEvent()
+        z.pos_x, z.pos_ptrs = None, []
+        if self.seq_cap:
+            z.pos_x, k = mem.empty(max(self.capacity, 4), torch.int64)
+            z.pos_ptrs = mem.ptrs(k)
         return z
 
     def ensure_second_zone(self):
@@ -197,6 +210,50 @@ class FakePeerOps(OracleKernelOps):
         o = out.view(B, out_stride)
         for k, c in enumerate(_np(out_col)):
             o[:, int(c): int(c) + D] = torch.from_numpy(acc[:, k])
+
+    # ---- tdfo_kjt_scatter_positions: out[permute[i]] = positions_in[i] (or i), i < min(n, *n_dev)
+    def scatter_positions(self, permute, positions_in, n, n_dev=None):
+        if n_dev is not None:
+            n = min(n, int(_np(n_dev)[0]))
+        out = np.zeros(max(int(permute.numel()), 1), np.int64)
+        src = np.arange(n, dtype=np.int64) if positions_in is None else _np(positions_in)[:n]
+        out[_np(permute)[:n]] = src
+        return torch.from_numpy(out)
+
+    # ---- tdfo_kjt_push_rows: like push_ids, rows of D floats picked through `positions`
+    def push_rows(self, rows, positions, offsets, B, meta, capacity, err_flag):
+        m = _np(meta).reshape(3, -1)
+        src, off = _np(rows), _np(offsets)
+        D = src.shape[1]
+        pos = None if positions is None else _np(positions)
+        for j in range(m.shape[1]):
+            seg = int(m[0, j])
+            s0, s1 = int(off[seg * B]), int(off[(seg + 1) * B])
+            if s1 <= s0:
+                continue
+            dst_off = int(self.mem.view(int(m[1, j]), np.int64, 1)[0])
+            if dst_off < 0 or dst_off + (s1 - s0) > capacity:
+                err_flag |= 4
+                continue
+            take = np.arange(s0, s1) if pos is None else pos[s0:s1]
+            self.mem.view(int(m[2, j]) + 4 * dst_off * D, np.float32, (s1 - s0) * D)[:] = src[take].reshape(-1)
+
+    # ---- tdfo_embedding_forward_seq_peer: landed id p of segment s -> row positions[p] of rank (s % world)'s buffer
+    def embedding_forward_seq_peer(self, group, indices, offsets, B, positions, peer_out, world, sort_pairs=None):
+        w = np.ascontiguousarray(_table(group.weights))
+        if w.dtype == np.uint16:
+            w = orc.bf16_to_f32(w)
+        D = w.shape[1]
+        idx, off, pos = _np(indices), _np(offsets), _np(positions)
+        base, rows, ptrs = _np(group.feat_row_base), _np(group.feat_rows), _np(peer_out)
+        S = base.size
+        for s_ in range(S):
+            for p in range(int(off[s_ * B]), int(off[(s_ + 1) * B])):
+                i = int(idx[p])
+                row = w[int(base[s_]) + i] if 0 <= i < int(rows[s_]) else np.zeros(D, np.float32)
+                if not 0 <= i < int(rows[s_]):
+                    group.err_flag |= 1
+                self.mem.view(int(ptrs[s_ % world]) + 4 * int(pos[p]) * D, np.float32, D)[:] = row
 
     # ---- the id-only half of the backward has nothing to precompute for the oracle
     def backward_scratch_bytes(self, L, total_rows):

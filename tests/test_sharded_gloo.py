@@ -164,7 +164,9 @@ def seq_grad(rank, L):
     return np.random.default_rng(500 + rank).normal(size=(L, D)).astype(np.float32)
 
 
-def run_rank_sequence(rank, port, plan_kind, results, cuda=False):
+def run_rank_sequence(rank, port, plan_kind, results, cuda=False, fake_tag=None):
+    """cuda: real GPUs (peer memory by default).  fake_tag: CPU ranks driving the peer-memory branch against
+    tests/fake_peer.py.  Neither: the all-to-all branch with the oracle-backed kernel table."""
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     if cuda:
@@ -187,8 +189,15 @@ def run_rank_sequence(rank, port, plan_kind, results, cuda=False):
                 "rw": {c.name: td.row_wise() for c in tables},
                 "mixed": {"t0": td.table_wise(1), "t1": td.row_wise(), "t2": td.table_wise(0), "t3": td.row_wise(),
                           "t4": td.table_wise(1)}}[plan_kind]
-        m = td.ShardedEmbeddingCollection(tables, plan, dev, kernel_ops=None if cuda else OracleKernelOps(),
-                                          init_seed=5)
+        mem = None
+        if fake_tag:
+            from fake_peer import FakeMem, FakePeerOps
+            mem = FakeMem(fake_tag, rank, W)
+            m = td.ShardedEmbeddingCollection(tables, plan, dev, kernel_ops=FakePeerOps(mem), init_seed=5, peer_memory=True)
+        else:
+            m = td.ShardedEmbeddingCollection(tables, plan, dev, kernel_ops=None if cuda else OracleKernelOps(),
+                                              init_seed=5)
+        assert m._use_peer == bool(cuda or fake_tag)
         m.set_fused_optimizer(t.EmbOptimType.EXACT_SGD, learning_rate=0.05)
         m.train()
         lengths, idx, _ = local_batch(rank, rows)
@@ -230,17 +239,25 @@ def run_rank_sequence(rank, port, plan_kind, results, cuda=False):
             np.testing.assert_allclose(got_t, w_ref[base[i]:base[i] + rows[i]], rtol=1e-5, atol=1e-6,
                                        err_msg=f"table {c.name} ({plan_kind})")
         results[rank] = "ok"
+        if mem is not None:
+            dist.barrier()
+            mem.cleanup()
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("plan_kind", ["tw", "rw", "mixed"])
-def test_sharded_sequence_equals_unsharded_world2(plan_kind):
+@pytest.mark.parametrize("plan_kind,fake_peer", [("tw", False), ("rw", False), ("mixed", False),
+                                                 ("tw", True), ("rw", True), ("mixed", True)])
+def test_sharded_sequence_equals_unsharded_world2(plan_kind, fake_peer):
+    """fake_peer: the peer-memory branch (rows stored by the owners at the ids' own positions, gradient rows pushed
+    back) on CPU ranks against tests/fake_peer.py; otherwise the all-to-all branch."""
+    import uuid
     port = free_port()
+    tag = ("tdfo_fake_" + uuid.uuid4().hex[:8]) if fake_peer else None
     ctx = mp.get_context("spawn")
     with ctx.Manager() as mgr:
         results = mgr.dict()
-        procs = [ctx.Process(target=run_rank_sequence, args=(r, port, plan_kind, results)) for r in range(W)]
+        procs = [ctx.Process(target=run_rank_sequence, args=(r, port, plan_kind, results, False, tag)) for r in range(W)]
         for p in procs:
             p.start()
         for p in procs:
