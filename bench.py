@@ -609,6 +609,57 @@ def sharded_workload(cfg, args, rank, world, dev, headline):
     return res, extra
 
 
+def sharded_ec_block(args, rank, world, dev):
+    """The module the reference itself shards (torchrec/models.py:150-164, torchrec/train.py:241-247): one item table in
+    an EmbeddingCollection (one row per id), row-wise over the GPUs, fused ADAM (torchrec/train.py:191,236-240), at the
+    reference's own shape and at a large one.  fwd + bwd + update per step, ids resident on the device."""
+    import gc
+    import torch
+    import torch.distributed as dist
+    import tdfo_b200 as t
+    from tdfo_b200 import distributed as td
+    out = {}
+    shapes = {"reference shape: batch 16 per GPU, 20 ids per sequence, dim 16": (16, 20, 16, 100_000),
+              "batch 16384 per GPU, 20 ids per sequence, dim 128": (16384, 20, 128, 1_000_000)}
+    for name, (B, T, D, V) in shapes.items():
+        tables = [t.EmbeddingConfig(name="item_embedding", embedding_dim=D, num_embeddings=V, feature_names=["item"],
+                                    weight_init_max=1.0, weight_init_min=-1.0)]
+        m = td.ShardedEmbeddingCollection(tables, {"item_embedding": td.row_wise()}, dev, init_on_device=True,
+                                          max_ids_per_rank=world * B * T + 1024, max_local_ids=B * T)
+        m.set_fused_optimizer(t.EmbOptimType.ADAM, learning_rate=3e-4, weight_decay=1e-4)
+        m.train()
+        gen = torch.Generator(device=dev).manual_seed(7 + rank)
+        ids = [torch.randint(1, V, (B * T,), device=dev, generator=gen) for _ in range(2)]
+        lengths = torch.full((B,), T, dtype=torch.int32, device=dev)
+        grad = torch.randn((B * T, D), device=dev, generator=gen)
+
+        def step(i):
+            jt = m(t.KeyedJaggedTensor(["item"], ids[i % 2], lengths=lengths, stride=B))["item"]
+            jt.values().backward(grad)
+
+        for i in range(args.warmup):
+            step(i)
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(args.steps):
+            step(i)
+        e1.record()
+        dist.barrier()
+        torch.cuda.synchronize()
+        tt = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms = float(tt.item()) / args.steps
+        m.check_errors()
+        out[name] = {"ms_per_step": ms, "value": world * B * T / (ms * 1e-3), "unit": UNIT, "rows": V,
+                     "exchange": "NVLink peer memory" if m._use_peer else "NCCL all-to-all"}
+        del m, ids, grad
+        gc.collect()
+        torch.cuda.empty_cache()
+    return out
+
+
 def run_ours_sharded(args):
     """N > 1.  Headline: BASELINE config 2 (or --config) with its tables sharded over the N GPUs of the box,
     every rank feeding its own batch.  Each workload is preceded by a seeded value check against the oracle
@@ -634,6 +685,12 @@ def run_ours_sharded(args):
             others[c] = r_
         except Exception as e:                              # keep the headline even if a side workload fails
             others[c] = {"error": f"{type(e).__name__}: {e}"[:400]}
+    ec = None
+    if args.config == 2:
+        try:
+            ec = sharded_ec_block(args, rank, world, dev)
+        except Exception as e:
+            ec = {"error": f"{type(e).__name__}: {e}"[:400]}
     ok = res["parity_check"]["ok"] and all(o.get("parity_check", {}).get("ok", False) for o in others.values()
                                             if "error" not in o)
     if rank == 0:
@@ -666,6 +723,8 @@ def run_ours_sharded(args):
         }
         if others:
             line["configs"] = others
+        if ec is not None:
+            line["sharded_embedding_collection"] = ec
         print(json.dumps(line), flush=True)
     dist.barrier()
     dist.destroy_process_group()

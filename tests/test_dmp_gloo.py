@@ -110,35 +110,52 @@ V2, T2, B2 = 40, 5, 6
 
 
 class TinyBert(nn.Module):
-    def __init__(self, t):
+    """The reference's HistoryArch + output layer in miniature (torchrec/models.py:150-178, 206-223): item table in
+    an EmbeddingCollection, jagged -> [B, T, D] through jagged_2d_to_dense, padding mask from to_padded_dense."""
+
+    def __init__(self, t, device=torch.device("cpu")):
         super().__init__()
+        self._t, self._dense_op = t, device.type == "cuda"
         self.embed_collection = t.EmbeddingCollection(
             tables=[t.EmbeddingConfig(name="item_embedding", embedding_dim=D, num_embeddings=V2, feature_names=["item"],
-                                      weight_init_max=1.0, weight_init_min=-1.0)], device=torch.device("cpu"))
+                                      weight_init_max=1.0, weight_init_min=-1.0)], device=device)
         self.out = nn.Linear(D, V2)
 
     def forward(self, kjt):
         jt = self.embed_collection(kjt)["item"]
+        if self._dense_op:                                     # the reference's own calls, on the GPU kernels
+            padded = self._t.jagged_2d_to_dense(values=jt.values(), offsets=jt.offsets(), max_sequence_length=T2)
+            mask = kjt["item"].to_padded_dense(desired_length=T2, padding_value=0) != 0
+            assert bool(mask.all())                            # ids start at 1 in this test: nothing is padding
+            return self.out(padded.view(-1, T2, D))
         return self.out(jt.values().view(-1, T2, D))          # every sequence has T2 ids here
 
 
-def run_rank_sequence(rank, port, results):
+def run_rank_sequence(rank, port, results, cuda=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
-    dist.init_process_group("gloo", rank=rank, world_size=W)
+    if cuda:
+        torch.cuda.set_device(rank)
+        dev = torch.device("cuda", rank)
+        dist.init_process_group("nccl", rank=rank, world_size=W, device_id=dev)
+    else:
+        dev = torch.device("cpu")
+        dist.init_process_group("gloo", rank=rank, world_size=W)
     try:
         import tdfo_b200 as t
         from tdfo_b200 import distributed as td
         from oracle_ops import OracleKernelOps
         torch.manual_seed(77)
-        model = TinyBert(t)
-        table0 = model.embed_collection.state_dict()["embeddings.item_embedding.weight"].clone()
+        model = TinyBert(t, dev)
+        table0 = model.embed_collection.state_dict()["embeddings.item_embedding.weight"].clone().cpu()
         fused_params = {"optimizer": t.EmbOptimType.ADAM, "learning_rate": 3e-2, "weight_decay": 1e-4}
-        dmp = t.DistributedModelParallel(module=model, device=torch.device("cpu"),
+        dmp = t.DistributedModelParallel(module=model, device=dev,
                                          sharders=[t.EmbeddingCollectionSharder(fused_params)],
-                                         plan={"item_embedding": td.row_wise()}, kernel_ops=OracleKernelOps())
+                                         plan={"item_embedding": td.row_wise()},
+                                         kernel_ops=None if cuda else OracleKernelOps())
         inner = dmp.module.module
         assert isinstance(inner.embed_collection, td.ShardedEmbeddingCollection)
+        assert inner.embed_collection._use_peer == cuda           # on GPUs: rows and gradients through NVLink peer memory
         dense_optimizer = t.KeyedOptimizerWrapper(dict(t.in_backward_optimizer_filter(dmp.named_parameters())),
                                                   lambda params: torch.optim.Adam(params, lr=3e-2))
         optimizer = t.CombinedOptimizer([dmp.fused_optimizer, dense_optimizer])
@@ -151,11 +168,11 @@ def run_rank_sequence(rank, port, results):
         per = [torch.from_numpy(np.random.default_rng(900 + r).integers(1, V2, size=(B2, T2))) for r in range(W)]
         seqs = per[rank]
         kjt = t.KeyedJaggedTensor.from_lengths_sync(keys=["item"], values=torch.cat(list(seqs), dim=0),
-                                                    lengths=torch.IntTensor([T2] * B2))
+                                                    lengths=torch.IntTensor([T2] * B2)).to(dev)     # torchrec/train.py:33-41
         dmp.train()
-        w_out, b_out = inner.out.weight.detach().clone(), inner.out.bias.detach().clone()
+        w_out, b_out = inner.out.weight.detach().clone().cpu(), inner.out.bias.detach().clone().cpu()
         logits = dmp(kjt)
-        loss = nn.CrossEntropyLoss()(logits.view(-1, V2), seqs.view(-1))
+        loss = nn.CrossEntropyLoss()(logits.view(-1, V2), seqs.view(-1).to(dev))
         optimizer.zero_grad()
         loss.backward()
         optimizer.step()
@@ -181,7 +198,7 @@ def run_rank_sequence(rank, port, results):
         np.testing.assert_allclose(got, w_ref, rtol=1e-5, atol=2e-6)
         # DDP kept the dense half identical on both ranks
         both = [None] * W
-        dist.all_gather_object(both, inner.out.weight.detach().numpy())
+        dist.all_gather_object(both, inner.out.weight.detach().cpu().numpy())
         np.testing.assert_array_equal(both[0], both[1])
         assert not np.array_equal(both[0], w_out.numpy())
         results[rank] = "ok"

@@ -235,3 +235,26 @@ def test_peer_memory_exchange_on_4_and_8_gpus(case, prefetch):
                 p.terminate()
         assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
         assert dict(results) == {r: "ok" for r in range(world)}
+
+
+def test_dmp_over_the_reference_item_table_on_2_gpus():
+    """torchrec/train.py:235-254 on two GPUs: DistributedModelParallel shards the item EmbeddingCollection row-wise with
+    fused ADAM (the reference's GPU choice), the model calls jagged_2d_to_dense / to_padded_dense as
+    torchrec/models.py:163-178,208-219 does, the dense half is under DDP; one step equals the unsharded oracle."""
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from test_dmp_gloo import run_rank_sequence as run_dmp_rank
+    port = free_port()
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        results = mgr.dict()
+        procs = [ctx.Process(target=run_dmp_rank, args=(r, port, results, True)) for r in range(W)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=300)
+        for p in procs:
+            if p.is_alive():
+                p.terminate()
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        assert dict(results) == {0: "ok", 1: "ok"}
