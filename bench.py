@@ -743,11 +743,15 @@ def run_e2e(args, t, ebc, keys, lengths_dev, batches, grad_out, F, B, D, L, worl
     # 68 MB batch takes 1.9-2.9 ms (tools/h2d_contention.py), close to the 3.3 ms step: one step of
     # look-ahead leaves no slack for jitter, two do.
     DEPTH = 2
-    host_vals = [b.cpu().pin_memory() for b in batches]
+    # ids cross PCIe as int32 (every table has far fewer than 2^31 rows) and are widened on the device by the
+    # KeyedJaggedTensor (tdfo_kjt_widen_ids): half the bytes of the copy that bounds the 8-GPU end-to-end rate
+    host_vals = [b.cpu().to(torch.int32).pin_memory() for b in batches]
     host_lens = lengths_dev.cpu().pin_memory()
     copy_stream = torch.cuda.Stream(device=dev)
-    slots = [dict(v=torch.empty(L, dtype=torch.int64, device=dev), l=torch.empty(F * B, dtype=torch.int32, device=dev),
+    slots = [dict(v=torch.empty(L, dtype=torch.int32, device=dev), l=torch.empty(F * B, dtype=torch.int32, device=dev),
                   ev=torch.cuda.Event()) for _ in range(DEPTH + 1)]
+    dist_prefetch = bool(getattr(args, "prefetch_input_dist", False)) and hasattr(ebc, "prefetch_input_dist") and world > 1
+    pending = {}
     main = torch.cuda.current_stream(dev)
 
     nocopy = os.environ.get("TDFO_E2E_NOCOPY") == "1"      # diagnostic only: marks the result as not end-to-end
@@ -777,8 +781,16 @@ def run_e2e(args, t, ebc, keys, lengths_dev, batches, grad_out, F, B, D, L, worl
         main.wait_event(s["ev"])
         if i + DEPTH < n_total:
             prefetch(i + DEPTH)
-        kjt = t.KeyedJaggedTensor.from_lengths_sync(keys, s["v"], s["l"])
+        kjt = pending.pop(i, None)
+        if kjt is None:
+            kjt = t.KeyedJaggedTensor.from_lengths_sync(keys, s["v"], s["l"])
         kt = ebc(kjt)
+        if dist_prefetch and i + 1 < n_total:
+            # batch i+1 is already on the device (copied two steps ahead): start its lengths / ids exchange now
+            s1 = slots[(i + 1) % (DEPTH + 1)]
+            main.wait_event(s1["ev"])
+            pending[i + 1] = t.KeyedJaggedTensor.from_lengths_sync(keys, s1["v"], s1["l"])
+            ebc.prefetch_input_dist(pending[i + 1])
         loss = torch.dot(kt.values().view(-1), grad_flat)     # scalar loss; d(loss)/d(pooled) = grad_out
         loss.backward()
         # device->host read of the step's loss: asynchronous copy into pinned memory, consumed one step
@@ -816,11 +828,13 @@ def run_e2e(args, t, ebc, keys, lengths_dev, batches, grad_out, F, B, D, L, worl
         ms = float(tt.item())
     return {"value": L * world * args.steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / args.steps,
             "wall_ms_per_step": wall_ms / args.steps,
-            "h2d_bytes_per_step": 0 if nocopy else L * 8 + F * B * 4, "d2h_bytes_per_step": 4,
+            "h2d_bytes_per_step": 0 if nocopy else L * 4 + F * B * 4, "d2h_bytes_per_step": 4,
+            "id_format": "int32 on the host and over PCIe, widened to int64 on the device",
+            "prefetch_input_dist": dist_prefetch,
             "losses_read": len(losses),
             "prefetch_depth": DEPTH,
-            "api": "pinned ids/lengths -> H2D -> KeyedJaggedTensor.from_lengths_sync -> EmbeddingBagCollection.forward -> "
-                   "loss.backward() (fused update) -> loss D2H"}
+            "api": "pinned int32 ids / lengths -> H2D -> KeyedJaggedTensor.from_lengths_sync -> (Sharded)EmbeddingBagCollection"
+                   ".forward -> loss.backward() (fused update) -> loss D2H"}
 
 
 def main():
@@ -839,8 +853,9 @@ def main():
     ap.add_argument("--configs", default="auto",
                     help="N>1: further configs reported under `configs` after the headline: auto (3,4,5 on 8 GPUs), "
                          "none, or a comma list such as 3,4")
-    ap.add_argument("--prefetch-input-dist", action="store_true",
-                    help="N>1: issue batch i+1's lengths / ids exchange before batch i's backward")
+    ap.add_argument("--no-prefetch-input-dist", dest="prefetch_input_dist", action="store_false",
+                    help="N>1: do NOT issue batch i+1's lengths / ids exchange before batch i's backward (it is on by "
+                         "default: 3.00 vs 3.17 ms/step on 8 GPUs, profiles/r2_bench_n8*.json)")
     ap.add_argument("--plan", choices=["tw", "mixed", "cw"], default="cw",
                     help="N>1: cw = table-wise round-robin with the tables that do not divide evenly split column-wise "
                          "(balanced; 21.1 G lookups/s at N=8), tw = all table-wise (19.5), mixed = remainder row-wise (16.7)")

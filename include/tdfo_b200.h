@@ -261,6 +261,9 @@ int tdfo_embedding_forward(const void* weights, int32_t weights_dtype, int64_t t
  * peer_out is a device array of `B / peer_batch` base addresses (as uint64), one per source rank,
  * pointing into NVLink peer memory (e.g. a torch symmetric-memory buffer); the caller puts a
  * barrier between this call and the readers.  Everything else as tdfo_embedding_forward.
+ * `indices` is normally a receive buffer whose fill the host does not know yet: pass its capacity as L
+ * (bags are cut there) and, as L_hint, how many ids to expect (0 = unknown); the hint only selects the
+ * launch shape (short bags are streamed in blocks of 32 bags).
  * Replaces: TBE forward + PooledEmbeddingsAllToAll of the sharded module DMP builds
  *   (torchrec/train.py:241-247, 98).
  */
@@ -272,7 +275,7 @@ int tdfo_embedding_forward_peer(const void* weights, int32_t weights_dtype, int6
                                 int32_t F, int64_t B, int64_t L, int32_t pooling_mode,
                                 const uint64_t* peer_out, int64_t peer_batch, int64_t out_stride,
                                 uint32_t* sort_keys, uint32_t* sort_vals,
-                                int32_t* err_flag, void* stream);
+                                int32_t* err_flag, int64_t L_hint, void* stream);
 
 /*
  * Sequence lookup (EmbeddingCollection, one row per id) with the output dist fused in, on the owner of the
@@ -475,6 +478,17 @@ int tdfo_embedding_backward_update(void* weights, int32_t weights_dtype, int64_t
  */
 int tdfo_copy_feature_blocks(const float* src, float* dst, int64_t B, int32_t D, int32_t nslots,
                              const int64_t* meta, void* stream);
+
+/*
+ * tdfo_copy_feature_blocks with absolute destinations that are NVLS MULTICAST addresses (dst_off = address / 4
+ * of a multicast mapping of a buffer every rank holds): each 16-byte chunk is written with one multimem store
+ * and the NVSwitch delivers it to every rank's copy.  Used for the row-wise backward, where every rank needs
+ * the gradient rows of every sample: an all-gather that costs each GPU one copy of its own rows on its link
+ * instead of world - 1.  Stores only; nothing is loaded through the multicast mapping.
+ * Replaces: the all-gather behind the backward of PooledEmbeddingsReduceScatter (torchrec/train.py:241-247, 104).
+ */
+int tdfo_copy_feature_blocks_multicast(const float* src, int64_t B, int32_t D, int32_t nslots,
+                                       const int64_t* meta, void* stream);
 
 /*
  * Row-wise output dist, second half: every rank s holds the partial pooled sums of its row block for

@@ -52,7 +52,7 @@ _SIGNATURES = {
     "tdfo_embedding_forward": (c_int, [P, c_int32, c_int64, c_int32, P, P, P, P, P, P, c_int32, c_int64, c_int64,
                                        c_int32, P, c_int64, P, P, P, P]),
     "tdfo_embedding_forward_peer": (c_int, [P, c_int32, c_int64, c_int32, P, P, P, P, P, P, c_int32, c_int64, c_int64,
-                                            c_int32, P, c_int64, c_int64, P, P, P, P]),
+                                            c_int32, P, c_int64, c_int64, P, P, P, c_int64, P]),
     "tdfo_linearize_indices": (c_int, [P, P, P, P, c_int32, c_int64, c_int64, c_int32, P, P, P, P]),
     "tdfo_radix_sort_scratch_bytes": (c_size_t, [c_int64, c_int32]),
     "tdfo_radix_sort_pairs": (c_int, [P, P, P, P, c_int64, c_int32, P, P, c_size_t, P]),
@@ -75,6 +75,7 @@ _SIGNATURES = {
                                                 P, c_int32, P, P, P, P]),
     "tdfo_embedding_backward_prepare_pairs": (c_int, [P, P, c_int64, c_int64, P, P, c_size_t, P]),
     "tdfo_copy_feature_blocks": (c_int, [P, P, c_int64, c_int32, c_int32, P, P]),
+    "tdfo_copy_feature_blocks_multicast": (c_int, [P, c_int64, c_int32, c_int32, P, P]),
     "tdfo_reduce_partial_sums": (c_int, [P, c_int32, c_int64, c_int64, c_int32, c_int32, P, P, c_int64, P]),
     "tdfo_jagged_2d_to_dense": (c_int, [P, P, c_int64, c_int32, c_int64, P, P]),
     "tdfo_dense_to_jagged": (c_int, [P, P, c_int64, c_int32, c_int64, c_int64, P, P]),

@@ -198,7 +198,15 @@ __device__ __forceinline__ CopyItem copy_item(const float* src, float* dst, int6
 // UNROLL independent 16-byte loads are issued before their stores.  The peer-push form (dst == NULL,
 // destinations are NVLink peer addresses) runs with few CTAs and UNROLL 4: it is NVLink-bound, and a
 // small grid leaves the SMs to the kernels that overlap it (the sort of the sharded backward).
-template <int UNROLL>
+// MC: the destinations are NVLS multicast addresses; one multimem store lands in the same place of every
+// rank's buffer (the switch replicates it), so an all-gather costs each GPU one copy of its data on the wire.
+__device__ __forceinline__ void multimem_st_128(void* mc_addr, uint4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 :: "l"(mc_addr), "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)),
+                    "f"(__uint_as_float(v.w)) : "memory");
+}
+
+template <int UNROLL, bool MC = false>
 __global__ void __launch_bounds__(256)
 copy_feature_blocks_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t B,
                            int32_t D4, int32_t nslots, const int64_t* __restrict__ meta) {
@@ -216,7 +224,10 @@ copy_feature_blocks_kernel(const float* __restrict__ src, float* __restrict__ ds
         for (int u = 0; u < UNROLL; ++u) v[u] = __ldcs(it[u].src);
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u)
-            if (i0 + u * stride < total) __stcs(it[u].dst, v[u]);
+            if (i0 + u * stride < total) {
+                if (MC) multimem_st_128(it[u].dst, v[u]);
+                else __stcs(it[u].dst, v[u]);
+            }
     }
 }
 
@@ -587,5 +598,20 @@ extern "C" int tdfo_kjt_scatter_positions(const int64_t* permute, const int64_t*
     scatter_positions_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(permute, positions_in, n, n_dev, out);
     count_launch();
     TDFO_LAUNCH_CHECK("kjt_scatter_positions");
+    return TDFO_OK;
+}
+
+extern "C" int tdfo_copy_feature_blocks_multicast(const float* src, int64_t B, int32_t D, int32_t nslots,
+                                                  const int64_t* meta, void* stream) {
+    TDFO_CHECK_ARG(B >= 0 && D > 0 && D % 4 == 0 && nslots >= 0, "copy_feature_blocks_multicast: bad size (D must be a multiple of 4)");
+    if (B == 0 || nslots == 0) return TDFO_OK;
+    TDFO_CHECK_ARG(src && meta, "copy_feature_blocks_multicast: null pointer");
+    TDFO_CHECK_ARG(aligned(src, 16), "copy_feature_blocks_multicast: src not 16-byte aligned");
+    const int64_t items = (int64_t)nslots * B * (D / 4);
+    unsigned g = grid_for((items + 3) / 4, 256);
+    if (g > (unsigned)kNumSMs * 2) g = kNumSMs * 2;
+    copy_feature_blocks_kernel<4, true><<<g, 256, 0, static_cast<cudaStream_t>(stream)>>>(src, nullptr, B, D / 4, nslots, meta);
+    count_launch();
+    TDFO_LAUNCH_CHECK("copy_feature_blocks_multicast");
     return TDFO_OK;
 }

@@ -29,6 +29,7 @@ struct LookupArgs {
     int64_t B;
     int64_t num_bags;     // F * B
     int64_t L;
+    int64_t L_shape;      // number of ids the launch shape is chosen for (== L unless the caller knows better)
     int64_t out_stride;
     int32_t F;
     int32_t nchunks;      // 16-byte chunks per row
@@ -441,7 +442,7 @@ static int launch_forward(const LookupArgs& a, int pooling_mode, cudaStream_t st
         sequence_forward_kernel<T, LPR, CPL><<<(unsigned)blocks, kFwdThreads, 0, st>>>(a);
     } else {
         if (a.num_bags == 0) return TDFO_OK;
-        if (a.L < 4 * a.num_bags) {
+        if (a.L_shape < 4 * a.num_bags) {
             // short bags (fewer than 4 ids on average): stream the ids of 32-bag blocks, rows in flight across bags
             constexpr int SCPL = (LPR == 32) ? CPL : 1;
             const int64_t warps = (a.num_bags + 31) / 32;
@@ -492,7 +493,7 @@ static int embedding_forward_impl(const void* weights, int32_t weights_dtype, in
                                   const uint64_t* peer_out, int64_t peer_batch,
                                   uint32_t* sort_keys, uint32_t* sort_vals,
                                   int32_t* err_flag, void* stream,
-                                  const int64_t* peer_pos = nullptr, int32_t peer_world = 0) {
+                                  const int64_t* peer_pos = nullptr, int32_t peer_world = 0, int64_t L_hint = 0) {
     TDFO_CHECK_ARG(weights_dtype == TDFO_F32 || weights_dtype == TDFO_BF16,
                    "embedding_forward: unknown weights_dtype %d", weights_dtype);
     TDFO_CHECK_ARG(pooling_mode >= TDFO_POOL_SUM && pooling_mode <= TDFO_POOL_NONE,
@@ -531,6 +532,7 @@ static int embedding_forward_impl(const void* weights, int32_t weights_dtype, in
     TDFO_CHECK_ARG(sort_keys == nullptr || ((int64_t)F * B < (1ll << 32) && L < (1ll << 32)),
                    "embedding_forward: sort keys need F*B and L below 2^32");
     a.peer_pos = peer_pos; a.peer_world = peer_world;
+    a.L_shape = (L_hint > 0 && L_hint < L) ? L_hint : L;
     a.out = out; a.peer_out = peer_out; a.peer_batch = peer_batch; a.sort_keys = sort_keys; a.sort_vals = sort_vals; a.oob_key = (uint32_t)total_rows; a.err_flag = err_flag; a.B = B; a.num_bags = (int64_t)F * B; a.L = L;
     a.out_stride = out_stride; a.F = F; a.nchunks = (int32_t)(D * esz / 16);
     a.mean = pooling_mode == TDFO_POOL_MEAN;
@@ -559,14 +561,14 @@ extern "C" int tdfo_embedding_forward_peer(const void* weights, int32_t weights_
                                            const int64_t* feat_out_col, int32_t F, int64_t B, int64_t L,
                                            int32_t pooling_mode, const uint64_t* peer_out, int64_t peer_batch,
                                            int64_t out_stride, uint32_t* sort_keys, uint32_t* sort_vals,
-                                           int32_t* err_flag, void* stream) {
+                                           int32_t* err_flag, int64_t L_hint, void* stream) {
     if (!peer_out) {
         set_error("embedding_forward_peer: peer_out is null");
         return TDFO_ERR_INVALID_ARG;
     }
     return embedding_forward_impl(weights, weights_dtype, total_rows, D, indices, offsets, per_sample_weights,
                                   feat_row_base, feat_rows, feat_out_col, F, B, L, pooling_mode, nullptr, out_stride,
-                                  peer_out, peer_batch, sort_keys, sort_vals, err_flag, stream);
+                                  peer_out, peer_batch, sort_keys, sort_vals, err_flag, stream, nullptr, 0, L_hint);
 }
 
 extern "C" int tdfo_embedding_forward_seq_peer(const void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,

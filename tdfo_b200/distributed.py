@@ -27,6 +27,7 @@ from __future__ import annotations
 
 import contextlib
 import enum
+import os
 import zlib
 from dataclasses import dataclass
 from types import SimpleNamespace
@@ -151,9 +152,10 @@ class CudaKernelOps:
         return self._ops.backward_layout(L, total_rows).total_bytes
 
     def embedding_forward_peer(self, group, indices, offsets, B, pooling_mode, peer_out, peer_batch,
-                               backward_scratch=None, sort_pairs=None):
+                               backward_scratch=None, sort_pairs=None, expected_ids=0):
         self._ops.embedding_forward_peer(group, indices, offsets, B, pooling_mode, peer_out, peer_batch,
-                                         backward_scratch=backward_scratch, sort_pairs=sort_pairs)
+                                         backward_scratch=backward_scratch, sort_pairs=sort_pairs,
+                                         expected_ids=expected_ids)
 
     def embedding_backward_prepare_pairs(self, group, keys, vals, L, scratch):
         self._ops.embedding_backward_prepare_pairs(group, keys, vals, L, scratch)
@@ -181,6 +183,9 @@ class CudaKernelOps:
 
     def reduce_partial_sums(self, parts, W, B, nslots, D, out_col, out, out_stride):
         self._ops.reduce_partial_sums(parts, W, B, nslots, D, out_col, out, out_stride)
+
+    def copy_feature_blocks_multicast(self, src, B, D, meta):
+        self._ops.copy_feature_blocks_multicast(src, B, D, meta)
 
 
 class _Shard:
@@ -249,12 +254,20 @@ class _PeerExchange:
             self.grad_cw_ptrs = list(symm.rendezvous(self.grad_cw, group).buffer_ptrs)
         # row-wise tables: slot s of `rw_part` receives rank s's partial pooled sums for MY samples
         # ([W][B][n_rw*D]); `grad_rw` receives every rank's gradient rows of the row-wise features ([W*B][n_rw*D])
-        self.rw_part, self.rw_part_ptrs, self.grad_rw, self.grad_rw_ptrs = None, [], None, []
+        self.rw_part, self.rw_part_ptrs, self.grad_rw, self.grad_rw_ptrs, self.grad_rw_mc = None, [], None, [], 0
         if n_rw > 0:
             self.rw_part = symm.empty(W * B * n_rw * D, dtype=torch.float32, device=device)
             self.rw_part_ptrs = list(symm.rendezvous(self.rw_part, group).buffer_ptrs)
             self.grad_rw = symm.empty(W * B * n_rw * D, dtype=torch.float32, device=device)
-            self.grad_rw_ptrs = list(symm.rendezvous(self.grad_rw, group).buffer_ptrs)
+            hdl = symm.rendezvous(self.grad_rw, group)
+            self.grad_rw_ptrs = list(hdl.buffer_ptrs)
+            # NVLS multicast address of the same buffer (0 when the fabric has none): one store reaches every rank
+            self.grad_rw_mc = 0
+            if os.environ.get("TDFO_NO_MULTICAST") != "1":
+                try:
+                    self.grad_rw_mc = int(hdl.multicast_ptr or 0)
+                except Exception:
+                    self.grad_rw_mc = 0
         # sequence module: rotating row buffers [seq_cap, D] the owners store looked-up rows into (at the ids' own
         # positions), and the landing buffer for the gradient rows of the ids this rank owns
         self.seq_out, self.seq_out_ptrs, self.grad_seq, self.grad_seq_ptrs = [], [], None, []
@@ -522,6 +535,14 @@ class ShardedEmbeddingBagCollection(nn.Module):
                     ss.append(Ft * D_)
                     do.append(self._peer_by_B[B].grad_ptrs[d] // 4 + r * B * n * D_ + j * D_)     # absolute address / 4
                     ds.append(n * D_)
+            elif cls == "rw_mc":
+                # the same all-gather through the NVLS multicast mapping of the landing buffer: one slot per feature
+                n = self._n_rw
+                for k_, f in enumerate(self._rw_feats):
+                    so.append(f * D_)
+                    ss.append(Ft * D_)
+                    do.append(self._peer_by_B[B].grad_rw_mc // 4 + r * B * n * D_ + k_ * D_)
+                    ds.append(n * D_)
             elif cls == "rw":
                 # every rank needs the gradient of every sample for the row-wise features (an all-gather,
                 # written by the sample owners straight into the other ranks' landing buffers)
@@ -761,7 +782,8 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 lo_ = torch.zeros(1, dtype=torch.int64, device=dev)
                 lv = recv_values
         return dict(lv=lv, lo=lo_, tw_total=tw_total, cw_total=cw_total, n_tw_r=n_tw_r, n_cw_r=n_cw_r, peer=peer,
-                    dev=dev, slot=slot if peer is not None else 0, seq=seq if peer is not None else None)
+                    dev=dev, slot=slot if peer is not None else 0, seq=seq if peer is not None else None,
+                    mean_len=values.numel() / max(lengths.numel(), 1))
 
     def _pooled_lookup(self, c, B):
         W, r, D, ops = self._world, self._rank, self._D, self._ops
@@ -786,20 +808,24 @@ class ShardedEmbeddingBagCollection(nn.Module):
                 if pairs is None:
                     pairs = peer.sort_pairs = (torch.empty(max(peer.capacity, 4), dtype=torch.int32, device=dev),
                                                torch.empty(max(peer.capacity, 4), dtype=torch.int32, device=dev))
+            # how many ids a shard should expect (the landing zone's fill is not known on the host yet): the local
+            # batch's mean bag length times the shard's bags; it only picks the lookup's launch shape
+            mean_len = c.get("mean_len", 0.0)
+            hint = lambda n_feat: int(mean_len * n_feat * GB) + 1
             if n_tw_r:
                 # pooled rows go straight into the output buffer of the rank that owns the sample
                 grp = self._group("tw", False)
                 grp.feat_out_col = self._tw_global_col        # columns of the final [B, F_total*D] layout
                 grp.out_stride = self._F_total * D
                 ops.embedding_forward_peer(grp, lv, lo_[: n_tw_r * GB + 1], GB, self._pooling, peer.out_ptrs[k], B,
-                                           sort_pairs=pairs)
+                                           sort_pairs=pairs, expected_ids=hint(n_tw_r))
             if n_cw_r:
                 # column shards: the same, Dc columns per pooled row
                 grp = self._group("cw", False)
                 grp.feat_out_col = self._cw_global_col
                 grp.out_stride = self._F_total * D
                 ops.embedding_forward_peer(grp, lv, lo_[n_tw_r * GB: n_own * GB + 1], GB, self._pooling,
-                                           peer.out_ptrs[k], B, sort_pairs=pairs)
+                                           peer.out_ptrs[k], B, sort_pairs=pairs, expected_ids=hint(n_cw_r))
             if n_rw:
                 # row-wise: my block's partial sums of sample (src, b) go into slot `r` of rank src's buffer
                 key = (B, "rw_part_out", str(dev))
@@ -808,7 +834,7 @@ class ShardedEmbeddingBagCollection(nn.Module):
                     slot_ptrs = self._meta_cache[key] = torch.tensor(
                         [p + 4 * r * B * n_rw * D for p in peer.rw_part_ptrs], dtype=torch.int64, device=dev)
                 ops.embedding_forward_peer(self._group("rw", False), lv, lo_[n_own * GB: Fl * GB + 1], GB, _lib.POOL_SUM,
-                                           slot_ptrs, B, sort_pairs=pairs)
+                                           slot_ptrs, B, sort_pairs=pairs, expected_ids=hint(n_rw) // W + 1)
             peer.barrier()                                    # all pooled rows / partial sums have landed
             if n_rw:
                 # add the W slots in rank order into the row-wise columns of the output (fixed order: reproducible)
@@ -993,7 +1019,10 @@ class ShardedEmbeddingBagCollection(nn.Module):
                     ops.copy_feature_blocks(grad_out, None, B, Dc, self._peer_grad_meta(B, grad_out.device, "cw"))
                     recv_cw = px.grad_cw[: GB * n_cw_r * Dc]
                 if n_rw:
-                    ops.copy_feature_blocks(grad_out, None, B, D, self._peer_grad_meta(B, grad_out.device, "rw"))
+                    if getattr(px, "grad_rw_mc", 0) and hasattr(ops, "copy_feature_blocks_multicast"):
+                        ops.copy_feature_blocks_multicast(grad_out, B, D, self._peer_grad_meta(B, grad_out.device, "rw_mc"))
+                    else:
+                        ops.copy_feature_blocks(grad_out, None, B, D, self._peer_grad_meta(B, grad_out.device, "rw"))
                     recv_rw = px.grad_rw.view(GB, n_rw * D)
                 if n_tw_all or n_cw_all or n_rw:
                     px.barrier()

@@ -284,7 +284,7 @@ def embedding_forward(group: TableGroup, indices: torch.Tensor, offsets: torch.T
 def embedding_forward_peer(group: TableGroup, indices: torch.Tensor, offsets: torch.Tensor, B: int, pooling_mode: int,
                            peer_out: torch.Tensor, peer_batch: int,
                            backward_scratch: Optional[torch.Tensor] = None,
-                           sort_pairs: Optional[tuple] = None) -> None:
+                           sort_pairs: Optional[tuple] = None, expected_ids: int = 0) -> None:
     """Pooled lookup whose rows are stored into the output buffers of the samples' source ranks
     (``peer_out``: int64 device tensor of base addresses, one per source rank)."""
     indices = _cuda(indices, torch.int64, "indices")
@@ -304,7 +304,7 @@ def embedding_forward_peer(group: TableGroup, indices: torch.Tensor, offsets: to
     check(_lib.load().tdfo_embedding_forward_peer(
         _ptr(w), _wdtype(w), group.total_rows, group.D, _ptr(indices), _ptr(offsets), None,
         _ptr(group.feat_row_base), _ptr(group.feat_rows), _ptr(group.feat_out_col), group.F, B, L, pooling_mode,
-        _ptr(peer_out), peer_batch, group.out_stride, sk, sv, _ptr(group.err_flag), _stream()))
+        _ptr(peer_out), peer_batch, group.out_stride, sk, sv, _ptr(group.err_flag), int(expected_ids), _stream()))
 
 
 # --------------------------------------------------------------------------- backward
@@ -444,6 +444,12 @@ def copy_feature_blocks(src: torch.Tensor, dst: torch.Tensor, B: int, D: int, me
     if dst is not None and not (dst.is_cuda and dst.dtype == torch.float32 and dst.is_contiguous()):
         raise TypeError("dst must be a contiguous float32 CUDA tensor (or None for absolute destinations)")
     check(_lib.load().tdfo_copy_feature_blocks(_ptr(src), _ptr(dst), B, D, meta.numel() // 4, _ptr(meta), _stream()))
+
+
+def copy_feature_blocks_multicast(src: torch.Tensor, B: int, D: int, meta: torch.Tensor) -> None:
+    """`copy_feature_blocks` whose absolute destinations are NVLS multicast addresses (one store reaches every rank)."""
+    src = _cuda(src, torch.float32, "src")
+    check(_lib.load().tdfo_copy_feature_blocks_multicast(_ptr(src), B, D, meta.numel() // 4, _ptr(meta), _stream()))
 
 
 def reduce_partial_sums(parts: torch.Tensor, W: int, B: int, nslots: int, D: int, out_col: torch.Tensor,

@@ -174,7 +174,7 @@ class FakePeerOps(OracleKernelOps):
     # ---- tdfo_embedding_forward_peer: bag (f, gb) belongs to rank gb // peer_batch; its pooled row is
     # stored at out[rank] + ((gb % peer_batch) * out_stride + feat_out_col[f]) floats
     def embedding_forward_peer(self, group, indices, offsets, B, pooling_mode, peer_out, peer_batch,
-                               backward_scratch=None, sort_pairs=None):
+                               backward_scratch=None, sort_pairs=None, expected_ids=0):
         F = group.feat_row_base.numel()
         w = np.ascontiguousarray(_table(group.weights))
         Dw = w.shape[1]
