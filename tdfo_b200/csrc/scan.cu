@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(kScanThreads)
 unique_segments_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t n,
                        uint32_t* __restrict__ unique_keys, uint32_t* __restrict__ seg_starts,
                        uint32_t* __restrict__ first_vals, uint32_t* __restrict__ num_unique, ScanScratch* hdr, uint64_t* status,
-                       int32_t* err_flag) {
+                       int32_t* err_flag, uint32_t* long_hint) {
     __shared__ uint32_t warp_totals[8];
     __shared__ uint64_t s_prefix;
     __shared__ int s_tile;
@@ -80,6 +80,9 @@ unique_segments_kernel(const uint32_t* __restrict__ keys, const uint32_t* __rest
         if (lane == 0) prev = carry;
         const bool head = idx < n && (idx == 0 || k[i] != prev);
         heads[i] = __ballot_sync(kFullMask, head);
+        // A run of more than 64 equal keys covers at least one whole 32-key step without a head in it: such steps
+        // flag "there may be hot rows" (never missed, rarely false), which lets the update skip its hot-row scan.
+        if (long_hint != nullptr && heads[i] == 0 && lane == 0 && wbase + i * 32 + 31 < n) *long_hint = 1u;
         count += __popc(heads[i]);
         carry = __shfl_sync(kFullMask, k[i], 31);
     }
@@ -148,7 +151,9 @@ int complete_cumsum_impl(const int32_t* lengths, int64_t n, int64_t* offsets, vo
 
 int unique_segments_impl(const uint32_t* sorted_keys, const uint32_t* sorted_vals, int64_t n,
                          uint32_t* unique_keys, uint32_t* seg_starts, uint32_t* first_vals,
-                         uint32_t* num_unique, int32_t* err_flag, void* scratch, cudaStream_t st) {
+                         uint32_t* num_unique, int32_t* err_flag, void* scratch, cudaStream_t st,
+                         uint32_t* long_hint) {
+    if (long_hint) TDFO_CUDA(cudaMemsetAsync(long_hint, 0, sizeof(uint32_t), st));
     if (n == 0) {
         TDFO_CUDA(cudaMemsetAsync(num_unique, 0, sizeof(uint32_t), st));
         TDFO_CUDA(cudaMemsetAsync(seg_starts, 0, sizeof(uint32_t), st));
@@ -159,7 +164,7 @@ int unique_segments_impl(const uint32_t* sorted_keys, const uint32_t* sorted_val
     auto* hdr = static_cast<ScanScratch*>(scratch);
     auto* status = reinterpret_cast<uint64_t*>(static_cast<char*>(scratch) + sizeof(ScanScratch));
     unique_segments_kernel<<<(unsigned)((n + kUniqTile - 1) / kUniqTile), kScanThreads, 0, st>>>(
-        sorted_keys, sorted_vals, n, unique_keys, seg_starts, first_vals, num_unique, hdr, status, err_flag);
+        sorted_keys, sorted_vals, n, unique_keys, seg_starts, first_vals, num_unique, hdr, status, err_flag, long_hint);
     count_launch();
     TDFO_LAUNCH_CHECK("unique_segments");
     return TDFO_OK;
@@ -199,7 +204,7 @@ extern "C" int tdfo_unique_segments(const uint32_t* sorted_keys, const uint32_t*
         if (rc) return rc;
     }
     return unique_segments_impl(sorted_keys, sorted_vals, n, unique_keys, seg_starts, first_vals, num_unique,
-                                err_flag, scratch, static_cast<cudaStream_t>(stream));
+                                err_flag, scratch, static_cast<cudaStream_t>(stream), nullptr);
 }
 
 

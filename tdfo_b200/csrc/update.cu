@@ -16,7 +16,8 @@ size_t radix_sort_scratch_bytes_impl(int64_t n, int key_bits);
 int radix_sort_passes_impl(int key_bits);
 int unique_segments_impl(const uint32_t* sorted_keys, const uint32_t* sorted_vals, int64_t n,
                          uint32_t* unique_keys, uint32_t* seg_starts, uint32_t* first_vals,
-                         uint32_t* num_unique, int32_t* err_flag, void* scratch, cudaStream_t st);
+                         uint32_t* num_unique, int32_t* err_flag, void* scratch, cudaStream_t st,
+                         uint32_t* long_hint);
 
 constexpr int kUpdThreads = 256;    // linearise kernel
 
@@ -375,7 +376,8 @@ __global__ void __launch_bounds__(256)
 hot_rows_enqueue_kernel(const uint32_t* __restrict__ seg_starts, const uint32_t* __restrict__ num_unique,
                         const uint32_t* __restrict__ unique_keys, uint32_t total_rows, uint32_t* hdr, uint4* recs,
                         uint2* items, uint32_t rec_cap, uint32_t item_cap, uint32_t part_cap, uint32_t chunk,
-                        int32_t* err_flag) {
+                        int32_t* err_flag, const uint32_t* long_hint) {
+    if (long_hint != nullptr && *long_hint == 0u) return;     // the run-length pass saw no run longer than 32 keys
     const uint32_t nu = *num_unique;
     const int lane = lane_id();
     // whole warps walk the segment starts: one coalesced load per step, the neighbour's start by shuffle
@@ -642,7 +644,7 @@ int sparse_update_impl(void* weights, int32_t weights_dtype, int64_t total_rows,
                        const int64_t* offsets, const int64_t* feat_out_col, int32_t F, int64_t B,
                        int64_t L, int32_t pooling_mode, const tdfo_optimizer_args* opt,
                        uint32_t* worklist, int64_t worklist_entries, const float* psw, const uint32_t* pos_bag,
-                       int32_t* err_flag, cudaStream_t st) {
+                       int32_t* err_flag, cudaStream_t st, const uint32_t* long_hint = nullptr) {
     if (L == 0) return TDFO_OK;
     const size_t esz = weights_dtype == TDFO_F32 ? 4 : 2;
     UpdateArgs a;
@@ -668,7 +670,7 @@ int sparse_update_impl(void* weights, int32_t weights_dtype, int64_t total_rows,
         if (eb > kNumSMs * 8) eb = kNumSMs * 8;
         hot_rows_enqueue_kernel<<<(unsigned)eb, 256, 0, st>>>(seg_starts, num_unique, unique_keys, (uint32_t)total_rows,
                                                              a.hot_hdr, a.hot_recs, a.hot_items, a.rec_cap, a.item_cap,
-                                                             a.part_cap, a.hot_chunk, err_flag);
+                                                             a.part_cap, a.hot_chunk, err_flag, long_hint);
         count_launch();
         TDFO_LAUNCH_CHECK("hot_rows_enqueue");
     }
@@ -845,14 +847,14 @@ static int backward_stages(int stages, const char* who, void* weights, int32_t w
             set_error("%s: internal layout mismatch", who);
             return TDFO_ERR_INVALID_ARG;
         }
-        rc = unique_segments_impl(sk, sv, L, uk, ss, fv, num_unique, err_flag, scan_scratch, st);
+        rc = unique_segments_impl(sk, sv, L, uk, ss, fv, num_unique, err_flag, scan_scratch, st, num_unique + 1);
         if (rc) return rc;
     }
     if (stages & 2) {
         rc = sparse_update_impl(weights, weights_dtype, total_rows, D, state0, state1, grad_out, grad_stride,
                                 sv, uk, ss, fv, num_unique, offsets, feat_out_col, F, B, L, pooling_mode, opt,
                                 reinterpret_cast<uint32_t*>(base + lay.worklist), (int64_t)lay.worklist_entries,
-                                per_sample_weights, pos_bag, err_flag, st);
+                                per_sample_weights, pos_bag, err_flag, st, num_unique + 1);
         if (rc) return rc;
     }
     return TDFO_OK;

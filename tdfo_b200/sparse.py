@@ -37,10 +37,6 @@ class JaggedTensor:
         self._values, self._weights, self._lengths, self._offsets = values, weights, lengths, offsets
 
     def values(self) -> torch.Tensor:
-        """int64 ids.  A batch built from int32 ids (half the host->device bytes; fine whenever every table
-        has fewer than 2^31 rows) is widened here, once, by `tdfo_kjt_widen_ids` on the device."""
-        if self._values.dtype == torch.int32:
-            self._values = ops.widen_ids(self._values) if self._values.is_cuda else self._values.to(torch.int64)
         return self._values
 
     def weights(self) -> torch.Tensor:
@@ -130,6 +126,10 @@ class KeyedJaggedTensor:
         return self._keys
 
     def values(self) -> torch.Tensor:
+        """int64 ids.  A batch built from int32 ids (half the host->device bytes; fine whenever every table
+        has fewer than 2^31 rows) is widened here, once, by `tdfo_kjt_widen_ids` on the device."""
+        if self._values.dtype == torch.int32:
+            self._values = ops.widen_ids(self._values) if self._values.is_cuda else self._values.to(torch.int64)
         return self._values
 
     def weights(self) -> torch.Tensor:

@@ -375,3 +375,30 @@ def test_dense_gradient_mode_matches_torch_modules_under_a_dense_optimizer(t):
     (bag(ids.cuda(), kjt.offsets()) * proj).sum().backward()
     torch.testing.assert_close(next(ebc.parameters()).grad, bag.weight.grad, rtol=1e-5, atol=1e-6)
     ebc.check_errors()
+
+
+def test_int32_ids_are_widened_on_the_device(t):
+    """ids may cross PCIe as int32: a KeyedJaggedTensor built from int32 values gives the same lookup and the same
+    fused update as the int64 one (tdfo_kjt_widen_ids runs once, on first use)."""
+    dev = torch.device("cuda")
+    rng = np.random.default_rng(8)
+    rows, D, B = [300, 41], 32, 50
+    tables = [t.EmbeddingBagConfig(num_embeddings=r, embedding_dim=D, name=f"t{i}", feature_names=[f"f{i}"])
+              for i, r in enumerate(rows)]
+    lengths = rng.integers(0, 7, size=2 * B).astype(np.int32)
+    off = np.concatenate([[0], np.cumsum(lengths)])
+    idx = np.concatenate([rng.integers(0, rows[f], size=int(off[(f + 1) * B] - off[f * B])) for f in range(2)])
+    outs, tabs = [], []
+    for dtype in (torch.int64, torch.int32):
+        torch.manual_seed(3)
+        ebc = t.EmbeddingBagCollection(tables, device=dev)
+        ebc.set_fused_optimizer(t.EmbOptimType.EXACT_SGD, learning_rate=0.1)
+        ebc.train()
+        kjt = t.KeyedJaggedTensor.from_lengths_sync(["f0", "f1"], torch.from_numpy(idx).to(dtype),
+                                                    torch.from_numpy(lengths)).to(dev)
+        out = ebc(kjt).values()
+        assert kjt.values().dtype == torch.int64 and kjt.values().numel() == idx.size
+        out.sum().backward()
+        outs.append(out.detach().clone())
+        tabs.append(torch.cat([v for v in ebc.state_dict().values()]).clone())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(tabs[0], tabs[1])
