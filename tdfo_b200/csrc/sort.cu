@@ -9,7 +9,10 @@
 namespace tdfo {
 
 constexpr int kSortThreads = 256;
-constexpr int kSortItems = 16;
+#ifndef TDFO_SORT_ITEMS
+#define TDFO_SORT_ITEMS 16
+#endif
+constexpr int kSortItems = TDFO_SORT_ITEMS;
 constexpr int kSortTile = kSortThreads * kSortItems;    // 4096 pairs per tile
 constexpr int kRadixLog = 9;                            // up to 9 bits per pass
 constexpr int kRadix = 1 << kRadixLog;                  // bins per pass (lookback / histogram row stride)
