@@ -270,6 +270,35 @@ def test_backward_update_vs_oracle(ops, D, mode, optimizer, bf16):
 
 @pytest.mark.parametrize("bf16", [False, True])
 @pytest.mark.parametrize("optimizer", [orc.OPT_SGD, orc.OPT_ROWWISE_ADAGRAD, orc.OPT_ADAM])
+@pytest.mark.parametrize("mode", [orc.POOL_SUM, orc.POOL_MEAN, orc.POOL_NONE])
+def test_backward_update_many_rows_per_warp(ops, mode, optimizer, bf16):
+    """~60 000 unique rows of D = 128: more than one grid of row slots (148 SMs x 3 CTAs x 8 warps x 4
+    rows = 14 208), so every warp of the persistent update kernel takes several steps and its row
+    pipeline wraps around; mixed run lengths (1 .. ~10 occurrences, a few hot rows) between steps.
+    The toy cases above never leave a warp's first step."""
+    c = make_case(seed=77 + mode * 5 + optimizer, F=2, B=8000, D=128, rows=[90_000, 50_000], max_len=12,
+                  p_empty=0.1, long_bag=300)
+    idx = c.indices.copy()
+    idx[::17] = 3            # row 3 of table 0 / 1 turns hot (> 64 occurrences): skipped by the main kernel
+    w_o, s0_o, s1_o, grp, routing, scratch = _run_backward_pair(ops, c, mode, optimizer, bf16, wd=0.01, steps=2, idx=idx)
+    assert routing["num_unique"] > 3.5 * 14_208
+    rtol, atol = (BF16_RTOL, BF16_ATOL) if bf16 else (FP32_RTOL, 2e-6)
+    got, want = table_to_f32(grp.weights), oracle_table_to_f32(w_o)
+    hot = np.zeros(c.total_rows, dtype=bool)            # hot rows: other summation order, checked elsewhere against fp64
+    seg = np.diff(routing["seg_starts"].astype(np.int64))
+    hot[routing["unique_keys"][:routing["num_unique"]][seg > 64]] = True
+    assert 1 <= hot.sum() <= 8
+    np.testing.assert_allclose(got[~hot], want[~hot], rtol=rtol, atol=atol)
+    np.testing.assert_allclose(got[hot], want[hot], rtol=max(rtol, 1e-4), atol=1e-4 if not bf16 else atol)
+    if s0_o is not None:
+        np.testing.assert_allclose(grp.state0.cpu().numpy()[~hot], s0_o[~hot], rtol=max(rtol, 2e-5), atol=atol)
+    if s1_o is not None:
+        np.testing.assert_allclose(grp.state1.cpu().numpy()[~hot], s1_o[~hot], rtol=max(rtol, 2e-5), atol=atol)
+    assert int(grp.err_flag.item()) == 0
+
+
+@pytest.mark.parametrize("bf16", [False, True])
+@pytest.mark.parametrize("optimizer", [orc.OPT_SGD, orc.OPT_ROWWISE_ADAGRAD, orc.OPT_ADAM])
 @pytest.mark.parametrize("mode", [orc.POOL_SUM, orc.POOL_MEAN])
 @pytest.mark.parametrize("D", [16, 128])
 def test_weighted_backward_update_vs_oracle(ops, D, mode, optimizer, bf16):
