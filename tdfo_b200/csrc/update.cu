@@ -857,12 +857,12 @@ static int dispatch_update(const UpdateArgs& a, int opt, int64_t max_unique, int
     constexpr bool kWide = sizeof(T) == 4;          // fp32: 4 chunks per lane; bf16 (8 elems / chunk): 2
 #if TDFO_UPD_STAGED
     // D = 128 rows (512 B fp32, 256 B bf16): the shared-memory-staged kernel
-    constexpr int kS = TDFO_UPD_STAGES, kTh = TDFO_UPD_ST_THREADS, kMs = TDFO_UPD_ST_MINB;
+    constexpr int kS = TDFO_UPD_STAGES, kSt = TDFO_UPD_ST_THREADS, kMs = TDFO_UPD_ST_MINB;
     constexpr bool kGs = TDFO_UPD_ST_GRAD != 0;
     if constexpr (kWide) {
-        if (n > 16 && n <= 32) return launch_update_staged<T, 8, 4, kS, kTh, kMs, kGs>(a, opt, max_unique, st);
+        if (n > 16 && n <= 32) return launch_update_staged<T, 8, 4, kS, kSt, kMs, kGs>(a, opt, max_unique, st);
     } else {
-        if (n > 8 && n <= 16) return launch_update_staged<T, 8, 2, kS, kTh, kMs, kGs>(a, opt, max_unique, st);
+        if (n > 8 && n <= 16) return launch_update_staged<T, 8, 2, kS, kSt, kMs, kGs>(a, opt, max_unique, st);
     }
 #endif
     if (kWide) {
