@@ -38,8 +38,18 @@ struct LookupArgs {
 };
 
 constexpr int kFwdThreads = 256;
+#ifndef TDFO_FWD_THREADS
+#define TDFO_FWD_THREADS 288
+#endif
+#ifndef TDFO_FWD_MINB
+#define TDFO_FWD_MINB 3
+#endif
+// Bag-per-warp pooled kernel: persistent grid of 148 x 3 CTAs of 288 threads = 27 warps per SM at 72 registers.
+// Measured on B200 (profiles/r2_tuning_kernels.txt): 24 warps (256 x 3, 80 registers) 6260 GB/s, 27-28 warps
+// 6400-6430 GB/s, 30-32 warps (64 registers, spills) 5500 GB/s.
+constexpr int kPoolThreads = TDFO_FWD_THREADS;
 constexpr int kFwdUnroll = 8;      // independent row requests in flight per sub-group
-constexpr int kFwdBlocksPerSM = 3; // persistent grid: 148 x 3 CTAs, 24 warps / SM (<= 85 registers)
+constexpr int kFwdBlocksPerSM = TDFO_FWD_MINB;
 
 // First chunk (<= 32 ids) of a bag, one id per lane, already turned into a row of the group.
 struct BagHead {
@@ -122,7 +132,7 @@ __device__ __forceinline__ void gather_batch(const uint4* __restrict__ wbase, in
 // tools/gather_micro.cu: 6.5 TB/s vs 4.5 TB/s for the same loop without the prefetch, and
 // vs 5.3 TB/s for rows staged in shared memory by per-row bulk async copies).
 template <typename T, int LPR, int CPL, bool WEIGHTED>
-__global__ void __launch_bounds__(kFwdThreads, kFwdBlocksPerSM)
+__global__ void __launch_bounds__(kPoolThreads, kFwdBlocksPerSM)
 pooled_forward_kernel(const LookupArgs a) {
     constexpr int E = Chunk<T>::kElems;
     constexpr int RPW = 32 / LPR;                       // rows gathered in parallel per warp
@@ -130,8 +140,8 @@ pooled_forward_kernel(const LookupArgs a) {
     const int lane = lane_id();
     const int sub = lane % LPR;
     const int grp = lane / LPR;
-    const int64_t nwarps = (int64_t)gridDim.x * (kFwdThreads / 32);
-    int64_t g = (int64_t)blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * (kPoolThreads / 32);
+    int64_t g = (int64_t)blockIdx.x * (kPoolThreads / 32) + (threadIdx.x >> 5);
     if (g >= a.num_bags) return;
     const uint4* __restrict__ wbase = reinterpret_cast<const uint4*>(a.weights);
     uint32_t flags = 0;
@@ -454,10 +464,10 @@ static int launch_forward(const LookupArgs& a, int pooling_mode, cudaStream_t st
             TDFO_LAUNCH_CHECK("embedding_forward");
             return TDFO_OK;
         }
-        int64_t blocks = (a.num_bags + kFwdThreads / 32 - 1) / (kFwdThreads / 32);
+        int64_t blocks = (a.num_bags + kPoolThreads / 32 - 1) / (kPoolThreads / 32);
         if (blocks > (int64_t)kNumSMs * kFwdBlocksPerSM) blocks = (int64_t)kNumSMs * kFwdBlocksPerSM;
-        if (a.psw) pooled_forward_kernel<T, LPR, CPL, true><<<(unsigned)blocks, kFwdThreads, 0, st>>>(a);
-        else       pooled_forward_kernel<T, LPR, CPL, false><<<(unsigned)blocks, kFwdThreads, 0, st>>>(a);
+        if (a.psw) pooled_forward_kernel<T, LPR, CPL, true><<<(unsigned)blocks, kPoolThreads, 0, st>>>(a);
+        else       pooled_forward_kernel<T, LPR, CPL, false><<<(unsigned)blocks, kPoolThreads, 0, st>>>(a);
     }
     count_launch();
     TDFO_LAUNCH_CHECK("embedding_forward");

@@ -109,7 +109,6 @@ constexpr int kUpdCtaThreads = 256;
 #define TDFO_UPD_THREADS 288
 #endif
 constexpr int kUpdMainThreads = TDFO_UPD_THREADS;    // CTA size of the main kernel for 512-byte rows (see dispatch_update)
-constexpr int kExpSingleThreads = TDFO_UPD_THREADS;  // tuning builds: CTA size of the one-occurrence kernel
 constexpr uint32_t kLongSegment = 64;    // occurrences above which a row goes to the block-per-chunk kernel
 constexpr int kLongMaxFloats = 8192;      // shared-memory floats for the partial sums of that kernel
 constexpr uint32_t kHotChunkMin = 2048;  // occurrences one CTA reduces at most (grows with L, see hot_layout)
@@ -298,18 +297,18 @@ __device__ __forceinline__ void accumulate_occurrences(const UpdateArgs& a, uint
 }
 
 // Persistent warps; a warp works on RPW*UR consecutive unique rows per step, one row per
-// LPR-lane group and unroll slot.  Under load a B200 memory round trip takes ~3 us, so the
-// kernel is built to keep as many independent 128-bit row requests in flight per SM as the
-// register file allows (tools/rmw2_micro.cu: 32 warps x 4 rows x (weight + gradient) reach
-// 5.6 TB/s of row read+write traffic, 93 % of the pure read-modify-write ceiling):
-//   * the four metadata words of the NEXT step's rows are requested before this step's rows
-//     are consumed (the unique pass also emits each row's first payload, so finding the first
-//     gradient row needs no dependent load);
+// LPR-lane group and unroll slot.  Under load a B200 memory round trip takes ~3 us, and what the
+// kernel can keep in flight is set by the register file (shared-memory staging with cp.async was
+// measured and is 13-60 % slower, profiles/r2_tuning_kernels.txt):
 //   * per step every lane requests its chunks of the weight row, of the first gradient row and
-//     the row state before consuming any of them; all of these loads are unconditional (rows
-//     that do not exist are redirected to row 0 and masked) so ptxas issues them back to back;
+//     the row state before consuming any of them (the unique pass also emits each row's first
+//     payload, so finding the first gradient row needs no dependent load); all of these loads are
+//     unconditional (rows that do not exist are redirected to row 0 and masked) so ptxas issues
+//     them back to back;
 //   * few lanes per row (LPR 8 x 4 chunks for a 512 B row): per-row bookkeeping is replicated
-//     in every lane of a group, so narrow groups spend a quarter of the issue slots per row.
+//     in every lane of a group, so narrow groups spend a quarter of the issue slots per row;
+//   * as many warps per SM as run WITHOUT spilling the row loop: 27 (288 threads x 3 CTAs,
+//     72 registers) for D = 128 rows; 30 warps leave 64 registers and lose 15 %.
 template <typename T, int LPR, int CPL, int UR, int MINB, int OPT, bool PREFETCH = true, int THREADS = kUpdCtaThreads,
           bool STREAM = false>
 __global__ void __launch_bounds__(THREADS, MINB)
@@ -390,201 +389,6 @@ sparse_update_kernel(const UpdateArgs a) {
 #pragma unroll
         for (int q = 0; q < UR; ++q) cur[q] = PREFETCH ? nxt[q] : load_row_meta(a, u0 + q * RPW + grp, nu);
     }
-}
-
-// ---------------------------------------------------------------- update, rows with ONE occurrence
-// Most unique rows of a step occur once (85 % on BASELINE config 2).  The run-length pass hands those
-// over as a compact list of {row key, payload}; with no run to walk, no hot-row test and two metadata
-// words per row instead of four, this kernel fits 64 registers: 4 CTAs per SM instead of 3, the
-// occupancy at which the read-modify-write micro-benchmark peaks (profiles/r1_tuning_update.txt).
-template <typename T, int LPR, int CPL, int MINB, int OPT>
-__global__ void __launch_bounds__(kExpSingleThreads, MINB)
-sparse_update_single_kernel(const UpdateArgs a, const uint2* __restrict__ singles, const uint32_t* __restrict__ n_singles) {
-    constexpr int E = Chunk<T>::kElems;
-    constexpr int RPW = 32 / LPR;
-    constexpr int GQ = E / 4;
-    const int lane = lane_id();
-    const int sub = lane % LPR;
-    const int grp = lane / LPR;
-    const unsigned gmask = (LPR == 32) ? kFullMask : (((1u << (LPR & 31)) - 1u) << (grp * LPR));
-    const uint32_t n = *n_singles;
-    const uint32_t stride = gridDim.x * (kExpSingleThreads / 32) * RPW;
-    uint4* __restrict__ wbase = reinterpret_cast<uint4*>(a.weights);
-    for (uint32_t i0 = (blockIdx.x * (kExpSingleThreads / 32) + (threadIdx.x >> 5)) * RPW; i0 < n; i0 += stride) {
-        const uint32_t i = i0 + grp;
-        const bool valid = i < n;
-        const uint2 kv = __ldg(singles + (valid ? i : 0u));
-        float scale;
-        const float* grow = grad_row_of(a, kv.y, scale);
-        const size_t wrow = (size_t)kv.x * a.nchunks;
-        uint4 wv[CPL], gv[CPL][GQ];
-#pragma unroll
-        for (int k = 0; k < CPL; ++k) {
-            const int c = min(sub + k * LPR, a.nchunks - 1);
-            wv[k] = upd_load_weight<false>(wbase + wrow + c);
-#pragma unroll
-            for (int t = 0; t < GQ; ++t) gv[k][t] = upd_load_grad(grow + (size_t)c * E + 4 * t);
-        }
-        float h_old = 0.f;
-        if (OPT == TDFO_OPT_ROWWISE_ADAGRAD) h_old = __ldcg(a.state0 + kv.x);
-        float g[CPL][E], w[CPL][E];
-#pragma unroll
-        for (int k = 0; k < CPL; ++k) {
-#pragma unroll
-            for (int t = 0; t < GQ; ++t) {
-                g[k][4 * t]     = scale * __uint_as_float(gv[k][t].x);
-                g[k][4 * t + 1] = scale * __uint_as_float(gv[k][t].y);
-                g[k][4 * t + 2] = scale * __uint_as_float(gv[k][t].z);
-                g[k][4 * t + 3] = scale * __uint_as_float(gv[k][t].w);
-            }
-            Chunk<T>::unpack(wv[k], w[k]);
-        }
-        apply_row_update<T, LPR, CPL, OPT>(a, kv.x, valid, h_old, g, w, sub, gmask);
-    }
-}
-
-// ---------------------------------------------------------------- update, rows staged in shared memory
-// The register kernel above can hold one step (4 rows x 1 KB per warp) in flight: 96 KB per SM at
-// 3 CTAs, and a B200 needs more than that to cover a ~3 us round trip at 6 TB/s.  This variant
-// requests rows with cp.async (LDGSTS: the data lands in shared memory, no destination registers),
-// so S steps per warp are on their way at once and the depth is set by the 227 KB of shared memory,
-// not by the register file.  Every thread copies and later reads only ITS OWN 16-byte pieces, laid
-// out [stage][piece][thread] (conflict-free), so no barrier is needed: cp.async.wait_group orders a
-// thread's own copies.  Arithmetic and summation order are those of sparse_update_kernel.
-__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gsrc) {
-    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_4(void* smem_dst, const void* gsrc) {
-    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(d), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() {
-    asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory");
-}
-
-// GSTAGED: the first gradient row travels through the ring too (it is an L2 hit, so it may also be
-// fetched into registers right before the wait: half the shared memory per stage, one stage more).
-template <int CPL, int GQ, bool GSTAGED>
-struct StagedRing {
-    static constexpr int kPieces = CPL + (GSTAGED ? CPL * GQ : 0) + 1;   // weight chunks, gradient pieces, one word group
-    static constexpr size_t bytes(int stages, int threads) { return (size_t)stages * kPieces * threads * 16; }
-};
-
-template <typename T, int LPR, int CPL, int S, int THREADS, int MINB, int OPT, bool GSTAGED>
-__global__ void __launch_bounds__(THREADS, MINB)
-sparse_update_staged_kernel(const UpdateArgs a) {
-    constexpr int E = Chunk<T>::kElems;
-    constexpr int RPW = 32 / LPR;
-    constexpr int GQ = E / 4;
-    constexpr int NG = GSTAGED ? CPL * GQ : 0;
-    constexpr int PIECES = StagedRing<CPL, GQ, GSTAGED>::kPieces;
-    extern __shared__ uint4 ring[];                   // [S][PIECES][THREADS]
-    const int tid = threadIdx.x;
-    const int lane = lane_id();
-    const int sub = lane % LPR;
-    const int grp = lane / LPR;
-    const unsigned gmask = (LPR == 32) ? kFullMask : (((1u << (LPR & 31)) - 1u) << (grp * LPR));
-    const uint32_t nu = *a.num_unique;
-    const uint32_t stride = gridDim.x * (THREADS / 32) * RPW;
-    uint32_t u0 = (blockIdx.x * (THREADS / 32) + (tid >> 5)) * RPW;
-    if (u0 >= nu) return;
-    const uint4* __restrict__ wbase = reinterpret_cast<const uint4*>(a.weights);
-    uint4* const mine = ring + tid;
-
-    // Request everything one row needs into ring slot `st`.  The word group keeps what the consumer
-    // needs later: {row key or 0xffffffff (nothing to do), row state, scale | first payload, run length}.
-    auto issue = [&](int st, const RowMeta& m) {
-        bool valid = m.key < a.total_rows;
-        if (a.hot_hdr != nullptr && m.e - m.s > kLongSegment) valid = false;    // queued for the block-per-chunk kernel
-        uint4* slot = mine + (size_t)st * PIECES * THREADS;
-        const uint32_t row = valid ? m.key : 0u;
-        const size_t wrow = (size_t)row * a.nchunks;
-        uint32_t third = m.v0;
-        if (GSTAGED) {
-            float scale;
-            const float* grow = grad_row_of(a, valid ? m.v0 : 0u, scale);
-            third = __float_as_uint(scale);
-#pragma unroll
-            for (int k = 0; k < CPL; ++k) {
-                const int c = min(sub + k * LPR, a.nchunks - 1);
-#pragma unroll
-                for (int t = 0; t < GQ; ++t)
-                    cp_async_16(slot + (size_t)(CPL + k * GQ + t) * THREADS, grow + (size_t)c * E + 4 * t);
-            }
-        }
-#pragma unroll
-        for (int k = 0; k < CPL; ++k) {
-            const int c = min(sub + k * LPR, a.nchunks - 1);
-            cp_async_16(slot + (size_t)k * THREADS, wbase + wrow + c);
-        }
-        uint32_t* words = reinterpret_cast<uint32_t*>(slot + (size_t)(CPL + NG) * THREADS);
-        words[0] = valid ? m.key : 0xffffffffu;
-        words[2] = third;
-        words[3] = m.e - m.s;
-        if (OPT == TDFO_OPT_ROWWISE_ADAGRAD) cp_async_4(words + 1, a.state0 + row);
-        else words[1] = 0u;
-        cp_async_commit();
-    };
-
-    RowMeta nxt = load_row_meta(a, u0 + grp, nu);
-#pragma unroll
-    for (int p = 0; p < S - 1; ++p) {                 // fill the ring: steps 0 .. S-2
-        issue(p, nxt);
-        nxt = load_row_meta(a, u0 + (uint32_t)(p + 1) * stride + grp, nu);
-    }
-    int st = 0;                                       // ring slot of the step consumed next
-    while (u0 < nu) {
-        issue(st == 0 ? S - 1 : st - 1, nxt);         // step u0 + (S-1) * stride (past the end: a masked dummy)
-        nxt = load_row_meta(a, u0 + (uint32_t)S * stride + grp, nu);      // on its way while this step is consumed
-        const uint4* slot = mine + (size_t)st * PIECES * THREADS;
-
-        uint4 gv[CPL][GQ];
-        float scale = 1.f;
-        if (!GSTAGED) {
-            // the word group of this step was written by plain stores S-1 iterations ago
-            const uint32_t key0 = reinterpret_cast<const uint32_t*>(slot + (size_t)CPL * THREADS)[0];
-            const uint32_t v0 = reinterpret_cast<const uint32_t*>(slot + (size_t)CPL * THREADS)[2];
-            const float* grow = grad_row_of(a, key0 != 0xffffffffu ? v0 : 0u, scale);
-#pragma unroll
-            for (int k = 0; k < CPL; ++k) {
-                const int c = min(sub + k * LPR, a.nchunks - 1);
-#pragma unroll
-                for (int t = 0; t < GQ; ++t) gv[k][t] = ldg_128(grow + (size_t)c * E + 4 * t);
-            }
-        }
-        cp_async_wait<S - 1>();                       // this thread's copies of step u0 have landed
-
-        const uint4 words = slot[(size_t)(CPL + NG) * THREADS];
-        const bool valid = words.x != 0xffffffffu;
-        const uint32_t row = words.x;
-        const float h_old = __uint_as_float(words.y);
-        const uint32_t len = words.w;
-        if (GSTAGED) scale = __uint_as_float(words.z);
-        float g[CPL][E], w[CPL][E];
-#pragma unroll
-        for (int k = 0; k < CPL; ++k) {
-            Chunk<T>::unpack(slot[(size_t)k * THREADS], w[k]);
-#pragma unroll
-            for (int t = 0; t < GQ; ++t) {
-                const uint4 x = GSTAGED ? slot[(size_t)(CPL + k * GQ + t) * THREADS] : gv[k][t];
-                g[k][4 * t]     = scale * __uint_as_float(x.x);
-                g[k][4 * t + 1] = scale * __uint_as_float(x.y);
-                g[k][4 * t + 2] = scale * __uint_as_float(x.z);
-                g[k][4 * t + 3] = scale * __uint_as_float(x.w);
-            }
-        }
-        // further occurrences of the row, in sorted (= original) order
-        if (valid && len > 1) {
-            const uint32_t s = __ldg(a.seg_starts + u0 + grp);
-            accumulate_occurrences<T, LPR, CPL, false>(a, s + 1, s + len, g, sub, grp, gmask);
-        }
-        apply_row_update<T, LPR, CPL, OPT>(a, row, valid, h_old, g, w, sub, gmask);
-        u0 += stride;
-        st = (st + 1 == S) ? 0 : st + 1;
-    }
-    cp_async_wait<0>();
 }
 
 // Hot rows, step 1: one thread per unique row; a row with more than kLongSegment occurrences becomes a
@@ -775,62 +579,10 @@ static int launch_update(const UpdateArgs& a, int opt, int64_t max_unique, cudaS
     return launch_update_long<T, LPR, CPL>(a, opt, st);
 }
 
-// The same launch for the shared-memory-staged kernel.  Its ring is dynamic shared memory above the
-// 48 KB default, so the function attributes are set on every call (a host-side table write; the
-// attribute is per device, and this library does not track which devices have seen it).
-template <typename T, int LPR, int CPL, int S, int THREADS, int MINB, bool GSTAGED>
-static int launch_update_staged(const UpdateArgs& a, int opt, int64_t max_unique, cudaStream_t st) {
-    constexpr int RPW = 32 / LPR;
-    constexpr int GQ = Chunk<T>::kElems / 4;
-    constexpr size_t smem = StagedRing<CPL, GQ, GSTAGED>::bytes(S, THREADS);
-    static_assert(S >= 2, "the ring needs at least two stages");
-    static_assert((smem + 1024) * MINB <= 227 * 1024, "ring does not fit the shared memory of one SM");
-    const int64_t steps = (max_unique + RPW - 1) / RPW;
-    int64_t blocks = (steps + THREADS / 32 - 1) / (THREADS / 32);
-    const int64_t cap = (int64_t)kNumSMs * MINB;
-    if (blocks > cap) blocks = cap;
-    if (blocks < 1) blocks = 1;
-    auto go = [&](auto kern) -> cudaError_t {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-        if (e != cudaSuccess) return e;
-        kern<<<(unsigned)blocks, THREADS, smem, st>>>(a);
-        return cudaSuccess;
-    };
-    switch (opt) {
-        case TDFO_OPT_SGD:
-            TDFO_CUDA(go(sparse_update_staged_kernel<T, LPR, CPL, S, THREADS, MINB, TDFO_OPT_SGD, GSTAGED>)); break;
-        case TDFO_OPT_ROWWISE_ADAGRAD:
-            TDFO_CUDA(go(sparse_update_staged_kernel<T, LPR, CPL, S, THREADS, MINB, TDFO_OPT_ROWWISE_ADAGRAD, GSTAGED>)); break;
-        default:
-            TDFO_CUDA(go(sparse_update_staged_kernel<T, LPR, CPL, S, THREADS, MINB, TDFO_OPT_ADAM, GSTAGED>)); break;
-    }
-    count_launch();
-    TDFO_LAUNCH_CHECK("sparse_update_staged");
-    return launch_update_long<T, LPR, CPL>(a, opt, st);
-}
-
-// Shapes measured on B200 (tools/tune_update.py, BASELINE config 2): 8 lanes x 4 chunks per
-// 512 B row, one row per group per step, 3 CTAs / SM (80 registers, no spills) = 1.46 ms;
-// anything that spills, or 32 lanes per row, is 15-60 % slower.  Few lanes per row matter:
-// per-row bookkeeping is replicated in every lane of the group.
+// Shapes measured on B200 (tools/tune_update.py, tools/tune_update_multi.py, BASELINE config 2): 8 lanes x 4 chunks
+// per 512 B row, one row per group per step; anything that spills, or 32 lanes per row, is 15-60 % slower.
 #ifndef TDFO_UPD_PREFETCH
 #define TDFO_UPD_PREFETCH 0
-#endif
-#ifndef TDFO_UPD_STAGED
-#define TDFO_UPD_STAGED 0
-#endif
-#ifndef TDFO_UPD_STAGES
-#define TDFO_UPD_STAGES 2
-#endif
-#ifndef TDFO_UPD_ST_THREADS
-#define TDFO_UPD_ST_THREADS 256
-#endif
-#ifndef TDFO_UPD_ST_MINB
-#define TDFO_UPD_ST_MINB 3
-#endif
-#ifndef TDFO_UPD_ST_GRAD
-#define TDFO_UPD_ST_GRAD 1
 #endif
 #ifndef TDFO_UPD_MINB
 #define TDFO_UPD_MINB 3
@@ -855,16 +607,6 @@ static int dispatch_update(const UpdateArgs& a, int opt, int64_t max_unique, int
 #endif
     constexpr int kL = TDFO_UPD_LPR512, kC = 32 / TDFO_UPD_LPR512;     // lanes x chunks for a 512-byte row
     constexpr bool kWide = sizeof(T) == 4;          // fp32: 4 chunks per lane; bf16 (8 elems / chunk): 2
-#if TDFO_UPD_STAGED
-    // D = 128 rows (512 B fp32, 256 B bf16): the shared-memory-staged kernel
-    constexpr int kS = TDFO_UPD_STAGES, kSt = TDFO_UPD_ST_THREADS, kMs = TDFO_UPD_ST_MINB;
-    constexpr bool kGs = TDFO_UPD_ST_GRAD != 0;
-    if constexpr (kWide) {
-        if (n > 16 && n <= 32) return launch_update_staged<T, 8, 4, kS, kSt, kMs, kGs>(a, opt, max_unique, st);
-    } else {
-        if (n > 8 && n <= 16) return launch_update_staged<T, 8, 2, kS, kSt, kMs, kGs>(a, opt, max_unique, st);
-    }
-#endif
     if (kWide) {
         if (n <= 1)   return launch_update<T, 1, 1, 1, 3, false>(a, opt, max_unique, st);
         if (n <= 2)   return launch_update<T, 1, 2, 1, 3, false>(a, opt, max_unique, st);
@@ -892,19 +634,6 @@ static int dispatch_update(const UpdateArgs& a, int opt, int64_t max_unique, int
     return TDFO_ERR_UNSUPPORTED;
 }
 
-#ifdef TDFO_EXP_SINGLE
-// Tuning builds only (tools/tune_update_multi.py): the one-occurrence kernel on a caller-built {key, payload} list.
-int exp_single_update(const UpdateArgs& a, const uint2* singles, const uint32_t* n_singles, int64_t max_rows, cudaStream_t st) {
-    constexpr int MINB = TDFO_EXP_SINGLE;
-    int64_t blocks = (max_rows / 4 + kExpSingleThreads / 32 - 1) / (kExpSingleThreads / 32);
-    if (blocks > kNumSMs * MINB) blocks = kNumSMs * MINB;
-    if (blocks < 1) blocks = 1;
-    sparse_update_single_kernel<float, 8, 4, MINB, TDFO_OPT_ROWWISE_ADAGRAD><<<(unsigned)blocks, kExpSingleThreads, 0, st>>>(a, singles, n_singles);
-    count_launch();
-    TDFO_LAUNCH_CHECK("exp_single_update");
-    return TDFO_OK;
-}
-#endif
 static int key_bits_for(int64_t total_rows) {   // bits needed to hold the value total_rows itself
     int b = 1;
     while (b < 32 && (total_rows >> b) != 0) ++b;
@@ -945,9 +674,6 @@ static int check_opt(const char* who, const tdfo_optimizer_args* opt, const floa
     return TDFO_OK;
 }
 
-#ifdef TDFO_EXP_SINGLE
-static const uint2* g_exp_singles = nullptr;
-#endif
 int sparse_update_impl(void* weights, int32_t weights_dtype, int64_t total_rows, int32_t D,
                        float* state0, float* state1, const float* grad_out, int64_t grad_stride,
                        const uint32_t* sorted_vals, const uint32_t* unique_keys,
@@ -1001,9 +727,6 @@ int sparse_update_impl(void* weights, int32_t weights_dtype, int64_t total_rows,
         a.bc2 = (float)(1.0 - pow((double)opt->beta2, (double)opt->step));
     }
     const int64_t max_unique = L < total_rows + 1 ? L : total_rows + 1;
-#ifdef TDFO_EXP_SINGLE
-    if (g_exp_singles != nullptr) return exp_single_update(a, g_exp_singles, num_unique, max_unique, st);
-#endif
     // bytes of gradient rows one feature's rows draw from (they are re-read out of L2 in sorted order)
     const int64_t slice_rows = pooling_mode == TDFO_POOL_NONE ? L / (F > 0 ? F : 1) : B;
     const int64_t slice = slice_rows * (int64_t)D * 4;
@@ -1074,10 +797,6 @@ extern "C" int tdfo_sparse_update(void* weights, int32_t weights_dtype, int64_t 
                               F, B, L, pooling_mode, opt, worklist, worklist_entries, nullptr, nullptr, nullptr,
                               static_cast<cudaStream_t>(stream));
 }
-
-#ifdef TDFO_EXP_SINGLE
-extern "C" void tdfo_exp_set_singles(const void* singles) { tdfo::g_exp_singles = static_cast<const uint2*>(singles); }
-#endif
 
 extern "C" int tdfo_backward_scratch_layout(int64_t L, int64_t total_rows, tdfo_backward_layout* layout) {
     TDFO_CHECK_ARG(layout != nullptr, "backward_scratch_layout: null layout");

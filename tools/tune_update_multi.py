@@ -7,7 +7,7 @@ config 4's row-wise shard of one rank in bf16) the first
 library named sorts the batch once; then every library runs `tdfo_sparse_update` on a fresh copy of the tables
 and state (compared BIT FOR BIT with the first library's result: the variants keep its arithmetic and summation
 order) and is timed over `REPS` launches on rotating batches."""
-import ctypes, os, statistics, sys
+import os, statistics, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from pathlib import Path
@@ -67,16 +67,8 @@ for tag, F, rows, D, P, B, dt in shapes:
     ref_w = ref_s = None
     for name, _ in libs:
         use(name)
-        exp = name.startswith("single")      # tuning build with the one-occurrence kernel on a {key, payload} list
-        if exp and not tag.endswith("_uniq"):
-            continue
-        if exp:
-            handles[name].tdfo_exp_set_singles.argtypes = [ctypes.c_void_p]
-            pair_lists = [torch.stack([p_[1][:U + 1], p_[3][:U + 1]], dim=1).contiguous() for p_ in prepared]
-        set_list = (lambda i: handles[name].tdfo_exp_set_singles(pair_lists[i].data_ptr())) if exp else (lambda i: None)
         w.copy_(w0); state.zero_()
         sv, uk, ss, fv, nu = prepared[0]
-        set_list(0)
         ops.sparse_update(grp, grad, sv, uk, ss, fv, nu, offsets, B, L, 0, opt, worklist=worklist)
         torch.cuda.synchronize()
         if ref_w is None:
@@ -88,16 +80,37 @@ for tag, F, rows, D, P, B, dt in shapes:
         for it in range(REPS + 2):
             sv, uk, ss, fv, nu = prepared[it % 3]
             e = ev[max(it - 2, 0)]
-            set_list(it % 3)
             e[0].record()
             ops.sparse_update(grp, grad, sv, uk, ss, fv, nu, offsets, B, L, 0, opt, worklist=worklist)
             e[1].record()
         torch.cuda.synchronize()
-        if exp:
-            handles[name].tdfo_exp_set_singles(None)
         ms = [a.elapsed_time(b) for a, b in ev]
         m = statistics.mean(ms)
         print(f"{name:10s} upd {m:.3f} ms (min {min(ms):.3f})  {upd_bytes / m / 1e6:6.0f} GB/s  {same}", flush=True)
+    if os.environ.get("FWD"):          # the pooled lookup of every build on the same batch (bit-identical outputs expected)
+        fwd_bytes = L * (D * esz + 8) + (F * B + 1) * 8 + F * B * D * 4
+        idxs = [torch.randint(0, rows, (L,), device=dev, generator=gen) for _ in range(3)]
+        out = torch.empty((B, F * D), device=dev)
+        ref_o = None
+        for name, _ in libs:
+            use(name)
+            ops.embedding_forward(grp, idxs[0], offsets, B, 0, out=out)
+            torch.cuda.synchronize()
+            if ref_o is None:
+                ref_o, same = out.clone(), "reference"
+            else:
+                same = "bit-identical" if torch.equal(out, ref_o) else "DIFFERS"
+            ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(REPS)]
+            for it in range(REPS + 2):
+                e = ev[max(it - 2, 0)]
+                e[0].record()
+                ops.embedding_forward(grp, idxs[it % 3], offsets, B, 0, out=out)
+                e[1].record()
+            torch.cuda.synchronize()
+            ms = [a.elapsed_time(b) for a, b in ev]
+            m = statistics.mean(ms)
+            print(f"{name:10s} fwd {m:.3f} ms (min {min(ms):.3f})  {fwd_bytes / m / 1e6:6.0f} GB/s  {same}", flush=True)
+        del idxs, out, ref_o
     assert int(grp.err_flag.item()) == 0
     del w0, w, state, grp, grad, prepared, ref_w, ref_s, worklist
     torch.cuda.empty_cache()
