@@ -298,6 +298,20 @@ def test_backward_update_many_rows_per_warp(ops, mode, optimizer, bf16):
 
 
 @pytest.mark.parametrize("bf16", [False, True])
+def test_backward_update_with_a_large_gradient_slice(ops, bf16):
+    """Batch 70 000 x D 128: one feature's gradient slice is 36 MB, above the 32 MB at which the update kernel
+    reads and writes weight rows evict-first (csrc/update.cu, dispatch_update).  Same arithmetic, other
+    instantiation: checked against the oracle like the default one."""
+    c = make_case(seed=5, F=1, B=70_000, D=128, rows=[40_000], max_len=2, p_empty=0.3)
+    assert c.B * c.D * 4 > 32 << 20
+    w_o, s0_o, _, grp, routing, _ = _run_backward_pair(ops, c, orc.POOL_SUM, orc.OPT_ROWWISE_ADAGRAD, bf16, wd=0.0, steps=1)
+    rtol, atol = (BF16_RTOL, BF16_ATOL) if bf16 else (FP32_RTOL, 2e-6)
+    np.testing.assert_allclose(table_to_f32(grp.weights), oracle_table_to_f32(w_o), rtol=rtol, atol=atol)
+    np.testing.assert_allclose(grp.state0.cpu().numpy(), s0_o, rtol=max(rtol, 2e-5), atol=atol)
+    assert routing["num_unique"] > 14_208 and int(grp.err_flag.item()) == 0
+
+
+@pytest.mark.parametrize("bf16", [False, True])
 @pytest.mark.parametrize("optimizer", [orc.OPT_SGD, orc.OPT_ROWWISE_ADAGRAD, orc.OPT_ADAM])
 @pytest.mark.parametrize("mode", [orc.POOL_SUM, orc.POOL_MEAN])
 @pytest.mark.parametrize("D", [16, 128])
