@@ -103,7 +103,8 @@ struct UpdateArgs {
     float inv_D;
 };
 
-// Launch shape of the update kernel: 8 warps per CTA, persistent grid of 148 x MINB CTAs.
+// Launch shape of the update kernels: persistent grid of 148 x MINB CTAs of 8 warps (the block-per-chunk kernel and
+// most row sizes) or 9 warps (the main kernel for D = 128 rows, see dispatch_update).
 constexpr int kUpdCtaThreads = 256;
 #ifndef TDFO_UPD_THREADS
 #define TDFO_UPD_THREADS 288
